@@ -1,0 +1,138 @@
+/* nmf_b200 -- C ABI of the B200 (sm_100a) NMF solver hot path.
+ *
+ * The reference (raleng/nmf) is pure Python and has no FFI of its own; its solver loops are the
+ * boundary: `mur.mur` (nmf/mur.py:119-136), `admm.admm` (nmf/admm.py:292-334) and
+ * `ao_admm.ao_admm` (nmf/ao_admm.py:259-301), reached from `NMF.factorize` (nmf/nmf.py:59-73).
+ * Each entry point below names the reference lines whose arithmetic it replaces.  A maintainer
+ * binds this library with ctypes; `nmf_b200/_lib.py` is that binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative nmfb_status otherwise; the message is in
+ *     nmfb_last_error() (thread-local).  Nothing throws across the boundary.
+ *   - the CALLER owns all memory.  Pointers are device pointers unless a name ends in `_host`.
+ *     The library allocates nothing and keeps no global state besides one-time kernel attributes.
+ *   - all work is enqueued on the `stream` argument (a cudaStream_t passed as void*); no call
+ *     synchronises the device.
+ *   - scalars that the host needs (objective, flags) are written to caller-provided device slots;
+ *     the caller copies them out when it wants them.
+ *
+ * Device layouts (all padded regions must be zero-initialised by the caller; the library keeps
+ * them zero):  k <= 256 components are padded to KP = 64, 128 or 256;  a length L (m or n) is
+ * padded to Lp = round_up(L, 256).
+ *   data planes  bf16 [nv][rows_p][ld]   row-major planes of V (rows = m) or V^T (rows = n);
+ *                                        rows_p = round_up(rows, 256), ld = round_up(cols, 256);
+ *                                        plane 0 = hi, plane 1 = lo (nv = 1 when V is bf16-exact)
+ *   master       fp32 [KP][Lp]           solver state of a factor, component-major (W^T or H)
+ *   cplanes      bf16 [3][256][Lp]       hi / lo / lo2 planes of the master, component-major
+ *   rplanes      bf16 [2][Lp][KP]        hi / lo planes, row-major (W or H^T)
+ *   gram         fp32 [KP][KP] (+ fp64)  Gram matrix of a factor
+ *   partial      fp32 [slots][KP][Lp]    per-(K-split) partial sums written by the panel GEMM
+ */
+#ifndef NMF_B200_H
+#define NMF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum nmfb_status {
+    NMFB_OK = 0,
+    NMFB_ERR_ARG = -1,       /* bad argument / unsupported shape */
+    NMFB_ERR_CUDA = -2,      /* a CUDA runtime / driver call failed */
+    NMFB_ERR_WORKSPACE = -3, /* caller workspace too small */
+    NMFB_ERR_NOT_PD = -4     /* Gram + rho I not positive definite (numpy.linalg.LinAlgError) */
+} nmfb_status;
+
+typedef struct nmfb_data {          /* V (rows = m, cols = n) or V^T (rows = n, cols = m) */
+    void* planes;                   /* bf16 [nv][rows_p][ld] */
+    int rows, cols, rows_p, ld, nv;
+} nmfb_data;
+
+typedef struct nmfb_factor {        /* W (L = m) or H (L = n) */
+    float* master;                  /* fp32 [KP][Lp] */
+    void* cplanes;                  /* bf16 [3][256][Lp] */
+    void* rplanes;                  /* bf16 [2][Lp][KP] */
+    int L, Lp;
+} nmfb_factor;
+
+typedef struct nmfb_problem {
+    int m, n, k, KP;
+    nmfb_data v_rows;               /* V   : data for the W-side contraction V.H^T            */
+    nmfb_data v_cols;               /* V^T : data for the H-side contraction (W^T.V)^T        */
+    nmfb_factor w, h;
+    float* gram32;                  /* fp32 [2][KP][KP]: [0] = W^T W, [1] = H H^T             */
+    double* gram64;                 /* fp64 [2][KP][KP]                                       */
+    float* partial;                 /* GEMM partial-sum workspace                             */
+    size_t partial_bytes;
+    double* obj_partial;            /* fp64 [obj_partial_len] per-CTA objective partials      */
+    int obj_partial_len;
+    int num_sms;                    /* SM count of the device (148 on B200)                   */
+} nmfb_problem;
+
+const char* nmfb_last_error(void);
+int nmfb_abi_version(void);
+
+/* Padding rules, so that callers size buffers the way the kernels expect. */
+int nmfb_padded_components(int k);                 /* 64 / 128 / 256, or NMFB_ERR_ARG if k > 256 */
+int nmfb_padded_length(int L);                     /* round_up(L, 256) */
+size_t nmfb_partial_bytes(int m, int n, int k, int num_sms);   /* workspace for any GEMM of the problem */
+int nmfb_obj_partial_len(int m, int n, int num_sms);
+
+/* ---- ingest / export ------------------------------------------------------------------------ */
+/* Split a chunk of `nrows` rows of the caller's V (fp32 or fp64, row-major, pitch src_ld elements,
+ * already on the device) starting at global row `row0` into the row-major planes of `v_rows` and the
+ * transposed planes of `v_cols`.  stats[0] = order-preserving key of min(V) (init 0xFFFFFFFF),
+ * stats[1] = 1 if a lo plane is needed, stats[2] = 1 if a non-finite value was seen.
+ * Replaces the implicit float64 view of `x` in mur.py:52 / admm.py:233 / ao_admm.py:201. */
+int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int nrows,
+                     const nmfb_data* v_rows, const nmfb_data* v_cols, uint32_t* stats, void* stream);
+
+/* Import an initial factor (mur.py:108-109, admm.py:23-24, ao_admm.py:22-23 or utils.nndsvd).
+ * Element (r, c) of the factor is src[r*stride_l + c*stride_c]; W [m][k]: (k, 1); H [k][n]: (1, n).
+ * Fills master, cplanes and rplanes. */
+int nmfb_import_factor(const void* src, int src_is_f64, long stride_l, long stride_c, int k, int KP,
+                       const nmfb_factor* f, void* stream);
+/* Re-derive cplanes / rplanes from the master. */
+int nmfb_refresh_planes(int KP, const nmfb_factor* f, void* stream);
+/* Export the master to a caller buffer (device) with the same stride convention. */
+int nmfb_export_factor(const nmfb_factor* f, int k, int KP, void* dst, int dst_is_f64, long stride_l,
+                       long stride_c, void* stream);
+
+/* ---- building blocks ------------------------------------------------------------------------ */
+/* partial[slot][c][r] = sum_t factor_plane[c][t] * data_plane[r][t] over the slot's K range
+ * (`x @ h.T` mur.py:29, `w.T @ x` mur.py:45, `other_aux.T @ data_aux` admm.py:221, `w.T @ y`
+ * ao_admm.py:56).  nb = number of factor planes used (2 for non-negative factors, 3 for signed
+ * ADMM auxiliaries).  Returns the number of slots written (> 0) or a negative status.
+ * force_bn / force_split = 0 lets the library choose. */
+int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int factor_Lp, int KP, int nb,
+                    float* partial, size_t partial_bytes, int out_Lp, int num_sms, int force_bn,
+                    int force_split, void* stream);
+
+/* Gram matrix G = F F^T of a factor from its cplanes (`w.T @ w` ao_admm.py:53, `other_aux.T @
+ * other_aux` admm.py:220, and the W (H H^T) / (W^T W) H re-association of mur.py:29,45).
+ * Uses `partial` as scratch; writes gram32 [KP][KP] and gram64 [KP][KP]. */
+int nmfb_gram(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+              double* gram64, int num_sms, void* stream);
+
+/* Fused multiplicative update  x <- x * num / (G x + lambda x + 1e-9)  (mur.py:29 / mur.py:45):
+ * num = sum of `slots` partial slots, G = Gram of the other factor.  Writes master + all planes. */
+int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other, const nmfb_factor* f,
+                       int k, int KP, float lambda, void* stream);
+
+/* 0.5 * ||V - W H||_F^2 (utils.py:29) in residual form, fp64 accumulation, written to *obj_out
+ * (device).  impl = 0: tcgen05 kernel, 1: CUDA-core kernel (cross-check / tiny problems). */
+int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream);
+
+/* ---- solver steps --------------------------------------------------------------------------- */
+/* One outer iteration of MUR-Euclidean (mur.py:122-127): W update with the old H, H update with the
+ * new W, then the objective of the new pair into *obj_out (skipped when obj_out == NULL). */
+int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NMF_B200_H */

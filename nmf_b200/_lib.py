@@ -1,0 +1,108 @@
+"""ctypes binding of libnmf_b200.so (the C ABI declared in include/nmf_b200.h).
+
+There is deliberately no fallback: if the shared library is missing or a call fails, an
+exception is raised -- the product path never computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import _build
+
+c_void_p, c_int, c_long, c_float, c_size_t = C.c_void_p, C.c_int, C.c_long, C.c_float, C.c_size_t
+
+
+class NmfbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"nmf_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Data(C.Structure):            # struct nmfb_data
+    _fields_ = [("planes", c_void_p), ("rows", c_int), ("cols", c_int), ("rows_p", c_int),
+                ("ld", c_int), ("nv", c_int)]
+
+
+class Factor(C.Structure):          # struct nmfb_factor
+    _fields_ = [("master", c_void_p), ("cplanes", c_void_p), ("rplanes", c_void_p),
+                ("L", c_int), ("Lp", c_int)]
+
+
+class Problem(C.Structure):         # struct nmfb_problem
+    _fields_ = [("m", c_int), ("n", c_int), ("k", c_int), ("KP", c_int),
+                ("v_rows", Data), ("v_cols", Data), ("w", Factor), ("h", Factor),
+                ("gram32", c_void_p), ("gram64", c_void_p),
+                ("partial", c_void_p), ("partial_bytes", c_size_t),
+                ("obj_partial", c_void_p), ("obj_partial_len", c_int), ("num_sms", c_int)]
+
+
+class AdmmSide(C.Structure):        # struct nmfb_admm_side
+    _fields_ = [("aux", Factor), ("dual", c_void_p)]
+
+
+P = C.POINTER
+
+_SIGNATURES = {
+    "nmfb_last_error": (C.c_char_p, []),
+    "nmfb_abi_version": (c_int, []),
+    "nmfb_padded_components": (c_int, [c_int]),
+    "nmfb_padded_length": (c_int, [c_int]),
+    "nmfb_partial_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "nmfb_obj_partial_len": (c_int, [c_int, c_int, c_int]),
+    "nmfb_ingest_data": (c_int, [c_void_p, c_int, c_long, c_int, c_int, P(Data), P(Data), c_void_p, c_void_p]),
+    "nmfb_import_factor": (c_int, [c_void_p, c_int, c_long, c_long, c_int, c_int, P(Factor), c_void_p]),
+    "nmfb_refresh_planes": (c_int, [c_int, P(Factor), c_void_p]),
+    "nmfb_export_factor": (c_int, [P(Factor), c_int, c_int, c_void_p, c_int, c_long, c_long, c_void_p]),
+    "nmfb_panel_gemm": (c_int, [P(Data), c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_int,
+                                c_int, c_int, c_void_p]),
+    "nmfb_gram": (c_int, [P(Factor), c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
+    "nmfb_mur_eu_update": (c_int, [c_void_p, c_int, c_void_p, P(Factor), c_int, c_int, c_float, c_void_p]),
+    "nmfb_objective_eu": (c_int, [P(Problem), c_int, c_void_p, c_void_p]),
+    "nmfb_mur_eu_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
+}
+
+_OPTIONAL = set()
+
+_lib = None
+
+
+def exported_symbols():
+    """Names this binding expects libnmf_b200.so to export (checked by the CPU tests)."""
+    return sorted(_SIGNATURES)
+
+
+def load(build_if_needed: bool = True):
+    """Load (building first if the in-tree .so is stale and nvcc is present) the C-ABI library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if build_if_needed and _build.is_stale():
+        try:
+            _build.build()
+        except Exception as exc:       # no nvcc on the box: use the prebuilt .so if there is one
+            if not os.path.exists(path):
+                raise RuntimeError(f"libnmf_b200.so is missing and could not be built: {exc}") from exc
+    if not os.path.exists(path):
+        raise RuntimeError("libnmf_b200.so not found; run `python -c 'import __graft_entry__ as g; g.build()'`")
+    lib = C.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            if name in _OPTIONAL:
+                continue
+            raise
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> int:
+    """Raise on a negative status, pass non-negative results through."""
+    if rc < 0:
+        msg = load().nmfb_last_error().decode("utf-8", "replace")
+        raise NmfbError(rc, msg)
+    return rc

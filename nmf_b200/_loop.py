@@ -1,0 +1,81 @@
+"""Outer-iteration driver shared by mur / admm / ao_admm.
+
+The GPU runs one iteration ahead of the host: iteration i+1 is enqueued before the objective of
+iteration i has been read back, so the per-iteration print + stop test of the reference
+(mur.py:127-136, admm.py:324-334, ao_admm.py:291-301) never stalls the device.  When a stop test
+can fire, the factor masters of iteration i are snapshotted on the stream (device-to-device) before
+iteration i+1 overwrites them, so the returned factors are exactly those of the stopping iteration.
+"""
+from __future__ import annotations
+
+import logging
+from collections import deque
+
+import torch
+
+from .utils import convergence_check
+
+RING = 8          # scalar mailbox ring (slots of 8 doubles each)
+LAG = 1
+
+
+class LoopResult:
+    __slots__ = ("i", "obj_history", "masters", "extras")
+
+    def __init__(self):
+        self.i = -1
+        self.obj_history = []
+        self.masters = None
+        self.extras = []
+
+
+def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision, verbose=True,
+        on_extra=None):
+    """enqueue_step(slot) must enqueue one outer iteration that leaves the objective in
+    engine.scalars[slot*8] (and optional extras in [slot*8+1 : slot*8+8])."""
+    res = LoopResult()
+    res.obj_history = [obj0]
+    host = torch.zeros(RING * 8, dtype=torch.float64).pin_memory()
+    snaps = [None, None]
+    pending = deque()
+    stopped = False
+
+    def process(item):
+        nonlocal stopped
+        i, slot, ev = item
+        ev.synchronize()
+        vals = host[slot * 8: slot * 8 + 8].clone()
+        obj = float(vals[0])
+        res.obj_history.append(obj)
+        res.i = i
+        if on_extra is not None:
+            on_extra(i, vals)
+        if verbose:
+            print('[{}]: {:.{}f}'.format(i, obj, precision))
+        if i > min_iter and convergence_check(res.obj_history[-1], res.obj_history[-2], tol1, tol2):
+            logging.warning('Converged.')
+            res.masters = snaps[i % 2]
+            stopped = True
+
+    for i in range(max_iter):
+        slot = i % RING
+        enqueue_step(slot)
+        host[slot * 8: slot * 8 + 8].copy_(engine.scalars[slot * 8: slot * 8 + 8], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(engine.device))
+        if i > min_iter:
+            if snaps[i % 2] is None:
+                snaps[i % 2] = (torch.empty_like(engine.w.master), torch.empty_like(engine.h.master))
+            snaps[i % 2][0].copy_(engine.w.master, non_blocking=True)
+            snaps[i % 2][1].copy_(engine.h.master, non_blocking=True)
+        pending.append((i, slot, ev))
+        while len(pending) > LAG and not stopped:
+            process(pending.popleft())
+        if stopped:
+            break
+    while pending and not stopped:
+        process(pending.popleft())
+    if not stopped:
+        logging.info('Max iteration reached.')
+    torch.cuda.current_stream(engine.device).synchronize()
+    return res

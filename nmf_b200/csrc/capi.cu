@@ -1,0 +1,269 @@
+// extern "C" surface of libnmf_b200.so (declared in include/nmf_b200.h): argument checking,
+// TMA tensor-map construction and kernel sequencing.  No torch types, no allocation, no syncs.
+#include <cstdarg>
+#include <cstring>
+
+#include "../../include/nmf_b200.h"
+#include "elementwise.cuh"
+#include "kernels.cuh"
+
+using namespace nmfb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess)                                                              \
+            return fail(NMFB_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                           \
+    } while (0)
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// bf16 row-major [rows][ld] matrix, box = [box_rows][64 elements], 128-byte swizzle.
+int make_map(CUtensorMap* map, const void* base, long rows, long ld, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NMFB_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    cuuint64_t gdim[2] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows)};
+    cuuint64_t gstr[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NMFB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%ld ld=%ld box_rows=%d base=%p",
+                    static_cast<int>(r), rows, ld, box_rows, base);
+    return 0;
+}
+
+inline __nv_bfloat16* bf(void* p) { return static_cast<__nv_bfloat16*>(p); }
+inline const __nv_bfloat16* bf(const void* p) { return static_cast<const __nv_bfloat16*>(p); }
+inline cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
+
+int round_up(int x, int a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" {
+
+const char* nmfb_last_error(void) { return g_err; }
+int nmfb_abi_version(void) { return 1; }
+
+int nmfb_padded_components(int k) {
+    if (k < 1 || k > 256) return fail(NMFB_ERR_ARG, "components must be in [1, 256], got %d", k);
+    return k <= 64 ? 64 : (k <= 128 ? 128 : 256);
+}
+int nmfb_padded_length(int L) { return round_up(L, 256); }
+
+size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
+    const int KP = nmfb_padded_components(k);
+    if (KP < 0) return 0;
+    size_t best = 0;
+    const int Ls[3] = {m, n, 256}, Rs[3] = {n, m, (m > n ? m : n)};
+    for (int i = 0; i < 3; ++i)
+        for (int nb = 2; nb <= 3; ++nb)
+            for (int na = 1; na <= 2; ++na) {
+                PanelGemmPlan pl;
+                if (panel_gemm_plan(KP, nb, na, Ls[i], Rs[i], 0, 0, num_sms, &pl) != 0) continue;
+                const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
+                if (b > best) best = b;
+            }
+    return best;
+}
+
+int nmfb_obj_partial_len(int m, int n, int num_sms) {
+    const long simt = static_cast<long>((m + 63) / 64) * ((n + 63) / 64);
+    (void)simt;
+    return static_cast<int>(simt > num_sms ? simt : num_sms);
+}
+
+int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int nrows, const nmfb_data* vr,
+                     const nmfb_data* vc, uint32_t* stats, void* stream) {
+    if (!src || !vr || !vc || !stats) return fail(NMFB_ERR_ARG, "ingest_data: null argument");
+    if (vr->rows != vc->cols || vr->cols != vc->rows || vr->nv != vc->nv)
+        return fail(NMFB_ERR_ARG, "ingest_data: v_rows / v_cols shapes disagree");
+    if (row0 < 0 || row0 + nrows > vr->rows) return fail(NMFB_ERR_ARG, "ingest_data: row range");
+    CUDA_TRY(ingest_data_launch(src, src_is_f64, src_ld, row0, nrows, vr->cols, bf(vr->planes),
+                                static_cast<long>(vr->rows_p) * vr->ld, vr->ld, bf(vc->planes),
+                                static_cast<long>(vc->rows_p) * vc->ld, vc->ld, vr->nv, stats, st(stream)));
+    return 0;
+}
+
+int nmfb_refresh_planes(int KP, const nmfb_factor* f, void* stream) {
+    CUDA_TRY(refresh_planes_launch(f->master, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
+                                   static_cast<long>(f->Lp) * KP, st(stream)));
+    return 0;
+}
+
+int nmfb_import_factor(const void* src, int src_is_f64, long stride_l, long stride_c, int k, int KP,
+                       const nmfb_factor* f, void* stream) {
+    if (!src || !f) return fail(NMFB_ERR_ARG, "import_factor: null argument");
+    CUDA_TRY(import_factor_launch(src, src_is_f64, stride_l, stride_c, f->L, k, f->master, KP, f->Lp,
+                                  st(stream)));
+    return nmfb_refresh_planes(KP, f, stream);
+}
+
+int nmfb_export_factor(const nmfb_factor* f, int k, int KP, void* dst, int dst_is_f64, long stride_l,
+                       long stride_c, void* stream) {
+    if (!dst || !f) return fail(NMFB_ERR_ARG, "export_factor: null argument");
+    CUDA_TRY(export_factor_launch(f->master, KP, f->Lp, dst, dst_is_f64, stride_l, stride_c, f->L, k,
+                                  st(stream)));
+    return 0;
+}
+
+int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int factor_Lp, int KP, int nb,
+                    float* partial, size_t partial_bytes, int out_Lp, int num_sms, int force_bn,
+                    int force_split, void* stream) {
+    if (!data || !factor_cplanes || !partial) return fail(NMFB_ERR_ARG, "panel_gemm: null argument");
+    if (factor_Lp < data->ld) return fail(NMFB_ERR_ARG, "panel_gemm: factor pitch %d < data pitch %d", factor_Lp, data->ld);
+    PanelGemmPlan pl;
+    if (panel_gemm_plan(KP, nb, data->nv, data->rows, data->cols, force_bn, force_split, num_sms, &pl) != 0)
+        return fail(NMFB_ERR_ARG, "panel_gemm: unsupported configuration KP=%d nb=%d nv=%d", KP, nb, data->nv);
+    if (pl.npanels * pl.BN > out_Lp || pl.npanels * pl.BN > data->rows_p)
+        return fail(NMFB_ERR_ARG, "panel_gemm: padded extents too small (panels=%d BN=%d out_Lp=%d rows_p=%d)",
+                    pl.npanels, pl.BN, out_Lp, data->rows_p);
+    const size_t need = static_cast<size_t>(pl.slots) * KP * out_Lp * 4;
+    if (need > partial_bytes)
+        return fail(NMFB_ERR_WORKSPACE, "panel_gemm: partial workspace %zu < %zu bytes", partial_bytes, need);
+    PanelGemmArgs a;
+    memset(&a, 0, sizeof(a));
+    const int a_box_rows = (KP == 64) ? 64 : 128;
+    for (int j = 0; j < nb; ++j) {
+        const __nv_bfloat16* base = bf(factor_cplanes) + static_cast<long>(j) * 256 * factor_Lp;
+        int rc = make_map(&a.fac[j], base, 256, factor_Lp, a_box_rows);
+        if (rc) return rc;
+    }
+    for (int i = 0; i < data->nv; ++i) {
+        const __nv_bfloat16* base = bf(data->planes) + static_cast<long>(i) * data->rows_p * data->ld;
+        int rc = make_map(&a.dat[i], base, data->rows_p, data->ld, pl.BN);
+        if (rc) return rc;
+    }
+    a.out = partial;
+    a.KP = KP; a.NB = nb; a.NA = data->nv; a.BN = pl.BN;
+    a.npanels = pl.npanels; a.nsplit = pl.nsplit; a.kb_per_split = pl.kb_per_split;
+    a.kblocks_total = pl.kblocks_total;
+    a.Lp = out_Lp;
+    a.nstages = pl.nstages;
+    CUDA_TRY(panel_gemm_launch(a, pl, num_sms, st(stream)));
+    return pl.slots;
+}
+
+int nmfb_gram(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+              double* gram64, int num_sms, void* stream) {
+    // The factor's own hi/lo planes act as the "data": rows = components, contraction over L.
+    nmfb_data d;
+    d.planes = f->cplanes;
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 2;
+    const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, 2, partial, partial_bytes, 256, num_sms,
+                                      KP <= 128 ? 128 : 256, 0, stream);
+    if (slots < 0) return slots;
+    CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
+    return 0;
+}
+
+int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other, const nmfb_factor* f,
+                       int k, int KP, float lambda, void* stream) {
+    CUDA_TRY(mur_eu_update_launch(partial, slots, gram_other, f->master, bf(f->cplanes), 256L * f->Lp,
+                                  bf(f->rplanes), static_cast<long>(f->Lp) * KP, KP, k, f->L, f->Lp, lambda,
+                                  st(stream)));
+    return 0;
+}
+
+int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream) {
+    if (!p || !obj_out) return fail(NMFB_ERR_ARG, "objective: null argument");
+    const nmfb_data* v = &p->v_rows;
+    int nparts = 0;
+    if (impl == 0 && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
+    if (impl == 1) {
+        const long need = static_cast<long>((p->m + 63) / 64) * ((p->n + 63) / 64);
+        if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
+        CUDA_TRY(objective_simt_launch(bf(v->planes), static_cast<long>(v->rows_p) * v->ld, v->ld, v->nv,
+                                       p->w.master, p->w.Lp, p->h.master, p->h.Lp, p->k, p->m, p->n,
+                                       p->obj_partial, &nparts, st(stream)));
+    } else {
+        ResidualArgs a;
+        memset(&a, 0, sizeof(a));
+        for (int q = 0; q < 2; ++q) {
+            int rc = make_map(&a.wr[q], bf(p->w.rplanes) + static_cast<long>(q) * p->w.Lp * p->KP, p->w.Lp,
+                              p->KP, 128);
+            if (rc) return rc;
+            rc = make_map(&a.hr[q], bf(p->h.rplanes) + static_cast<long>(q) * p->h.Lp * p->KP, p->h.Lp, p->KP,
+                          128);
+            if (rc) return rc;
+        }
+        for (int q = 0; q < v->nv; ++q) {
+            int rc = make_map(&a.v[q], bf(v->planes) + static_cast<long>(q) * v->rows_p * v->ld, v->rows_p,
+                              v->ld, 128);
+            if (rc) return rc;
+        }
+        a.partial = p->obj_partial;
+        a.KP = p->KP; a.NV = v->nv; a.BN = 128;
+        a.m = p->m; a.n = p->n;
+        a.mtiles = (p->m + 127) / 128;
+        a.ntiles = (p->n + 127) / 128;
+        a.kl = 0;
+        const long ntot = static_cast<long>(a.mtiles) * a.ntiles;
+        int grid = p->num_sms;
+        if (ntot < grid) grid = static_cast<int>(ntot);
+        if (grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
+        nparts = grid;
+        CUDA_TRY(residual_launch(a, grid, st(stream)));
+    }
+    CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, 0.5, obj_out, st(stream)));
+    return 0;
+}
+
+int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
+    if (!p) return fail(NMFB_ERR_ARG, "mur_eu_step: null problem");
+    const int KP = p->KP;
+    const size_t gsz = static_cast<size_t>(KP) * KP;
+    int rc;
+    // W <- W * (V H^T) / (W (H H^T) + lambda_w W + eps)                    mur.py:122 -> :29
+    if ((rc = nmfb_gram(&p->h, KP, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz,
+                        p->num_sms, stream)) < 0) return rc;
+    int slots = nmfb_panel_gemm(&p->v_rows, p->h.cplanes, p->h.Lp, KP, 2, p->partial, p->partial_bytes,
+                                p->w.Lp, p->num_sms, 0, 0, stream);
+    if (slots < 0) return slots;
+    if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32 + gsz, &p->w, p->k, KP, lambda_w, stream)) < 0)
+        return rc;
+    // H <- H * (W^T V) / ((W^T W) H + lambda_h H + eps), with the NEW W    mur.py:123 -> :45
+    if ((rc = nmfb_gram(&p->w, KP, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0)
+        return rc;
+    slots = nmfb_panel_gemm(&p->v_cols, p->w.cplanes, p->w.Lp, KP, 2, p->partial, p->partial_bytes, p->h.Lp,
+                            p->num_sms, 0, 0, stream);
+    if (slots < 0) return slots;
+    if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32, &p->h, p->k, KP, lambda_h, stream)) < 0)
+        return rc;
+    // objective of the new pair                                            mur.py:124,127
+    if (obj_out) return nmfb_objective_eu(p, 0, obj_out, stream);
+    return 0;
+}
+
+}  // extern "C"

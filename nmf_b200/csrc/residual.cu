@@ -1,0 +1,272 @@
+// Residual-form objective on tcgen05:  sum_{i,j} f(V_ij, S_ij),  S = W.H formed tile by tile in
+// TMEM and never written to HBM.
+//   mode 0 (eu):  f = (v - s)^2                         -> 0.5 * sum = utils.py:29
+//   mode 1 (kl):  f = v*log(v/s) - v + s  (+inf/NaN of the log term -> 0, utils.py:23-26)
+//
+// S needs fp32-grade accuracy because the residual is ~1e-4 of |V| on low-rank data (the trace
+// form ||V||^2 - 2<W^T V,H> + <W^T W,H H^T> cancels catastrophically in fp32), so each 128x128
+// tile is three bf16 MMAs chains: Whi.Hhi + Whi.Hlo + Wlo.Hhi.
+//
+// One CTA walks a contiguous run of 128x128 tiles in row-major tile order.  The W planes of the
+// current tile row stay resident in shared memory; H^T planes stream through a ring of 64-wide
+// K-chunks; V tiles are double-buffered.  warp 0 = TMA producer, warp 1 = MMA issuer, warps
+// 2..9 = eight epilogue warps (two per TMEM lane quarter, 64 columns each).
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace nmfb {
+
+namespace {
+constexpr int kThreadsR = 320;
+constexpr int kBox = 128 * 128;      // bytes of one [128 rows x 64 bf16] box
+
+struct ResLayout {
+    int a_bytes, b_stage_bytes, v_buf_bytes;
+    int nbs, nvs;
+    int total;
+};
+
+__host__ __device__ inline ResLayout res_layout(int KP, int NV) {
+    ResLayout l;
+    l.a_bytes = 2 * (KP / 64) * kBox;
+    l.b_stage_bytes = 2 * kBox;
+    l.v_buf_bytes = NV * 2 * kBox;
+    const int budget = 227 * 1024 - 1024 - 512;
+    int rest = budget - l.a_bytes;
+    l.nvs = (rest - 2 * l.v_buf_bytes >= 2 * l.b_stage_bytes) ? 2 : 1;
+    rest -= l.nvs * l.v_buf_bytes;
+    l.nbs = rest / l.b_stage_bytes;
+    if (l.nbs > 4) l.nbs = 4;
+    l.total = l.a_bytes + l.nbs * l.b_stage_bytes + l.nvs * l.v_buf_bytes;
+    return l;
+}
+}  // namespace
+
+int residual_smem_bytes(int KP, int NV, int BN) {
+    (void)BN;
+    const ResLayout l = res_layout(KP, NV);
+    if (l.nbs < 2) return -1;
+    return l.total + 1024 + 512;
+}
+
+__global__ void __launch_bounds__(kThreadsR, 1)
+residual_kernel(const __grid_constant__ ResidualArgs args) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    const int KP = args.KP, NV = args.NV;
+    const int kchunks = KP / 64;
+    const ResLayout L = res_layout(KP, NV);
+    uint8_t* a_smem = smem;
+    uint8_t* b_smem = a_smem + L.a_bytes;
+    uint8_t* v_smem = b_smem + L.nbs * L.b_stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(v_smem + L.nvs * L.v_buf_bytes);
+    uint64_t* b_full = bars;             // [4]
+    uint64_t* b_empty = bars + 4;        // [4]
+    uint64_t* v_full = bars + 8;         // [2]
+    uint64_t* v_empty = bars + 10;       // [2]
+    uint64_t* acc_full = bars + 12;      // [2]
+    uint64_t* acc_empty = bars + 14;     // [2]
+    uint64_t* a_full = bars + 16;
+    uint64_t* a_empty = bars + 17;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+    double* red = reinterpret_cast<double*>(bars + 20);      // [8]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long ntot = static_cast<long>(args.mtiles) * args.ntiles;
+    const long t_begin = ntot * blockIdx.x / gridDim.x;
+    const long t_end = ntot * (blockIdx.x + 1) / gridDim.x;
+
+    if (warp == 0 && lane == 0) {
+        for (int p = 0; p < 2; ++p) { tma_prefetch_desc(&args.wr[p]); tma_prefetch_desc(&args.hr[p]); }
+        for (int p = 0; p < NV; ++p) tma_prefetch_desc(&args.v[p]);
+        for (int s = 0; s < 4; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&v_full[s], 1);   mbar_init(&v_empty[s], 8);
+            mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8);
+        }
+        mbar_init(a_full, 1);
+        mbar_init(a_empty, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int bs = 0; uint32_t bph = 0;
+            int vs = 0; uint32_t vph = 0;
+            uint32_t aph = 0;
+            int cur_i = -1;
+            for (long t = t_begin; t < t_end; ++t) {
+                const int ti = static_cast<int>(t / args.ntiles);
+                const int tj = static_cast<int>(t - static_cast<long>(ti) * args.ntiles);
+                if (ti != cur_i) {
+                    mbar_wait(a_empty, aph ^ 1);
+                    mbar_expect_tx(a_full, L.a_bytes);
+                    for (int p = 0; p < 2; ++p)
+                        for (int kc = 0; kc < kchunks; ++kc)
+                            tma_load_2d_hint(a_smem + (p * kchunks + kc) * kBox, &args.wr[p], a_full, kc * 64,
+                                             ti * 128, kPolicyEvictLast);
+                    aph ^= 1;
+                    cur_i = ti;
+                }
+                // V tile
+                mbar_wait(&v_empty[vs], vph ^ 1);
+                mbar_expect_tx(&v_full[vs], L.v_buf_bytes);
+                for (int p = 0; p < NV; ++p)
+                    for (int hb = 0; hb < 2; ++hb)
+                        tma_load_2d_hint(v_smem + vs * L.v_buf_bytes + (p * 2 + hb) * kBox, &args.v[p],
+                                         &v_full[vs], tj * 128 + hb * 64, ti * 128, kPolicyEvictFirst);
+                if (++vs == L.nvs) { vs = 0; vph ^= 1; }
+                // H^T chunks
+                for (int kc = 0; kc < kchunks; ++kc) {
+                    mbar_wait(&b_empty[bs], bph ^ 1);
+                    mbar_expect_tx(&b_full[bs], L.b_stage_bytes);
+                    for (int p = 0; p < 2; ++p)
+                        tma_load_2d_hint(b_smem + bs * L.b_stage_bytes + p * kBox, &args.hr[p], &b_full[bs],
+                                         kc * 64, tj * 128, kPolicyEvictLast);
+                    if (++bs == L.nbs) { bs = 0; bph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(128, 128);
+            int bs = 0; uint32_t bph = 0;
+            int acc = 0; uint32_t accph = 0;
+            uint32_t aph = 0;
+            int cur_i = -1;
+            const uint32_t a_addr = smem_u32(a_smem), b_addr = smem_u32(b_smem);
+            for (long t = t_begin; t < t_end; ++t) {
+                const int ti = static_cast<int>(t / args.ntiles);
+                if (ti != cur_i) {
+                    mbar_wait(a_full, aph);
+                    aph ^= 1;
+                    cur_i = ti;
+                }
+                mbar_wait(&acc_empty[acc], accph ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + acc * 128;
+                uint32_t started = 0;
+                for (int kc = 0; kc < kchunks; ++kc) {
+                    mbar_wait(&b_full[bs], bph);
+                    tc_fence_after();
+                    const uint32_t bst = b_addr + bs * L.b_stage_bytes;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t a_hi = umma_desc_k_sw128(a_addr + (0 * kchunks + kc) * kBox + ks * 32);
+                        const uint64_t a_lo = umma_desc_k_sw128(a_addr + (1 * kchunks + kc) * kBox + ks * 32);
+                        const uint64_t b_hi = umma_desc_k_sw128(bst + ks * 32);
+                        const uint64_t b_lo = umma_desc_k_sw128(bst + kBox + ks * 32);
+                        umma_bf16(d, a_hi, b_hi, idesc, started);
+                        started = 1;
+                        umma_bf16(d, a_hi, b_lo, idesc, 1);
+                        umma_bf16(d, a_lo, b_hi, idesc, 1);
+                    }
+                    umma_commit(&b_empty[bs]);
+                    if (++bs == L.nbs) { bs = 0; bph ^= 1; }
+                }
+                umma_commit(&acc_full[acc]);
+                const long tn = t + 1;
+                if (tn >= t_end || static_cast<int>(tn / args.ntiles) != ti) umma_commit(a_empty);
+                if (++acc == 2) { acc = 0; accph ^= 1; }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------ epilogue
+        const int ew = warp - 2;
+        const int q = warp & 3;                   // TMEM lane quarter
+        const int hb = ew >> 2;                   // which 64-column half of the tile
+        const int row = q * 32 + lane;
+        int acc = 0; uint32_t accph = 0;
+        int vs = 0; uint32_t vph = 0;
+        double total = 0.0;
+        for (long t = t_begin; t < t_end; ++t) {
+            mbar_wait(&acc_full[acc], accph);
+            mbar_wait(&v_full[vs], vph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + hb * 64;
+            const uint8_t* vrow = v_smem + vs * L.v_buf_bytes + hb * kBox + row * 128;
+            float tsum = 0.f;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                uint32_t s[32];
+                tmem_ld32(taddr + g * 32, s);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    const int chunk = (g * 4 + c8) ^ (row & 7);          // SWIZZLE_128B
+                    const uint4 raw = *reinterpret_cast<const uint4*>(vrow + chunk * 16);
+                    const uint32_t w4[4] = {raw.x, raw.y, raw.z, raw.w};
+                    float vv[8];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        vv[2 * e] = __uint_as_float(w4[e] << 16);
+                        vv[2 * e + 1] = __uint_as_float(w4[e] & 0xFFFF0000u);
+                    }
+                    if (NV > 1) {
+                        const uint4 rl = *reinterpret_cast<const uint4*>(vrow + 2 * kBox + chunk * 16);
+                        const uint32_t l4[4] = {rl.x, rl.y, rl.z, rl.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            vv[2 * e] += __uint_as_float(l4[e] << 16);
+                            vv[2 * e + 1] += __uint_as_float(l4[e] & 0xFFFF0000u);
+                        }
+                    }
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float sv = __uint_as_float(s[c8 * 8 + e]);
+                        if (args.kl == 0) {
+                            const float dlt = vv[e] - sv;
+                            tsum = fmaf(dlt, dlt, tsum);
+                        } else {
+                            float term = vv[e] * __logf(vv[e] / sv);
+                            if (term == INFINITY || term != term) term = 0.f;
+                            tsum += term - vv[e] + sv;
+                        }
+                    }
+                }
+            }
+            total += static_cast<double>(tsum);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&acc_empty[acc]); mbar_arrive(&v_empty[vs]); }
+            if (++acc == 2) { acc = 0; accph ^= 1; }
+            if (++vs == L.nvs) { vs = 0; vph ^= 1; }
+        }
+        for (int o = 16; o; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        if (lane == 0) red[ew] = total;
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        args.partial[blockIdx.x] = t;
+    }
+}
+
+cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e =
+            cudaFuncSetAttribute(residual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const int smem = residual_smem_bytes(args.KP, args.NV, args.BN);
+    if (smem < 0) return cudaErrorInvalidValue;
+    residual_kernel<<<grid, kThreadsR, smem, stream>>>(args);
+    return cudaGetLastError();
+}
+
+}  // namespace nmfb

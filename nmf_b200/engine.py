@@ -1,0 +1,196 @@
+"""Device-side state of one factorisation and the calls that advance it.
+
+PyTorch is used for what it is good at here -- device memory, streams, pinned host buffers --
+and nothing else: every arithmetic step is a kernel of libnmf_b200.so reached through the C ABI
+(`_lib.py`).  There is no CPU path; constructing an Engine without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Data, Factor, Problem, check
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _key_to_float(key: int) -> float:
+    """Inverse of the order-preserving uint32 key the ingest kernel folds min(V) into."""
+    if key == 0xFFFFFFFF:
+        return float("inf")
+    bits = (key & 0x7FFFFFFF) if (key & 0x80000000) else (~key & 0xFFFFFFFF)
+    return float(np.array([bits], dtype=np.uint32).view(np.float32)[0])
+
+
+class FactorBuffers:
+    """master / cplanes / rplanes of one factor (layouts in include/nmf_b200.h)."""
+
+    def __init__(self, L: int, KP: int, device):
+        self.L, self.KP = L, KP
+        self.Lp = (L + 255) // 256 * 256
+        self.master = torch.zeros((KP, self.Lp), dtype=torch.float32, device=device)
+        self.cplanes = torch.zeros((3, 256, self.Lp), dtype=torch.bfloat16, device=device)
+        self.rplanes = torch.zeros((2, self.Lp, KP), dtype=torch.bfloat16, device=device)
+
+    def struct(self) -> Factor:
+        return Factor(self.master.data_ptr(), self.cplanes.data_ptr(), self.rplanes.data_ptr(),
+                      self.L, self.Lp)
+
+
+class Engine:
+    """Owns the HBM-resident problem: V and V^T planes, both factors, Grams and workspaces."""
+
+    ROW_CHUNK_BYTES = 512 << 20
+
+    def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("nmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.m, self.n, self.k = int(m), int(n), int(k)
+        self.KP = check(self.lib.nmfb_padded_components(self.k))
+        self.Mp = (self.m + 255) // 256 * 256
+        self.Np = (self.n + 255) // 256 * 256
+        props = torch.cuda.get_device_properties(self.device)
+        if props.major != 10:
+            raise RuntimeError(f"nmf_b200 is built for sm_100a only; device is sm_{props.major}{props.minor}")
+        self.num_sms = props.multi_processor_count
+        with torch.cuda.device(self.device):
+            self.w = FactorBuffers(self.m, self.KP, self.device)
+            self.h = FactorBuffers(self.n, self.KP, self.device)
+            self.gram32 = torch.zeros((2, self.KP, self.KP), dtype=torch.float32, device=self.device)
+            self.gram64 = torch.zeros((2, self.KP, self.KP), dtype=torch.float64, device=self.device)
+            pbytes = int(self.lib.nmfb_partial_bytes(self.m, self.n, self.k, self.num_sms))
+            self.partial = torch.empty(pbytes // 4, dtype=torch.float32, device=self.device)
+            self.obj_partial_len = int(self.lib.nmfb_obj_partial_len(self.m, self.n, self.num_sms))
+            self.obj_partial = torch.zeros(self.obj_partial_len, dtype=torch.float64, device=self.device)
+            self.stats = torch.zeros(4, dtype=torch.int32, device=self.device)
+            self.scalars = torch.zeros(64, dtype=torch.float64, device=self.device)
+        self.nv = 0
+        self.v_rows = None
+        self.v_cols = None
+        self.vmin = None
+        self._problem = None
+
+    # ------------------------------------------------------------------ plumbing
+    @property
+    def stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _alloc_data(self, nv: int):
+        self.v_rows = self.v_cols = None
+        self.nv = nv
+        self.v_rows = torch.zeros((nv, self.Mp, self.Np), dtype=torch.bfloat16, device=self.device)
+        self.v_cols = torch.zeros((nv, self.Np, self.Mp), dtype=torch.bfloat16, device=self.device)
+        self._problem = None
+
+    def _data_structs(self) -> Tuple[Data, Data]:
+        vr = Data(self.v_rows.data_ptr(), self.m, self.n, self.Mp, self.Np, self.nv)
+        vc = Data(self.v_cols.data_ptr(), self.n, self.m, self.Np, self.Mp, self.nv)
+        return vr, vc
+
+    def problem(self) -> Problem:
+        if self._problem is None:
+            vr, vc = self._data_structs()
+            self._problem = Problem(self.m, self.n, self.k, self.KP, vr, vc, self.w.struct(), self.h.struct(),
+                                    self.gram32.data_ptr(), self.gram64.data_ptr(),
+                                    self.partial.data_ptr(), self.partial.numel() * 4,
+                                    self.obj_partial.data_ptr(), self.obj_partial_len, self.num_sms)
+        return self._problem
+
+    # ------------------------------------------------------------------ data in
+    def _ingest_pass(self, v: np.ndarray):
+        vr, vc = self._data_structs()
+        self.stats.copy_(torch.tensor([-1, 0, 0, 0], dtype=torch.int32))
+        is_f64 = 1 if v.dtype == np.float64 else 0
+        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
+        for r0 in range(0, self.m, rows_per):
+            r1 = min(self.m, r0 + rows_per)
+            chunk = torch.from_numpy(v[r0:r1]).to(self.device, non_blocking=False)
+            check(self.lib.nmfb_ingest_data(chunk.data_ptr(), is_f64, chunk.stride(0), r0, r1 - r0,
+                                            C.byref(vr), C.byref(vc), self.stats.data_ptr(), self.stream))
+            del chunk
+        st = self.stats.cpu().numpy().view(np.uint32)
+        return _key_to_float(int(st[0])), bool(st[1]), bool(st[2])
+
+    def upload_data(self, v: np.ndarray, planes: Optional[int] = None) -> float:
+        """Copy the caller's V (host, fp32/fp64) to HBM as bf16 planes of V and V^T.
+        Tries the single lossless plane first and re-ingests with a lo plane only when the data is
+        not bf16-exact.  Returns min(V)."""
+        if v.ndim != 2 or v.shape != (self.m, self.n):
+            raise ValueError(f"data must be a 2-D array of shape {(self.m, self.n)}")
+        if v.dtype not in (np.float32, np.float64):
+            v = v.astype(np.float64)
+        if not v.flags.c_contiguous:
+            v = np.ascontiguousarray(v)
+        self._alloc_data(planes or 1)
+        vmin, need_lo, bad = self._ingest_pass(v)
+        if need_lo and planes is None:
+            self._alloc_data(2)
+            vmin, need_lo, bad = self._ingest_pass(v)
+        if bad:
+            raise ValueError("data contains non-finite values")
+        self.vmin = vmin
+        return vmin
+
+    def upload_data_device(self, v: torch.Tensor, planes: int = 1) -> float:
+        """Same as upload_data for a V that already lives on this device (fp32/fp64, row-major)."""
+        assert v.is_cuda and v.shape == (self.m, self.n) and v.stride(1) == 1
+        self._alloc_data(planes)
+        vr, vc = self._data_structs()
+        self.stats.copy_(torch.tensor([-1, 0, 0, 0], dtype=torch.int32))
+        check(self.lib.nmfb_ingest_data(v.data_ptr(), 1 if v.dtype == torch.float64 else 0, v.stride(0), 0,
+                                        self.m, C.byref(vr), C.byref(vc), self.stats.data_ptr(), self.stream))
+        st = self.stats.cpu().numpy().view(np.uint32)
+        self.vmin = _key_to_float(int(st[0]))
+        return self.vmin
+
+    def set_factors(self, w0: np.ndarray, h0: np.ndarray):
+        """w0: (m, k), h0: (k, n) host arrays (fp32/fp64)."""
+        if w0.shape != (self.m, self.k) or h0.shape != (self.k, self.n):
+            raise ValueError("initial factors have the wrong shape")
+        for arr, fac, sl, sc in ((w0, self.w, None, None), (h0, self.h, None, None)):
+            a = np.ascontiguousarray(arr, dtype=np.float64 if arr.dtype == np.float64 else np.float32)
+            d = torch.from_numpy(a).to(self.device)
+            if fac is self.w:
+                stride_l, stride_c = self.k, 1
+            else:
+                stride_l, stride_c = 1, self.n
+            fs = fac.struct()
+            check(self.lib.nmfb_import_factor(d.data_ptr(), 1 if a.dtype == np.float64 else 0, stride_l,
+                                              stride_c, self.k, self.KP, C.byref(fs), self.stream))
+            torch.cuda.current_stream(self.device).synchronize()
+            del d
+        self._problem = None
+
+    def get_factors(self, dtype=np.float64, masters=None) -> Tuple[np.ndarray, np.ndarray]:
+        """Download W (m, k) and H (k, n) as host arrays."""
+        tdt = torch.float64 if dtype == np.float64 else torch.float32
+        w_d = torch.empty((self.m, self.k), dtype=tdt, device=self.device)
+        h_d = torch.empty((self.k, self.n), dtype=tdt, device=self.device)
+        wf, hf = self.w.struct(), self.h.struct()
+        if masters is not None:
+            wf.master, hf.master = masters[0].data_ptr(), masters[1].data_ptr()
+        is64 = 1 if tdt == torch.float64 else 0
+        check(self.lib.nmfb_export_factor(C.byref(wf), self.k, self.KP, w_d.data_ptr(), is64, self.k, 1, self.stream))
+        check(self.lib.nmfb_export_factor(C.byref(hf), self.k, self.KP, h_d.data_ptr(), is64, 1, self.n, self.stream))
+        return w_d.cpu().numpy(), h_d.cpu().numpy()
+
+    # ------------------------------------------------------------------ steps
+    def objective_eu(self, slot: int = 0, impl: int = 0):
+        p = self.problem()
+        check(self.lib.nmfb_objective_eu(C.byref(p), impl, self.scalars.data_ptr() + 8 * slot, self.stream))
+
+    def mur_eu_step(self, lambda_w: float, lambda_h: float, obj_slot: Optional[int] = 0):
+        p = self.problem()
+        out = None if obj_slot is None else self.scalars.data_ptr() + 8 * obj_slot
+        check(self.lib.nmfb_mur_eu_step(C.byref(p), float(lambda_w), float(lambda_h), out, self.stream))
+
+    def read_scalar(self, slot: int = 0) -> float:
+        return float(self.scalars[slot].item())

@@ -1,0 +1,35 @@
+"""Host-side helpers shared by the solver drivers: stop test, console format, result saving.
+
+Mirrors the role of the reference's nmf/utils.py (convergence_check :4-15, save_results :96-105);
+the objective itself (utils.distance :18-33) is computed on the GPU by libnmf_b200.so.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def convergence_check(new, old, tol1, tol2):
+    """Absolute-tolerance stop test of the reference (utils.py:4-15), same console messages."""
+    if new < tol1:
+        print('Algorithm converged (1).')
+        return True
+    if new >= old - tol2:
+        print('Algorithm converged (2).')
+        return True
+    return False
+
+
+def tol_precision(tol1, tol2):
+    """Decimal places shown per iteration (mur.py:93-95).  The reference raises IndexError for a
+    zero tolerance; here that case simply prints 2 decimals."""
+    tol = min(tol1, tol2)
+    if tol < 1:
+        parts = format(tol, 'e').split('-')
+        return int(parts[1]) if len(parts) > 1 else 2
+    return 2
+
+
+def save_results(save_str, w, h, i, obj_history, experiment):
+    """np.savez with the reference's key set (utils.py:103): w, h, i, obj_history, experiment."""
+    np.savez(save_str, w=w, h=h, i=i, obj_history=obj_history, experiment=experiment)
+    print('Results saved in {}.'.format(save_str))
