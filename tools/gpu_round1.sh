@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
 for t in gemm gram update objective mur; do
-  timeout 600 python tools/selftest.py $t > gpurun_out/st_$t.log 2>&1
+  timeout 300 python tools/selftest.py $t > gpurun_out/st_$t.log 2>&1
   echo "$t exit $?" >> gpurun_out/summary.log
   tail -3 gpurun_out/st_$t.log
 done
