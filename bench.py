@@ -1,0 +1,444 @@
+#!/usr/bin/env python3
+"""Headline benchmark: NMF outer iterations / second on B200 (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one outer iteration of the solver (both factor updates + the objective, exactly the
+body of the reference loop mur.py:119-136 / admm.py:292-334 / ao_admm.py:259-301) on synthetic
+planted non-negative data.  Prints ONE JSON line (rank 0).
+
+  value        iterations/s with V resident in HBM (CUDA events, max over ranks)
+  e2e          iterations/s through NMF(V_host, k).factorize(...): upload of the host V, K
+               iterations, download of W and H -- all inside the timed region
+  roofline     dominant kernel (the split-bf16 tcgen05 panel GEMM) timed live with CUDA events
+  cpu_baseline the oracle port of the reference loop (NumPy fp64) timed on this box's host cores
+
+`--impl reference` times the reference algorithm (oracle port; the reference is pure Python and
+cannot travel to the GPU box) on the host cores, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# name -> (method, distance, m, n, k, extra kwargs)
+WORKLOADS = {
+    "mur_eu_65536x65536_k128": ("mur", "eu", 65536, 65536, 128, {}),
+    "mur_eu_32768x32768_k64": ("mur", "eu", 32768, 32768, 64, {}),
+    "mur_kl_20000x50000_k128": ("mur", "kl", 20000, 50000, 128, {}),
+    "admm_65536x16384_k128": ("admm", "eu", 65536, 16384, 128,
+                              dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))),
+    "ao_admm_65536x16384_k128": ("ao_admm", "eu", 65536, 16384, 128,
+                                 dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)),
+    "mur_eu_262144x131072_k256": ("mur", "eu", 262144, 131072, 256, {}),
+    "mur_eu_4096x4096_k64": ("mur", "eu", 4096, 4096, 64, {}),          # quick functional check
+}
+DEFAULT_WORKLOAD = "mur_eu_65536x65536_k128"
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm_gbs=p["hbm_gbs"], bf16_tflops=p["bf16_tflops"],
+                    bf16_tflops_sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                    source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20}
+    NOTE = {"sw_power_cap": 0x4, "hw_power_brake": 0x80}
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:                                   # NVML missing: report nulls
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for name, bit in {**self.BAD, **self.NOTE}.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+
+    def summary(self):
+        med = int(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------------------------
+# synthetic workload on the device: planted low-rank + 1% noise on the bf16 grid
+# ----------------------------------------------------------------------------------------------
+def synth_fill_engine(eng, seed: int):
+    """Fill eng.v_rows / eng.v_cols (1 lossless bf16 plane) for the engine's row / column shard.
+    Every rank walks the same row chunks with the same per-chunk generator, so shards of
+    different ranks are slices of one and the same V."""
+    import torch
+    dev = eng.device
+    m, n, k = eng.m, eng.n, eng.k
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    wt = torch.rand((m, k), device=dev, generator=g)
+    ht = torch.rand((k, n), device=dev, generator=g)
+    eng._alloc_data(1)
+    r_lo, r_hi = eng.row_range
+    c_lo, c_hi = eng.col_range
+    chunk = 2048
+    for r0 in range(0, m, chunk):
+        r1 = min(m, r0 + chunk)
+        g.manual_seed(seed * 1000003 + 17 + r0)
+        blk = wt[r0:r1] @ ht
+        blk.add_(torch.rand((r1 - r0, n), device=dev, generator=g), alpha=0.01)
+        blk = blk.bfloat16()
+        a, b = max(r0, r_lo), min(r1, r_hi)
+        if a < b:
+            eng.v_rows[0, a - r_lo:b - r_lo, :n] = blk[a - r0:b - r0]
+        if c_lo < c_hi:
+            eng.v_cols[0, :c_hi - c_lo, r0:r1] = blk[:, c_lo:c_hi].t()
+        del blk
+    return wt, ht
+
+
+def synth_init(eng, seed: int):
+    """|randn| initial factors generated on the device (reference order W then H)."""
+    import ctypes as C
+    import torch
+    from nmf_b200._lib import check
+    g = torch.Generator(device=eng.device)
+    g.manual_seed(seed)
+    eng.w.master.zero_()
+    eng.h.master.zero_()
+    eng.w.master[:eng.k, :eng.m] = torch.randn((eng.k, eng.m), device=eng.device, generator=g).abs_()
+    eng.h.master[:eng.k, :eng.n] = torch.randn((eng.k, eng.n), device=eng.device, generator=g).abs_()
+    for f in (eng.w, eng.h):
+        fs = f.struct()
+        check(eng.lib.nmfb_refresh_planes(eng.KP, C.byref(fs), eng.stream))
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference loop on a bounded sample of the workload
+# ----------------------------------------------------------------------------------------------
+def cpu_sample_shape(m, n, k, budget_elems):
+    """Largest (m/2^a, n/2^b) block with at most budget_elems elements (halve the longer side)."""
+    ms, ns = m, n
+    while ms * ns > budget_elems:
+        if ms >= ns:
+            ms //= 2
+        else:
+            ns //= 2
+    return ms, ns
+
+
+def cpu_step_fn(method, dist, ms, ns, k, extra, seed=0):
+    """Returns (step, cores): `step()` runs ONE outer iteration of the oracle on the sample."""
+    from oracle import nmf_oracle as orc
+    v = orc.planted(ms, ns, k, seed).astype(np.float64)
+    w0, h0 = orc.seeded_init(ms, ns, k, seed + 1)
+    st = {"w": w0, "h": h0}
+    if method == "mur":                          # loop body of mur.py:122-127
+        st["wh"] = w0 @ h0
+
+        def step():
+            w = orc.mur_w_step(dist, v, st["w"], st["h"], st["wh"], 0.0)
+            h = orc.mur_h_step(dist, v, w, st["h"], w @ st["h"], 0.0)
+            st["wh"] = w @ h
+            st["w"], st["h"] = w, h
+            return orc.objective(v, st["wh"], dist)
+    elif method == "admm":                       # loop body of admm.py:294-301,320-324
+        rho, reg_w, reg_h = extra["rho"], extra["reg_w"], extra["reg_h"]
+        st.update(w_aux=w0.copy(), h_aux=h0.copy(), dw=np.zeros_like(w0), dh=np.zeros_like(h0))
+
+        def step():
+            h_aux = orc.admm_aux(st["h"], st["dh"], st["w_aux"], v, rho)
+            w_aux = orc.admm_aux(st["w"].T, st["dw"].T, h_aux.T, v.T, rho).T
+            h = orc.prox(reg_h[1], h_aux, st["dh"], rho, reg_h[0])
+            w = orc.prox(reg_w[1], w_aux, st["dw"], rho, reg_w[0])
+            st["dh"] = st["dh"] + h - h_aux
+            st["dw"] = st["dw"] + w - w_aux
+            st.update(w=w, h=h, w_aux=w_aux, h_aux=h_aux)
+            return orc.objective(v, w @ h)
+    else:                                        # loop body of ao_admm.py:261-270,291
+        reg_w, reg_h, inner = extra["reg_w"], extra["reg_h"], extra["admm_iter"]
+        st.update(dw=np.zeros_like(w0), dh=np.zeros_like(h0))
+
+        def step():
+            h, dh, _ = orc.ao_factor_update(v, st["w"], st["h"], st["dh"], k, reg_h[1], reg_h[0], inner)
+            wt, dwt, _ = orc.ao_factor_update(v.T, h.T, st["w"].T, st["dw"].T, k, reg_w[1], reg_w[0], inner)
+            st.update(w=wt.T, h=h, dw=dwt.T, dh=dh)
+            return orc.objective(v, st["w"] @ h)
+    try:
+        from threadpoolctl import threadpool_info
+        cores = max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
+    except Exception:
+        cores = os.cpu_count() or 1
+    return step, cores
+
+
+def time_cpu(method, dist, m, n, k, extra, steps, warmup, budget_s):
+    """Times `steps` oracle iterations on a sample sized so that the run fits budget_s; returns
+    (full-size iterations/s, ms per sample step, cores, description)."""
+    # calibrate on a small block, then pick the sample size
+    probe_m, probe_n = cpu_sample_shape(m, n, k, 1 << 20)
+    step, cores = cpu_step_fn(method, dist, probe_m, probe_n, k, extra)
+    step()
+    t0 = time.perf_counter()
+    step()
+    per_elem = (time.perf_counter() - t0) / (probe_m * probe_n)
+    total_steps = steps + warmup
+    budget_elems = max(1 << 23, int(budget_s / max(per_elem, 1e-12) / total_steps))
+    budget_elems = min(budget_elems, 1 << 28)                  # <= 2 GiB of fp64 V
+    ms, ns = cpu_sample_shape(m, n, k, budget_elems)
+    step, cores = cpu_step_fn(method, dist, ms, ns, k, extra)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    scale = (m * n) / (ms * ns)
+    desc = (f"{ms}x{ns} block of the {m}x{n} workload (1/{scale:g} of V), k={k}, {steps} oracle iterations "
+            f"at {dt * 1e3:.1f} ms each, time scaled by {scale:g} (work is proportional to m*n)")
+    return 1.0 / (dt * scale), dt * 1e3, cores, desc
+
+
+# ----------------------------------------------------------------------------------------------
+# algorithmic work
+# ----------------------------------------------------------------------------------------------
+def alg_flops_per_iter(method, dist, m, n, k, extra):
+    if method == "mur" and dist == "eu":
+        return 4.0 * m * n * k + 4.0 * (m + n) * k * k
+    if method == "mur":
+        return 8.0 * m * n * k
+    if method == "admm":
+        return 6.0 * m * n * k + 4.0 * (m + n) * k * k + 4.0 / 3.0 * k ** 3
+    inner = extra.get("admm_iter", 10)
+    return 4.0 * m * n * k + (2.0 * inner + 2.0) * (m + n) * k * k + 4.0 / 3.0 * k ** 3
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for cpu_baseline")
+    return ap.parse_args()
+
+
+def run_reference(args):
+    """`--impl reference`: the reference algorithm (oracle port, NumPy fp64, all host threads)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    method, dist, m, n, k, extra = WORKLOADS[args.workload]
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    budget = min(150.0, 4.0 * (steps + warmup))
+    its, ms_step, cores, desc = time_cpu(method, dist, m, n, k, extra, steps, warmup, budget)
+    line = {
+        "impl": "reference", "metric": "nmf_outer_iterations_per_second", "value": its, "unit": "it/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 / its,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": args.workload, "method": method, "distance": dist, "m": m, "n": n, "k": k,
+                   **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
+        "cpu_baseline": {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": its, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------
+PHASES = {  # names of the intervals between consecutive phase events of a solver step
+    ("mur", "eu"): ["gram_h", "gemm_w", "update_w", "gram_w", "gemm_h", "update_h", "objective"],
+}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from nmf_b200 import solvers
+    from nmf_b200.engine import Engine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    method, dtype_, m, n, k, extra = WORKLOADS[args.workload]
+    steps, warmup = max(1, args.steps), max(3, args.warmup)
+    peaks = load_peaks()
+
+    eng = Engine(m, n, k, device=dev, rank=rank, world=world)
+    synth_fill_engine(eng, seed=0)
+    synth_init(eng, seed=1)
+    stepper = solvers.make_stepper(eng, method, dtype_, **extra)
+    stepper.prepare()
+    launches0 = eng.launch_count()
+    for i in range(warmup):
+        stepper.step(i % 8)
+    torch.cuda.synchronize(dev)
+    launches_per_step = (eng.launch_count() - launches0) // warmup
+
+    names = PHASES.get((method, dtype_), stepper.phase_names())
+    nev = len(names) + 1
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(nev)] for _ in range(steps)]
+    for row in evs:
+        for e in row:
+            e.record()                                   # materialise the cudaEvent_t handles
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    with ClockSampler(local_rank) as clk:
+        t0.record()
+        for i in range(steps):
+            eng.set_phase_events(evs[i])
+            stepper.step(i % 8)
+        t1.record()
+        torch.cuda.synchronize(dev)
+    eng.set_phase_events(None)
+    ms_total = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+        dist.barrier()
+    ms_step = float(ms_total.item()) / steps
+    value = 1e3 / ms_step
+    obj_last = eng.read_scalar(((steps - 1) % 8) * 8)
+
+    phase_ms = {nm: float(np.mean([evs[i][j].elapsed_time(evs[i][j + 1]) for i in range(steps)]))
+                for j, nm in enumerate(names)}
+    roof = stepper.roofline(phase_ms, peaks)
+
+    line = {
+        "metric": "nmf_outer_iterations_per_second", "value": value, "unit": "it/s", "n_gpus": world,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16x2-split/f32-accumulate",
+        "data": "synthetic",
+        "config": {"workload": args.workload, "method": method, "distance": dtype_, "m": m, "n": n, "k": k,
+                   "v_storage": "bf16 (lossless, V and V^T resident)", "l2": "inputs_exceed_l2",
+                   "objective_every_iteration": True, "parallelism": f"rows/cols x{world}",
+                   **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
+        "clocks": clk.summary(),
+        "gpu_launches": int(launches_per_step * steps),
+        "phase_ms": {kk: round(vv, 4) for kk, vv in phase_ms.items()},
+        "roofline": roof,
+        "alg_tflops": alg_flops_per_iter(method, dtype_, m, n, k, extra) / (ms_step * 1e-3) / 1e12 / world,
+        "objective_last": obj_last,
+        "peaks": peaks["source"],
+    }
+
+    # ---- end to end through the public API with HOST buffers (N = 1) ----
+    if not args.no_e2e and world == 1:
+        line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps)
+    else:
+        line["e2e"] = None
+    if not args.no_cpu and rank == 0 and world == 1:
+        its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
+        line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
+    """NMF(V_host, k).factorize(...) with V, W0, H0 in (pinned) host memory; the timed region
+    covers upload, `steps` iterations (objective every iteration) and the download of W, H."""
+    import contextlib
+    import io
+
+    import torch
+    from nmf_b200 import NMF
+
+    dev = eng.device
+    v_host = torch.empty((m, n), dtype=torch.float32).pin_memory()
+    chunk = 4096
+    for r0 in range(0, m, chunk):
+        r1 = min(m, r0 + chunk)
+        v_host[r0:r1].copy_(eng.v_rows[0, r0:r1, :n].float())
+    w0 = eng.w.master[:k, :m].t().contiguous().cpu().numpy()     # current factors as the start
+    h0 = eng.h.master[:k, :n].contiguous().cpu().numpy()
+    torch.cuda.synchronize(dev)
+    eng.release()
+    torch.cuda.empty_cache()
+    v_np = v_host.numpy()
+    kw = dict(extra)
+    if method == "mur":
+        kw["distance_type"] = dtype_
+    else:
+        kw["nndsvd_init"] = (False, "zero")
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    model = NMF(v_np, k)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model.factorize(method=method, min_iter=10**9, max_iter=steps, w0=w0, h0=h0, verbose=False, **kw)
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    res = model.results
+    assert res.i == steps - 1 and len(res.obj_history) == steps + 1
+    h2d = v_np.nbytes + w0.nbytes + h0.nbytes
+    d2h = res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1)    # factors travel as fp32
+    return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
+            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps,
+            "what": "NMF(V_host fp32 pinned, k).factorize(max_iter=steps): ingest + iterations + factor download"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

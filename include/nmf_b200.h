@@ -70,10 +70,14 @@ typedef struct nmfb_problem {
     double* obj_partial;            /* fp64 [obj_partial_len] per-CTA objective partials      */
     int obj_partial_len;
     int num_sms;                    /* SM count of the device (148 on B200)                   */
+    void** phase_events;            /* optional cudaEvent_t[n_phase_events] recorded at the phase */
+    int n_phase_events;             /* boundaries of a solver step (profiling; NULL = off)        */
 } nmfb_problem;
 
 const char* nmfb_last_error(void);
 int nmfb_abi_version(void);
+/* kernels launched by this process through the library so far (for benchmarks' launch counts) */
+unsigned long long nmfb_launch_count(void);
 
 /* Padding rules, so that callers size buffers the way the kernels expect. */
 int nmfb_padded_components(int k);                 /* 64 / 128 / 256, or NMFB_ERR_ARG if k > 256 */

@@ -19,6 +19,9 @@ class NmfbError(RuntimeError):
         self.code = code
 
 
+P = C.POINTER
+
+
 class Data(C.Structure):            # struct nmfb_data
     _fields_ = [("planes", c_void_p), ("rows", c_int), ("cols", c_int), ("rows_p", c_int),
                 ("ld", c_int), ("nv", c_int)]
@@ -34,18 +37,18 @@ class Problem(C.Structure):         # struct nmfb_problem
                 ("v_rows", Data), ("v_cols", Data), ("w", Factor), ("h", Factor),
                 ("gram32", c_void_p), ("gram64", c_void_p),
                 ("partial", c_void_p), ("partial_bytes", c_size_t),
-                ("obj_partial", c_void_p), ("obj_partial_len", c_int), ("num_sms", c_int)]
+                ("obj_partial", c_void_p), ("obj_partial_len", c_int), ("num_sms", c_int),
+                ("phase_events", P(c_void_p)), ("n_phase_events", c_int)]
 
 
 class AdmmSide(C.Structure):        # struct nmfb_admm_side
     _fields_ = [("aux", Factor), ("dual", c_void_p)]
 
 
-P = C.POINTER
-
 _SIGNATURES = {
     "nmfb_last_error": (C.c_char_p, []),
     "nmfb_abi_version": (c_int, []),
+    "nmfb_launch_count": (C.c_ulonglong, []),
     "nmfb_padded_components": (c_int, [c_int]),
     "nmfb_padded_length": (c_int, [c_int]),
     "nmfb_partial_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

@@ -9,6 +9,10 @@
 
 using namespace nmfb;
 
+namespace nmfb {
+unsigned long long g_launch_count = 0;
+}
+
 namespace {
 
 thread_local char g_err[512] = "";
@@ -69,12 +73,19 @@ inline cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
 
 int round_up(int x, int a) { return (x + a - 1) / a * a; }
 
+// Profiling hook: record the caller's event `idx` on the stream (no-op when none were supplied).
+inline void mark(const nmfb_problem* p, int idx, void* stream) {
+    if (p->phase_events && idx < p->n_phase_events && p->phase_events[idx])
+        cudaEventRecord(static_cast<cudaEvent_t>(p->phase_events[idx]), st(stream));
+}
+
 }  // namespace
 
 extern "C" {
 
 const char* nmfb_last_error(void) { return g_err; }
 int nmfb_abi_version(void) { return 1; }
+unsigned long long nmfb_launch_count(void) { return g_launch_count; }
 
 int nmfb_padded_components(int k) {
     if (k < 1 || k > 256) return fail(NMFB_ERR_ARG, "components must be in [1, 256], got %d", k);
@@ -182,7 +193,7 @@ int nmfb_gram(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes
     d.planes = f->cplanes;
     d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 2;
     const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, 2, partial, partial_bytes, 256, num_sms,
-                                      KP <= 128 ? 128 : 256, 0, stream);
+                                      128, 0, stream);
     if (slots < 0) return slots;
     CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
     return 0;
@@ -245,24 +256,33 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
     const int KP = p->KP;
     const size_t gsz = static_cast<size_t>(KP) * KP;
     int rc;
+    // phase events: 0 start | 1 gram(H) | 2 V.H^T | 3 W update | 4 gram(W) | 5 W^T.V | 6 H update | 7 objective
+    mark(p, 0, stream);
     // W <- W * (V H^T) / (W (H H^T) + lambda_w W + eps)                    mur.py:122 -> :29
     if ((rc = nmfb_gram(&p->h, KP, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz,
                         p->num_sms, stream)) < 0) return rc;
+    mark(p, 1, stream);
     int slots = nmfb_panel_gemm(&p->v_rows, p->h.cplanes, p->h.Lp, KP, 2, p->partial, p->partial_bytes,
                                 p->w.Lp, p->num_sms, 0, 0, stream);
     if (slots < 0) return slots;
+    mark(p, 2, stream);
     if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32 + gsz, &p->w, p->k, KP, lambda_w, stream)) < 0)
         return rc;
+    mark(p, 3, stream);
     // H <- H * (W^T V) / ((W^T W) H + lambda_h H + eps), with the NEW W    mur.py:123 -> :45
     if ((rc = nmfb_gram(&p->w, KP, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0)
         return rc;
+    mark(p, 4, stream);
     slots = nmfb_panel_gemm(&p->v_cols, p->w.cplanes, p->w.Lp, KP, 2, p->partial, p->partial_bytes, p->h.Lp,
                             p->num_sms, 0, 0, stream);
     if (slots < 0) return slots;
+    mark(p, 5, stream);
     if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32, &p->h, p->k, KP, lambda_h, stream)) < 0)
         return rc;
+    mark(p, 6, stream);
     // objective of the new pair                                            mur.py:124,127
-    if (obj_out) return nmfb_objective_eu(p, 0, obj_out, stream);
+    if (obj_out && (rc = nmfb_objective_eu(p, 0, obj_out, stream)) < 0) return rc;
+    mark(p, 7, stream);
     return 0;
 }
 

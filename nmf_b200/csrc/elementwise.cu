@@ -83,6 +83,7 @@ cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row
         ingest_data_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), src_ld, row0,
                                                            nrows, ncols, rowp, rowp_plane, rowp_ld, colp,
                                                            colp_plane, colp_ld, nv, stats);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -118,6 +119,7 @@ cudaError_t refresh_planes_launch(const float* master, int KP, int Lp, __nv_bflo
                                   __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream) {
     refresh_planes_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, KP, Lp, cpl, cpl_plane, rpl,
                                                                rpl_plane);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -144,6 +146,7 @@ cudaError_t import_factor_launch(const void* src, int is_f64, long stride_l, lon
     else
         import_factor_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), stride_l,
                                                              stride_c, L, k, master, KP, Lp);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -167,6 +170,7 @@ cudaError_t export_factor_launch(const float* master, int KP, int Lp, void* dst,
     else
         export_factor_kernel<float><<<grid, 256, 0, stream>>>(master, KP, Lp, static_cast<float*>(dst),
                                                              stride_l, stride_c, L, k);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -188,6 +192,7 @@ gram_reduce_kernel(const float* __restrict__ part, int slots, int KP, int Lp, fl
 cudaError_t gram_reduce_launch(const float* part, int slots, int KP, int Lp, float* g32, double* g64,
                                cudaStream_t stream) {
     gram_reduce_kernel<<<(KP * KP + 255) / 256, 256, 0, stream>>>(part, slots, KP, Lp, g32, g64);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -305,6 +310,7 @@ cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram
                                                               rpl_plane, k, L, Lp, lambda);
     }
     if (e != cudaSuccess) return e;
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -372,6 +378,7 @@ cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int ld
     dim3 grid((n + 63) / 64, (m + 63) / 64);
     *nparts = static_cast<int>(grid.x * grid.y);
     objective_simt_kernel<<<grid, 256, 0, stream>>>(vpl, v_plane, ldv, nv, wt, Mp, ht, Np, k, m, n, partial);
+    count_launch();
     return cudaGetLastError();
 }
 
@@ -393,6 +400,7 @@ sum_partials_kernel(const double* __restrict__ partial, int n, double scale, dou
 cudaError_t sum_partials_launch(const double* partial, int n, double scale, double* out,
                                 cudaStream_t stream) {
     sum_partials_kernel<<<1, 256, 0, stream>>>(partial, n, scale, out);
+    count_launch();
     return cudaGetLastError();
 }
 

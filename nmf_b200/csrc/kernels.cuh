@@ -9,6 +9,10 @@
 
 namespace nmfb {
 
+// Number of kernels this process has launched through the library (bench.py `gpu_launches`).
+extern unsigned long long g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count += static_cast<unsigned long long>(n); }
+
 // ------------------------------------------------------------------ panel GEMM (panel_gemm.cu)
 struct alignas(64) PanelGemmArgs {
     CUtensorMap fac[3];      // factor planes, component-major [>=KP rows][ld], box {64, 64|128}

@@ -295,6 +295,7 @@ cudaError_t panel_gemm_launch(const PanelGemmArgs& args, const PanelGemmPlan& pl
     const int nitems = plan.npanels * plan.nsplit;
     const int grid = nitems < num_sms ? nitems : num_sms;
     panel_gemm_kernel<<<grid, kThreads, plan.smem_bytes, stream>>>(args);
+    count_launch();
     return cudaGetLastError();
 }
 

@@ -266,6 +266,7 @@ cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t str
     const int smem = residual_smem_bytes(args.KP, args.NV, args.BN);
     if (smem < 0) return cudaErrorInvalidValue;
     residual_kernel<<<grid, kThreadsR, smem, stream>>>(args);
+    count_launch();
     return cudaGetLastError();
 }
 

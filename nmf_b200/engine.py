@@ -48,12 +48,18 @@ class Engine:
 
     ROW_CHUNK_BYTES = 512 << 20
 
-    def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None):
+    def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None, rank: int = 0,
+                 world: int = 1):
         if not torch.cuda.is_available():
             raise RuntimeError("nmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
         self.lib = _lib.load()
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.m, self.n, self.k = int(m), int(n), int(k)
+        self.rank, self.world = int(rank), int(world)
+        if self.world != 1:
+            raise NotImplementedError("sharded engines are built by nmf_b200.sharded.ShardedEngine")
+        self.row_range = (0, self.m)          # rows of V held in v_rows
+        self.col_range = (0, self.n)          # columns of V held (transposed) in v_cols
         self.KP = check(self.lib.nmfb_padded_components(self.k))
         self.Mp = (self.m + 255) // 256 * 256
         self.Np = (self.n + 255) // 256 * 256
@@ -101,8 +107,23 @@ class Engine:
             self._problem = Problem(self.m, self.n, self.k, self.KP, vr, vc, self.w.struct(), self.h.struct(),
                                     self.gram32.data_ptr(), self.gram64.data_ptr(),
                                     self.partial.data_ptr(), self.partial.numel() * 4,
-                                    self.obj_partial.data_ptr(), self.obj_partial_len, self.num_sms)
+                                    self.obj_partial.data_ptr(), self.obj_partial_len, self.num_sms,
+                                    None, 0)
         return self._problem
+
+    def set_phase_events(self, events):
+        """Profiling hook: torch.cuda.Event(enable_timing=True) objects (already recorded once, so
+        that their cudaEvent_t exists) that the next solver step records at its phase boundaries.
+        Pass None to switch the hook off."""
+        p = self.problem()
+        if not events:
+            self._phase_arr = None
+            p.phase_events, p.n_phase_events = None, 0
+            return
+        arr = (C.c_void_p * len(events))(*[int(e.cuda_event) for e in events])
+        self._phase_arr = arr                       # keep alive
+        p.phase_events = C.cast(arr, C.POINTER(C.c_void_p))
+        p.n_phase_events = len(events)
 
     # ------------------------------------------------------------------ data in
     def _ingest_pass(self, v: np.ndarray):
@@ -194,3 +215,13 @@ class Engine:
 
     def read_scalar(self, slot: int = 0) -> float:
         return float(self.scalars[slot].item())
+
+    def launch_count(self) -> int:
+        return int(self.lib.nmfb_launch_count())
+
+    def release(self):
+        """Drop every device buffer (the object is unusable afterwards)."""
+        self.v_rows = self.v_cols = None
+        self.w = self.h = None
+        self.partial = self.obj_partial = self.gram32 = self.gram64 = None
+        self._problem = None

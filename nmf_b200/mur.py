@@ -13,6 +13,7 @@ import numpy as np
 
 from . import _loop
 from .engine import Engine
+from .solvers import make_stepper
 from .utils import tol_precision
 
 Experiment = namedtuple('Experiment', 'method components distance_type nndsvd_init max_iter tol1 tol2 lambda_w lambda_h')
@@ -47,13 +48,10 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
         w0, h0 = initial_factors(x, k, nndsvd_init)
     eng.set_factors(np.asarray(w0), np.asarray(h0))
 
-    if distance_type == 'eu':
-        eng.objective_eu(slot=0)
-        step = lambda slot: eng.mur_eu_step(lambda_w, lambda_h, obj_slot=slot * 8)
-    else:
-        eng.objective_kl(slot=0)
-        step = lambda slot: eng.mur_kl_step(lambda_w, lambda_h, obj_slot=slot * 8)
+    stepper = make_stepper(eng, 'mur', distance_type, lambda_w=lambda_w, lambda_h=lambda_h)
+    stepper.prepare()                                  # objective of the initial pair -> scalars[0]
     obj0 = eng.read_scalar(0)
+    step = stepper.step
 
     logging.info('Entering Main Loop.')
     lr = _loop.run(eng, step, obj0=obj0, min_iter=min_iter, max_iter=max_iter, tol1=tol1, tol2=tol2,
