@@ -1,0 +1,375 @@
+// ADMM / AO-ADMM kernels around the tensor-core contractions.
+//
+//   chol_inverse_kernel   k x k SPD system matrix  A = G + rho I  (fp64): Cholesky factor in shared
+//                         memory (one CTA), then A^-1 by forward/backward substitution against the
+//                         identity.  rho is either the caller's scalar (admm.py:220) or trace(G)/k
+//                         (ao_admm.py:54).  A non-positive pivot raises the not-PD flag
+//                         (scipy.linalg.cholesky -> LinAlgError, ao_admm.py:55).
+//   admm_apply_kernel     aux = A^-1 (C + rho (x + u))   [admm.py:221,230 / ao_admm.py:59]
+//                         x   = max(aux - u - lambda/rho, 0)      [prox nn / l1n, admm.py:126-139]
+//                         u  += x - aux                            [admm.py:320-321 / ao_admm.py:62]
+//                         fused with the four Frobenius norms of ao_admm.terminate (ao_admm.py:36-38)
+//                         and with every bf16 plane the next contraction needs.  C is the fp32 partial
+//                         sums of the panel GEMM reduced in fp64; the k x k product runs on the FP64
+//                         pipe (fp32 is not accurate enough here: SURVEY.md 7.3-1b).
+//   admm_inner_flag_kernel  reduces the norm partials in a fixed order and raises the device-side
+//                         "inner loop done" flag: r < 1e-2 and s < 1e-2, NaN/inf compare false.
+#include "admm.cuh"
+#include "ptx.cuh"
+
+namespace nmfb {
+
+// ------------------------------------------------------------------ Cholesky + inverse
+// One CTA of 1024 threads.  `a` is the working matrix (pitch lda doubles): shared memory when
+// KP <= 128, a global scratch otherwise.  Threads are grouped 8 per column for the substitutions;
+// lane l of a group keeps the entries p == l (mod 8) of its column in registers.
+template <int KP>
+__global__ void __launch_bounds__(1024, 1)
+chol_inverse_kernel(const double* __restrict__ gram, int k, int rho_mode, double rho_in,
+                    double* __restrict__ gscratch, double* __restrict__ ainv,
+                    double* __restrict__ rho_out, int* __restrict__ flags) {
+    extern __shared__ double sm_d[];
+    constexpr int NQ = KP / 8;
+    constexpr bool kInSmem = (KP <= 128);
+    const int lda = KP + 1;
+    double* a = kInSmem ? sm_d : gscratch;
+    __shared__ double s_rho;
+    __shared__ int s_bad;
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        double rho = rho_in;
+        if (rho_mode == 1) {                       // ao_admm.py:54  rho = trace(G) / k
+            double tr = 0.0;
+            for (int i = 0; i < k; ++i) tr += gram[static_cast<long>(i) * KP + i];
+            rho = tr / static_cast<double>(k);
+        }
+        s_rho = rho;
+        s_bad = 0;
+        rho_out[0] = rho;
+    }
+    __syncthreads();
+    const double rho = s_rho;
+    for (int idx = tid; idx < KP * KP; idx += 1024) {
+        const int i = idx / KP, j = idx - i * KP;
+        double v = gram[idx];
+        if (i == j) v += (i < k) ? rho : 1.0;      // padded components: identity block
+        a[i * lda + j] = v;
+    }
+    __syncthreads();
+
+    // right-looking Cholesky, lower triangle in place
+    for (int j = 0; j < KP; ++j) {
+        const double d = a[j * lda + j];
+        if (!(d > 0.0)) {                          // also catches NaN
+            if (tid == 0) s_bad = 1;
+            break;                                 // uniform: every thread reads the same d
+        }
+        const double inv_s = 1.0 / sqrt(d);
+        __syncthreads();
+        for (int i = j + tid; i < KP; i += 1024) a[i * lda + j] *= inv_s;     // a[j][j] -> sqrt(d)
+        __syncthreads();
+        const int rem = KP - 1 - j;                // trailing block (j+1 .. KP-1)^2, lower part
+        for (int idx = tid; idx < rem * rem; idx += 1024) {
+            const int ii = idx / rem, cc = idx - ii * rem;
+            if (cc <= ii) {
+                const int i = j + 1 + ii, c = j + 1 + cc;
+                a[i * lda + c] -= a[i * lda + j] * a[c * lda + j];
+            }
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    if (s_bad) {
+        if (tid == 0) flags[0] = 1;
+        return;
+    }
+
+    // A^-1 column by column: L y = e_c (forward), L^T x = y (backward); 8 lanes per column.
+    const int l = tid & 7;
+    for (int c = tid >> 3; c < KP; c += 128) {
+        double y[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) y[q] = 0.0;
+        for (int i = 0; i < KP; ++i) {             // uniform trip count: the shuffles are warp-wide
+            double part = 0.0;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int p = l + 8 * q;
+                if (p >= c && p < i) part += a[i * lda + p] * y[q];
+            }
+            part += __shfl_xor_sync(0xffffffffu, part, 1);
+            part += __shfl_xor_sync(0xffffffffu, part, 2);
+            part += __shfl_xor_sync(0xffffffffu, part, 4);
+            const double yi = ((i == c ? 1.0 : 0.0) - part) / a[i * lda + i];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+                if (l + 8 * q == i) y[q] = yi;
+        }
+        for (int i = KP - 1; i >= 0; --i) {
+            double part = 0.0;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int p = l + 8 * q;
+                if (p > i) part += a[p * lda + i] * y[q];
+            }
+            part += __shfl_xor_sync(0xffffffffu, part, 1);
+            part += __shfl_xor_sync(0xffffffffu, part, 2);
+            part += __shfl_xor_sync(0xffffffffu, part, 4);
+            double yi = 0.0;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+                if (l + 8 * q == i) yi = y[q];
+            yi = __shfl_sync(0xffffffffu, yi, (threadIdx.x & 24) | (i & 7));   // owner lane of entry i
+            const double xi = (yi - part) / a[i * lda + i];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+                if (l + 8 * q == i) y[q] = xi;
+        }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) ainv[static_cast<long>(c) * KP + l + 8 * q] = y[q];
+    }
+}
+
+cudaError_t chol_inverse_launch(const double* gram, int KP, int k, int rho_mode, double rho_in,
+                                double* gscratch, double* ainv, double* rho_out, int* flags,
+                                cudaStream_t stream) {
+    cudaError_t e = cudaSuccess;
+    if (KP == 64) {
+        const size_t sm = 64 * 65 * sizeof(double);
+        chol_inverse_kernel<64><<<1, 1024, sm, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
+    } else if (KP == 128) {
+        const size_t sm = 128 * 129 * sizeof(double);
+        static bool set = false;
+        if (!set) {
+            e = cudaFuncSetAttribute(chol_inverse_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(sm));
+            if (e != cudaSuccess) return e;
+            set = true;
+        }
+        chol_inverse_kernel<128><<<1, 1024, sm, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
+    } else {
+        chol_inverse_kernel<256><<<1, 1024, 0, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ solve + prox + dual (+ norms)
+// One block owns 64 consecutive columns r of the k x L factor and all KP components.
+//   b[c][r]   = C[c][r] + rho (x[c][r] + u[c][r])                (fp64, shared memory)
+//   aux[c][r] = sum_c' Ainv[c][c'] b[c'][r]                      (fp64 FMA, register tile CPT x 4)
+//   x' = max(aux - u - lambda/rho, 0),  u' = u + x' - aux
+template <int CPT>
+__global__ void __launch_bounds__(256)
+admm_apply_kernel(const AdmmApplyArgs p) {
+    constexpr int KP = CPT * 16;
+    constexpr int TR = 64;
+    constexpr int CK = 32;
+    extern __shared__ double sm_d[];
+    double* bs = sm_d;                    // [KP][TR]
+    double* gs = sm_d + KP * TR;          // [CK][KP]
+    __shared__ double red[8][4];
+    if (p.done_flag != nullptr && *p.done_flag != 0) return;
+    const int tid = threadIdx.x;
+    const int tr = tid & 15, tc = tid >> 4;
+    const int r0 = blockIdx.x * TR;
+    const int Lp = p.Lp;
+    const double rho = *p.rho;
+    const double thr = (p.prox == 1) ? static_cast<double>(p.lambda) / rho : 0.0;
+
+    for (int i = tid; i < KP * TR; i += 256) {
+        const int c = i / TR, rr = i - c * TR;
+        const long off = static_cast<long>(c) * Lp + r0 + rr;
+        double cv;
+        if (p.part != nullptr) {
+            cv = 0.0;
+            for (int s = 0; s < p.slots; ++s)
+                cv += static_cast<double>(p.part[static_cast<long>(s) * KP * Lp + off]);
+            if (p.c64 != nullptr) p.c64[off] = cv;
+        } else {
+            cv = p.c64[off];
+        }
+        bs[i] = cv + rho * (static_cast<double>(p.x[off]) + static_cast<double>(p.u[off]));
+    }
+    double acc[CPT][4];
+#pragma unroll
+    for (int a = 0; a < CPT; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+
+    for (int ck = 0; ck < KP; ck += CK) {
+        __syncthreads();
+        for (int i = tid; i < CK * KP / 2; i += 256)
+            reinterpret_cast<double2*>(gs)[i] =
+                *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + i * 2);
+        __syncthreads();
+#pragma unroll 2
+        for (int cc = 0; cc < CK; ++cc) {
+            const double2 x01 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4);
+            const double2 x23 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4 + 2);
+            const double* grow = gs + cc * KP + tc * CPT;         // Ainv symmetric: row (ck+cc)
+#pragma unroll
+            for (int a = 0; a < CPT; a += 2) {
+                const double2 g = *reinterpret_cast<const double2*>(grow + a);
+                acc[a][0] = fma(g.x, x01.x, acc[a][0]);     acc[a][1] = fma(g.x, x01.y, acc[a][1]);
+                acc[a][2] = fma(g.x, x23.x, acc[a][2]);     acc[a][3] = fma(g.x, x23.y, acc[a][3]);
+                acc[a + 1][0] = fma(g.y, x01.x, acc[a + 1][0]); acc[a + 1][1] = fma(g.y, x01.y, acc[a + 1][1]);
+                acc[a + 1][2] = fma(g.y, x23.x, acc[a + 1][2]); acc[a + 1][3] = fma(g.y, x23.y, acc[a + 1][3]);
+            }
+        }
+    }
+
+    double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
+    __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
+#pragma unroll
+    for (int a = 0; a < CPT; ++a) {
+        const int c = tc * CPT + a;
+        const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
+        const float4 xo4 = *reinterpret_cast<const float4*>(p.x + off);
+        const float4 uo4 = *reinterpret_cast<const float4*>(p.u + off);
+        const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
+        float xn[4], un[4], ax[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
+            const double aux = live ? acc[a][b] : 0.0;
+            double xv = aux - static_cast<double>(uo[b]) - thr;
+            xv = (live && xv > 0.0) ? xv : 0.0;
+            const double uv = live ? static_cast<double>(uo[b]) + xv - aux : 0.0;
+            xn[b] = static_cast<float>(xv);
+            un[b] = static_cast<float>(uv);
+            ax[b] = static_cast<float>(aux);
+            const double d0 = xv - aux, d2 = xv - static_cast<double>(xo[b]);
+            n_ra = fma(d0, d0, n_ra); n_x = fma(xv, xv, n_x); n_dx = fma(d2, d2, n_dx); n_u = fma(uv, uv, n_u);
+        }
+        *reinterpret_cast<float4*>(p.x + off) = make_float4(xn[0], xn[1], xn[2], xn[3]);
+        *reinterpret_cast<float4*>(p.u + off) = make_float4(un[0], un[1], un[2], un[3]);
+        if (p.aux_master != nullptr)
+            *reinterpret_cast<float4*>(p.aux_master + off) = make_float4(ax[0], ax[1], ax[2], ax[3]);
+        if (p.aux_cpl != nullptr) {
+            __align__(8) __nv_bfloat16 p0[4], p1[4], p2[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) split3(ax[b], p0[b], p1[b], p2[b]);
+            *reinterpret_cast<uint2*>(p.aux_cpl + off) = *reinterpret_cast<const uint2*>(p0);
+            *reinterpret_cast<uint2*>(p.aux_cpl + p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p1);
+            *reinterpret_cast<uint2*>(p.aux_cpl + 2 * p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p2);
+        }
+        __align__(8) __nv_bfloat16 q0[4], q1[4], q2[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            split3(xn[b], q0[b], q1[b], q2[b]);
+            rh[b][a] = q0[b];
+            rl[b][a] = q1[b];
+        }
+        if (p.x_cpl != nullptr) {
+            *reinterpret_cast<uint2*>(p.x_cpl + off) = *reinterpret_cast<const uint2*>(q0);
+            *reinterpret_cast<uint2*>(p.x_cpl + p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q1);
+            *reinterpret_cast<uint2*>(p.x_cpl + 2 * p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q2);
+        }
+    }
+    if (p.x_rpl != nullptr) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const long ro = static_cast<long>(r0 + tr * 4 + b) * KP + tc * CPT;
+#pragma unroll
+            for (int a = 0; a < CPT; a += 4) {
+                *reinterpret_cast<uint2*>(p.x_rpl + ro + a) = *reinterpret_cast<const uint2*>(&rh[b][a]);
+                *reinterpret_cast<uint2*>(p.x_rpl + p.x_rpl_plane + ro + a) = *reinterpret_cast<const uint2*>(&rl[b][a]);
+            }
+        }
+    }
+    if (p.norm_partial != nullptr) {
+        for (int o = 16; o; o >>= 1) {
+            n_ra += __shfl_xor_sync(0xffffffffu, n_ra, o);
+            n_x += __shfl_xor_sync(0xffffffffu, n_x, o);
+            n_dx += __shfl_xor_sync(0xffffffffu, n_dx, o);
+            n_u += __shfl_xor_sync(0xffffffffu, n_u, o);
+        }
+        if ((tid & 31) == 0) {
+            red[tid >> 5][0] = n_ra; red[tid >> 5][1] = n_x; red[tid >> 5][2] = n_dx; red[tid >> 5][3] = n_u;
+        }
+        __syncthreads();
+        if (tid < 4) {
+            double t = 0.0;
+            for (int w = 0; w < 8; ++w) t += red[w][tid];
+            p.norm_partial[static_cast<long>(blockIdx.x) * 4 + tid] = t;
+        }
+    }
+}
+
+cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
+    const int grid = a.Lp / 64;
+    const size_t smem = (static_cast<size_t>(a.KP) * 64 + 32 * static_cast<size_t>(a.KP)) * sizeof(double);
+    static bool set[3] = {false, false, false};
+    cudaError_t e = cudaSuccess;
+    if (a.KP == 64) {
+        if (!set[0]) { e = cudaFuncSetAttribute(admm_apply_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); set[0] = true; }
+        admm_apply_kernel<4><<<grid, 256, smem, stream>>>(a);
+    } else if (a.KP == 128) {
+        if (!set[1]) { e = cudaFuncSetAttribute(admm_apply_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024); set[1] = true; }
+        admm_apply_kernel<8><<<grid, 256, smem, stream>>>(a);
+    } else {
+        if (!set[2]) { e = cudaFuncSetAttribute(admm_apply_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); set[2] = true; }
+        admm_apply_kernel<16><<<grid, 256, smem, stream>>>(a);
+    }
+    if (e != cudaSuccess) return e;
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ inner-loop termination flag
+__global__ void __launch_bounds__(256)
+admm_inner_flag_kernel(const double* __restrict__ norm_partial, int nblocks, int* __restrict__ flags,
+                       int used_idx) {
+    __shared__ double red[256][4];
+    if (flags[1] != 0) return;                          // already broke out of the inner loop
+    double t[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int i = threadIdx.x; i < nblocks; i += 256)
+        for (int q = 0; q < 4; ++q) t[q] += norm_partial[static_cast<long>(i) * 4 + q];
+    for (int q = 0; q < 4; ++q) red[threadIdx.x][q] = t[q];
+    __syncthreads();
+    for (int s = 128; s; s >>= 1) {
+        if (threadIdx.x < s)
+            for (int q = 0; q < 4; ++q) red[threadIdx.x][q] += red[threadIdx.x + s][q];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        // ao_admm.py:36-43: r = |x - aux| / |x|, s = |x - x_prev| / |u|; NaN / inf compare false
+        const double r = sqrt(red[0][0]) / sqrt(red[0][1]);
+        const double s = sqrt(red[0][2]) / sqrt(red[0][3]);
+        if (r < 1e-2 && s < 1e-2) flags[1] = 1;
+        else flags[used_idx] += 1;
+    }
+}
+
+cudaError_t admm_inner_flag_launch(const double* norm_partial, int nblocks, int* flags, int used_idx,
+                                   cudaStream_t stream) {
+    admm_inner_flag_kernel<<<1, 256, 0, stream>>>(norm_partial, nblocks, flags, used_idx);
+    count_launch();
+    return cudaGetLastError();
+}
+
+__global__ void admm_flags_reset_kernel(int* flags, int mask) {
+    if (threadIdx.x < 8 && ((mask >> threadIdx.x) & 1)) flags[threadIdx.x] = 0;
+}
+cudaError_t admm_flags_reset_launch(int* flags, int mask, cudaStream_t stream) {
+    admm_flags_reset_kernel<<<1, 32, 0, stream>>>(flags, mask);
+    count_launch();
+    return cudaGetLastError();
+}
+
+__global__ void admm_flags_publish_kernel(const int* flags, double* mailbox) {
+    if (threadIdx.x == 0) {
+        mailbox[1] = static_cast<double>(flags[2]);
+        mailbox[2] = static_cast<double>(flags[3]);
+        mailbox[3] = static_cast<double>(flags[0]);
+    }
+}
+cudaError_t admm_flags_publish_launch(const int* flags, double* mailbox, cudaStream_t stream) {
+    admm_flags_publish_kernel<<<1, 32, 0, stream>>>(flags, mailbox);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace nmfb
