@@ -130,11 +130,7 @@ def synth_fill_engine(eng, seed: int):
         blk = wt[r0:r1] @ ht
         blk.add_(torch.rand((r1 - r0, n), device=dev, generator=g), alpha=0.01)
         blk = blk.bfloat16()
-        a, b = max(r0, r_lo), min(r1, r_hi)
-        if a < b:
-            eng.v_rows[0, a - r_lo:b - r_lo, :n] = blk[a - r0:b - r0]
-        if c_lo < c_hi:
-            eng.v_cols[0, :c_hi - c_lo, r0:r1] = blk[:, c_lo:c_hi].t()
+        eng.store_block(blk, r0)
         del blk
     return wt, ht
 
@@ -404,7 +400,7 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
     chunk = 4096
     for r0 in range(0, m, chunk):
         r1 = min(m, r0 + chunk)
-        v_host[r0:r1].copy_(eng.v_rows[0, r0:r1, :n].float())
+        v_host[r0:r1].copy_(eng.v_rows[0, :, r0:r1, :].permute(1, 0, 2).reshape(r1 - r0, -1)[:, :n].float())
     w0 = eng.w.master[:k, :m].t().contiguous().cpu().numpy()     # current factors as the start
     h0 = eng.h.master[:k, :n].contiguous().cpu().numpy()
     torch.cuda.synchronize(dev)

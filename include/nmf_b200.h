@@ -19,7 +19,9 @@
  * Device layouts (all padded regions must be zero-initialised by the caller; the library keeps
  * them zero):  k <= 256 components are padded to KP = 64, 128 or 256;  a length L (m or n) is
  * padded to Lp = round_up(L, 256).
- *   data planes  bf16 [nv][rows_p][ld]   row-major planes of V (rows = m) or V^T (rows = n);
+ *   data planes  bf16 [nv][ld/64][rows_p][64]  K-blocked planes of V (rows = m) or V^T (rows = n):
+ *                                        element (r, c) lives at ((c/64)*rows_p + r)*64 + c%64, so the
+ *                                        [rows x 64] box of one contraction block is contiguous in HBM;
  *                                        rows_p = round_up(rows, 256), ld = round_up(cols, 256);
  *                                        plane 0 = hi, plane 1 = lo (nv = 1 when V is bf16-exact)
  *   master       fp32 [KP][Lp]           solver state of a factor, component-major (W^T or H)
@@ -47,8 +49,9 @@ typedef enum nmfb_status {
 } nmfb_status;
 
 typedef struct nmfb_data {          /* V (rows = m, cols = n) or V^T (rows = n, cols = m) */
-    void* planes;                   /* bf16 [nv][rows_p][ld] */
+    void* planes;                   /* bf16 [nv][ld/64][rows_p][64] (K-blocked) or [nv][rows_p][ld] */
     int rows, cols, rows_p, ld, nv;
+    int blocked;                    /* 1: K-blocked layout (V, V^T); 0: plain row-major           */
 } nmfb_data;
 
 typedef struct nmfb_factor {        /* W (L = m) or H (L = n) */
@@ -117,8 +120,9 @@ int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int facto
 
 /* Gram matrix G = F F^T of a factor from its cplanes (`w.T @ w` ao_admm.py:53, `other_aux.T @
  * other_aux` admm.py:220, and the W (H H^T) / (W^T W) H re-association of mur.py:29,45).
+ * nplanes = 2: hi/lo planes (16-bit operands, MUR), 3: hi/lo/lo2 (24-bit operands, ADMM / AO-ADMM).
  * Uses `partial` as scratch; writes gram32 [KP][KP] and gram64 [KP][KP]. */
-int nmfb_gram(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
               double* gram64, int num_sms, void* stream);
 
 /* Fused multiplicative update  x <- x * num / (G x + lambda x + 1e-9)  (mur.py:29 / mur.py:45):
@@ -135,6 +139,41 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
  * new W, then the objective of the new pair into *obj_out (skipped when obj_out == NULL). */
 int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out,
                      void* stream);
+
+/* ---- ADMM / AO-ADMM ------------------------------------------------------------------------- */
+typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1 } nmfb_prox;   /* admm.py:126-139 */
+
+typedef struct nmfb_admm_state {
+    nmfb_factor w_aux, h_aux;       /* ADMM only: signed auxiliaries (admm.py:27-28); cplanes hold 3 planes */
+    float* dual_w;                  /* fp32 [KP][Mp]  scaled dual of W (component-major, like the master) */
+    float* dual_h;                  /* fp32 [KP][Np]                                                     */
+    double* ainv;                   /* fp64 [2][KP][KP]: inverse of (Gram + rho I); [0] H-side, [1] W-side */
+    double* chol_scratch;           /* fp64 [KP][KP+1]  working matrix when KP = 256 (else unused)        */
+    double* c64;                    /* fp64 [KP][max(Mp,Np)]  reduced numerator (AO-ADMM inner loop)      */
+    double* scal;                   /* fp64 [4]: [0] rho of the H-side system, [1] rho of the W-side      */
+    int* flags;                     /* int  [8]: [0] not-PD (sticky) [1] inner done [2] inner iterations  */
+                                    /*           used by the H update [3] ... by the W update             */
+    double* norm_partial;           /* fp64 [4 * max(Mp,Np)/64]                                           */
+} nmfb_admm_state;
+
+/* ainv = (gram + rho I)^-1 by a shared-memory Cholesky (fp64), rho = rho_in (rho_mode 0, admm.py:220)
+ * or trace(gram)/k (rho_mode 1, ao_admm.py:54); *rho_out = rho.  flags[0] is raised when the matrix is
+ * not positive definite (scipy.linalg.cholesky / numpy.linalg.solve -> LinAlgError). */
+int nmfb_chol_inverse(const double* gram64, int k, int KP, int rho_mode, double rho_in, double* scratch,
+                      double* ainv, double* rho_out, int* flags, void* stream);
+
+/* One outer iteration of ADMM, Euclidean (admm.py:294-301, 320-324): h_aux, w_aux (with the new h_aux),
+ * both prox steps with the old duals, both dual updates, objective of the prox'd pair.
+ * mailbox[0] = objective, mailbox[3] = not-PD flag. */
+int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, float lambda_w, int prox_w,
+                   float lambda_h, int prox_h, double* mailbox, void* stream);
+
+/* One outer iteration of AO-ADMM, Euclidean (ao_admm.py:261-270, 291): per factor Gram, rho = tr/k,
+ * Cholesky, numerator GEMM, then up to admm_iter x (solve, prox, dual, residual test ao_admm.py:33-43)
+ * with the early break decided on the device.  mailbox[0] = objective, [1] / [2] = inner iterations
+ * completed without a break for H / W (== admm_iter when no break), [3] = not-PD flag. */
+int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_iter, float lambda_w,
+                     int prox_w, float lambda_h, int prox_h, double* mailbox, void* stream);
 
 #ifdef __cplusplus
 }

@@ -24,7 +24,7 @@ P = C.POINTER
 
 class Data(C.Structure):            # struct nmfb_data
     _fields_ = [("planes", c_void_p), ("rows", c_int), ("cols", c_int), ("rows_p", c_int),
-                ("ld", c_int), ("nv", c_int)]
+                ("ld", c_int), ("nv", c_int), ("blocked", c_int)]
 
 
 class Factor(C.Structure):          # struct nmfb_factor
@@ -41,8 +41,10 @@ class Problem(C.Structure):         # struct nmfb_problem
                 ("phase_events", P(c_void_p)), ("n_phase_events", c_int)]
 
 
-class AdmmSide(C.Structure):        # struct nmfb_admm_side
-    _fields_ = [("aux", Factor), ("dual", c_void_p)]
+class AdmmState(C.Structure):       # struct nmfb_admm_state
+    _fields_ = [("w_aux", Factor), ("h_aux", Factor), ("dual_w", c_void_p), ("dual_h", c_void_p),
+                ("ainv", c_void_p), ("chol_scratch", c_void_p), ("c64", c_void_p), ("scal", c_void_p),
+                ("flags", c_void_p), ("norm_partial", c_void_p)]
 
 
 _SIGNATURES = {
@@ -59,10 +61,16 @@ _SIGNATURES = {
     "nmfb_export_factor": (c_int, [P(Factor), c_int, c_int, c_void_p, c_int, c_long, c_long, c_void_p]),
     "nmfb_panel_gemm": (c_int, [P(Data), c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_int,
                                 c_int, c_int, c_void_p]),
-    "nmfb_gram": (c_int, [P(Factor), c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
+    "nmfb_gram": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
     "nmfb_mur_eu_update": (c_int, [c_void_p, c_int, c_void_p, P(Factor), c_int, c_int, c_float, c_void_p]),
     "nmfb_objective_eu": (c_int, [P(Problem), c_int, c_void_p, c_void_p]),
     "nmfb_mur_eu_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
+    "nmfb_chol_inverse": (c_int, [c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p]),
+    "nmfb_admm_step": (c_int, [P(Problem), P(AdmmState), C.c_double, c_float, c_int, c_float, c_int, c_void_p,
+                               c_void_p]),
+    "nmfb_aoadmm_step": (c_int, [P(Problem), P(AdmmState), c_int, c_float, c_int, c_float, c_int, c_void_p,
+                                 c_void_p]),
 }
 
 _OPTIONAL = set()

@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "../../include/nmf_b200.h"
+#include "admm.cuh"
 #include "elementwise.cuh"
 #include "kernels.cuh"
 
@@ -100,7 +101,7 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
     const int Ls[3] = {m, n, 256}, Rs[3] = {n, m, (m > n ? m : n)};
     for (int i = 0; i < 3; ++i)
         for (int nb = 2; nb <= 3; ++nb)
-            for (int na = 1; na <= 2; ++na) {
+            for (int na = 1; na <= 3; ++na) {
                 PanelGemmPlan pl;
                 if (panel_gemm_plan(KP, nb, na, Ls[i], Rs[i], 0, 0, num_sms, &pl) != 0) continue;
                 const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
@@ -121,9 +122,10 @@ int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int
     if (vr->rows != vc->cols || vr->cols != vc->rows || vr->nv != vc->nv)
         return fail(NMFB_ERR_ARG, "ingest_data: v_rows / v_cols shapes disagree");
     if (row0 < 0 || row0 + nrows > vr->rows) return fail(NMFB_ERR_ARG, "ingest_data: row range");
+    if (!vr->blocked || !vc->blocked) return fail(NMFB_ERR_ARG, "ingest_data: data planes must be K-blocked");
     CUDA_TRY(ingest_data_launch(src, src_is_f64, src_ld, row0, nrows, vr->cols, bf(vr->planes),
-                                static_cast<long>(vr->rows_p) * vr->ld, vr->ld, bf(vc->planes),
-                                static_cast<long>(vc->rows_p) * vc->ld, vc->ld, vr->nv, stats, st(stream)));
+                                static_cast<long>(vr->rows_p) * vr->ld, vr->rows_p, bf(vc->planes),
+                                static_cast<long>(vc->rows_p) * vc->ld, vc->rows_p, vr->nv, stats, st(stream)));
     return 0;
 }
 
@@ -165,7 +167,7 @@ int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int facto
         return fail(NMFB_ERR_WORKSPACE, "panel_gemm: partial workspace %zu < %zu bytes", partial_bytes, need);
     PanelGemmArgs a;
     memset(&a, 0, sizeof(a));
-    const int a_box_rows = (KP == 64) ? 64 : 128;
+    const int a_box_rows = ((KP == 64) ? 64 : 128) / pl.cluster;     // each CTA fetches 1/cluster of a tile
     for (int j = 0; j < nb; ++j) {
         const __nv_bfloat16* base = bf(factor_cplanes) + static_cast<long>(j) * 256 * factor_Lp;
         int rc = make_map(&a.fac[j], base, 256, factor_Lp, a_box_rows);
@@ -173,7 +175,9 @@ int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int facto
     }
     for (int i = 0; i < data->nv; ++i) {
         const __nv_bfloat16* base = bf(data->planes) + static_cast<long>(i) * data->rows_p * data->ld;
-        int rc = make_map(&a.dat[i], base, data->rows_p, data->ld, pl.BN);
+        int rc = data->blocked
+                     ? make_map(&a.dat[i], base, static_cast<long>(data->ld / 64) * data->rows_p, 64, pl.dat_box_rows)
+                     : make_map(&a.dat[i], base, data->rows_p, data->ld, pl.dat_box_rows);
         if (rc) return rc;
     }
     a.out = partial;
@@ -182,17 +186,22 @@ int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int facto
     a.kblocks_total = pl.kblocks_total;
     a.Lp = out_Lp;
     a.nstages = pl.nstages;
+    a.dat_rows_p = data->blocked ? data->rows_p : 0;
+    a.cluster = pl.cluster; a.ngroups = pl.ngroups; a.chunk_kb = pl.chunk_kb;
+    a.dat_box_rows = pl.dat_box_rows; a.prefetch_kb = pl.prefetch_kb;
     CUDA_TRY(panel_gemm_launch(a, pl, num_sms, st(stream)));
     return pl.slots;
 }
 
-int nmfb_gram(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
               double* gram64, int num_sms, void* stream) {
-    // The factor's own hi/lo planes act as the "data": rows = components, contraction over L.
+    // The factor's own bf16 planes act as the "data": rows = components, contraction over L.
+    if (nplanes != 2 && nplanes != 3) return fail(NMFB_ERR_ARG, "gram: nplanes must be 2 or 3");
+    if (KP == 256) nplanes = 2;          // 3 x 3 planes do not fit two smem stages at KP = 256
     nmfb_data d;
     d.planes = f->cplanes;
-    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 2;
-    const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, 2, partial, partial_bytes, 256, num_sms,
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0;
+    const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, nplanes, partial, partial_bytes, 256, num_sms,
                                       128, 0, stream);
     if (slots < 0) return slots;
     CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
@@ -215,34 +224,41 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
     if (impl == 1) {
         const long need = static_cast<long>((p->m + 63) / 64) * ((p->n + 63) / 64);
         if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
-        CUDA_TRY(objective_simt_launch(bf(v->planes), static_cast<long>(v->rows_p) * v->ld, v->ld, v->nv,
+        CUDA_TRY(objective_simt_launch(bf(v->planes), static_cast<long>(v->rows_p) * v->ld, v->rows_p, v->nv,
                                        p->w.master, p->w.Lp, p->h.master, p->h.Lp, p->k, p->m, p->n,
                                        p->obj_partial, &nparts, st(stream)));
     } else {
         ResidualArgs a;
         memset(&a, 0, sizeof(a));
+        a.mtiles = (p->m + 127) / 128;
+        a.ntiles = (p->n + 127) / 128;
+        int cs = 2;
+        if (const char* e = getenv("NMFB_RES_CLUSTER")) cs = atoi(e);
+        if (cs != 1 && cs != 2 && cs != 4) cs = 1;
+        while (cs > 1 && a.mtiles < 2 * cs) cs >>= 1;
+        a.cluster = cs;
         for (int q = 0; q < 2; ++q) {
             int rc = make_map(&a.wr[q], bf(p->w.rplanes) + static_cast<long>(q) * p->w.Lp * p->KP, p->w.Lp,
                               p->KP, 128);
             if (rc) return rc;
             rc = make_map(&a.hr[q], bf(p->h.rplanes) + static_cast<long>(q) * p->h.Lp * p->KP, p->h.Lp, p->KP,
-                          128);
+                          128 / cs);
             if (rc) return rc;
         }
         for (int q = 0; q < v->nv; ++q) {
-            int rc = make_map(&a.v[q], bf(v->planes) + static_cast<long>(q) * v->rows_p * v->ld, v->rows_p,
-                              v->ld, 128);
+            int rc = make_map(&a.v[q], bf(v->planes) + static_cast<long>(q) * v->rows_p * v->ld,
+                              static_cast<long>(v->ld / 64) * v->rows_p, 64, 128);
             if (rc) return rc;
         }
         a.partial = p->obj_partial;
         a.KP = p->KP; a.NV = v->nv; a.BN = 128;
         a.m = p->m; a.n = p->n;
-        a.mtiles = (p->m + 127) / 128;
-        a.ntiles = (p->n + 127) / 128;
         a.kl = 0;
-        const long ntot = static_cast<long>(a.mtiles) * a.ntiles;
-        int grid = p->num_sms;
-        if (ntot < grid) grid = static_cast<int>(ntot);
+        a.v_rows_p = v->rows_p;
+        const long ntot = static_cast<long>((a.mtiles + cs - 1) / cs) * a.ntiles;
+        int ncl = residual_max_clusters(cs, p->num_sms);
+        if (ntot < ncl) ncl = static_cast<int>(ntot);
+        const int grid = ncl * cs;
         if (grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
         nparts = grid;
         CUDA_TRY(residual_launch(a, grid, st(stream)));
@@ -259,7 +275,7 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
     // phase events: 0 start | 1 gram(H) | 2 V.H^T | 3 W update | 4 gram(W) | 5 W^T.V | 6 H update | 7 objective
     mark(p, 0, stream);
     // W <- W * (V H^T) / (W (H H^T) + lambda_w W + eps)                    mur.py:122 -> :29
-    if ((rc = nmfb_gram(&p->h, KP, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz,
+    if ((rc = nmfb_gram(&p->h, KP, 2, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz,
                         p->num_sms, stream)) < 0) return rc;
     mark(p, 1, stream);
     int slots = nmfb_panel_gemm(&p->v_rows, p->h.cplanes, p->h.Lp, KP, 2, p->partial, p->partial_bytes,
@@ -270,7 +286,7 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
         return rc;
     mark(p, 3, stream);
     // H <- H * (W^T V) / ((W^T W) H + lambda_h H + eps), with the NEW W    mur.py:123 -> :45
-    if ((rc = nmfb_gram(&p->w, KP, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0)
+    if ((rc = nmfb_gram(&p->w, KP, 2, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0)
         return rc;
     mark(p, 4, stream);
     slots = nmfb_panel_gemm(&p->v_cols, p->w.cplanes, p->w.Lp, KP, 2, p->partial, p->partial_bytes, p->h.Lp,
@@ -282,6 +298,124 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
     mark(p, 6, stream);
     // objective of the new pair                                            mur.py:124,127
     if (obj_out && (rc = nmfb_objective_eu(p, 0, obj_out, stream)) < 0) return rc;
+    mark(p, 7, stream);
+    return 0;
+}
+
+int nmfb_chol_inverse(const double* gram64, int k, int KP, int rho_mode, double rho_in, double* scratch,
+                      double* ainv, double* rho_out, int* flags, void* stream) {
+    if (!gram64 || !ainv || !rho_out || !flags) return fail(NMFB_ERR_ARG, "chol_inverse: null argument");
+    if (KP == 256 && !scratch) return fail(NMFB_ERR_ARG, "chol_inverse: KP = 256 needs the scratch matrix");
+    CUDA_TRY(chol_inverse_launch(gram64, KP, k, rho_mode, rho_in, scratch, ainv, rho_out, flags, st(stream)));
+    return 0;
+}
+
+namespace {
+
+// aux / prox / dual of one factor (x = `f`, dual `u`) from the numerator in p->partial (or s->c64).
+int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* part, int slots, bool use_c64,
+               int side /*0 = H, 1 = W*/, const nmfb_factor* f, float* u, const nmfb_factor* aux, float lambda,
+               int prox, bool want_cpl, bool norms, void* stream) {
+    AdmmApplyArgs a;
+    memset(&a, 0, sizeof(a));
+    a.part = part; a.slots = slots;
+    a.c64 = use_c64 ? s->c64 : nullptr;
+    a.ainv = s->ainv + static_cast<size_t>(side) * p->KP * p->KP;
+    a.rho = s->scal + side;
+    a.lambda = lambda; a.prox = prox;
+    a.x = f->master; a.u = u;
+    if (aux) {
+        a.aux_master = aux->master;
+        a.aux_cpl = bf(aux->cplanes); a.aux_cpl_plane = 256L * aux->Lp;
+    }
+    if (want_cpl) { a.x_cpl = bf(f->cplanes); a.x_cpl_plane = 256L * f->Lp; }
+    a.x_rpl = bf(f->rplanes); a.x_rpl_plane = static_cast<long>(f->Lp) * p->KP;
+    if (norms) { a.norm_partial = s->norm_partial; a.done_flag = s->flags + 1; }
+    a.KP = p->KP; a.k = p->k; a.L = f->L; a.Lp = f->Lp;
+    CUDA_TRY(admm_apply_launch(a, st(stream)));
+    return 0;
+}
+
+int check_prox(int prox) {
+    if (prox != NMFB_PROX_NN && prox != NMFB_PROX_L1N) return fail(NMFB_ERR_ARG, "unknown prox code %d", prox);
+    return 0;
+}
+
+}  // namespace
+
+int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, float lambda_w, int prox_w,
+                   float lambda_h, int prox_h, double* mailbox, void* stream) {
+    if (!p || !s || !mailbox) return fail(NMFB_ERR_ARG, "admm_step: null argument");
+    int rc;
+    if ((rc = check_prox(prox_w)) < 0 || (rc = check_prox(prox_h)) < 0) return rc;
+    const int KP = p->KP;
+    const size_t gsz = static_cast<size_t>(KP) * KP;
+    mark(p, 0, stream);
+    // h_aux = (W_aux^T W_aux + rho I)^-1 (W_aux^T V + rho (H + U_h))               admm.py:295
+    if ((rc = nmfb_gram(&s->w_aux, KP, 3, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0) return rc;
+    if ((rc = nmfb_chol_inverse(p->gram64, p->k, KP, 0, rho, s->chol_scratch, s->ainv, s->scal, s->flags, stream)) < 0) return rc;
+    mark(p, 1, stream);
+    int slots = nmfb_panel_gemm(&p->v_cols, s->w_aux.cplanes, s->w_aux.Lp, KP, 3, p->partial, p->partial_bytes,
+                                p->h.Lp, p->num_sms, 0, 0, stream);
+    if (slots < 0) return slots;
+    mark(p, 2, stream);
+    // + h = prox(h_aux, U_h), U_h += h - h_aux                                      admm.py:299,320
+    if ((rc = admm_apply(p, s, p->partial, slots, false, 0, &p->h, s->dual_h, &s->h_aux, lambda_h, prox_h, false,
+                         false, stream)) < 0) return rc;
+    mark(p, 3, stream);
+    // w_aux with the NEW h_aux                                                      admm.py:296-297
+    if ((rc = nmfb_gram(&s->h_aux, KP, 3, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz, p->num_sms, stream)) < 0) return rc;
+    if ((rc = nmfb_chol_inverse(p->gram64 + gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + gsz, s->scal + 1, s->flags, stream)) < 0) return rc;
+    mark(p, 4, stream);
+    slots = nmfb_panel_gemm(&p->v_rows, s->h_aux.cplanes, s->h_aux.Lp, KP, 3, p->partial, p->partial_bytes,
+                            p->w.Lp, p->num_sms, 0, 0, stream);
+    if (slots < 0) return slots;
+    mark(p, 5, stream);
+    if ((rc = admm_apply(p, s, p->partial, slots, false, 1, &p->w, s->dual_w, &s->w_aux, lambda_w, prox_w, false,
+                         false, stream)) < 0) return rc;
+    mark(p, 6, stream);
+    if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // admm.py:324
+    CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
+    mark(p, 7, stream);
+    return 0;
+}
+
+int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_iter, float lambda_w,
+                     int prox_w, float lambda_h, int prox_h, double* mailbox, void* stream) {
+    if (!p || !s || !mailbox) return fail(NMFB_ERR_ARG, "aoadmm_step: null argument");
+    if (admm_iter < 0) return fail(NMFB_ERR_ARG, "aoadmm_step: admm_iter < 0");
+    int rc;
+    if ((rc = check_prox(prox_w)) < 0 || (rc = check_prox(prox_h)) < 0) return rc;
+    const int KP = p->KP;
+    const size_t gsz = static_cast<size_t>(KP) * KP;
+    mark(p, 0, stream);
+    for (int side = 0; side < 2; ++side) {
+        // side 0: H update with a = W, y = V (ao_admm.py:261-264); side 1: W update with a = H^T, y = V^T (:265-270)
+        const nmfb_factor* other = side == 0 ? &p->w : &p->h;
+        const nmfb_factor* self = side == 0 ? &p->h : &p->w;
+        const nmfb_data* data = side == 0 ? &p->v_cols : &p->v_rows;
+        float* dual = side == 0 ? s->dual_h : s->dual_w;
+        const float lambda = side == 0 ? lambda_h : lambda_w;
+        const int prox = side == 0 ? prox_h : prox_w;
+        CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
+        if ((rc = nmfb_gram(other, KP, 3, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
+                            p->num_sms, stream)) < 0) return rc;
+        if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
+                                    s->scal + side, s->flags, stream)) < 0) return rc;
+        mark(p, 1 + 3 * side, stream);
+        const int slots = nmfb_panel_gemm(data, other->cplanes, other->Lp, KP, 3, p->partial, p->partial_bytes,
+                                          self->Lp, p->num_sms, 0, 0, stream);
+        if (slots < 0) return slots;
+        mark(p, 2 + 3 * side, stream);
+        for (int it = 0; it < admm_iter; ++it) {
+            if ((rc = admm_apply(p, s, it == 0 ? p->partial : nullptr, slots, true, side, self, dual, nullptr, lambda,
+                                 prox, true, true, stream)) < 0) return rc;
+            CUDA_TRY(admm_inner_flag_launch(s->norm_partial, self->Lp / 64, s->flags, 2 + side, st(stream)));
+        }
+        mark(p, 3 + 3 * side, stream);
+    }
+    if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // ao_admm.py:291
+    CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
     mark(p, 7, stream);
     return 0;
 }

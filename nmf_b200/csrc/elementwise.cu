@@ -19,8 +19,8 @@ namespace nmfb {
 template <typename T>
 __global__ void __launch_bounds__(256)
 ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, int ncols,
-                   __nv_bfloat16* __restrict__ rowp, long rowp_plane, int rowp_ld,
-                   __nv_bfloat16* __restrict__ colp, long colp_plane, int colp_ld, int nv,
+                   __nv_bfloat16* __restrict__ rowp, long rowp_plane, int rowp_rows_p,
+                   __nv_bfloat16* __restrict__ colp, long colp_plane, int colp_rows_p, int nv,
                    unsigned int* __restrict__ stats) {
     __shared__ float tile[64][65];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;      // 64 x 4
@@ -36,7 +36,7 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
             if (!isfinite(x)) bad = 1;
             __nv_bfloat16 hi, lo;
             split2(x, hi, lo);
-            const long o = static_cast<long>(row0 + r) * rowp_ld + c;
+            const long o = blocked_index(row0 + r, c, rowp_rows_p);
             rowp[o] = hi;
             if (nv > 1) rowp[rowp_plane + o] = lo;
             if (__bfloat162float(lo) != 0.f) need_lo = 1;
@@ -49,7 +49,7 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
         if (r < nrows && c < ncols) {
             __nv_bfloat16 hi, lo;
             split2(tile[tx][cc], hi, lo);
-            const long o = static_cast<long>(c) * colp_ld + row0 + r;
+            const long o = blocked_index(c, row0 + r, colp_rows_p);
             colp[o] = hi;
             if (nv > 1) colp[colp_plane + o] = lo;
         }
@@ -70,19 +70,19 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
 }
 
 cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
-                               __nv_bfloat16* rowp, long rowp_plane, int rowp_ld, __nv_bfloat16* colp,
-                               long colp_plane, int colp_ld, int nv, unsigned int* stats,
+                               __nv_bfloat16* rowp, long rowp_plane, int rowp_rows_p, __nv_bfloat16* colp,
+                               long colp_plane, int colp_rows_p, int nv, unsigned int* stats,
                                cudaStream_t stream) {
     dim3 grid((ncols + 63) / 64, (nrows + 63) / 64);
     if (grid.x == 0 || grid.y == 0) return cudaSuccess;
     if (is_f64)
         ingest_data_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(src), src_ld, row0,
-                                                            nrows, ncols, rowp, rowp_plane, rowp_ld, colp,
-                                                            colp_plane, colp_ld, nv, stats);
+                                                            nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
+                                                            colp_plane, colp_rows_p, nv, stats);
     else
         ingest_data_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), src_ld, row0,
-                                                           nrows, ncols, rowp, rowp_plane, rowp_ld, colp,
-                                                           colp_plane, colp_ld, nv, stats);
+                                                           nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
+                                                           colp_plane, colp_rows_p, nv, stats);
     count_launch();
     return cudaGetLastError();
 }
@@ -318,7 +318,7 @@ cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram
 // 0.5 * sum (v - w.h)^2 over a 64x64 tile per block from the fp32 masters (utils.py:29).
 // O(mnk) on the FP32 pipe: used for small problems and to cross-check the tcgen05 residual kernel.
 __global__ void __launch_bounds__(256)
-objective_simt_kernel(const __nv_bfloat16* __restrict__ vpl, long v_plane, int ldv, int nv,
+objective_simt_kernel(const __nv_bfloat16* __restrict__ vpl, long v_plane, int v_rows_p, int nv,
                       const float* __restrict__ wt, int Mp, const float* __restrict__ ht, int Np, int k,
                       int m, int n, double* __restrict__ partial) {
     __shared__ float ws[16][64], hs[16][64];
@@ -353,9 +353,10 @@ objective_simt_kernel(const __nv_bfloat16* __restrict__ vpl, long v_plane, int l
         for (int q = 0; q < 4; ++q) {
             const int j = j0 + tx * 4 + q;
             if (i < m && j < n) {
-                float v = __bfloat162float(vpl[static_cast<long>(i) * ldv + j]);
+                const long o = blocked_index(i, j, v_rows_p);
+                float v = __bfloat162float(vpl[o]);
                 float d = v - acc[p][q];
-                if (nv > 1) d += __bfloat162float(vpl[v_plane + static_cast<long>(i) * ldv + j]);
+                if (nv > 1) d += __bfloat162float(vpl[v_plane + o]);
                 rowsum += d * d;
             }
         }
@@ -372,12 +373,12 @@ objective_simt_kernel(const __nv_bfloat16* __restrict__ vpl, long v_plane, int l
     }
 }
 
-cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int ldv, int nv, const float* wt,
+cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int v_rows_p, int nv, const float* wt,
                                   int Mp, const float* ht, int Np, int k, int m, int n, double* partial,
                                   int* nparts, cudaStream_t stream) {
     dim3 grid((n + 63) / 64, (m + 63) / 64);
     *nparts = static_cast<int>(grid.x * grid.y);
-    objective_simt_kernel<<<grid, 256, 0, stream>>>(vpl, v_plane, ldv, nv, wt, Mp, ht, Np, k, m, n, partial);
+    objective_simt_kernel<<<grid, 256, 0, stream>>>(vpl, v_plane, v_rows_p, nv, wt, Mp, ht, Np, k, m, n, partial);
     count_launch();
     return cudaGetLastError();
 }

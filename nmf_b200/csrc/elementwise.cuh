@@ -5,8 +5,8 @@
 namespace nmfb {
 
 cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
-                               __nv_bfloat16* rowp, long rowp_plane, int rowp_ld, __nv_bfloat16* colp,
-                               long colp_plane, int colp_ld, int nv, unsigned int* stats,
+                               __nv_bfloat16* rowp, long rowp_plane, int rowp_rows_p, __nv_bfloat16* colp,
+                               long colp_plane, int colp_rows_p, int nv, unsigned int* stats,
                                cudaStream_t stream);
 cudaError_t refresh_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
                                   __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream);
@@ -19,7 +19,7 @@ cudaError_t gram_reduce_launch(const float* part, int slots, int KP, int Lp, flo
 cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram, float* master,
                                  __nv_bfloat16* cpl, long cpl_plane, __nv_bfloat16* rpl, long rpl_plane,
                                  int KP, int k, int L, int Lp, float lambda, cudaStream_t stream);
-cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int ldv, int nv, const float* wt,
+cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int v_rows_p, int nv, const float* wt,
                                   int Mp, const float* ht, int Np, int k, int m, int n, double* partial,
                                   int* nparts, cudaStream_t stream);
 cudaError_t sum_partials_launch(const double* partial, int n, double scale, double* out,

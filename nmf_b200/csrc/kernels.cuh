@@ -3,6 +3,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -13,20 +14,32 @@ namespace nmfb {
 extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += static_cast<unsigned long long>(n); }
 
+// Data planes (V, V^T) are stored K-blocked: [col / 64][rows_p][64], so that the [rows x 64] box a
+// TMA load fetches for one contraction block is ONE contiguous run of HBM (rows * 128 bytes).
+__host__ __device__ inline long blocked_index(int row, int col, int rows_p) {
+    return (static_cast<long>(col >> 6) * rows_p + row) * 64 + (col & 63);
+}
+
 // ------------------------------------------------------------------ panel GEMM (panel_gemm.cu)
 struct alignas(64) PanelGemmArgs {
     CUtensorMap fac[3];      // factor planes, component-major [>=KP rows][ld], box {64, 64|128}
-    CUtensorMap dat[2];      // data planes [rows][ld], box {64, BN}
+    CUtensorMap dat[3];      // data planes [rows][ld], box {64, BN}
     float* out;              // partial slots [slots][KP][Lp]
     int KP, NB, NA, BN;
     int npanels, nsplit, kb_per_split, kblocks_total;
     int Lp;
     int nstages;
+    int dat_rows_p;          // > 0: data planes are K-blocked with this many rows per block; 0: row-major
+    int cluster, ngroups;    // CTAs per cluster; panel groups (= ceil(npanels / cluster))
+    int chunk_kb;            // contraction blocks per TMEM accumulation chunk
+    int dat_box_rows;        // rows per TMA box of the data planes (BN is fetched as BN / dat_box_rows boxes)
+    int prefetch_kb;         // L2 prefetch distance of the data stream, in contraction blocks (0 = off)
 };
 
 struct PanelGemmPlan {
     int BN, nstages, npanels, nsplit, kb_per_split, kblocks_total, slots;
     int smem_bytes;
+    int cluster, ngroups, chunk_kb, max_clusters, dat_box_rows, prefetch_kb;
 };
 
 int panel_gemm_plan(int KP, int NB, int NA, int L, int R, int force_bn, int force_split, int num_sms,
@@ -44,8 +57,11 @@ struct alignas(64) ResidualArgs {
     int m, n;                // true extents (tail masking)
     int mtiles, ntiles;
     int kl;                  // 0: sum (v-s)^2 ; 1: generalised KL terms
+    int v_rows_p;            // rows per K-block of the blocked V planes
+    int cluster;             // CTAs per cluster (H^T stages are multicast across it)
 };
 cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_smem_bytes(int KP, int NV, int BN);
+int residual_max_clusters(int cs, int num_sms);
 
 }  // namespace nmfb

@@ -19,6 +19,7 @@ namespace nmfb {
 namespace {
 constexpr int kThreadsR = 320;
 constexpr int kBox = 128 * 128;      // bytes of one [128 rows x 64 bf16] box
+constexpr int kPrefetchTiles = 6;    // L2 prefetch distance of the V stream, in 128 x 128 tiles
 
 struct ResLayout {
     int a_bytes, b_stage_bytes, v_buf_bytes;
@@ -49,13 +50,16 @@ int residual_smem_bytes(int KP, int NV, int BN) {
     return l.total + 1024 + 512;
 }
 
+// Compile-time <KCH = KP / 64, NV>: the single MMA-issuing thread must not spend its time computing
+// loop bounds and descriptor fields (see panel_gemm.cu).
+template <int KCH, int NV>
 __global__ void __launch_bounds__(kThreadsR, 1)
 residual_kernel(const __grid_constant__ ResidualArgs args) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    const int KP = args.KP, NV = args.NV;
-    const int kchunks = KP / 64;
+    constexpr int KP = KCH * 64;
+    constexpr int kchunks = KCH;
     const ResLayout L = res_layout(KP, NV);
     uint8_t* a_smem = smem;
     uint8_t* b_smem = a_smem + L.a_bytes;
@@ -73,14 +77,22 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
     double* red = reinterpret_cast<double*>(bars + 20);      // [8]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long ntot = static_cast<long>(args.mtiles) * args.ntiles;
-    const long t_begin = ntot * blockIdx.x / gridDim.x;
-    const long t_end = ntot * (blockIdx.x + 1) / gridDim.x;
+    // Clusters of CS CTAs walk "super rows" of CS adjacent row tiles in lockstep over the same column
+    // tiles, so the H^T stage every one of them needs is fetched once per cluster (each CTA loads
+    // 1/CS of it and multicasts): the kernel is bound by L2 output otherwise (3 x |V| of L2 reads).
+    const int CS = args.cluster;
+    const uint32_t crank = (CS > 1) ? cluster_ctarank() : 0;
+    const uint16_t cmask = static_cast<uint16_t>((1u << CS) - 1);
+    const int ncl = gridDim.x / CS, cid = blockIdx.x / CS;
+    const int msuper = (args.mtiles + CS - 1) / CS;
+    const long ntot = static_cast<long>(msuper) * args.ntiles;
+    const long t_begin = ntot * cid / ncl;
+    const long t_end = ntot * (cid + 1) / ncl;
 
     if (warp == 0 && lane == 0) {
         for (int p = 0; p < 2; ++p) { tma_prefetch_desc(&args.wr[p]); tma_prefetch_desc(&args.hr[p]); }
         for (int p = 0; p < NV; ++p) tma_prefetch_desc(&args.v[p]);
-        for (int s = 0; s < 4; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        for (int s = 0; s < 4; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], CS); }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&v_full[s], 1);   mbar_init(&v_empty[s], 8);
             mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8);
@@ -92,19 +104,22 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
     if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
         if (lane == 0) {
+            const int srow = 128 / CS;
             int bs = 0; uint32_t bph = 0;
             int vs = 0; uint32_t vph = 0;
             uint32_t aph = 0;
             int cur_i = -1;
             for (long t = t_begin; t < t_end; ++t) {
-                const int ti = static_cast<int>(t / args.ntiles);
-                const int tj = static_cast<int>(t - static_cast<long>(ti) * args.ntiles);
-                if (ti != cur_i) {
+                const int sr = static_cast<int>(t / args.ntiles);
+                const int tj = static_cast<int>(t - static_cast<long>(sr) * args.ntiles);
+                const int ti = min(sr * CS + static_cast<int>(crank), args.mtiles - 1);   // clamp: padded rows are masked
+                if (sr != cur_i) {
                     mbar_wait(a_empty, aph ^ 1);
                     mbar_expect_tx(a_full, L.a_bytes);
                     for (int p = 0; p < 2; ++p)
@@ -112,7 +127,20 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                             tma_load_2d_hint(a_smem + (p * kchunks + kc) * kBox, &args.wr[p], a_full, kc * 64,
                                              ti * 128, kPolicyEvictLast);
                     aph ^= 1;
-                    cur_i = ti;
+                    cur_i = sr;
+                }
+                // pull the V tile of a later step into L2: only two V buffers fit in shared memory, far
+                // too few bytes in flight to cover HBM latency on their own
+                {
+                    const long tp = t + kPrefetchTiles;
+                    if (tp < t_end) {
+                        const int srp = static_cast<int>(tp / args.ntiles);
+                        const int tjp = static_cast<int>(tp - static_cast<long>(srp) * args.ntiles);
+                        const int tip = min(srp * CS + static_cast<int>(crank), args.mtiles - 1);
+                        for (int p = 0; p < NV; ++p)
+                            for (int hb = 0; hb < 2; ++hb)
+                                tma_prefetch_2d(&args.v[p], 0, (tjp * 2 + hb) * args.v_rows_p + tip * 128);
+                    }
                 }
                 // V tile
                 mbar_wait(&v_empty[vs], vph ^ 1);
@@ -120,29 +148,37 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                 for (int p = 0; p < NV; ++p)
                     for (int hb = 0; hb < 2; ++hb)
                         tma_load_2d_hint(v_smem + vs * L.v_buf_bytes + (p * 2 + hb) * kBox, &args.v[p],
-                                         &v_full[vs], tj * 128 + hb * 64, ti * 128, kPolicyEvictFirst);
+                                         &v_full[vs], 0, (tj * 2 + hb) * args.v_rows_p + ti * 128, kPolicyEvictFirst);
                 if (++vs == L.nvs) { vs = 0; vph ^= 1; }
                 // H^T chunks
                 for (int kc = 0; kc < kchunks; ++kc) {
                     mbar_wait(&b_empty[bs], bph ^ 1);
                     mbar_expect_tx(&b_full[bs], L.b_stage_bytes);
-                    for (int p = 0; p < 2; ++p)
-                        tma_load_2d_hint(b_smem + bs * L.b_stage_bytes + p * kBox, &args.hr[p], &b_full[bs],
-                                         kc * 64, tj * 128, kPolicyEvictLast);
+                    for (int p = 0; p < 2; ++p) {
+                        uint8_t* dst = b_smem + bs * L.b_stage_bytes + p * kBox + crank * srow * 128;
+                        if (CS > 1)
+                            tma_load_2d_mcast(dst, &args.hr[p], &b_full[bs], kc * 64, tj * 128 + crank * srow, cmask,
+                                              kPolicyEvictLast);
+                        else
+                            tma_load_2d_hint(dst, &args.hr[p], &b_full[bs], kc * 64, tj * 128, kPolicyEvictLast);
+                    }
                     if (++bs == L.nbs) { bs = 0; bph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(128, 128);
+            constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+            const uint64_t desc0 = umma_desc_k_sw128(0);
             int bs = 0; uint32_t bph = 0;
             int acc = 0; uint32_t accph = 0;
             uint32_t aph = 0;
             int cur_i = -1;
-            const uint32_t a_addr = smem_u32(a_smem), b_addr = smem_u32(b_smem);
+            const uint64_t a_desc = desc0 + (smem_u32(a_smem) >> 4);
+            const uint32_t b_addr = smem_u32(b_smem);
+            const int b_stage = L.b_stage_bytes, nbs = L.nbs;
             for (long t = t_begin; t < t_end; ++t) {
-                const int ti = static_cast<int>(t / args.ntiles);
+                const int ti = static_cast<int>(t / args.ntiles);      // super row (same in every CTA)
                 if (ti != cur_i) {
                     mbar_wait(a_full, aph);
                     aph ^= 1;
@@ -151,24 +187,24 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                 mbar_wait(&acc_empty[acc], accph ^ 1);
                 tc_fence_after();
                 const uint32_t d = tmem_base + acc * 128;
-                uint32_t started = 0;
+#pragma unroll
                 for (int kc = 0; kc < kchunks; ++kc) {
                     mbar_wait(&b_full[bs], bph);
                     tc_fence_after();
-                    const uint32_t bst = b_addr + bs * L.b_stage_bytes;
+                    const uint64_t b_desc = desc0 + ((b_addr + bs * b_stage) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t a_hi = umma_desc_k_sw128(a_addr + (0 * kchunks + kc) * kBox + ks * 32);
-                        const uint64_t a_lo = umma_desc_k_sw128(a_addr + (1 * kchunks + kc) * kBox + ks * 32);
-                        const uint64_t b_hi = umma_desc_k_sw128(bst + ks * 32);
-                        const uint64_t b_lo = umma_desc_k_sw128(bst + kBox + ks * 32);
-                        umma_bf16(d, a_hi, b_hi, idesc, started);
-                        started = 1;
+                        const uint64_t a_hi = a_desc + (((0 * kchunks + kc) * kBox + ks * 32) >> 4);
+                        const uint64_t a_lo = a_desc + (((1 * kchunks + kc) * kBox + ks * 32) >> 4);
+                        const uint64_t b_hi = b_desc + ((ks * 32) >> 4);
+                        const uint64_t b_lo = b_desc + ((kBox + ks * 32) >> 4);
+                        umma_bf16(d, a_hi, b_hi, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
                         umma_bf16(d, a_hi, b_lo, idesc, 1);
                         umma_bf16(d, a_lo, b_hi, idesc, 1);
                     }
-                    umma_commit(&b_empty[bs]);
-                    if (++bs == L.nbs) { bs = 0; bph ^= 1; }
+                    if (CS > 1) umma_commit_mcast(&b_empty[bs], cmask);
+                    else        umma_commit(&b_empty[bs]);
+                    if (++bs == nbs) { bs = 0; bph ^= 1; }
                 }
                 umma_commit(&acc_full[acc]);
                 const long tn = t + 1;
@@ -186,6 +222,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
         int vs = 0; uint32_t vph = 0;
         double total = 0.0;
         for (long t = t_begin; t < t_end; ++t) {
+            const bool live = static_cast<int>(t / args.ntiles) * CS + static_cast<int>(crank) < args.mtiles;
             mbar_wait(&acc_full[acc], accph);
             mbar_wait(&v_full[vs], vph);
             tc_fence_after();
@@ -231,7 +268,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                     }
                 }
             }
-            total += static_cast<double>(tsum);
+            if (live) total += static_cast<double>(tsum);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) { mbar_arrive(&acc_empty[acc]); mbar_arrive(&v_empty[vs]); }
@@ -244,6 +281,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
 
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 256);
@@ -255,17 +293,55 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
     }
 }
 
-cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e =
-            cudaFuncSetAttribute(residual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
+static void residual_pick(const ResidualArgs& args, void (**fn)(const ResidualArgs)) {
+    const int kch = args.KP / 64;
+    if (args.NV == 1) *fn = kch == 1 ? residual_kernel<1, 1> : (kch == 2 ? residual_kernel<2, 1> : residual_kernel<4, 1>);
+    else              *fn = kch == 1 ? residual_kernel<1, 2> : (kch == 2 ? residual_kernel<2, 2> : residual_kernel<4, 2>);
+}
+
+// Resident clusters of `cs` CTAs for this kernel (one CTA per SM); cached per cluster size.
+int residual_max_clusters(int cs, int num_sms) {
+    static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (cs == 1) return num_sms;
+    if (cache[cs] > 0) return cache[cs];
+    void (*fn)(const ResidualArgs) = residual_kernel<2, 1>;
+    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(num_sms / cs * cs);
+    cfg.blockDim = dim3(kThreadsR);
+    cfg.dynamicSmemBytes = 200 * 1024;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = num_sms / cs * 3 / 4;
     }
+    if (n > num_sms / cs) n = num_sms / cs;
+    cache[cs] = n;
+    return n;
+}
+
+cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream) {
     const int smem = residual_smem_bytes(args.KP, args.NV, args.BN);
     if (smem < 0) return cudaErrorInvalidValue;
-    residual_kernel<<<grid, kThreadsR, smem, stream>>>(args);
+    void (*fn)(const ResidualArgs) = nullptr;
+    residual_pick(args, &fn);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);                       // a multiple of args.cluster
+    cfg.blockDim = dim3(kThreadsR);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = args.cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, fn, args);
+    if (e != cudaSuccess) return e;
     count_launch();
     return cudaGetLastError();
 }

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import Data, Factor, Problem, check
+from ._lib import AdmmState, Data, Factor, Problem, check
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -92,13 +92,31 @@ class Engine:
     def _alloc_data(self, nv: int):
         self.v_rows = self.v_cols = None
         self.nv = nv
-        self.v_rows = torch.zeros((nv, self.Mp, self.Np), dtype=torch.bfloat16, device=self.device)
-        self.v_cols = torch.zeros((nv, self.Np, self.Mp), dtype=torch.bfloat16, device=self.device)
+        # K-blocked planes: [plane][column block of 64][row][64]  (include/nmf_b200.h)
+        self.v_rows = torch.zeros((nv, self.Np // 64, self.Mp, 64), dtype=torch.bfloat16, device=self.device)
+        self.v_cols = torch.zeros((nv, self.Mp // 64, self.Np, 64), dtype=torch.bfloat16, device=self.device)
         self._problem = None
 
+    def store_block(self, blk: torch.Tensor, r0: int):
+        """Write rows [r0, r0+rows) of V (a device tensor (rows, n), any float dtype whose values are
+        bf16-exact) into plane 0 of both K-blocked copies.  Plumbing for on-device synthetic data."""
+        rows, n = blk.shape
+        b = blk.to(torch.bfloat16)
+        npad = (-n) % 64
+        if npad:
+            b = torch.nn.functional.pad(b, (0, npad))
+        self.v_rows[0, : b.shape[1] // 64, r0:r0 + rows, :] = b.view(rows, -1, 64).permute(1, 0, 2)
+        bt = b[:, :n].t()                                     # (n, rows): rows r0.. of V are columns of V^T
+        if r0 % 64 or (rows % 64 and r0 + rows != self.m):
+            raise ValueError("store_block: row blocks must be 64-aligned")
+        rpad = (-rows) % 64
+        if rpad:
+            bt = torch.nn.functional.pad(bt, (0, rpad))
+        self.v_cols[0, r0 // 64:(r0 + rows + rpad) // 64, :n, :] = bt.reshape(n, -1, 64).permute(1, 0, 2)
+
     def _data_structs(self) -> Tuple[Data, Data]:
-        vr = Data(self.v_rows.data_ptr(), self.m, self.n, self.Mp, self.Np, self.nv)
-        vc = Data(self.v_cols.data_ptr(), self.n, self.m, self.Np, self.Mp, self.nv)
+        vr = Data(self.v_rows.data_ptr(), self.m, self.n, self.Mp, self.Np, self.nv, 1)
+        vc = Data(self.v_cols.data_ptr(), self.n, self.m, self.Np, self.Mp, self.nv, 1)
         return vr, vc
 
     def problem(self) -> Problem:
@@ -213,6 +231,47 @@ class Engine:
         out = None if obj_slot is None else self.scalars.data_ptr() + 8 * obj_slot
         check(self.lib.nmfb_mur_eu_step(C.byref(p), float(lambda_w), float(lambda_h), out, self.stream))
 
+    # ------------------------------------------------------------------ ADMM / AO-ADMM state
+    def alloc_admm(self, with_aux: bool):
+        """Duals (zero, admm.py:31-32 / ao_admm.py:26-27), the k x k inverse workspace and, for ADMM,
+        the signed auxiliaries initialised to copies of W and H (admm.py:27-28)."""
+        dev, KP = self.device, self.KP
+        Lmax = max(self.Mp, self.Np)
+        self.dual_w = torch.zeros((KP, self.Mp), dtype=torch.float32, device=dev)
+        self.dual_h = torch.zeros((KP, self.Np), dtype=torch.float32, device=dev)
+        self.ainv = torch.zeros((2, KP, KP), dtype=torch.float64, device=dev)
+        self.chol_scratch = torch.zeros((KP, KP + 1), dtype=torch.float64, device=dev)
+        self.c64 = torch.zeros((KP, Lmax), dtype=torch.float64, device=dev)
+        self.admm_scal = torch.zeros(4, dtype=torch.float64, device=dev)
+        self.admm_flags = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.norm_partial = torch.zeros(4 * (Lmax // 64), dtype=torch.float64, device=dev)
+        if with_aux:
+            self.w_aux = FactorBuffers(self.m, KP, dev)
+            self.h_aux = FactorBuffers(self.n, KP, dev)
+            for src, dst in ((self.w, self.w_aux), (self.h, self.h_aux)):
+                dst.master.copy_(src.master)
+                fs = dst.struct()
+                check(self.lib.nmfb_refresh_planes(KP, C.byref(fs), self.stream))
+            wa, ha = self.w_aux.struct(), self.h_aux.struct()
+        else:
+            self.w_aux = self.h_aux = None
+            wa, ha = Factor(), Factor()
+        self._admm = AdmmState(wa, ha, self.dual_w.data_ptr(), self.dual_h.data_ptr(), self.ainv.data_ptr(),
+                               self.chol_scratch.data_ptr(), self.c64.data_ptr(), self.admm_scal.data_ptr(),
+                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr())
+
+    def admm_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
+        p = self.problem()
+        check(self.lib.nmfb_admm_step(C.byref(p), C.byref(self._admm), float(rho), float(lambda_w), int(prox_w),
+                                      float(lambda_h), int(prox_h), self.scalars.data_ptr() + 64 * ring_slot,
+                                      self.stream))
+
+    def aoadmm_step(self, admm_iter, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
+        p = self.problem()
+        check(self.lib.nmfb_aoadmm_step(C.byref(p), C.byref(self._admm), int(admm_iter), float(lambda_w),
+                                        int(prox_w), float(lambda_h), int(prox_h),
+                                        self.scalars.data_ptr() + 64 * ring_slot, self.stream))
+
     def read_scalar(self, slot: int = 0) -> float:
         return float(self.scalars[slot].item())
 
@@ -224,4 +283,6 @@ class Engine:
         self.v_rows = self.v_cols = None
         self.w = self.h = None
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
+        for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch'):
+            setattr(self, name, None)
         self._problem = None

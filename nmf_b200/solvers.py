@@ -27,17 +27,18 @@ class MurEuStepper:
         W^T.V).  Algorithmic work of one launch: 2*m*n*k FLOP over m*n*2 bytes of V."""
         e = self.eng
         ms = 0.5 * (phase_ms["gemm_w"] + phase_ms["gemm_h"])
+        mpp = getattr(self, "mma_per_product", 2)
         flops = 2.0 * e.m * e.n * e.k
         vbytes = 2.0 * e.m * e.n * e.nv
         tf = flops / (ms * 1e-3) / 1e12
         gbs = vbytes / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
         tensor_frac, hbm_frac = tf / peak, gbs / peaks["hbm_gbs"]
-        bound = "tensor" if tensor_frac * 2 >= hbm_frac else "hbm"     # 2 MMAs execute per product
+        bound = "tensor" if tensor_frac * mpp >= hbm_frac else "hbm"   # mpp MMAs execute per product
         out = {"kernel": "panel_gemm_kernel", "bound": bound, "ms_per_launch": ms,
-               "executed_mma_per_product": 2, "traffic": None,
+               "executed_mma_per_product": mpp, "traffic": None,
                "tensor": {"achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tensor_frac,
-                          "executed_frac": 2 * tensor_frac},
+                          "executed_frac": mpp * tensor_frac},
                "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac}}
         pick = out["tensor"] if bound == "tensor" else out["hbm"]
         out.update(achieved=pick["achieved"], peak=pick["peak"], unit=pick["unit"], frac=pick["frac"],
@@ -45,7 +46,79 @@ class MurEuStepper:
         return out
 
 
+PROX_CODES = {"nn": 0, "l1n": 1}
+
+
+def prox_code(reg):
+    """(lambda, name) -> (lambda, C-ABI prox code).  'l2n' with lambda == 0 is the identity system of
+    admm.py:141-156, i.e. plain non-negativity; other operators are not part of this build."""
+    lam, name = reg
+    if name == "l2n" and lam == 0:
+        name = "nn"
+    if name in PROX_CODES:
+        return float(lam), PROX_CODES[name]
+    if name in ("l2n", "l1inf", "l1inf_transpose"):
+        raise NotImplementedError(f"prox operator {name!r} with lambda={lam} is not provided by the B200 build "
+                                  "(available: 'nn', 'l1n', and 'l2n' with lambda=0)")
+    raise TypeError('Unknown prox_type.')
+
+
+class _GemmRoofline:
+    """Shared roofline report: the dominant kernel is the panel GEMM (two launches per iteration)."""
+    mma_per_product = 2
+    gemm_phases = ("gemm_w", "gemm_h")
+
+    def roofline(self, phase_ms, peaks):
+        return MurEuStepper.roofline(self, phase_ms, peaks)
+
+
+class AdmmStepper(_GemmRoofline):
+    """admm.py:292-334 (Euclidean) -> nmfb_admm_step."""
+    phases = ["gram_chol_h", "gemm_h", "solve_prox_dual_h", "gram_chol_w", "gemm_w", "solve_prox_dual_w", "objective"]
+    mma_per_product = 3
+
+    def __init__(self, eng, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n")):
+        self.eng, self.rho = eng, float(rho)
+        self.lw, self.pw = prox_code(reg_w)
+        self.lh, self.ph = prox_code(reg_h)
+
+    def prepare(self):
+        self.eng.alloc_admm(with_aux=True)
+        self.eng.objective_eu(slot=0)
+
+    def step(self, ring_slot):
+        self.eng.admm_step(self.rho, self.lw, self.pw, self.lh, self.ph, ring_slot)
+
+    def phase_names(self):
+        return self.phases
+
+
+class AoAdmmStepper(_GemmRoofline):
+    """ao_admm.py:259-301 (Euclidean) -> nmfb_aoadmm_step."""
+    phases = ["gram_chol_h", "gemm_h", "inner_h", "gram_chol_w", "gemm_w", "inner_w", "objective"]
+    mma_per_product = 3
+
+    def __init__(self, eng, reg_w=(0, "nn"), reg_h=(0, "l2n"), admm_iter=10):
+        self.eng, self.admm_iter = eng, int(admm_iter)
+        self.lw, self.pw = prox_code(reg_w)
+        self.lh, self.ph = prox_code(reg_h)
+
+    def prepare(self):
+        self.eng.alloc_admm(with_aux=False)
+        self.eng.objective_eu(slot=0)
+
+    def step(self, ring_slot):
+        self.eng.aoadmm_step(self.admm_iter, self.lw, self.pw, self.lh, self.ph, ring_slot)
+
+    def phase_names(self):
+        return self.phases
+
+
 def make_stepper(eng, method, distance_type="eu", **kw):
     if method == "mur" and distance_type == "eu":
         return MurEuStepper(eng, kw.get("lambda_w", 0.0), kw.get("lambda_h", 0.0))
+    if method == "admm" and distance_type == "eu":
+        return AdmmStepper(eng, kw.get("rho", 1), kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")))
+    if method == "ao_admm" and distance_type == "eu":
+        return AoAdmmStepper(eng, kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")), kw.get("admm_iter", 10))
     raise NotImplementedError(f"no stepper for method={method!r} distance_type={distance_type!r}")

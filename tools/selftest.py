@@ -42,6 +42,10 @@ def make_engine(m, n, k, exact=True, seed=0, signed_w=False):
     if exact:
         v = bf16_round(v)
     eng = Engine(m, n, k)
+    big = 16 * eng.KP * max(eng.Mp, eng.Np)                 # room for forced K-splits
+    if eng.partial.numel() < big:
+        eng.partial = torch.empty(big, dtype=torch.float32, device=eng.device)
+        eng._problem = None
     eng.upload_data(v)
     w0 = rng.random((m, k)).astype(np.float64) + 0.05
     h0 = rng.random((k, n)).astype(np.float64) + 0.05
@@ -99,7 +103,7 @@ def test_gram():
         for which, fac, ref in ((0, eng.w, w0.astype(np.float32).astype(np.float64)),
                                 (1, eng.h, h0.astype(np.float32).astype(np.float64).T)):
             fs = fac.struct()
-            check(lib.nmfb_gram(C.byref(fs), eng.KP, eng.partial.data_ptr(), eng.partial.numel() * 4,
+            check(lib.nmfb_gram(C.byref(fs), eng.KP, 2, eng.partial.data_ptr(), eng.partial.numel() * 4,
                                 eng.gram32[which].data_ptr(), eng.gram64[which].data_ptr(), eng.num_sms,
                                 eng.stream))
             torch.cuda.synchronize()
@@ -122,7 +126,7 @@ def test_update():
         p = eng.problem()
         KP = eng.KP
         hs = eng.h.struct()
-        check(lib.nmfb_gram(C.byref(hs), KP, eng.partial.data_ptr(), eng.partial.numel() * 4,
+        check(lib.nmfb_gram(C.byref(hs), KP, 2, eng.partial.data_ptr(), eng.partial.numel() * 4,
                             eng.gram32[1].data_ptr(), eng.gram64[1].data_ptr(), eng.num_sms, eng.stream))
         vr, vc = eng._data_structs()
         slots = check(lib.nmfb_panel_gemm(C.byref(vr), eng.h.cplanes.data_ptr(), eng.h.Lp, KP, 2,
@@ -228,11 +232,16 @@ def _time(fn, iters=5, warm=2):
 def bench(m, n, k, what):
     lib = _lib.load()
     eng = Engine(m, n, k)
+    big = 16 * eng.KP * max(eng.Mp, eng.Np)
+    if eng.partial.numel() < big:
+        eng.partial = torch.empty(big, dtype=torch.float32, device=eng.device)
+        eng._problem = None
     g = torch.Generator(device='cuda').manual_seed(0)
     # synthesize bf16-exact planes directly on the device (values in [0, 4))
     eng._alloc_data(1)
-    eng.v_rows[0, :m, :n] = (torch.rand((m, n), device='cuda', generator=g) * 4).bfloat16()
-    eng.v_cols[0, :n, :m] = eng.v_rows[0, :m, :n].t()
+    for r0 in range(0, m, 4096):
+        r1 = min(m, r0 + 4096)
+        eng.store_block((torch.rand((r1 - r0, n), device='cuda', generator=g) * 4).bfloat16(), r0)
     w0 = torch.rand((k, m), device='cuda', generator=g) + 0.05
     h0 = torch.rand((k, n), device='cuda', generator=g) + 0.05
     eng.w.master[:k, :m] = w0
@@ -260,7 +269,7 @@ def bench(m, n, k, what):
     if what in ("parts", "all"):
         hs = eng.h.struct()
         ws = eng.w.struct()
-        f = lambda: check(lib.nmfb_gram(C.byref(hs), KP, eng.partial.data_ptr(), eng.partial.numel() * 4,
+        f = lambda: check(lib.nmfb_gram(C.byref(hs), KP, 2, eng.partial.data_ptr(), eng.partial.numel() * 4,
                                         eng.gram32[1].data_ptr(), eng.gram64[1].data_ptr(), eng.num_sms, eng.stream))
         print(f"bench gram(H) {_time(f):.3f} ms", flush=True)
         slots = check(lib.nmfb_panel_gemm(C.byref(vr), eng.h.cplanes.data_ptr(), eng.h.Lp, KP, 2,
