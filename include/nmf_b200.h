@@ -75,6 +75,7 @@ typedef struct nmfb_problem {
     int num_sms;                    /* SM count of the device (148 on B200)                   */
     void** phase_events;            /* optional cudaEvent_t[n_phase_events] recorded at the phase */
     int n_phase_events;             /* boundaries of a solver step (profiling; NULL = off)        */
+    double* ksum;                   /* fp64 [2][KP]: row sums of H / column sums of W (MUR-KL)    */
 } nmfb_problem;
 
 const char* nmfb_last_error(void);
@@ -139,6 +140,15 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
  * new W, then the objective of the new pair into *obj_out (skipped when obj_out == NULL). */
 int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out,
                      void* stream);
+
+/* Generalised Kullback-Leibler objective sum(v log(v/wh) - v + wh) with the reference's special values
+ * (utils.py:23-26), W.H formed tile by tile on the tensor cores, fp64 accumulation. */
+int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream);
+
+/* One outer iteration of MUR-Kullback-Leibler (mur.py:122-127 with distance_type='kl'): both updates
+ * through the fused GEMM -> quotient -> GEMM kernel (W.H never reaches HBM), row / column sums by
+ * shuffle reductions, then the objective of the new pair.  k <= 128 in this build. */
+int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream);
 
 /* ---- ADMM / AO-ADMM ------------------------------------------------------------------------- */
 typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1 } nmfb_prox;   /* admm.py:126-139 */

@@ -38,7 +38,7 @@ class Problem(C.Structure):         # struct nmfb_problem
                 ("gram32", c_void_p), ("gram64", c_void_p),
                 ("partial", c_void_p), ("partial_bytes", c_size_t),
                 ("obj_partial", c_void_p), ("obj_partial_len", c_int), ("num_sms", c_int),
-                ("phase_events", P(c_void_p)), ("n_phase_events", c_int)]
+                ("phase_events", P(c_void_p)), ("n_phase_events", c_int), ("ksum", c_void_p)]
 
 
 class AdmmState(C.Structure):       # struct nmfb_admm_state
@@ -65,6 +65,8 @@ _SIGNATURES = {
     "nmfb_mur_eu_update": (c_int, [c_void_p, c_int, c_void_p, P(Factor), c_int, c_int, c_float, c_void_p]),
     "nmfb_objective_eu": (c_int, [P(Problem), c_int, c_void_p, c_void_p]),
     "nmfb_mur_eu_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
+    "nmfb_objective_kl": (c_int, [P(Problem), c_void_p, c_void_p]),
+    "nmfb_mur_kl_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
     "nmfb_chol_inverse": (c_int, [c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p]),
     "nmfb_admm_step": (c_int, [P(Problem), P(AdmmState), C.c_double, c_float, c_int, c_float, c_int, c_void_p,

@@ -7,6 +7,7 @@
 #include "admm.cuh"
 #include "elementwise.cuh"
 #include "kernels.cuh"
+#include "kl.cuh"
 
 using namespace nmfb;
 
@@ -107,6 +108,14 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
                 const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
                 if (b > best) best = b;
             }
+    if (KP <= 128)
+        for (int side = 0; side < 2; ++side) {
+            KlPlan kp;
+            const int R = side == 0 ? m : n, T = side == 0 ? n : m;
+            if (kl_plan(KP, 1, R, T, num_sms, &kp) != 0) continue;
+            const size_t b = static_cast<size_t>(kp.slots) * KP * nmfb_padded_length(R) * 4;
+            if (b > best) best = b;
+        }
     return best;
 }
 
@@ -216,7 +225,8 @@ int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other,
     return 0;
 }
 
-int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream) {
+namespace {
+int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, void* stream) {
     if (!p || !obj_out) return fail(NMFB_ERR_ARG, "objective: null argument");
     const nmfb_data* v = &p->v_rows;
     int nparts = 0;
@@ -253,7 +263,7 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
         a.partial = p->obj_partial;
         a.KP = p->KP; a.NV = v->nv; a.BN = 128;
         a.m = p->m; a.n = p->n;
-        a.kl = 0;
+        a.kl = kl;
         a.v_rows_p = v->rows_p;
         const long ntot = static_cast<long>((a.mtiles + cs - 1) / cs) * a.ntiles;
         int ncl = residual_max_clusters(cs, p->num_sms);
@@ -263,8 +273,19 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
         nparts = grid;
         CUDA_TRY(residual_launch(a, grid, st(stream)));
     }
-    CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, 0.5, obj_out, st(stream)));
+    CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, kl ? 1.0 : 0.5, obj_out, st(stream)));
     return 0;
+}
+}  // namespace
+
+int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream) {
+    return objective_common(p, impl, 0, obj_out, stream);
+}
+
+int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
+    if (p && residual_smem_bytes(p->KP, p->v_rows.nv, 128) < 0)
+        return fail(NMFB_ERR_ARG, "objective_kl: unsupported shape");
+    return objective_common(p, 0, 1, obj_out, stream);
 }
 
 int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
@@ -299,6 +320,57 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
     // objective of the new pair                                            mur.py:124,127
     if (obj_out && (rc = nmfb_objective_eu(p, 0, obj_out, stream)) < 0) return rc;
     mark(p, 7, stream);
+    return 0;
+}
+
+namespace {
+// One side of the KL update: X (rows of `data`) <- KL rule with the other factor Y.
+int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, const nmfb_factor* y,
+            double* ysum, float lambda, void* stream) {
+    const int KP = p->KP;
+    KlPlan pl;
+    if (kl_plan(KP, data->nv, data->rows, data->cols, p->num_sms, &pl) != 0)
+        return fail(NMFB_ERR_ARG, "mur_kl: unsupported configuration KP=%d nv=%d (k <= 128 in this build)", KP, data->nv);
+    const size_t need = static_cast<size_t>(pl.slots) * KP * x->Lp * 4;
+    if (need > p->partial_bytes)
+        return fail(NMFB_ERR_WORKSPACE, "mur_kl: partial workspace %zu < %zu bytes", p->partial_bytes, need);
+    if (pl.npanels * 128 > x->Lp || pl.ntiles * 64 > y->Lp || pl.npanels * 128 > data->rows_p)
+        return fail(NMFB_ERR_ARG, "mur_kl: padded extents too small");
+    KlArgs a;
+    memset(&a, 0, sizeof(a));
+    int rc;
+    for (int q = 0; q < 2; ++q) {
+        if ((rc = make_map(&a.xr[q], bf(x->rplanes) + static_cast<long>(q) * x->Lp * KP, x->Lp, KP, 128))) return rc;
+        if ((rc = make_map(&a.yc[q], bf(y->cplanes) + static_cast<long>(q) * 256 * y->Lp, 256, y->Lp, 128))) return rc;
+    }
+    for (int q = 0; q < data->nv; ++q)
+        if ((rc = make_map(&a.d[q], bf(data->planes) + static_cast<long>(q) * data->rows_p * data->ld,
+                           static_cast<long>(data->ld / 64) * data->rows_p, 64, 128))) return rc;
+    a.out = p->partial;
+    a.KP = KP; a.Lp = x->Lp;
+    a.npanels = pl.npanels; a.ntiles = pl.ntiles; a.nsplit = pl.nsplit; a.tiles_per_split = pl.tiles_per_split;
+    a.d_rows_p = data->rows_p;
+    CUDA_TRY(factor_rowsum_launch(y->master, KP, y->L, y->Lp, ysum, st(stream)));
+    CUDA_TRY(kl_panel_launch(a, pl, data->nv, p->num_sms, st(stream)));
+    CUDA_TRY(mur_kl_update_launch(p->partial, pl.slots, ysum, x->master, bf(x->cplanes), 256L * x->Lp,
+                                  bf(x->rplanes), static_cast<long>(x->Lp) * KP, KP, p->k, x->L, x->Lp, lambda,
+                                  st(stream)));
+    return 0;
+}
+}  // namespace
+
+int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
+    if (!p) return fail(NMFB_ERR_ARG, "mur_kl_step: null problem");
+    if (!p->ksum) return fail(NMFB_ERR_ARG, "mur_kl_step: problem.ksum workspace missing");
+    int rc;
+    // phase events: 0 start | 1 W update (V, old W.H) | 2 H update (V^T, new W) | 3 objective
+    mark(p, 0, stream);
+    if ((rc = kl_side(p, &p->v_rows, &p->w, &p->h, p->ksum, lambda_w, stream)) < 0) return rc;        // mur.py:122
+    mark(p, 1, stream);
+    if ((rc = kl_side(p, &p->v_cols, &p->h, &p->w, p->ksum + p->KP, lambda_h, stream)) < 0) return rc; // mur.py:123
+    mark(p, 2, stream);
+    if (obj_out && (rc = nmfb_objective_kl(p, obj_out, stream)) < 0) return rc;                       // mur.py:127
+    mark(p, 3, stream);
     return 0;
 }
 

@@ -52,6 +52,23 @@ int residual_smem_bytes(int KP, int NV, int BN) {
 
 // Compile-time <KCH = KP / 64, NV>: the single MMA-issuing thread must not spend its time computing
 // loop bounds and descriptor fields (see panel_gemm.cu).
+// v*log(v/s) - v + s (utils.py:23-26; +inf / NaN of the log term map to 0) without the cancellation
+// of the naive form: with d = (v - s)/s the term is s*((1+d)*log1p(d) - d) = s*d^2*(1/2 - d/6 + ...).
+__device__ __forceinline__ float kl_term(float v, float s) {
+    const float d = __fdividef(v - s, s);
+    float r;
+    if (fabsf(d) < 0.125f) {
+        const float p = 0.5f + d * (-1.f / 6.f + d * (1.f / 12.f + d * (-1.f / 20.f + d * (1.f / 30.f +
+                        d * (-1.f / 42.f + d * (1.f / 56.f + d * (-1.f / 72.f)))))));
+        r = s * d * d * p;
+    } else {
+        r = v * __logf(__fdividef(v, s)) - v + s;  // no cancellation to speak of out here
+    }
+    if (v == 0.f) r = s;                           // 0*log(0/s) = NaN -> 0
+    if (s == 0.f) r = -v;                          // v*log(v/0) = +inf -> 0 (and 0/0 -> NaN -> 0)
+    return r;
+}
+
 template <int KCH, int NV>
 __global__ void __launch_bounds__(kThreadsR, 1)
 residual_kernel(const __grid_constant__ ResidualArgs args) {
@@ -261,9 +278,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                             const float dlt = vv[e] - sv;
                             tsum = fmaf(dlt, dlt, tsum);
                         } else {
-                            float term = vv[e] * __logf(vv[e] / sv);
-                            if (term == INFINITY || term != term) term = 0.f;
-                            tsum += term - vv[e] + sv;
+                            tsum += kl_term(vv[e], sv);
                         }
                     }
                 }

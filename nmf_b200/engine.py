@@ -78,6 +78,7 @@ class Engine:
             self.obj_partial = torch.zeros(self.obj_partial_len, dtype=torch.float64, device=self.device)
             self.stats = torch.zeros(4, dtype=torch.int32, device=self.device)
             self.scalars = torch.zeros(64, dtype=torch.float64, device=self.device)
+            self.ksum = torch.zeros((2, self.KP), dtype=torch.float64, device=self.device)
         self.nv = 0
         self.v_rows = None
         self.v_cols = None
@@ -126,7 +127,7 @@ class Engine:
                                     self.gram32.data_ptr(), self.gram64.data_ptr(),
                                     self.partial.data_ptr(), self.partial.numel() * 4,
                                     self.obj_partial.data_ptr(), self.obj_partial_len, self.num_sms,
-                                    None, 0)
+                                    None, 0, self.ksum.data_ptr())
         return self._problem
 
     def set_phase_events(self, events):
@@ -271,6 +272,15 @@ class Engine:
         check(self.lib.nmfb_aoadmm_step(C.byref(p), C.byref(self._admm), int(admm_iter), float(lambda_w),
                                         int(prox_w), float(lambda_h), int(prox_h),
                                         self.scalars.data_ptr() + 64 * ring_slot, self.stream))
+
+    def objective_kl(self, slot: int = 0):
+        p = self.problem()
+        check(self.lib.nmfb_objective_kl(C.byref(p), self.scalars.data_ptr() + 8 * slot, self.stream))
+
+    def mur_kl_step(self, lambda_w: float, lambda_h: float, obj_slot: Optional[int] = 0):
+        p = self.problem()
+        out = None if obj_slot is None else self.scalars.data_ptr() + 8 * obj_slot
+        check(self.lib.nmfb_mur_kl_step(C.byref(p), float(lambda_w), float(lambda_h), out, self.stream))
 
     def read_scalar(self, slot: int = 0) -> float:
         return float(self.scalars[slot].item())

@@ -46,6 +46,37 @@ class MurEuStepper:
         return out
 
 
+class MurKlStepper:
+    """mur.py:122-127 with distance_type='kl' -> nmfb_mur_kl_step."""
+    phases = ["kl_w", "kl_h", "objective"]
+
+    def __init__(self, eng, lambda_w=0.0, lambda_h=0.0):
+        self.eng, self.lw, self.lh = eng, float(lambda_w), float(lambda_h)
+
+    def prepare(self):
+        self.eng.objective_kl(slot=0)
+
+    def step(self, ring_slot: int):
+        self.eng.mur_kl_step(self.lw, self.lh, obj_slot=ring_slot * 8)
+
+    def phase_names(self):
+        return self.phases
+
+    def roofline(self, phase_ms, peaks):
+        """Dominant kernel = the fused GEMM -> quotient -> GEMM kernel (one launch per side):
+        algorithmic 4*m*n*k FLOP per launch (S tile + Q.Y^T), executed 3 MMAs per product."""
+        e = self.eng
+        ms = 0.5 * (phase_ms["kl_w"] + phase_ms["kl_h"])
+        tf = 4.0 * e.m * e.n * e.k / (ms * 1e-3) / 1e12
+        gbs = 2.0 * e.m * e.n * e.nv / (ms * 1e-3) / 1e9
+        peak = peaks["bf16_tflops_sustained"]
+        return {"kernel": "kl_panel_kernel", "bound": "tensor", "ms_per_launch": ms, "executed_mma_per_product": 3,
+                "traffic": None, "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
+                "executed_frac": 3 * tf / peak,
+                "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"]},
+                "peak_source": peaks["source"] + " (sustained bf16)"}
+
+
 PROX_CODES = {"nn": 0, "l1n": 1}
 
 
@@ -117,6 +148,8 @@ class AoAdmmStepper(_GemmRoofline):
 def make_stepper(eng, method, distance_type="eu", **kw):
     if method == "mur" and distance_type == "eu":
         return MurEuStepper(eng, kw.get("lambda_w", 0.0), kw.get("lambda_h", 0.0))
+    if method == "mur" and distance_type == "kl":
+        return MurKlStepper(eng, kw.get("lambda_w", 0.0), kw.get("lambda_h", 0.0))
     if method == "admm" and distance_type == "eu":
         return AdmmStepper(eng, kw.get("rho", 1), kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")))
     if method == "ao_admm" and distance_type == "eu":
