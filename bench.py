@@ -324,6 +324,7 @@ def run_b200(args):
     launches_per_step = (eng.launch_count() - launches0) // warmup
 
     names = PHASES.get((method, dtype_), stepper.phase_names())
+    pairs = stepper.phase_pairs() if hasattr(stepper, "phase_pairs") else [(nm, j, j + 1) for j, nm in enumerate(names)]
     nev = len(names) + 1
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(nev)] for _ in range(steps)]
     for row in evs:
@@ -350,8 +351,8 @@ def run_b200(args):
     value = 1e3 / ms_step
     obj_last = eng.read_scalar(((steps - 1) % 8) * 8)
 
-    phase_ms = {nm: float(np.mean([evs[i][j].elapsed_time(evs[i][j + 1]) for i in range(steps)]))
-                for j, nm in enumerate(names)}
+    phase_ms = {nm: float(np.mean([evs[i][a].elapsed_time(evs[i][b]) for i in range(steps)]))
+                for nm, a, b in pairs}
     roof = stepper.roofline(phase_ms, peaks)
 
     line = {

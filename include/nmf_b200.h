@@ -59,6 +59,8 @@ typedef struct nmfb_factor {        /* W (L = m) or H (L = n) */
     void* cplanes;                  /* bf16 [3][256][Lp] */
     void* rplanes;                  /* bf16 [2][Lp][KP] */
     int L, Lp;
+    int win0, win_p;                /* sharded runs: this rank updates rows [win0, win0 + win_p) of the   */
+                                    /* factor and holds exactly those rows of V (win_p = 0: all rows)     */
 } nmfb_factor;
 
 typedef struct nmfb_problem {
@@ -140,6 +142,10 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
  * new W, then the objective of the new pair into *obj_out (skipped when obj_out == NULL). */
 int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out,
                      void* stream);
+/* One factor update of the iteration above (side 0 = W, 1 = H).  In a sharded run (factor windows set,
+ * v_rows / v_cols holding this rank's rows / columns) it updates the window only; the caller then
+ * all-gathers the factor across ranks and calls nmfb_refresh_planes before the next half step. */
+int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* stream);
 
 /* Generalised Kullback-Leibler objective sum(v log(v/wh) - v + wh) with the reference's special values
  * (utils.py:23-26), W.H formed tile by tile on the tensor cores, fp64 accumulation. */

@@ -29,7 +29,7 @@ class Data(C.Structure):            # struct nmfb_data
 
 class Factor(C.Structure):          # struct nmfb_factor
     _fields_ = [("master", c_void_p), ("cplanes", c_void_p), ("rplanes", c_void_p),
-                ("L", c_int), ("Lp", c_int)]
+                ("L", c_int), ("Lp", c_int), ("win0", c_int), ("win_p", c_int)]
 
 
 class Problem(C.Structure):         # struct nmfb_problem
@@ -65,6 +65,7 @@ _SIGNATURES = {
     "nmfb_mur_eu_update": (c_int, [c_void_p, c_int, c_void_p, P(Factor), c_int, c_int, c_float, c_void_p]),
     "nmfb_objective_eu": (c_int, [P(Problem), c_int, c_void_p, c_void_p]),
     "nmfb_mur_eu_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
+    "nmfb_mur_eu_half_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
     "nmfb_objective_kl": (c_int, [P(Problem), c_void_p, c_void_p]),
     "nmfb_mur_kl_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
     "nmfb_chol_inverse": (c_int, [c_void_p, c_int, c_int, c_int, C.c_double, c_void_p, c_void_p, c_void_p,

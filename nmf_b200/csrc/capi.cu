@@ -217,30 +217,46 @@ int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t 
     return 0;
 }
 
+namespace {
+// Window of a factor this rank updates: rows [w0, w0 + wp) with `live` true rows inside it.
+struct Window { int w0, wp, live; };
+Window window_of(const nmfb_factor* f) {
+    Window w;
+    w.w0 = f->win_p > 0 ? f->win0 : 0;
+    w.wp = f->win_p > 0 ? f->win_p : f->Lp;
+    int live = f->L - w.w0;
+    if (live > w.wp) live = w.wp;
+    w.live = live < 0 ? 0 : live;
+    return w;
+}
+}  // namespace
+
 int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other, const nmfb_factor* f,
                        int k, int KP, float lambda, void* stream) {
-    CUDA_TRY(mur_eu_update_launch(partial, slots, gram_other, f->master, bf(f->cplanes), 256L * f->Lp,
-                                  bf(f->rplanes), static_cast<long>(f->Lp) * KP, KP, k, f->L, f->Lp, lambda,
-                                  st(stream)));
+    const Window w = window_of(f);
+    CUDA_TRY(mur_eu_update_launch(partial + w.w0, slots, gram_other, f->master + w.w0, bf(f->cplanes) + w.w0,
+                                  256L * f->Lp, bf(f->rplanes) + static_cast<long>(w.w0) * KP,
+                                  static_cast<long>(f->Lp) * KP, KP, k, w.live, f->Lp, w.wp, lambda, st(stream)));
     return 0;
 }
 
 namespace {
 int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, void* stream) {
     if (!p || !obj_out) return fail(NMFB_ERR_ARG, "objective: null argument");
-    const nmfb_data* v = &p->v_rows;
+    const nmfb_data* v = &p->v_rows;            // the rows of V this rank holds == the window of W
+    const Window ww = window_of(&p->w);
     int nparts = 0;
     if (impl == 0 && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
     if (impl == 1) {
-        const long need = static_cast<long>((p->m + 63) / 64) * ((p->n + 63) / 64);
+        const long need = static_cast<long>((v->rows + 63) / 64) * ((p->n + 63) / 64);
         if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
         CUDA_TRY(objective_simt_launch(bf(v->planes), static_cast<long>(v->rows_p) * v->ld, v->rows_p, v->nv,
-                                       p->w.master, p->w.Lp, p->h.master, p->h.Lp, p->k, p->m, p->n,
+                                       p->w.master + ww.w0, p->w.Lp, p->h.master, p->h.Lp, p->k, v->rows, p->n,
                                        p->obj_partial, &nparts, st(stream)));
     } else {
         ResidualArgs a;
         memset(&a, 0, sizeof(a));
-        a.mtiles = (p->m + 127) / 128;
+        a.mtiles = (v->rows + 127) / 128;
         a.ntiles = (p->n + 127) / 128;
         int cs = 2;
         if (const char* e = getenv("NMFB_RES_CLUSTER")) cs = atoi(e);
@@ -248,7 +264,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         while (cs > 1 && a.mtiles < 2 * cs) cs >>= 1;
         a.cluster = cs;
         for (int q = 0; q < 2; ++q) {
-            int rc = make_map(&a.wr[q], bf(p->w.rplanes) + static_cast<long>(q) * p->w.Lp * p->KP, p->w.Lp,
+            int rc = make_map(&a.wr[q], bf(p->w.rplanes) + (static_cast<long>(q) * p->w.Lp + ww.w0) * p->KP, ww.wp,
                               p->KP, 128);
             if (rc) return rc;
             rc = make_map(&a.hr[q], bf(p->h.rplanes) + static_cast<long>(q) * p->h.Lp * p->KP, p->h.Lp, p->KP,
@@ -288,35 +304,37 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
     return objective_common(p, 0, 1, obj_out, stream);
 }
 
-int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
-    if (!p) return fail(NMFB_ERR_ARG, "mur_eu_step: null problem");
+int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+    if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_eu_half_step: bad argument");
     const int KP = p->KP;
     const size_t gsz = static_cast<size_t>(KP) * KP;
+    // side 0: W <- W * (V H^T) / (W (H H^T) + lambda W + eps)              mur.py:122 -> :29
+    // side 1: H <- H * (W^T V) / ((W^T W) H + lambda H + eps)              mur.py:123 -> :45
+    const nmfb_factor* self = side == 0 ? &p->w : &p->h;
+    const nmfb_factor* other = side == 0 ? &p->h : &p->w;
+    const nmfb_data* data = side == 0 ? &p->v_rows : &p->v_cols;
+    float* g32 = p->gram32 + (side == 0 ? gsz : 0);
+    double* g64 = p->gram64 + (side == 0 ? gsz : 0);
+    int rc;
+    if ((rc = nmfb_gram(other, KP, 2, p->partial, p->partial_bytes, g32, g64, p->num_sms, stream)) < 0) return rc;
+    mark(p, 1 + 3 * side, stream);
+    // sharded runs: this rank's rows of the product land at its window of the full-pitch partial
+    const int slots = nmfb_panel_gemm(data, other->cplanes, other->Lp, KP, 2, p->partial + window_of(self).w0,
+                                      p->partial_bytes, self->Lp, p->num_sms, 0, 0, stream);
+    if (slots < 0) return slots;
+    mark(p, 2 + 3 * side, stream);
+    if ((rc = nmfb_mur_eu_update(p->partial, slots, g32, self, p->k, KP, lambda, stream)) < 0) return rc;
+    mark(p, 3 + 3 * side, stream);
+    return 0;
+}
+
+int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
+    if (!p) return fail(NMFB_ERR_ARG, "mur_eu_step: null problem");
     int rc;
     // phase events: 0 start | 1 gram(H) | 2 V.H^T | 3 W update | 4 gram(W) | 5 W^T.V | 6 H update | 7 objective
     mark(p, 0, stream);
-    // W <- W * (V H^T) / (W (H H^T) + lambda_w W + eps)                    mur.py:122 -> :29
-    if ((rc = nmfb_gram(&p->h, KP, 2, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz,
-                        p->num_sms, stream)) < 0) return rc;
-    mark(p, 1, stream);
-    int slots = nmfb_panel_gemm(&p->v_rows, p->h.cplanes, p->h.Lp, KP, 2, p->partial, p->partial_bytes,
-                                p->w.Lp, p->num_sms, 0, 0, stream);
-    if (slots < 0) return slots;
-    mark(p, 2, stream);
-    if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32 + gsz, &p->w, p->k, KP, lambda_w, stream)) < 0)
-        return rc;
-    mark(p, 3, stream);
-    // H <- H * (W^T V) / ((W^T W) H + lambda_h H + eps), with the NEW W    mur.py:123 -> :45
-    if ((rc = nmfb_gram(&p->w, KP, 2, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0)
-        return rc;
-    mark(p, 4, stream);
-    slots = nmfb_panel_gemm(&p->v_cols, p->w.cplanes, p->w.Lp, KP, 2, p->partial, p->partial_bytes, p->h.Lp,
-                            p->num_sms, 0, 0, stream);
-    if (slots < 0) return slots;
-    mark(p, 5, stream);
-    if ((rc = nmfb_mur_eu_update(p->partial, slots, p->gram32, &p->h, p->k, KP, lambda_h, stream)) < 0)
-        return rc;
-    mark(p, 6, stream);
+    if ((rc = nmfb_mur_eu_half_step(p, 0, lambda_w, stream)) < 0) return rc;
+    if ((rc = nmfb_mur_eu_half_step(p, 1, lambda_h, stream)) < 0) return rc;   // with the NEW W
     // objective of the new pair                                            mur.py:124,127
     if (obj_out && (rc = nmfb_objective_eu(p, 0, obj_out, stream)) < 0) return rc;
     mark(p, 7, stream);

@@ -291,8 +291,8 @@ mur_eu_update_kernel(const float* __restrict__ part, int slots, const float* __r
 
 cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram, float* master,
                                  __nv_bfloat16* cpl, long cpl_plane, __nv_bfloat16* rpl, long rpl_plane,
-                                 int KP, int k, int L, int Lp, float lambda, cudaStream_t stream) {
-    const int grid = Lp / 64;
+                                 int KP, int k, int L, int Lp, int nrows_p, float lambda, cudaStream_t stream) {
+    const int grid = nrows_p / 64;
     const size_t smem = static_cast<size_t>(KP) * 64 * 4 + 32 * static_cast<size_t>(KP) * 4;
     cudaError_t e = cudaSuccess;
     if (KP == 64) {

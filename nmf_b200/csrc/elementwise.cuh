@@ -18,7 +18,7 @@ cudaError_t gram_reduce_launch(const float* part, int slots, int KP, int Lp, flo
                                cudaStream_t stream);
 cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram, float* master,
                                  __nv_bfloat16* cpl, long cpl_plane, __nv_bfloat16* rpl, long rpl_plane,
-                                 int KP, int k, int L, int Lp, float lambda, cudaStream_t stream);
+                                 int KP, int k, int L, int Lp, int nrows_p, float lambda, cudaStream_t stream);
 cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int v_rows_p, int nv, const float* wt,
                                   int Mp, const float* ht, int Np, int k, int m, int n, double* partial,
                                   int* nparts, cudaStream_t stream);

@@ -14,6 +14,7 @@ import torch
 
 from . import _lib
 from ._lib import AdmmState, Data, Factor, Problem, check
+from .sharding import allgather_windows, allreduce_sum_, live_rows, shard_bounds
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -31,16 +32,17 @@ def _key_to_float(key: int) -> float:
 class FactorBuffers:
     """master / cplanes / rplanes of one factor (layouts in include/nmf_b200.h)."""
 
-    def __init__(self, L: int, KP: int, device):
+    def __init__(self, L: int, KP: int, device, Lp: Optional[int] = None, win0: int = 0, win_p: int = 0):
         self.L, self.KP = L, KP
-        self.Lp = (L + 255) // 256 * 256
+        self.Lp = (L + 255) // 256 * 256 if Lp is None else Lp
+        self.win0, self.win_p = win0, win_p
         self.master = torch.zeros((KP, self.Lp), dtype=torch.float32, device=device)
         self.cplanes = torch.zeros((3, 256, self.Lp), dtype=torch.bfloat16, device=device)
         self.rplanes = torch.zeros((2, self.Lp, KP), dtype=torch.bfloat16, device=device)
 
     def struct(self) -> Factor:
         return Factor(self.master.data_ptr(), self.cplanes.data_ptr(), self.rplanes.data_ptr(),
-                      self.L, self.Lp)
+                      self.L, self.Lp, self.win0, self.win_p)
 
 
 class Engine:
@@ -49,30 +51,38 @@ class Engine:
     ROW_CHUNK_BYTES = 512 << 20
 
     def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None, rank: int = 0,
-                 world: int = 1):
+                 world: int = 1, group=None):
         if not torch.cuda.is_available():
             raise RuntimeError("nmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
         self.lib = _lib.load()
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.m, self.n, self.k = int(m), int(n), int(k)
         self.rank, self.world = int(rank), int(world)
-        if self.world != 1:
-            raise NotImplementedError("sharded engines are built by nmf_b200.sharded.ShardedEngine")
-        self.row_range = (0, self.m)          # rows of V held in v_rows
-        self.col_range = (0, self.n)          # columns of V held (transposed) in v_cols
+        self.group = group
         self.KP = check(self.lib.nmfb_padded_components(self.k))
-        self.Mp = (self.m + 255) // 256 * 256
-        self.Np = (self.n + 255) // 256 * 256
+        # 1-D sharding (sharding.py): this rank owns rows [row_range) of V / W and columns [col_range) of V / H
+        self.Mp, self.per_m, mb = shard_bounds(self.m, self.world)
+        self.Np, self.per_n, nb = shard_bounds(self.n, self.world)
+        self.row_win, self.col_win = mb[self.rank], nb[self.rank]
+        self.row_range = (self.row_win[0], self.row_win[0] + live_rows(self.m, *self.row_win))
+        self.col_range = (self.col_win[0], self.col_win[0] + live_rows(self.n, *self.col_win))
         props = torch.cuda.get_device_properties(self.device)
         if props.major != 10:
             raise RuntimeError(f"nmf_b200 is built for sm_100a only; device is sm_{props.major}{props.minor}")
         self.num_sms = props.multi_processor_count
         with torch.cuda.device(self.device):
-            self.w = FactorBuffers(self.m, self.KP, self.device)
-            self.h = FactorBuffers(self.n, self.KP, self.device)
+            sharded = self.world > 1
+            self.w = FactorBuffers(self.m, self.KP, self.device, self.Mp, self.row_win[0] if sharded else 0,
+                                   self.per_m if sharded else 0)
+            self.h = FactorBuffers(self.n, self.KP, self.device, self.Np, self.col_win[0] if sharded else 0,
+                                   self.per_n if sharded else 0)
             self.gram32 = torch.zeros((2, self.KP, self.KP), dtype=torch.float32, device=self.device)
             self.gram64 = torch.zeros((2, self.KP, self.KP), dtype=torch.float64, device=self.device)
-            pbytes = int(self.lib.nmfb_partial_bytes(self.m, self.n, self.k, self.num_sms))
+            pbytes = int(self.lib.nmfb_partial_bytes(self.Mp, self.Np, self.k, self.num_sms))
+            if self.world > 1:      # a shard has fewer panels -> more K-splits, at the full output pitch
+                pbytes = max(pbytes,
+                             self.world * int(self.lib.nmfb_partial_bytes(self.per_m, self.Np, self.k, self.num_sms)),
+                             self.world * int(self.lib.nmfb_partial_bytes(self.Mp, self.per_n, self.k, self.num_sms)))
             self.partial = torch.empty(pbytes // 4, dtype=torch.float32, device=self.device)
             self.obj_partial_len = int(self.lib.nmfb_obj_partial_len(self.m, self.n, self.num_sms))
             self.obj_partial = torch.zeros(self.obj_partial_len, dtype=torch.float64, device=self.device)
@@ -94,30 +104,56 @@ class Engine:
         self.v_rows = self.v_cols = None
         self.nv = nv
         # K-blocked planes: [plane][column block of 64][row][64]  (include/nmf_b200.h)
-        self.v_rows = torch.zeros((nv, self.Np // 64, self.Mp, 64), dtype=torch.bfloat16, device=self.device)
-        self.v_cols = torch.zeros((nv, self.Mp // 64, self.Np, 64), dtype=torch.bfloat16, device=self.device)
+        self.v_rows = torch.zeros((nv, self.Np // 64, self.per_m, 64), dtype=torch.bfloat16, device=self.device)
+        self.v_cols = torch.zeros((nv, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=self.device)
         self._problem = None
 
     def store_block(self, blk: torch.Tensor, r0: int):
-        """Write rows [r0, r0+rows) of V (a device tensor (rows, n), any float dtype whose values are
-        bf16-exact) into plane 0 of both K-blocked copies.  Plumbing for on-device synthetic data."""
+        """Write rows [r0, r0+rows) of V (a device tensor (rows, n) whose values are bf16-exact) into
+        plane 0 of this rank's shards of both K-blocked copies.  Plumbing for on-device data."""
         rows, n = blk.shape
-        b = blk.to(torch.bfloat16)
-        npad = (-n) % 64
-        if npad:
-            b = torch.nn.functional.pad(b, (0, npad))
-        self.v_rows[0, : b.shape[1] // 64, r0:r0 + rows, :] = b.view(rows, -1, 64).permute(1, 0, 2)
-        bt = b[:, :n].t()                                     # (n, rows): rows r0.. of V are columns of V^T
         if r0 % 64 or (rows % 64 and r0 + rows != self.m):
             raise ValueError("store_block: row blocks must be 64-aligned")
-        rpad = (-rows) % 64
-        if rpad:
-            bt = torch.nn.functional.pad(bt, (0, rpad))
-        self.v_cols[0, r0 // 64:(r0 + rows + rpad) // 64, :n, :] = bt.reshape(n, -1, 64).permute(1, 0, 2)
+        b = blk.to(torch.bfloat16)
+        a, e = max(r0, self.row_range[0]), min(r0 + rows, self.row_range[1])
+        if a < e:                                             # rows of this block inside my row shard
+            br = b[a - r0:e - r0]
+            npad = (-n) % 64
+            if npad:
+                br = torch.nn.functional.pad(br, (0, npad))
+            lo = a - self.row_win[0]
+            self.v_rows[0, : br.shape[1] // 64, lo:lo + (e - a), :] = br.reshape(e - a, -1, 64).permute(1, 0, 2)
+        c0, c1 = self.col_range
+        if c0 < c1:                                           # my columns of this block -> rows of V^T
+            bt = b[:, c0:c1].t()
+            rpad = (-rows) % 64
+            if rpad:
+                bt = torch.nn.functional.pad(bt, (0, rpad))
+            self.v_cols[0, r0 // 64:(r0 + rows + rpad) // 64, :c1 - c0, :] = bt.reshape(c1 - c0, -1, 64).permute(1, 0, 2)
+
+    # ------------------------------------------------------------------ sharded runs
+    def gather_factor(self, fac: "FactorBuffers"):
+        """All-gather the windows of a factor every rank just updated, then re-derive its bf16 planes."""
+        if self.world == 1:
+            return
+        allgather_windows(fac.master, self.per_m if fac is self.w else self.per_n, self.group)
+        fs = fac.struct()
+        check(self.lib.nmfb_refresh_planes(self.KP, C.byref(fs), self.stream))
+
+    def mur_eu_half_step(self, side: int, lam: float):
+        p = self.problem()
+        check(self.lib.nmfb_mur_eu_half_step(C.byref(p), int(side), float(lam), self.stream))
+
+    def reduce_scalar(self, index: int):
+        """Sum a mailbox scalar over ranks (each rank's objective covers its own rows of V)."""
+        if self.world > 1:
+            allreduce_sum_(self.scalars[index:index + 1], self.group)
 
     def _data_structs(self) -> Tuple[Data, Data]:
-        vr = Data(self.v_rows.data_ptr(), self.m, self.n, self.Mp, self.Np, self.nv, 1)
-        vc = Data(self.v_cols.data_ptr(), self.n, self.m, self.Np, self.Mp, self.nv, 1)
+        vr = Data(self.v_rows.data_ptr(), self.row_range[1] - self.row_range[0], self.n, self.per_m, self.Np,
+                  self.nv, 1)
+        vc = Data(self.v_cols.data_ptr(), self.col_range[1] - self.col_range[0], self.m, self.per_n, self.Mp,
+                  self.nv, 1)
         return vr, vc
 
     def problem(self) -> Problem:
@@ -169,6 +205,8 @@ class Engine:
             v = v.astype(np.float64)
         if not v.flags.c_contiguous:
             v = np.ascontiguousarray(v)
+        if self.world > 1:
+            return self._upload_sharded(v)
         self._alloc_data(planes or 1)
         vmin, need_lo, bad = self._ingest_pass(v)
         if need_lo and planes is None:
@@ -176,6 +214,24 @@ class Engine:
             vmin, need_lo, bad = self._ingest_pass(v)
         if bad:
             raise ValueError("data contains non-finite values")
+        self.vmin = vmin
+        return vmin
+
+    def _upload_sharded(self, v: np.ndarray) -> float:
+        """Sharded runs: every rank walks the host V in row chunks and keeps its row / column shard
+        (store_block).  This build needs bf16-exact data here (one lossless plane)."""
+        self._alloc_data(1)
+        vmin = float("inf")
+        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
+        for r0 in range(0, self.m, rows_per):
+            r1 = min(self.m, r0 + rows_per)
+            blk = torch.from_numpy(v[r0:r1]).to(self.device)
+            if not torch.isfinite(blk).all():
+                raise ValueError("data contains non-finite values")
+            if not torch.equal(blk.to(torch.bfloat16).to(blk.dtype), blk):
+                raise NotImplementedError("sharded runs need bfloat16-exact data in this build")
+            vmin = min(vmin, float(blk.min()))
+            self.store_block(blk, r0)
         self.vmin = vmin
         return vmin
 

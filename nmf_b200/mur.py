@@ -22,7 +22,7 @@ Results = namedtuple('Results', 'w h i obj_history experiment')
 
 def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, tol2=1e-5,
         lambda_w=0.0, lambda_h=0.0, nndsvd_init=(False, 'zero'), save_dir='./results/',
-        w0=None, h0=None, verbose=True, engine=None):
+        w0=None, h0=None, verbose=True, engine=None, comm=None):
     """x: (m, n) non-negative data, k: number of components.  Extra (non-reference) keywords:
     w0 / h0 = explicit initial factors, verbose = per-iteration print, engine = reuse device state."""
     experiment = Experiment(method='mur', components=k, distance_type=distance_type,
@@ -34,6 +34,13 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
     x = np.asarray(x) if not isinstance(x, np.ndarray) else x
     m, n = x.shape
 
+    if comm is not None and engine is None:              # sharded over the ranks of a torch.distributed group
+        import torch.distributed as dist
+        group = None if comm is True else comm
+        engine = Engine(m, n, k, rank=dist.get_rank(group), world=dist.get_world_size(group), group=group)
+        if engine.world > 1 and distance_type != 'eu':
+            raise NotImplementedError("sharded runs provide method='mur', distance_type='eu' in this build")
+        verbose = verbose and engine.rank == 0
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:
         vmin = eng.upload_data(x)

@@ -1,0 +1,52 @@
+"""1-D sharding of V across the GPUs of one box (MPI-FAUN layout).
+
+Rank p holds the row shard V[I_p, :] (for the W update) and the column shard V[:, J_p] (stored
+transposed, for the H update); both factors are replicated.  Per outer iteration each rank updates
+its window W[I_p, :] and H[:, J_p] and the windows are all-gathered -- the only data-path exchange
+besides the scalar objective.  Everything here is plumbing over torch.distributed and works on CPU
+tensors too (gloo), which is how the host logic is tested without GPUs.
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def round_up(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+def shard_bounds(L: int, world: int, align: int = 256) -> Tuple[int, int, List[Tuple[int, int]]]:
+    """Padded length (a multiple of align * world), rows per rank, and each rank's [lo, hi) window."""
+    Lp = round_up(max(L, 1), align * world)
+    per = Lp // world
+    return Lp, per, [(p * per, (p + 1) * per) for p in range(world)]
+
+
+def live_rows(L: int, lo: int, hi: int) -> int:
+    """True (unpadded) rows inside the window [lo, hi)."""
+    return max(0, min(hi, L) - lo)
+
+
+def allgather_windows(master: torch.Tensor, per: int, group=None) -> None:
+    """master: [KP][world * per]; on entry rank p's window master[:, p*per:(p+1)*per] is current,
+    on exit the whole tensor is.  One all-gather of KP * per elements per rank."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    KP = master.shape[0]
+    assert master.shape[1] == world * per
+    send = master[:, rank * per:(rank + 1) * per].contiguous()
+    recv = torch.empty((world, KP, per), dtype=master.dtype, device=master.device)
+    try:
+        dist.all_gather_into_tensor(recv, send, group=group)
+    except (RuntimeError, NotImplementedError):          # backends without the tensor variant
+        parts = [torch.empty_like(send) for _ in range(world)]
+        dist.all_gather(parts, send, group=group)
+        recv = torch.stack(parts)
+    master.view(KP, world, per).copy_(recv.permute(1, 0, 2))
+
+
+def allreduce_sum_(t: torch.Tensor, group=None) -> None:
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)

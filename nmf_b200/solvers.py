@@ -15,12 +15,29 @@ class MurEuStepper:
 
     def prepare(self):
         self.eng.objective_eu(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot: int):
-        self.eng.mur_eu_step(self.lw, self.lh, obj_slot=ring_slot * 8)
+        e = self.eng
+        if e.world == 1:
+            e.mur_eu_step(self.lw, self.lh, obj_slot=ring_slot * 8)
+            return
+        # sharded: update my window of W, all-gather W, my window of H, all-gather H, partial objective
+        e.mur_eu_half_step(0, self.lw)
+        e.gather_factor(e.w)
+        e.mur_eu_half_step(1, self.lh)
+        e.gather_factor(e.h)
+        e.objective_eu(slot=ring_slot * 8)
+        e.reduce_scalar(ring_slot * 8)
 
     def phase_names(self):
         return self.phases
+
+    def phase_pairs(self):
+        """(name, first event, last event) triples that are recorded in this mode."""
+        if self.eng.world == 1:
+            return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
+        return [("gemm_w", 1, 2), ("update_w", 2, 3), ("gemm_h", 4, 5), ("update_h", 5, 6)]
 
     def roofline(self, phase_ms, peaks):
         """Dominant kernel = the split-bf16 panel GEMM (two launches per iteration: V.H^T and
@@ -28,8 +45,8 @@ class MurEuStepper:
         e = self.eng
         ms = 0.5 * (phase_ms["gemm_w"] + phase_ms["gemm_h"])
         mpp = getattr(self, "mma_per_product", 2)
-        flops = 2.0 * e.m * e.n * e.k
-        vbytes = 2.0 * e.m * e.n * e.nv
+        flops = 2.0 * e.m * e.n * e.k / e.world              # per rank (its shard of V)
+        vbytes = 2.0 * e.m * e.n * e.nv / e.world
         tf = flops / (ms * 1e-3) / 1e12
         gbs = vbytes / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
