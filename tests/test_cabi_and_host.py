@@ -1,0 +1,148 @@
+"""CPU: the C-ABI library builds / loads and exports every symbol declared in include/nmf_b200.h
+(no compute calls -- there is no GPU here), and the host-side mirror of the reference API behaves
+like the reference (names, defaults, file naming, stop test, error types)."""
+import ctypes as C
+import inspect
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "nmf_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(nmfb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from nmf_b200 import _build, _lib
+    _build.build()
+    lib = C.CDLL(_build.LIB_PATH)
+    declared = _header_symbols()
+    assert len(declared) >= 20
+    missing = [s for s in declared if not hasattr(lib, s)]
+    assert not missing, f"declared in the header but not exported: {missing}"
+    bound = set(_lib.exported_symbols())
+    assert set(declared) == bound, f"ctypes binding and header disagree: {set(declared) ^ bound}"
+
+
+def test_pure_host_entry_points():
+    from nmf_b200 import _lib
+    lib = _lib.load()
+    assert lib.nmfb_abi_version() >= 1
+    assert [lib.nmfb_padded_components(k) for k in (1, 64, 65, 128, 129, 256)] == [64, 64, 128, 128, 256, 256]
+    assert lib.nmfb_padded_components(257) < 0 and b"256" in lib.nmfb_last_error()
+    assert lib.nmfb_padded_length(1000) == 1024 and lib.nmfb_padded_length(1024) == 1024
+
+
+def test_struct_layouts_match_header():
+    """sizeof of the ctypes mirrors == what a C compiler lays out (guards against drift)."""
+    import subprocess, tempfile
+    from nmf_b200 import _lib
+    src = '#include <stdio.h>\n#include "nmf_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(nmfb_data), sizeof(nmfb_factor), sizeof(nmfb_problem), sizeof(nmfb_admm_state));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "t.c")
+        open(c, "w").write(src)
+        exe = os.path.join(d, "t")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
+        sizes = [int(x) for x in subprocess.check_output([exe]).split()]
+    assert sizes == [C.sizeof(_lib.Data), C.sizeof(_lib.Factor), C.sizeof(_lib.Problem), C.sizeof(_lib.AdmmState)]
+
+
+def test_no_cpu_fallback():
+    """The product path must fail loudly without a CUDA device."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from nmf_b200 import NMF
+    with pytest.raises(RuntimeError, match="CUDA"):
+        NMF(np.ones((8, 8)), 2).factorize(method="mur", distance_type="eu", max_iter=1)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "nmf_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            assert "oracle" not in open(os.path.join(pkg, fn)).read(), fn
+
+
+def test_solver_signatures_mirror_the_reference():
+    """Keyword names and defaults of mur.py:52-53, admm.py:233-235, ao_admm.py:201-203."""
+    from nmf_b200.admm import admm
+    from nmf_b200.ao_admm import ao_admm
+    from nmf_b200.mur import mur
+    want = {
+        mur: dict(distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, tol2=1e-5, lambda_w=0.0,
+                  lambda_h=0.0, nndsvd_init=(False, 'zero'), save_dir='./results/'),
+        admm: dict(rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_iter=10, max_iter=100000,
+                   tol1=1e-3, tol2=1e-3, nndsvd_init=(True, 'zero'), save_dir='./results/'),
+        ao_admm: dict(distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_iter=10, max_iter=100000,
+                      admm_iter=10, tol1=1e-3, tol2=1e-3, nndsvd_init=(True, 'zero'), save_dir='./results/'),
+    }
+    for fn, kw in want.items():
+        params = inspect.signature(fn).parameters
+        for name, default in kw.items():
+            assert params[name].kind is inspect.Parameter.KEYWORD_ONLY
+            assert params[name].default == default, (fn.__name__, name)
+
+
+def test_stop_test_and_precision():
+    from nmf_b200.utils import convergence_check, tol_precision
+    assert convergence_check(0.5e-3, 1.0, 1e-3, 1e-3) is True          # (1) new < tol1
+    assert convergence_check(1.0, 1.0005, 1e-3, 1e-3) is True          # (2) new >= old - tol2
+    assert convergence_check(1.0, 1.1, 1e-3, 1e-3) is False
+    assert tol_precision(1e-5, 1e-3) == 5 and tol_precision(2.0, 3.0) == 2
+
+
+def test_prox_names():
+    from nmf_b200.solvers import prox_code
+    assert prox_code((0, 'nn')) == (0.0, 0) and prox_code((0.1, 'l1n')) == (0.1, 1)
+    assert prox_code((0, 'l2n')) == (0.0, 0)                           # admm.py:150: identity system
+    with pytest.raises(TypeError):
+        prox_code((0.1, 'l1'))                                         # not a reference name (admm.py:213)
+    with pytest.raises(NotImplementedError):
+        prox_code((0.5, 'l2n'))
+
+
+def test_facade_dispatch_and_save_names(tmp_path, capsys):
+    from collections import namedtuple
+    from nmf_b200 import NMF
+    model = NMF(np.ones((4, 3)), 2)
+    with pytest.raises(Exception, match="Method not known"):
+        model.factorize(method="bogus")                                # nmf.py:76
+    with pytest.raises(NotImplementedError):
+        model.factorize(method="anls")
+    assert model.w is None and model.h is None
+    # file naming of nmf.py:95-126 for the three solvers
+    R = namedtuple('Results', 'w h i obj_history experiment')
+    E1 = namedtuple('Experiment', 'method components distance_type nndsvd_init max_iter tol1 tol2 lambda_w lambda_h')
+    model.results = R(np.ones((4, 2)), np.ones((2, 3)), 3, [1.0, 0.5, 0.4, 0.3, 0.2],
+                      E1('mur', 2, 'eu', (False, 'zero'), 10, 1e-5, 1e-5, 0.0, 0.1))
+    assert model.default_save_name() == 'nmf_mur_2_eu_0.0_0.1_random'
+    E2 = namedtuple('Experiment', 'method components rho distance_type nndsvd_init min_iter max_iter tol1 tol2 lambda_w prox_w lambda_h prox_h')
+    model.results = model.results._replace(experiment=E2('admm', 2, 100, 'eu', (True, 'mean'), 1, 2, 1e-3, 1e-3, 0, 'nn', 0.1, 'l1n'))
+    assert model.default_save_name() == 'nmf_admm_2_eu_100_0:nn_0.1:l1n_nndsvdm'
+    E3 = namedtuple('Experiment', 'method components distance_type nndsvd_init min_iter max_iter admm_iter tol1 tol2 lambda_w prox_w lambda_h prox_h')
+    model.results = model.results._replace(experiment=E3('ao_admm', 2, 'eu', (False, 'zero'), 1, 2, 5, 1e-3, 1e-3, 0, 'nn', 0.1, 'l1n'))
+    assert model.default_save_name() == 'nmf_ao_admm_2_eu_0:nn_0.1:l1n_random'
+    model.save_factorization(save_dir=str(tmp_path))
+    z = np.load(tmp_path / 'nmf_ao_admm_2_eu_0:nn_0.1:l1n_random.npz', allow_pickle=True)
+    assert sorted(z.files) == ['experiment', 'h', 'i', 'obj_history', 'w']      # utils.py:103
+    assert z['experiment'].item()['admm_iter'] == 5 and int(z['i']) == 3
+    assert 'Results saved in' in capsys.readouterr().out
+
+
+def test_reference_order_initial_factors():
+    from nmf_b200.init import initial_factors
+    np.random.seed(7)
+    w, h = initial_factors(np.ones((5, 4)), 3, (False, 'zero'))
+    np.random.seed(7)
+    w_ref = np.abs(np.random.randn(5, 3)); h_ref = np.abs(np.random.randn(3, 4))   # mur.py:108-109
+    assert np.array_equal(w, w_ref) and np.array_equal(h, h_ref)
