@@ -109,7 +109,7 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------
 # synthetic workload on the device: planted low-rank + 1% noise on the bf16 grid
 # ----------------------------------------------------------------------------------------------
-def synth_fill_engine(eng, seed: int):
+def synth_fill_engine(eng, seed: int, fixed: bool = False):
     """Fill eng.v_rows / eng.v_cols (1 lossless bf16 plane) for the engine's row / column shard.
     Every rank walks the same row chunks with the same per-chunk generator, so shards of
     different ranks are slices of one and the same V."""
@@ -120,18 +120,29 @@ def synth_fill_engine(eng, seed: int):
     g.manual_seed(seed)
     wt = torch.rand((m, k), device=dev, generator=g)
     ht = torch.rand((k, n), device=dev, generator=g)
-    eng._alloc_data(1)
-    r_lo, r_hi = eng.row_range
-    c_lo, c_hi = eng.col_range
     chunk = 2048
-    for r0 in range(0, m, chunk):
-        r1 = min(m, r0 + chunk)
-        g.manual_seed(seed * 1000003 + 17 + r0)
-        blk = wt[r0:r1] @ ht
-        blk.add_(torch.rand((r1 - r0, n), device=dev, generator=g), alpha=0.01)
-        blk = blk.bfloat16()
-        eng.store_block(blk, r0)
-        del blk
+
+    def blocks():
+        for r0 in range(0, m, chunk):
+            r1 = min(m, r0 + chunk)
+            g.manual_seed(seed * 1000003 + 17 + r0)
+            blk = wt[r0:r1] @ ht
+            blk.add_(torch.rand((r1 - r0, n), device=dev, generator=g), alpha=0.01)
+            yield r0, blk.bfloat16().float()               # values on the bf16 grid, fp32 container
+
+    if eng.world > 1:                                      # shards: plumbing path
+        eng._alloc_data(1)
+        for r0, blk in blocks():
+            eng.store_block(blk, r0)
+    else:                                                  # through the library's ingest kernels
+        eng.begin_ingest(1, fixed=fixed)
+        if fixed:
+            for r0, blk in blocks():
+                eng.absmax_chunk(blk, r0)
+        for r0, blk in blocks():
+            eng.ingest_chunk(blk, r0)
+        vmin, inexact, bad = eng.finish_ingest()
+        assert not bad and not inexact
     return wt, ht
 
 
@@ -313,7 +324,7 @@ def run_b200(args):
     peaks = load_peaks()
 
     eng = Engine(m, n, k, device=dev, rank=rank, world=world)
-    synth_fill_engine(eng, seed=0)
+    synth_fill_engine(eng, seed=0, fixed=(method in ('admm', 'ao_admm')))
     synth_init(eng, seed=1)
     stepper = solvers.make_stepper(eng, method, dtype_, **extra)
     stepper.prepare()
@@ -401,7 +412,10 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
     chunk = 4096
     for r0 in range(0, m, chunk):
         r1 = min(m, r0 + chunk)
-        v_host[r0:r1].copy_(eng.v_rows[0, :, r0:r1, :].permute(1, 0, 2).reshape(r1 - r0, -1)[:, :n].float())
+        blk = eng.v_rows[0, :, r0:r1, :].permute(1, 0, 2).reshape(r1 - r0, -1)[:, :n].float()
+        if eng.fixed:
+            blk = blk + eng.v_rows[1, :, r0:r1, :].permute(1, 0, 2).reshape(r1 - r0, -1)[:, :n].float()
+        v_host[r0:r1].copy_(blk)
     w0 = eng.w.master[:k, :m].t().contiguous().cpu().numpy()     # current factors as the start
     h0 = eng.h.master[:k, :n].contiguous().cpu().numpy()
     torch.cuda.synchronize(dev)

@@ -52,6 +52,8 @@ typedef struct nmfb_data {          /* V (rows = m, cols = n) or V^T (rows = n, 
     void* planes;                   /* bf16 [nv][ld/64][rows_p][64] (K-blocked) or [nv][rows_p][ld] */
     int rows, cols, rows_p, ld, nv;
     int blocked;                    /* 1: K-blocked layout (V, V^T); 0: plain row-major           */
+    int fixed;                      /* 1: plane 0 is the fixed-point slice of each row (exact-mode   */
+                                    /*    ADMM contractions), planes 1.. the floating remainder       */
 } nmfb_data;
 
 typedef struct nmfb_factor {        /* W (L = m) or H (L = n) */
@@ -99,6 +101,18 @@ int nmfb_obj_partial_len(int m, int n, int num_sms);
  * Replaces the implicit float64 view of `x` in mur.py:52 / admm.py:233 / ao_admm.py:201. */
 int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int nrows,
                      const nmfb_data* v_rows, const nmfb_data* v_cols, uint32_t* stats, void* stream);
+/* Fixed-point variant (v_rows->fixed / v_cols->fixed): plane 0 = x rounded to a multiple of 2^(E-6), E the
+ * exponent of max|V| over the row of that copy (row of V for v_rows, column of V for v_cols), plane 1 =
+ * the bf16 remainder; stats[1] = 1 when two planes do not hold the data exactly.  rowmax [m] / colmax [n]
+ * are filled by nmfb_data_absmax over ALL chunks first (zero-initialised by the caller). */
+int nmfb_ingest_data_fixed(const void* src, int src_is_f64, long src_ld, int row0, int nrows,
+                           const nmfb_data* v_rows, const nmfb_data* v_cols, uint32_t* stats,
+                           const uint32_t* rowmax, const uint32_t* colmax, void* stream);
+int nmfb_data_absmax(const void* src, int src_is_f64, long src_ld, int row0, int nrows, int ncols,
+                     uint32_t* rowmax, uint32_t* colmax, void* stream);
+/* Re-derive the cplanes of a factor in fixed-point form (plane 0 = 7-bit slice relative to the row
+ * maximum, planes 1-2 = floating remainders): operands of nmfb_panel_gemm_exact / nmfb_gram_exact. */
+int nmfb_fixed_planes(int KP, const nmfb_factor* f, void* stream);
 
 /* Import an initial factor (mur.py:108-109, admm.py:23-24, ao_admm.py:22-23 or utils.nndsvd).
  * Element (r, c) of the factor is src[r*stride_l + c*stride_c]; W [m][k]: (k, 1); H [k][n]: (1, n).
@@ -120,6 +134,14 @@ int nmfb_export_factor(const nmfb_factor* f, int k, int KP, void* dst, int dst_i
 int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int factor_Lp, int KP, int nb,
                     float* partial, size_t partial_bytes, int out_Lp, int num_sms, int force_bn,
                     int force_split, void* stream);
+
+/* Exact-hi contraction for the ADMM right-hand sides (admm.py:221, ao_admm.py:56): fixed-point planes on
+ * both sides, the leading plane pair accumulated without rounding, (hi, lo) fp32 slot pairs out.
+ * Returns the number of slots (sum them in fp64) or a negative status. */
+int nmfb_panel_gemm_exact(const nmfb_data* data, const void* factor_cplanes, int factor_Lp, int KP,
+                          float* partial, size_t partial_bytes, int out_Lp, int num_sms, void* stream);
+int nmfb_gram_exact(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+                    double* gram64, int num_sms, void* stream);
 
 /* Gram matrix G = F F^T of a factor from its cplanes (`w.T @ w` ao_admm.py:53, `other_aux.T @
  * other_aux` admm.py:220, and the W (H H^T) / (W^T W) H re-association of mur.py:29,45).
@@ -170,6 +192,8 @@ typedef struct nmfb_admm_state {
     int* flags;                     /* int  [8]: [0] not-PD (sticky) [1] inner done [2] inner iterations  */
                                     /*           used by the H update [3] ... by the W update             */
     double* norm_partial;           /* fp64 [4 * max(Mp,Np)/64]                                           */
+    int exact;                      /* 1: V planes and factor cplanes are fixed-point; use the exact-hi   */
+                                    /*    contractions (needs problem.v_rows.fixed / v_cols.fixed)        */
 } nmfb_admm_state;
 
 /* ainv = (gram + rho I)^-1 by a shared-memory Cholesky (fp64), rho = rho_in (rho_mode 0, admm.py:220)

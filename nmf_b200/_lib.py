@@ -24,7 +24,7 @@ P = C.POINTER
 
 class Data(C.Structure):            # struct nmfb_data
     _fields_ = [("planes", c_void_p), ("rows", c_int), ("cols", c_int), ("rows_p", c_int),
-                ("ld", c_int), ("nv", c_int), ("blocked", c_int)]
+                ("ld", c_int), ("nv", c_int), ("blocked", c_int), ("fixed", c_int)]
 
 
 class Factor(C.Structure):          # struct nmfb_factor
@@ -44,7 +44,7 @@ class Problem(C.Structure):         # struct nmfb_problem
 class AdmmState(C.Structure):       # struct nmfb_admm_state
     _fields_ = [("w_aux", Factor), ("h_aux", Factor), ("dual_w", c_void_p), ("dual_h", c_void_p),
                 ("ainv", c_void_p), ("chol_scratch", c_void_p), ("c64", c_void_p), ("scal", c_void_p),
-                ("flags", c_void_p), ("norm_partial", c_void_p)]
+                ("flags", c_void_p), ("norm_partial", c_void_p), ("exact", c_int)]
 
 
 _SIGNATURES = {
@@ -56,6 +56,12 @@ _SIGNATURES = {
     "nmfb_partial_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "nmfb_obj_partial_len": (c_int, [c_int, c_int, c_int]),
     "nmfb_ingest_data": (c_int, [c_void_p, c_int, c_long, c_int, c_int, P(Data), P(Data), c_void_p, c_void_p]),
+    "nmfb_ingest_data_fixed": (c_int, [c_void_p, c_int, c_long, c_int, c_int, P(Data), P(Data), c_void_p, c_void_p,
+                                       c_void_p, c_void_p]),
+    "nmfb_data_absmax": (c_int, [c_void_p, c_int, c_long, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "nmfb_fixed_planes": (c_int, [c_int, P(Factor), c_void_p]),
+    "nmfb_panel_gemm_exact": (c_int, [P(Data), c_void_p, c_int, c_int, c_void_p, c_size_t, c_int, c_int, c_void_p]),
+    "nmfb_gram_exact": (c_int, [P(Factor), c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
     "nmfb_import_factor": (c_int, [c_void_p, c_int, c_long, c_long, c_int, c_int, P(Factor), c_void_p]),
     "nmfb_refresh_planes": (c_int, [c_int, P(Factor), c_void_p]),
     "nmfb_export_factor": (c_int, [P(Factor), c_int, c_int, c_void_p, c_int, c_long, c_long, c_void_p]),

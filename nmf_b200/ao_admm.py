@@ -40,7 +40,7 @@ def ao_admm(v, k, *, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_
 
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:
-        eng.upload_data(v)
+        eng.upload_data(v, fixed=True)
     if w0 is None or h0 is None:
         from .init import initial_factors
         w0, h0 = initial_factors(v, k, nndsvd_init)

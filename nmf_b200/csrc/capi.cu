@@ -108,6 +108,20 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
                 const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
                 if (b > best) best = b;
             }
+    for (int side = 0; side < 2; ++side) {           // exact-hi ADMM contractions (2 data planes)
+        PanelGemmPlan xp;
+        const int R = side == 0 ? m : n, T = side == 0 ? n : m;
+        if (panel_gemm_exact_plan(KP, 2, R, T, 1, num_sms, &xp) != 0) continue;
+        const size_t b = static_cast<size_t>(xp.slots) * KP * nmfb_padded_length(R) * 4;
+        if (b > best) best = b;
+    }
+    {
+        PanelGemmPlan xp;                            // exact Gram: data = the factor's own three planes
+        if (panel_gemm_exact_plan(KP, 3, KP, m > n ? m : n, 0, num_sms, &xp) == 0) {
+            const size_t b = static_cast<size_t>(xp.slots) * KP * 256 * 4;
+            if (b > best) best = b;
+        }
+    }
     if (KP <= 128)
         for (int side = 0; side < 2; ++side) {
             KlPlan kp;
@@ -125,8 +139,10 @@ int nmfb_obj_partial_len(int m, int n, int num_sms) {
     return static_cast<int>(simt > num_sms ? simt : num_sms);
 }
 
-int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int nrows, const nmfb_data* vr,
-                     const nmfb_data* vc, uint32_t* stats, void* stream) {
+namespace {
+int ingest_common(const void* src, int src_is_f64, long src_ld, int row0, int nrows, const nmfb_data* vr,
+                  const nmfb_data* vc, uint32_t* stats, const uint32_t* rowmax, const uint32_t* colmax,
+                  void* stream) {
     if (!src || !vr || !vc || !stats) return fail(NMFB_ERR_ARG, "ingest_data: null argument");
     if (vr->rows != vc->cols || vr->cols != vc->rows || vr->nv != vc->nv)
         return fail(NMFB_ERR_ARG, "ingest_data: v_rows / v_cols shapes disagree");
@@ -134,7 +150,36 @@ int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int
     if (!vr->blocked || !vc->blocked) return fail(NMFB_ERR_ARG, "ingest_data: data planes must be K-blocked");
     CUDA_TRY(ingest_data_launch(src, src_is_f64, src_ld, row0, nrows, vr->cols, bf(vr->planes),
                                 static_cast<long>(vr->rows_p) * vr->ld, vr->rows_p, bf(vc->planes),
-                                static_cast<long>(vc->rows_p) * vc->ld, vc->rows_p, vr->nv, stats, st(stream)));
+                                static_cast<long>(vc->rows_p) * vc->ld, vc->rows_p, vr->nv, stats, rowmax, colmax,
+                                st(stream)));
+    return 0;
+}
+}  // namespace
+
+int nmfb_ingest_data(const void* src, int src_is_f64, long src_ld, int row0, int nrows, const nmfb_data* vr,
+                     const nmfb_data* vc, uint32_t* stats, void* stream) {
+    return ingest_common(src, src_is_f64, src_ld, row0, nrows, vr, vc, stats, nullptr, nullptr, stream);
+}
+
+int nmfb_ingest_data_fixed(const void* src, int src_is_f64, long src_ld, int row0, int nrows, const nmfb_data* vr,
+                           const nmfb_data* vc, uint32_t* stats, const uint32_t* rowmax, const uint32_t* colmax,
+                           void* stream) {
+    if (!rowmax || !colmax) return fail(NMFB_ERR_ARG, "ingest_data_fixed: row / column maxima missing");
+    if (!vr || !vc || vr->nv < 2 || !vr->fixed || !vc->fixed)
+        return fail(NMFB_ERR_ARG, "ingest_data_fixed: needs two fixed-point planes");
+    return ingest_common(src, src_is_f64, src_ld, row0, nrows, vr, vc, stats, rowmax, colmax, stream);
+}
+
+int nmfb_data_absmax(const void* src, int src_is_f64, long src_ld, int row0, int nrows, int ncols,
+                     uint32_t* rowmax, uint32_t* colmax, void* stream) {
+    if (!src || !rowmax || !colmax) return fail(NMFB_ERR_ARG, "data_absmax: null argument");
+    CUDA_TRY(data_absmax_launch(src, src_is_f64, src_ld, row0, nrows, ncols, rowmax, colmax, st(stream)));
+    return 0;
+}
+
+int nmfb_fixed_planes(int KP, const nmfb_factor* f, void* stream) {
+    if (!f) return fail(NMFB_ERR_ARG, "fixed_planes: null factor");
+    CUDA_TRY(fixed_planes_launch(f->master, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, st(stream)));
     return 0;
 }
 
@@ -202,6 +247,59 @@ int nmfb_panel_gemm(const nmfb_data* data, const void* factor_cplanes, int facto
     return pl.slots;
 }
 
+int nmfb_panel_gemm_exact(const nmfb_data* data, const void* factor_cplanes, int factor_Lp, int KP,
+                          float* partial, size_t partial_bytes, int out_Lp, int num_sms, void* stream) {
+    if (!data || !factor_cplanes || !partial) return fail(NMFB_ERR_ARG, "panel_gemm_exact: null argument");
+    if (factor_Lp < data->ld) return fail(NMFB_ERR_ARG, "panel_gemm_exact: factor pitch %d < data pitch %d", factor_Lp, data->ld);
+    PanelGemmPlan pl;
+    if (panel_gemm_exact_plan(KP, data->nv, data->rows, data->cols, data->blocked, num_sms, &pl) != 0)
+        return fail(NMFB_ERR_ARG, "panel_gemm_exact: unsupported configuration KP=%d nv=%d", KP, data->nv);
+    if (pl.npanels * pl.BN > out_Lp || pl.npanels * pl.BN > data->rows_p)
+        return fail(NMFB_ERR_ARG, "panel_gemm_exact: padded extents too small");
+    const size_t need = static_cast<size_t>(pl.slots) * KP * out_Lp * 4;
+    if (need > partial_bytes)
+        return fail(NMFB_ERR_WORKSPACE, "panel_gemm_exact: partial workspace %zu < %zu bytes", partial_bytes, need);
+    PanelGemmArgs a;
+    memset(&a, 0, sizeof(a));
+    const int a_box_rows = ((KP == 64) ? 64 : 128) / pl.cluster;
+    for (int j = 0; j < 3; ++j) {
+        int rc = make_map(&a.fac[j], bf(factor_cplanes) + static_cast<long>(j) * 256 * factor_Lp, 256, factor_Lp,
+                          a_box_rows);
+        if (rc) return rc;
+    }
+    for (int i = 0; i < data->nv; ++i) {
+        const __nv_bfloat16* base = bf(data->planes) + static_cast<long>(i) * data->rows_p * data->ld;
+        int rc = data->blocked
+                     ? make_map(&a.dat[i], base, static_cast<long>(data->ld / 64) * data->rows_p, 64, pl.BN)
+                     : make_map(&a.dat[i], base, data->rows_p, data->ld, pl.BN);
+        if (rc) return rc;
+    }
+    a.out = partial;
+    a.KP = KP; a.NB = 3; a.NA = data->nv; a.BN = pl.BN;
+    a.npanels = pl.npanels; a.nsplit = pl.nsplit; a.kb_per_split = pl.kb_per_split;
+    a.kblocks_total = pl.kblocks_total;
+    a.Lp = out_Lp;
+    a.nstages = pl.nstages;
+    a.dat_rows_p = data->blocked ? data->rows_p : 0;
+    a.cluster = pl.cluster; a.ngroups = pl.ngroups; a.chunk_kb = pl.chunk_kb;
+    a.dat_box_rows = pl.dat_box_rows; a.prefetch_kb = pl.prefetch_kb;
+    CUDA_TRY(panel_gemm_exact_launch(a, pl, st(stream)));
+    return pl.slots;
+}
+
+int nmfb_gram_exact(const nmfb_factor* f, int KP, float* partial, size_t partial_bytes, float* gram32,
+                    double* gram64, int num_sms, void* stream) {
+    if (KP == 256)      // 3 x 3 planes do not fit two stages: floating 2-plane Gram
+        return nmfb_gram(f, KP, 2, partial, partial_bytes, gram32, gram64, num_sms, stream);
+    nmfb_data d;
+    d.planes = f->cplanes;
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 3; d.blocked = 0; d.fixed = 1;
+    const int slots = nmfb_panel_gemm_exact(&d, f->cplanes, f->Lp, KP, partial, partial_bytes, 256, num_sms, stream);
+    if (slots < 0) return slots;
+    CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
+    return 0;
+}
+
 int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
               double* gram64, int num_sms, void* stream) {
     // The factor's own bf16 planes act as the "data": rows = components, contraction over L.
@@ -209,7 +307,7 @@ int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t 
     if (KP == 256) nplanes = 2;          // 3 x 3 planes do not fit two smem stages at KP = 256
     nmfb_data d;
     d.planes = f->cplanes;
-    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0;
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0; d.fixed = 0;
     const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, nplanes, partial, partial_bytes, 256, num_sms,
                                       128, 0, stream);
     if (slots < 0) return slots;
@@ -416,14 +514,34 @@ int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* par
     a.x = f->master; a.u = u;
     if (aux) {
         a.aux_master = aux->master;
-        a.aux_cpl = bf(aux->cplanes); a.aux_cpl_plane = 256L * aux->Lp;
+        if (!s->exact) { a.aux_cpl = bf(aux->cplanes); a.aux_cpl_plane = 256L * aux->Lp; }
     }
-    if (want_cpl) { a.x_cpl = bf(f->cplanes); a.x_cpl_plane = 256L * f->Lp; }
+    if (want_cpl && !s->exact) { a.x_cpl = bf(f->cplanes); a.x_cpl_plane = 256L * f->Lp; }
     a.x_rpl = bf(f->rplanes); a.x_rpl_plane = static_cast<long>(f->Lp) * p->KP;
     if (norms) { a.norm_partial = s->norm_partial; a.done_flag = s->flags + 1; }
     a.KP = p->KP; a.k = p->k; a.L = f->L; a.Lp = f->Lp;
     CUDA_TRY(admm_apply_launch(a, st(stream)));
     return 0;
+}
+
+// Gram and numerator contraction of one ADMM side, in the floating 3-plane or the exact-hi arithmetic.
+int admm_gram(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_factor* f, int side, void* stream) {
+    const size_t gsz = static_cast<size_t>(p->KP) * p->KP;
+    if (s->exact)
+        return nmfb_gram_exact(f, p->KP, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
+                               p->num_sms, stream);
+    return nmfb_gram(f, p->KP, 3, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
+                     p->num_sms, stream);
+}
+int admm_gemm(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_data* data, const nmfb_factor* other,
+              int out_Lp, void* stream) {
+    if (s->exact) {
+        if (!data->fixed) return fail(NMFB_ERR_ARG, "admm: exact mode needs fixed-point data planes");
+        return nmfb_panel_gemm_exact(data, other->cplanes, other->Lp, p->KP, p->partial, p->partial_bytes, out_Lp,
+                                     p->num_sms, stream);
+    }
+    return nmfb_panel_gemm(data, other->cplanes, other->Lp, p->KP, 3, p->partial, p->partial_bytes, out_Lp,
+                           p->num_sms, 0, 0, stream);
 }
 
 int check_prox(int prox) {
@@ -442,27 +560,27 @@ int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, 
     const size_t gsz = static_cast<size_t>(KP) * KP;
     mark(p, 0, stream);
     // h_aux = (W_aux^T W_aux + rho I)^-1 (W_aux^T V + rho (H + U_h))               admm.py:295
-    if ((rc = nmfb_gram(&s->w_aux, KP, 3, p->partial, p->partial_bytes, p->gram32, p->gram64, p->num_sms, stream)) < 0) return rc;
+    if ((rc = admm_gram(p, s, &s->w_aux, 0, stream)) < 0) return rc;
     if ((rc = nmfb_chol_inverse(p->gram64, p->k, KP, 0, rho, s->chol_scratch, s->ainv, s->scal, s->flags, stream)) < 0) return rc;
     mark(p, 1, stream);
-    int slots = nmfb_panel_gemm(&p->v_cols, s->w_aux.cplanes, s->w_aux.Lp, KP, 3, p->partial, p->partial_bytes,
-                                p->h.Lp, p->num_sms, 0, 0, stream);
+    int slots = admm_gemm(p, s, &p->v_cols, &s->w_aux, p->h.Lp, stream);
     if (slots < 0) return slots;
     mark(p, 2, stream);
     // + h = prox(h_aux, U_h), U_h += h - h_aux                                      admm.py:299,320
     if ((rc = admm_apply(p, s, p->partial, slots, false, 0, &p->h, s->dual_h, &s->h_aux, lambda_h, prox_h, false,
                          false, stream)) < 0) return rc;
+    if (s->exact && (rc = nmfb_fixed_planes(KP, &s->h_aux, stream)) < 0) return rc;
     mark(p, 3, stream);
     // w_aux with the NEW h_aux                                                      admm.py:296-297
-    if ((rc = nmfb_gram(&s->h_aux, KP, 3, p->partial, p->partial_bytes, p->gram32 + gsz, p->gram64 + gsz, p->num_sms, stream)) < 0) return rc;
+    if ((rc = admm_gram(p, s, &s->h_aux, 1, stream)) < 0) return rc;
     if ((rc = nmfb_chol_inverse(p->gram64 + gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + gsz, s->scal + 1, s->flags, stream)) < 0) return rc;
     mark(p, 4, stream);
-    slots = nmfb_panel_gemm(&p->v_rows, s->h_aux.cplanes, s->h_aux.Lp, KP, 3, p->partial, p->partial_bytes,
-                            p->w.Lp, p->num_sms, 0, 0, stream);
+    slots = admm_gemm(p, s, &p->v_rows, &s->h_aux, p->w.Lp, stream);
     if (slots < 0) return slots;
     mark(p, 5, stream);
     if ((rc = admm_apply(p, s, p->partial, slots, false, 1, &p->w, s->dual_w, &s->w_aux, lambda_w, prox_w, false,
                          false, stream)) < 0) return rc;
+    if (s->exact && (rc = nmfb_fixed_planes(KP, &s->w_aux, stream)) < 0) return rc;
     mark(p, 6, stream);
     if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // admm.py:324
     CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
@@ -488,13 +606,11 @@ int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_i
         const float lambda = side == 0 ? lambda_h : lambda_w;
         const int prox = side == 0 ? prox_h : prox_w;
         CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
-        if ((rc = nmfb_gram(other, KP, 3, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
-                            p->num_sms, stream)) < 0) return rc;
+        if ((rc = admm_gram(p, s, other, side, stream)) < 0) return rc;
         if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
                                     s->scal + side, s->flags, stream)) < 0) return rc;
         mark(p, 1 + 3 * side, stream);
-        const int slots = nmfb_panel_gemm(data, other->cplanes, other->Lp, KP, 3, p->partial, p->partial_bytes,
-                                          self->Lp, p->num_sms, 0, 0, stream);
+        const int slots = admm_gemm(p, s, data, other, self->Lp, stream);
         if (slots < 0) return slots;
         mark(p, 2 + 3 * side, stream);
         for (int it = 0; it < admm_iter; ++it) {
@@ -502,6 +618,7 @@ int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_i
                                  prox, true, true, stream)) < 0) return rc;
             CUDA_TRY(admm_inner_flag_launch(s->norm_partial, self->Lp / 64, s->flags, 2 + side, st(stream)));
         }
+        if (s->exact && (rc = nmfb_fixed_planes(KP, self, stream)) < 0) return rc;
         mark(p, 3 + 3 * side, stream);
     }
     if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // ao_admm.py:291

@@ -21,7 +21,8 @@ __global__ void __launch_bounds__(256)
 ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, int ncols,
                    __nv_bfloat16* __restrict__ rowp, long rowp_plane, int rowp_rows_p,
                    __nv_bfloat16* __restrict__ colp, long colp_plane, int colp_rows_p, int nv,
-                   unsigned int* __restrict__ stats) {
+                   unsigned int* __restrict__ stats, const unsigned int* __restrict__ rowmax,
+                   const unsigned int* __restrict__ colmax) {
     __shared__ float tile[64][65];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;      // 64 x 4
     const int c0 = blockIdx.x * 64, r0 = blockIdx.y * 64;
@@ -35,11 +36,20 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
             vmin = fminf(vmin, x);
             if (!isfinite(x)) bad = 1;
             __nv_bfloat16 hi, lo;
-            split2(x, hi, lo);
+            if (rowmax != nullptr) {                       // fixed-point plane 0 + floating remainder
+                float u, iu;
+                fixed_unit(rowmax[row0 + r], u, iu);
+                const float v0 = fixed_slice(x, u, iu), rem = x - v0;
+                hi = __float2bfloat16_rn(v0);
+                lo = __float2bfloat16_rn(rem);
+                if (__bfloat162float(lo) != rem) need_lo = 1;          // two planes do not hold x exactly
+            } else {
+                split2(x, hi, lo);
+                if (__bfloat162float(lo) != 0.f) need_lo = 1;
+            }
             const long o = blocked_index(row0 + r, c, rowp_rows_p);
             rowp[o] = hi;
             if (nv > 1) rowp[rowp_plane + o] = lo;
-            if (__bfloat162float(lo) != 0.f) need_lo = 1;
         }
         tile[rr][tx] = x;
     }
@@ -48,7 +58,17 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
         const int c = c0 + cc, r = r0 + tx;
         if (r < nrows && c < ncols) {
             __nv_bfloat16 hi, lo;
-            split2(tile[tx][cc], hi, lo);
+            const float x = tile[tx][cc];
+            if (colmax != nullptr) {
+                float u, iu;
+                fixed_unit(colmax[c], u, iu);
+                const float v0 = fixed_slice(x, u, iu), rem = x - v0;
+                hi = __float2bfloat16_rn(v0);
+                lo = __float2bfloat16_rn(rem);
+                if (__bfloat162float(lo) != rem) need_lo = 1;
+            } else {
+                split2(x, hi, lo);
+            }
             const long o = blocked_index(c, row0 + r, colp_rows_p);
             colp[o] = hi;
             if (nv > 1) colp[colp_plane + o] = lo;
@@ -72,17 +92,17 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
 cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
                                __nv_bfloat16* rowp, long rowp_plane, int rowp_rows_p, __nv_bfloat16* colp,
                                long colp_plane, int colp_rows_p, int nv, unsigned int* stats,
-                               cudaStream_t stream) {
+                               const unsigned int* rowmax, const unsigned int* colmax, cudaStream_t stream) {
     dim3 grid((ncols + 63) / 64, (nrows + 63) / 64);
     if (grid.x == 0 || grid.y == 0) return cudaSuccess;
     if (is_f64)
         ingest_data_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(src), src_ld, row0,
                                                             nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
-                                                            colp_plane, colp_rows_p, nv, stats);
+                                                            colp_plane, colp_rows_p, nv, stats, rowmax, colmax);
     else
         ingest_data_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), src_ld, row0,
                                                            nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
-                                                           colp_plane, colp_rows_p, nv, stats);
+                                                           colp_plane, colp_rows_p, nv, stats, rowmax, colmax);
     count_launch();
     return cudaGetLastError();
 }
@@ -379,6 +399,90 @@ cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int v_
     dim3 grid((n + 63) / 64, (m + 63) / 64);
     *nparts = static_cast<int>(grid.x * grid.y);
     objective_simt_kernel<<<grid, 256, 0, stream>>>(vpl, v_plane, v_rows_p, nv, wt, Mp, ht, Np, k, m, n, partial);
+    count_launch();
+    return cudaGetLastError();
+}
+
+
+// ------------------------------------------------------------------ row / column |max| of a V chunk
+// rowmax[row0 + r], colmax[c] = max |x| as float bits (monotone for non-negative floats).
+template <typename T>
+__global__ void __launch_bounds__(256)
+data_absmax_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, int ncols,
+                   unsigned int* __restrict__ rowmax, unsigned int* __restrict__ colmax) {
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int c = blockIdx.x * 64 + tx, r0 = blockIdx.y * 64;
+    unsigned int cm = 0;
+    for (int rr = ty; rr < 64; rr += 4) {
+        const int r = r0 + rr;
+        unsigned int b = 0;
+        if (r < nrows && c < ncols)
+            b = __float_as_uint(fabsf(static_cast<float>(src[static_cast<long>(r) * src_ld + c])));
+        cm = max(cm, b);
+        unsigned int rm = b;
+        for (int o = 16; o; o >>= 1) rm = max(rm, __shfl_xor_sync(0xffffffffu, rm, o));
+        if ((threadIdx.x & 31) == 0 && r < nrows) atomicMax(&rowmax[row0 + r], rm);
+    }
+    if (c < ncols) atomicMax(&colmax[c], cm);
+}
+
+cudaError_t data_absmax_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
+                               unsigned int* rowmax, unsigned int* colmax, cudaStream_t stream) {
+    dim3 grid((ncols + 63) / 64, (nrows + 63) / 64);
+    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
+    if (is_f64)
+        data_absmax_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(src), src_ld, row0, nrows,
+                                                            ncols, rowmax, colmax);
+    else
+        data_absmax_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), src_ld, row0, nrows,
+                                                           ncols, rowmax, colmax);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ fixed-point factor planes
+// One block per component row: |max| of master[c][0..Lp) by shuffles, then cplanes = (fixed slice,
+// bf16 remainder, bf16 second remainder).  Operands of the exact-mode panel GEMM / Gram.
+__global__ void __launch_bounds__(256)
+fixed_planes_kernel(const float* __restrict__ master, int Lp, __nv_bfloat16* __restrict__ cpl, long cpl_plane) {
+    __shared__ unsigned int red[8];
+    const float* rowp = master + static_cast<long>(blockIdx.x) * Lp;
+    unsigned int m = 0;
+    for (int i = threadIdx.x * 4; i < Lp; i += 1024) {
+        const float4 v = *reinterpret_cast<const float4*>(rowp + i);
+        m = max(max(__float_as_uint(fabsf(v.x)), __float_as_uint(fabsf(v.y))),
+                max(max(__float_as_uint(fabsf(v.z)), __float_as_uint(fabsf(v.w))), m));
+    }
+    for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = 0;
+    for (int w = 0; w < 8; ++w) m = max(m, red[w]);
+    float u, iu;
+    fixed_unit(m, u, iu);
+    __nv_bfloat16* out = cpl + static_cast<long>(blockIdx.x) * Lp;
+    for (int i = threadIdx.x * 4; i < Lp; i += 1024) {
+        const float4 v = *reinterpret_cast<const float4*>(rowp + i);
+        const float x[4] = {v.x, v.y, v.z, v.w};
+        __align__(8) __nv_bfloat16 p0[4], p1[4], p2[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float a0 = fixed_slice(x[q], u, iu);
+            float rem = x[q] - a0;
+            p0[q] = __float2bfloat16_rn(a0);
+            p1[q] = __float2bfloat16_rn(rem);
+            rem -= __bfloat162float(p1[q]);
+            p2[q] = __float2bfloat16_rn(rem);
+        }
+        *reinterpret_cast<uint2*>(out + i) = *reinterpret_cast<const uint2*>(p0);
+        *reinterpret_cast<uint2*>(out + cpl_plane + i) = *reinterpret_cast<const uint2*>(p1);
+        *reinterpret_cast<uint2*>(out + 2 * cpl_plane + i) = *reinterpret_cast<const uint2*>(p2);
+    }
+}
+
+cudaError_t fixed_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
+                                cudaStream_t stream) {
+    fixed_planes_kernel<<<KP, 256, 0, stream>>>(master, Lp, cpl, cpl_plane);
     count_launch();
     return cudaGetLastError();
 }

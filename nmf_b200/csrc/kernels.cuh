@@ -46,6 +46,9 @@ int panel_gemm_plan(int KP, int NB, int NA, int L, int R, int force_bn, int forc
                     PanelGemmPlan* plan);
 cudaError_t panel_gemm_launch(const PanelGemmArgs& args, const PanelGemmPlan& plan, int num_sms,
                               cudaStream_t stream);
+// exact-hi variant (panel_gemm_exact.cu): NB = 3 fixed-point factor planes, NA >= 2 fixed-point data planes
+int panel_gemm_exact_plan(int KP, int NA, int L, int R, int blocked, int num_sms, PanelGemmPlan* plan);
+cudaError_t panel_gemm_exact_launch(const PanelGemmArgs& args, const PanelGemmPlan& plan, cudaStream_t stream);
 
 // ------------------------------------------------------------------ residual objective (residual.cu)
 struct alignas(64) ResidualArgs {

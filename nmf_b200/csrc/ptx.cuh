@@ -226,4 +226,21 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& p0, __nv_bfloat16
     p2 = __float2bfloat16_rn(r);
 }
 
+// ------------------------------------------------------------------ fixed-point first plane
+// "Exact" mode of the ADMM contractions: plane 0 of an operand row is x rounded to a multiple of
+// u = 2^(E-6), E = exponent of the row's largest magnitude, i.e. an integer of at most 128 units.
+// Products of two such planes are integers of at most 2^14 units, so the tensor core's fp32
+// accumulator adds up to 512 of them without rounding.  The remainder x - plane0 goes to ordinary
+// floating planes.
+__device__ __forceinline__ void fixed_unit(unsigned int absmax_bits, float& unit, float& inv_unit) {
+    int e = static_cast<int>(absmax_bits >> 23);            // biased exponent of the row maximum
+    if (e < 16) e = 16;                                     // all-zero / denormal rows: any unit works
+    if (e > 240) e = 240;
+    unit = __uint_as_float(static_cast<unsigned int>(e - 6) << 23);
+    inv_unit = __uint_as_float(static_cast<unsigned int>(254 - (e - 6)) << 23);
+}
+__device__ __forceinline__ float fixed_slice(float x, float unit, float inv_unit) {
+    return rintf(x * inv_unit) * unit;
+}
+
 }  // namespace nmfb

@@ -90,6 +90,7 @@ class Engine:
             self.scalars = torch.zeros(64, dtype=torch.float64, device=self.device)
             self.ksum = torch.zeros((2, self.KP), dtype=torch.float64, device=self.device)
         self.nv = 0
+        self.fixed = False                    # plane 0 of V is the fixed-point slice (exact-mode ADMM)
         self.v_rows = None
         self.v_cols = None
         self.vmin = None
@@ -151,9 +152,9 @@ class Engine:
 
     def _data_structs(self) -> Tuple[Data, Data]:
         vr = Data(self.v_rows.data_ptr(), self.row_range[1] - self.row_range[0], self.n, self.per_m, self.Np,
-                  self.nv, 1)
+                  self.nv, 1, int(self.fixed))
         vc = Data(self.v_cols.data_ptr(), self.col_range[1] - self.col_range[0], self.m, self.per_n, self.Mp,
-                  self.nv, 1)
+                  self.nv, 1, int(self.fixed))
         return vr, vc
 
     def problem(self) -> Problem:
@@ -181,24 +182,58 @@ class Engine:
         p.n_phase_events = len(events)
 
     # ------------------------------------------------------------------ data in
-    def _ingest_pass(self, v: np.ndarray):
-        vr, vc = self._data_structs()
+    # chunk-wise ingest (host arrays and on-device synthetic data share it)
+    def begin_ingest(self, nv: int, fixed: bool = False):
+        if self.world != 1:
+            raise NotImplementedError("ingest kernels serve unsharded engines; shards use store_block")
+        self.fixed = bool(fixed)
+        self._alloc_data(max(nv, 2) if fixed else nv)
         self.stats.copy_(torch.tensor([-1, 0, 0, 0], dtype=torch.int32))
-        is_f64 = 1 if v.dtype == np.float64 else 0
-        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
-        for r0 in range(0, self.m, rows_per):
-            r1 = min(self.m, r0 + rows_per)
-            chunk = torch.from_numpy(v[r0:r1]).to(self.device, non_blocking=False)
-            check(self.lib.nmfb_ingest_data(chunk.data_ptr(), is_f64, chunk.stride(0), r0, r1 - r0,
+        if fixed:
+            self.rowmax = torch.zeros(self.Mp, dtype=torch.int32, device=self.device)
+            self.colmax = torch.zeros(self.Np, dtype=torch.int32, device=self.device)
+
+    def absmax_chunk(self, chunk: torch.Tensor, r0: int):
+        """Pass 1 of a fixed-point ingest: fold |max| of rows r0.. of V into the row / column maxima."""
+        check(self.lib.nmfb_data_absmax(chunk.data_ptr(), 1 if chunk.dtype == torch.float64 else 0, chunk.stride(0),
+                                        r0, chunk.shape[0], self.n, self.rowmax.data_ptr(), self.colmax.data_ptr(),
+                                        self.stream))
+
+    def ingest_chunk(self, chunk: torch.Tensor, r0: int):
+        vr, vc = self._data_structs()
+        is64 = 1 if chunk.dtype == torch.float64 else 0
+        if self.fixed:
+            check(self.lib.nmfb_ingest_data_fixed(chunk.data_ptr(), is64, chunk.stride(0), r0, chunk.shape[0],
+                                                  C.byref(vr), C.byref(vc), self.stats.data_ptr(),
+                                                  self.rowmax.data_ptr(), self.colmax.data_ptr(), self.stream))
+        else:
+            check(self.lib.nmfb_ingest_data(chunk.data_ptr(), is64, chunk.stride(0), r0, chunk.shape[0],
                                             C.byref(vr), C.byref(vc), self.stats.data_ptr(), self.stream))
-            del chunk
+
+    def finish_ingest(self):
         st = self.stats.cpu().numpy().view(np.uint32)
         return _key_to_float(int(st[0])), bool(st[1]), bool(st[2])
 
-    def upload_data(self, v: np.ndarray, planes: Optional[int] = None) -> float:
+    def _host_chunks(self, v: np.ndarray):
+        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
+        for r0 in range(0, self.m, rows_per):
+            r1 = min(self.m, r0 + rows_per)
+            yield r0, torch.from_numpy(v[r0:r1]).to(self.device, non_blocking=False)
+
+    def _ingest_pass(self, v: np.ndarray, nv: int, fixed: bool = False):
+        self.begin_ingest(nv, fixed)
+        if fixed:
+            for r0, chunk in self._host_chunks(v):
+                self.absmax_chunk(chunk, r0)
+        for r0, chunk in self._host_chunks(v):
+            self.ingest_chunk(chunk, r0)
+        return self.finish_ingest()
+
+    def upload_data(self, v: np.ndarray, planes: Optional[int] = None, fixed: bool = False) -> float:
         """Copy the caller's V (host, fp32/fp64) to HBM as bf16 planes of V and V^T.
-        Tries the single lossless plane first and re-ingests with a lo plane only when the data is
-        not bf16-exact.  Returns min(V)."""
+        Default: the single lossless plane when V is bf16-exact, hi + lo planes otherwise.
+        fixed=True (ADMM / AO-ADMM): fixed-point plane + remainder for the exact-hi contractions; falls
+        back to the floating planes when two planes cannot hold the data exactly.  Returns min(V)."""
         if v.ndim != 2 or v.shape != (self.m, self.n):
             raise ValueError(f"data must be a 2-D array of shape {(self.m, self.n)}")
         if v.dtype not in (np.float32, np.float64):
@@ -207,11 +242,16 @@ class Engine:
             v = np.ascontiguousarray(v)
         if self.world > 1:
             return self._upload_sharded(v)
-        self._alloc_data(planes or 1)
-        vmin, need_lo, bad = self._ingest_pass(v)
+        if fixed:
+            vmin, inexact, bad = self._ingest_pass(v, 2, fixed=True)
+            if not inexact:
+                if bad:
+                    raise ValueError("data contains non-finite values")
+                self.vmin = vmin
+                return vmin
+        vmin, need_lo, bad = self._ingest_pass(v, planes or 1)
         if need_lo and planes is None:
-            self._alloc_data(2)
-            vmin, need_lo, bad = self._ingest_pass(v)
+            vmin, need_lo, bad = self._ingest_pass(v, 2)
         if bad:
             raise ValueError("data contains non-finite values")
         self.vmin = vmin
@@ -289,6 +329,10 @@ class Engine:
         check(self.lib.nmfb_mur_eu_step(C.byref(p), float(lambda_w), float(lambda_h), out, self.stream))
 
     # ------------------------------------------------------------------ ADMM / AO-ADMM state
+    def _fixed_planes(self, fac: "FactorBuffers"):
+        fs = fac.struct()
+        check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
+
     def alloc_admm(self, with_aux: bool):
         """Duals (zero, admm.py:31-32 / ao_admm.py:26-27), the k x k inverse workspace and, for ADMM,
         the signed auxiliaries initialised to copies of W and H (admm.py:27-28)."""
@@ -309,13 +353,18 @@ class Engine:
                 dst.master.copy_(src.master)
                 fs = dst.struct()
                 check(self.lib.nmfb_refresh_planes(KP, C.byref(fs), self.stream))
+                if self.fixed:
+                    self._fixed_planes(dst)
             wa, ha = self.w_aux.struct(), self.h_aux.struct()
         else:
             self.w_aux = self.h_aux = None
             wa, ha = Factor(), Factor()
+            if self.fixed:                      # AO-ADMM contracts against W and H themselves
+                self._fixed_planes(self.w)
+                self._fixed_planes(self.h)
         self._admm = AdmmState(wa, ha, self.dual_w.data_ptr(), self.dual_h.data_ptr(), self.ainv.data_ptr(),
                                self.chol_scratch.data_ptr(), self.c64.data_ptr(), self.admm_scal.data_ptr(),
-                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr())
+                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(self.fixed))
 
     def admm_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
         p = self.problem()
