@@ -54,6 +54,8 @@ typedef struct nmfb_data {          /* V (rows = m, cols = n) or V^T (rows = n, 
     int blocked;                    /* 1: K-blocked layout (V, V^T); 0: plain row-major           */
     int fixed;                      /* 1: plane 0 is the fixed-point slice of each row (exact-mode   */
                                     /*    ADMM contractions), planes 1.. the floating remainder       */
+    int origin;                     /* sharded runs: global index (row of V, or column of V for V^T) of   */
+                                    /* local row 0 of these planes; 0 otherwise                           */
 } nmfb_data;
 
 typedef struct nmfb_factor {        /* W (L = m) or H (L = n) */

@@ -24,7 +24,7 @@ P = C.POINTER
 
 class Data(C.Structure):            # struct nmfb_data
     _fields_ = [("planes", c_void_p), ("rows", c_int), ("cols", c_int), ("rows_p", c_int),
-                ("ld", c_int), ("nv", c_int), ("blocked", c_int), ("fixed", c_int)]
+                ("ld", c_int), ("nv", c_int), ("blocked", c_int), ("fixed", c_int), ("origin", c_int)]
 
 
 class Factor(C.Structure):          # struct nmfb_factor

@@ -144,14 +144,16 @@ int ingest_common(const void* src, int src_is_f64, long src_ld, int row0, int nr
                   const nmfb_data* vc, uint32_t* stats, const uint32_t* rowmax, const uint32_t* colmax,
                   void* stream) {
     if (!src || !vr || !vc || !stats) return fail(NMFB_ERR_ARG, "ingest_data: null argument");
-    if (vr->rows != vc->cols || vr->cols != vc->rows || vr->nv != vc->nv)
+    // v_rows holds rows [origin, origin + rows) of V over all n columns, v_cols columns [origin, origin + rows)
+    // over all m rows (origin = 0 and rows = m / n when the run is not sharded)
+    if (vr->origin + vr->rows > vc->cols || vc->origin + vc->rows > vr->cols || vr->nv != vc->nv)
         return fail(NMFB_ERR_ARG, "ingest_data: v_rows / v_cols shapes disagree");
-    if (row0 < 0 || row0 + nrows > vr->rows) return fail(NMFB_ERR_ARG, "ingest_data: row range");
+    if (row0 < 0 || row0 + nrows > vc->cols) return fail(NMFB_ERR_ARG, "ingest_data: row range");
     if (!vr->blocked || !vc->blocked) return fail(NMFB_ERR_ARG, "ingest_data: data planes must be K-blocked");
     CUDA_TRY(ingest_data_launch(src, src_is_f64, src_ld, row0, nrows, vr->cols, bf(vr->planes),
                                 static_cast<long>(vr->rows_p) * vr->ld, vr->rows_p, bf(vc->planes),
                                 static_cast<long>(vc->rows_p) * vc->ld, vc->rows_p, vr->nv, stats, rowmax, colmax,
-                                st(stream)));
+                                vr->origin, vr->rows, vc->origin, vc->rows, st(stream)));
     return 0;
 }
 }  // namespace
@@ -293,7 +295,7 @@ int nmfb_gram_exact(const nmfb_factor* f, int KP, float* partial, size_t partial
         return nmfb_gram(f, KP, 2, partial, partial_bytes, gram32, gram64, num_sms, stream);
     nmfb_data d;
     d.planes = f->cplanes;
-    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 3; d.blocked = 0; d.fixed = 1;
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = 3; d.blocked = 0; d.fixed = 1; d.origin = 0;
     const int slots = nmfb_panel_gemm_exact(&d, f->cplanes, f->Lp, KP, partial, partial_bytes, 256, num_sms, stream);
     if (slots < 0) return slots;
     CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
@@ -307,7 +309,7 @@ int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t 
     if (KP == 256) nplanes = 2;          // 3 x 3 planes do not fit two smem stages at KP = 256
     nmfb_data d;
     d.planes = f->cplanes;
-    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0; d.fixed = 0;
+    d.rows = KP; d.cols = f->L; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0; d.fixed = 0; d.origin = 0;
     const int slots = nmfb_panel_gemm(&d, f->cplanes, f->Lp, KP, nplanes, partial, partial_bytes, 256, num_sms,
                                       128, 0, stream);
     if (slots < 0) return slots;
@@ -440,40 +442,49 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
 }
 
 namespace {
-// One side of the KL update: X (rows of `data`) <- KL rule with the other factor Y.
+// One side of the KL update: X (rows of `data`) <- KL rule with the other factor Y.  In a sharded run
+// `data` holds this rank's rows only and the window of X is updated.
 int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, const nmfb_factor* y,
             double* ysum, float lambda, void* stream) {
     const int KP = p->KP;
+    const Window w = window_of(x);
     KlPlan pl;
     if (kl_plan(KP, data->nv, data->rows, data->cols, p->num_sms, &pl) != 0)
         return fail(NMFB_ERR_ARG, "mur_kl: unsupported configuration KP=%d nv=%d (k <= 128 in this build)", KP, data->nv);
     const size_t need = static_cast<size_t>(pl.slots) * KP * x->Lp * 4;
     if (need > p->partial_bytes)
         return fail(NMFB_ERR_WORKSPACE, "mur_kl: partial workspace %zu < %zu bytes", p->partial_bytes, need);
-    if (pl.npanels * 128 > x->Lp || pl.ntiles * 64 > y->Lp || pl.npanels * 128 > data->rows_p)
+    if (pl.npanels * 128 > w.wp || pl.ntiles * 64 > y->Lp || pl.npanels * 128 > data->rows_p)
         return fail(NMFB_ERR_ARG, "mur_kl: padded extents too small");
     KlArgs a;
     memset(&a, 0, sizeof(a));
     int rc;
     for (int q = 0; q < 2; ++q) {
-        if ((rc = make_map(&a.xr[q], bf(x->rplanes) + static_cast<long>(q) * x->Lp * KP, x->Lp, KP, 128))) return rc;
+        if ((rc = make_map(&a.xr[q], bf(x->rplanes) + (static_cast<long>(q) * x->Lp + w.w0) * KP, w.wp, KP, 128))) return rc;
         if ((rc = make_map(&a.yc[q], bf(y->cplanes) + static_cast<long>(q) * 256 * y->Lp, 256, y->Lp, 128))) return rc;
     }
     for (int q = 0; q < data->nv; ++q)
         if ((rc = make_map(&a.d[q], bf(data->planes) + static_cast<long>(q) * data->rows_p * data->ld,
                            static_cast<long>(data->ld / 64) * data->rows_p, 64, 128))) return rc;
-    a.out = p->partial;
+    a.out = p->partial + w.w0;
     a.KP = KP; a.Lp = x->Lp;
     a.npanels = pl.npanels; a.ntiles = pl.ntiles; a.nsplit = pl.nsplit; a.tiles_per_split = pl.tiles_per_split;
     a.d_rows_p = data->rows_p;
     CUDA_TRY(factor_rowsum_launch(y->master, KP, y->L, y->Lp, ysum, st(stream)));
     CUDA_TRY(kl_panel_launch(a, pl, data->nv, p->num_sms, st(stream)));
-    CUDA_TRY(mur_kl_update_launch(p->partial, pl.slots, ysum, x->master, bf(x->cplanes), 256L * x->Lp,
-                                  bf(x->rplanes), static_cast<long>(x->Lp) * KP, KP, p->k, x->L, x->Lp, lambda,
-                                  st(stream)));
+    CUDA_TRY(mur_kl_update_launch(p->partial + w.w0, pl.slots, ysum, x->master + w.w0, bf(x->cplanes) + w.w0,
+                                  256L * x->Lp, bf(x->rplanes) + static_cast<long>(w.w0) * KP,
+                                  static_cast<long>(x->Lp) * KP, KP, p->k, w.live, x->Lp, w.wp, lambda, st(stream)));
     return 0;
 }
 }  // namespace
+
+int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+    if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_kl_half_step: bad argument");
+    if (!p->ksum) return fail(NMFB_ERR_ARG, "mur_kl_half_step: problem.ksum workspace missing");
+    return side == 0 ? kl_side(p, &p->v_rows, &p->w, &p->h, p->ksum, lambda, stream)             // mur.py:122
+                     : kl_side(p, &p->v_cols, &p->h, &p->w, p->ksum + p->KP, lambda, stream);    // mur.py:123
+}
 
 int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
     if (!p) return fail(NMFB_ERR_ARG, "mur_kl_step: null problem");
@@ -481,9 +492,9 @@ int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
     int rc;
     // phase events: 0 start | 1 W update (V, old W.H) | 2 H update (V^T, new W) | 3 objective
     mark(p, 0, stream);
-    if ((rc = kl_side(p, &p->v_rows, &p->w, &p->h, p->ksum, lambda_w, stream)) < 0) return rc;        // mur.py:122
+    if ((rc = nmfb_mur_kl_half_step(p, 0, lambda_w, stream)) < 0) return rc;
     mark(p, 1, stream);
-    if ((rc = kl_side(p, &p->v_cols, &p->h, &p->w, p->ksum + p->KP, lambda_h, stream)) < 0) return rc; // mur.py:123
+    if ((rc = nmfb_mur_kl_half_step(p, 1, lambda_h, stream)) < 0) return rc;
     mark(p, 2, stream);
     if (obj_out && (rc = nmfb_objective_kl(p, obj_out, stream)) < 0) return rc;                       // mur.py:127
     mark(p, 3, stream);
@@ -506,20 +517,21 @@ int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* par
                int prox, bool want_cpl, bool norms, void* stream) {
     AdmmApplyArgs a;
     memset(&a, 0, sizeof(a));
-    a.part = part; a.slots = slots;
-    a.c64 = use_c64 ? s->c64 : nullptr;
+    const Window w = window_of(f);                        // sharded runs: this rank's rows of the factor only
+    a.part = part ? part + w.w0 : nullptr; a.slots = slots;
+    a.c64 = use_c64 ? s->c64 + w.w0 : nullptr;
     a.ainv = s->ainv + static_cast<size_t>(side) * p->KP * p->KP;
     a.rho = s->scal + side;
     a.lambda = lambda; a.prox = prox;
-    a.x = f->master; a.u = u;
+    a.x = f->master + w.w0; a.u = u + w.w0;
     if (aux) {
-        a.aux_master = aux->master;
-        if (!s->exact) { a.aux_cpl = bf(aux->cplanes); a.aux_cpl_plane = 256L * aux->Lp; }
+        a.aux_master = aux->master + w.w0;
+        if (!s->exact) { a.aux_cpl = bf(aux->cplanes) + w.w0; a.aux_cpl_plane = 256L * aux->Lp; }
     }
-    if (want_cpl && !s->exact) { a.x_cpl = bf(f->cplanes); a.x_cpl_plane = 256L * f->Lp; }
-    a.x_rpl = bf(f->rplanes); a.x_rpl_plane = static_cast<long>(f->Lp) * p->KP;
-    if (norms) { a.norm_partial = s->norm_partial; a.done_flag = s->flags + 1; }
-    a.KP = p->KP; a.k = p->k; a.L = f->L; a.Lp = f->Lp;
+    if (want_cpl && !s->exact) { a.x_cpl = bf(f->cplanes) + w.w0; a.x_cpl_plane = 256L * f->Lp; }
+    a.x_rpl = bf(f->rplanes) + static_cast<long>(w.w0) * p->KP; a.x_rpl_plane = static_cast<long>(f->Lp) * p->KP;
+    if (norms) { a.norm_partial = s->norm_partial + static_cast<long>(w.w0 / 64) * 4; a.done_flag = s->flags + 1; }
+    a.KP = p->KP; a.k = p->k; a.L = w.live; a.Lp = f->Lp; a.nrows_p = w.wp;
     CUDA_TRY(admm_apply_launch(a, st(stream)));
     return 0;
 }
@@ -534,13 +546,15 @@ int admm_gram(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_factor
                      p->num_sms, stream);
 }
 int admm_gemm(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_data* data, const nmfb_factor* other,
-              int out_Lp, void* stream) {
+              const nmfb_factor* self, void* stream) {
+    // sharded runs: this rank's rows of the product land at its window of the full-pitch partial
+    float* out = p->partial + window_of(self).w0;
     if (s->exact) {
         if (!data->fixed) return fail(NMFB_ERR_ARG, "admm: exact mode needs fixed-point data planes");
-        return nmfb_panel_gemm_exact(data, other->cplanes, other->Lp, p->KP, p->partial, p->partial_bytes, out_Lp,
+        return nmfb_panel_gemm_exact(data, other->cplanes, other->Lp, p->KP, out, p->partial_bytes, self->Lp,
                                      p->num_sms, stream);
     }
-    return nmfb_panel_gemm(data, other->cplanes, other->Lp, p->KP, 3, p->partial, p->partial_bytes, out_Lp,
+    return nmfb_panel_gemm(data, other->cplanes, other->Lp, p->KP, 3, out, p->partial_bytes, self->Lp,
                            p->num_sms, 0, 0, stream);
 }
 
@@ -551,40 +565,99 @@ int check_prox(int prox) {
 
 }  // namespace
 
+int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int side, double rho, float lambda,
+                        int prox, void* stream) {
+    if (!p || !s || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "admm_half_step: bad argument");
+    int rc;
+    if ((rc = check_prox(prox)) < 0) return rc;
+    const int KP = p->KP;
+    const size_t gsz = static_cast<size_t>(KP) * KP;
+    // side 0: h_aux = (W_aux^T W_aux + rho I)^-1 (W_aux^T V + rho (H + U_h))               admm.py:295
+    //         h = prox(h_aux, U_h), U_h += h - h_aux                                        admm.py:299,320
+    // side 1: the same for W^T with the NEW h_aux                                           admm.py:296-297,300,321
+    const nmfb_factor* other_aux = side == 0 ? &s->w_aux : &s->h_aux;
+    const nmfb_factor* self = side == 0 ? &p->h : &p->w;
+    const nmfb_factor* self_aux = side == 0 ? &s->h_aux : &s->w_aux;
+    const nmfb_data* data = side == 0 ? &p->v_cols : &p->v_rows;
+    float* dual = side == 0 ? s->dual_h : s->dual_w;
+    if ((rc = admm_gram(p, s, other_aux, side, stream)) < 0) return rc;
+    if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + side * gsz,
+                                s->scal + side, s->flags, stream)) < 0) return rc;
+    mark(p, 1 + 3 * side, stream);
+    const int slots = admm_gemm(p, s, data, other_aux, self, stream);
+    if (slots < 0) return slots;
+    mark(p, 2 + 3 * side, stream);
+    return admm_apply(p, s, p->partial, slots, false, side, self, dual, self_aux, lambda, prox, false, false, stream);
+}
+
+int nmfb_admm_publish(const nmfb_admm_state* s, double* mailbox, void* stream) {
+    if (!s || !mailbox) return fail(NMFB_ERR_ARG, "admm_publish: null argument");
+    CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
+    return 0;
+}
+
 int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, float lambda_w, int prox_w,
                    float lambda_h, int prox_h, double* mailbox, void* stream) {
     if (!p || !s || !mailbox) return fail(NMFB_ERR_ARG, "admm_step: null argument");
     int rc;
-    if ((rc = check_prox(prox_w)) < 0 || (rc = check_prox(prox_h)) < 0) return rc;
     const int KP = p->KP;
-    const size_t gsz = static_cast<size_t>(KP) * KP;
     mark(p, 0, stream);
-    // h_aux = (W_aux^T W_aux + rho I)^-1 (W_aux^T V + rho (H + U_h))               admm.py:295
-    if ((rc = admm_gram(p, s, &s->w_aux, 0, stream)) < 0) return rc;
-    if ((rc = nmfb_chol_inverse(p->gram64, p->k, KP, 0, rho, s->chol_scratch, s->ainv, s->scal, s->flags, stream)) < 0) return rc;
-    mark(p, 1, stream);
-    int slots = admm_gemm(p, s, &p->v_cols, &s->w_aux, p->h.Lp, stream);
-    if (slots < 0) return slots;
-    mark(p, 2, stream);
-    // + h = prox(h_aux, U_h), U_h += h - h_aux                                      admm.py:299,320
-    if ((rc = admm_apply(p, s, p->partial, slots, false, 0, &p->h, s->dual_h, &s->h_aux, lambda_h, prox_h, false,
-                         false, stream)) < 0) return rc;
+    if ((rc = nmfb_admm_half_step(p, s, 0, rho, lambda_h, prox_h, stream)) < 0) return rc;
     if (s->exact && (rc = nmfb_fixed_planes(KP, &s->h_aux, stream)) < 0) return rc;
     mark(p, 3, stream);
-    // w_aux with the NEW h_aux                                                      admm.py:296-297
-    if ((rc = admm_gram(p, s, &s->h_aux, 1, stream)) < 0) return rc;
-    if ((rc = nmfb_chol_inverse(p->gram64 + gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + gsz, s->scal + 1, s->flags, stream)) < 0) return rc;
-    mark(p, 4, stream);
-    slots = admm_gemm(p, s, &p->v_rows, &s->h_aux, p->w.Lp, stream);
-    if (slots < 0) return slots;
-    mark(p, 5, stream);
-    if ((rc = admm_apply(p, s, p->partial, slots, false, 1, &p->w, s->dual_w, &s->w_aux, lambda_w, prox_w, false,
-                         false, stream)) < 0) return rc;
+    if ((rc = nmfb_admm_half_step(p, s, 1, rho, lambda_w, prox_w, stream)) < 0) return rc;
     if (s->exact && (rc = nmfb_fixed_planes(KP, &s->w_aux, stream)) < 0) return rc;
     mark(p, 6, stream);
     if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // admm.py:324
-    CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
+    if ((rc = nmfb_admm_publish(s, mailbox, stream)) < 0) return rc;
     mark(p, 7, stream);
+    return 0;
+}
+
+namespace {
+void ao_roles(const nmfb_problem* p, const nmfb_admm_state* s, int side, const nmfb_factor** other,
+              const nmfb_factor** self, const nmfb_data** data, float** dual) {
+    // side 0: H update with a = W, y = V (ao_admm.py:261-264); side 1: W update with a = H^T, y = V^T (:265-270)
+    *other = side == 0 ? &p->w : &p->h;
+    *self = side == 0 ? &p->h : &p->w;
+    *data = side == 0 ? &p->v_cols : &p->v_rows;
+    *dual = side == 0 ? s->dual_h : s->dual_w;
+}
+}  // namespace
+
+int nmfb_aoadmm_side_begin(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream) {
+    if (!p || !s || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "aoadmm_side_begin: bad argument");
+    const nmfb_factor *other, *self; const nmfb_data* data; float* dual;
+    ao_roles(p, s, side, &other, &self, &data, &dual);
+    const int KP = p->KP;
+    const size_t gsz = static_cast<size_t>(KP) * KP;
+    int rc;
+    CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
+    if ((rc = admm_gram(p, s, other, side, stream)) < 0) return rc;                   // ao_admm.py:53-55
+    if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
+                                s->scal + side, s->flags, stream)) < 0) return rc;
+    mark(p, 1 + 3 * side, stream);
+    const int slots = admm_gemm(p, s, data, other, self, stream);                     // ao_admm.py:56
+    if (slots < 0) return slots;
+    mark(p, 2 + 3 * side, stream);
+    return slots;
+}
+
+int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side, int first, int slots,
+                      float lambda, int prox, void* stream) {
+    if (!p || !s || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "aoadmm_inner: bad argument");
+    int rc;
+    if ((rc = check_prox(prox)) < 0) return rc;
+    const nmfb_factor *other, *self; const nmfb_data* data; float* dual;
+    ao_roles(p, s, side, &other, &self, &data, &dual);
+    return admm_apply(p, s, first ? p->partial : nullptr, slots, true, side, self, dual, nullptr, lambda, prox, true,
+                      true, stream);                                                  // ao_admm.py:59-62
+}
+
+int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream) {
+    if (!p || !s || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "aoadmm_inner_flag: bad argument");
+    const nmfb_factor* self = side == 0 ? &p->h : &p->w;
+    CUDA_TRY(admm_inner_flag_launch(s->norm_partial, self->Lp / 64, s->flags, 2 + side, st(stream)));   // ao_admm.py:64
     return 0;
 }
 
@@ -595,34 +668,21 @@ int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_i
     int rc;
     if ((rc = check_prox(prox_w)) < 0 || (rc = check_prox(prox_h)) < 0) return rc;
     const int KP = p->KP;
-    const size_t gsz = static_cast<size_t>(KP) * KP;
     mark(p, 0, stream);
     for (int side = 0; side < 2; ++side) {
-        // side 0: H update with a = W, y = V (ao_admm.py:261-264); side 1: W update with a = H^T, y = V^T (:265-270)
-        const nmfb_factor* other = side == 0 ? &p->w : &p->h;
         const nmfb_factor* self = side == 0 ? &p->h : &p->w;
-        const nmfb_data* data = side == 0 ? &p->v_cols : &p->v_rows;
-        float* dual = side == 0 ? s->dual_h : s->dual_w;
-        const float lambda = side == 0 ? lambda_h : lambda_w;
-        const int prox = side == 0 ? prox_h : prox_w;
-        CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
-        if ((rc = admm_gram(p, s, other, side, stream)) < 0) return rc;
-        if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
-                                    s->scal + side, s->flags, stream)) < 0) return rc;
-        mark(p, 1 + 3 * side, stream);
-        const int slots = admm_gemm(p, s, data, other, self->Lp, stream);
+        const int slots = nmfb_aoadmm_side_begin(p, s, side, stream);
         if (slots < 0) return slots;
-        mark(p, 2 + 3 * side, stream);
         for (int it = 0; it < admm_iter; ++it) {
-            if ((rc = admm_apply(p, s, it == 0 ? p->partial : nullptr, slots, true, side, self, dual, nullptr, lambda,
-                                 prox, true, true, stream)) < 0) return rc;
-            CUDA_TRY(admm_inner_flag_launch(s->norm_partial, self->Lp / 64, s->flags, 2 + side, st(stream)));
+            if ((rc = nmfb_aoadmm_inner(p, s, side, it == 0, slots, side == 0 ? lambda_h : lambda_w,
+                                        side == 0 ? prox_h : prox_w, stream)) < 0) return rc;
+            if ((rc = nmfb_aoadmm_inner_flag(p, s, side, stream)) < 0) return rc;
         }
         if (s->exact && (rc = nmfb_fixed_planes(KP, self, stream)) < 0) return rc;
         mark(p, 3 + 3 * side, stream);
     }
     if ((rc = nmfb_objective_eu(p, 0, mailbox, stream)) < 0) return rc;               // ao_admm.py:291
-    CUDA_TRY(admm_flags_publish_launch(s->flags, mailbox, st(stream)));
+    if ((rc = nmfb_admm_publish(s, mailbox, stream)) < 0) return rc;
     mark(p, 7, stream);
     return 0;
 }

@@ -22,7 +22,10 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
                    __nv_bfloat16* __restrict__ rowp, long rowp_plane, int rowp_rows_p,
                    __nv_bfloat16* __restrict__ colp, long colp_plane, int colp_rows_p, int nv,
                    unsigned int* __restrict__ stats, const unsigned int* __restrict__ rowmax,
-                   const unsigned int* __restrict__ colmax) {
+                   const unsigned int* __restrict__ colmax, int row_lo, int row_n, int col_lo, int col_n) {
+    // Sharded runs: this rank keeps rows [row_lo, row_lo + row_n) of V in the row copy and columns
+    // [col_lo, col_lo + col_n) in the transposed copy (both stored from local index 0); the flags are
+    // folded over everything it reads, so that every rank reaches the same decisions.
     __shared__ float tile[64][65];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;      // 64 x 4
     const int c0 = blockIdx.x * 64, r0 = blockIdx.y * 64;
@@ -47,16 +50,19 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
                 split2(x, hi, lo);
                 if (__bfloat162float(lo) != 0.f) need_lo = 1;
             }
-            const long o = blocked_index(row0 + r, c, rowp_rows_p);
-            rowp[o] = hi;
-            if (nv > 1) rowp[rowp_plane + o] = lo;
+            const int lr = row0 + r - row_lo;
+            if (lr >= 0 && lr < row_n) {
+                const long o = blocked_index(lr, c, rowp_rows_p);
+                rowp[o] = hi;
+                if (nv > 1) rowp[rowp_plane + o] = lo;
+            }
         }
         tile[rr][tx] = x;
     }
     __syncthreads();
     for (int cc = ty; cc < 64; cc += 4) {
         const int c = c0 + cc, r = r0 + tx;
-        if (r < nrows && c < ncols) {
+        if (r < nrows && c < ncols && c >= col_lo && c < col_lo + col_n) {
             __nv_bfloat16 hi, lo;
             const float x = tile[tx][cc];
             if (colmax != nullptr) {
@@ -69,7 +75,7 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
             } else {
                 split2(x, hi, lo);
             }
-            const long o = blocked_index(c, row0 + r, colp_rows_p);
+            const long o = blocked_index(c - col_lo, row0 + r, colp_rows_p);
             colp[o] = hi;
             if (nv > 1) colp[colp_plane + o] = lo;
         }
@@ -92,17 +98,20 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
 cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
                                __nv_bfloat16* rowp, long rowp_plane, int rowp_rows_p, __nv_bfloat16* colp,
                                long colp_plane, int colp_rows_p, int nv, unsigned int* stats,
-                               const unsigned int* rowmax, const unsigned int* colmax, cudaStream_t stream) {
+                               const unsigned int* rowmax, const unsigned int* colmax, int row_lo, int row_n,
+                               int col_lo, int col_n, cudaStream_t stream) {
     dim3 grid((ncols + 63) / 64, (nrows + 63) / 64);
     if (grid.x == 0 || grid.y == 0) return cudaSuccess;
     if (is_f64)
         ingest_data_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(src), src_ld, row0,
                                                             nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
-                                                            colp_plane, colp_rows_p, nv, stats, rowmax, colmax);
+                                                            colp_plane, colp_rows_p, nv, stats, rowmax, colmax,
+                                                            row_lo, row_n, col_lo, col_n);
     else
         ingest_data_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(src), src_ld, row0,
                                                            nrows, ncols, rowp, rowp_plane, rowp_rows_p, colp,
-                                                           colp_plane, colp_rows_p, nv, stats, rowmax, colmax);
+                                                           colp_plane, colp_rows_p, nv, stats, rowmax, colmax,
+                                                            row_lo, row_n, col_lo, col_n);
     count_launch();
     return cudaGetLastError();
 }

@@ -7,7 +7,8 @@ namespace nmfb {
 cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
                                __nv_bfloat16* rowp, long rowp_plane, int rowp_rows_p, __nv_bfloat16* colp,
                                long colp_plane, int colp_rows_p, int nv, unsigned int* stats,
-                               const unsigned int* rowmax, const unsigned int* colmax, cudaStream_t stream);
+                               const unsigned int* rowmax, const unsigned int* colmax, int row_lo, int row_n,
+                               int col_lo, int col_n, cudaStream_t stream);
 cudaError_t data_absmax_launch(const void* src, int is_f64, long src_ld, int row0, int nrows, int ncols,
                                unsigned int* rowmax, unsigned int* colmax, cudaStream_t stream);
 cudaError_t fixed_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
