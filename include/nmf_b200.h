@@ -179,6 +179,8 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream);
  * through the fused GEMM -> quotient -> GEMM kernel (W.H never reaches HBM), row / column sums by
  * shuffle reductions, then the objective of the new pair.  k <= 128 in this build. */
 int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream);
+/* One factor update of the iteration above (side 0 = W, 1 = H); window semantics as nmfb_mur_eu_half_step. */
+int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, void* stream);
 
 /* ---- ADMM / AO-ADMM ------------------------------------------------------------------------- */
 typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1 } nmfb_prox;   /* admm.py:126-139 */
@@ -210,12 +212,34 @@ int nmfb_chol_inverse(const double* gram64, int k, int KP, int rho_mode, double 
 int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, float lambda_w, int prox_w,
                    float lambda_h, int prox_h, double* mailbox, void* stream);
 
+/* Sharded runs drive the iteration above in two halves.  side 0: h_aux / h / U_h (admm.py:295,299,320),
+ * side 1: w_aux / w / U_w with the new h_aux (admm.py:296-297,300,321); only the rank's window of the
+ * factor, its dual and its auxiliary is touched.  The caller then all-gathers the auxiliary (and the
+ * factor) masters and re-derives their planes (nmfb_refresh_planes, nmfb_fixed_planes in exact mode). */
+int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int side, double rho, float lambda,
+                        int prox, void* stream);
+/* mailbox[1], [2] = inner iterations used by the H / W update (AO-ADMM), mailbox[3] = not-PD flag. */
+int nmfb_admm_publish(const nmfb_admm_state* s, double* mailbox, void* stream);
+
 /* One outer iteration of AO-ADMM, Euclidean (ao_admm.py:261-270, 291): per factor Gram, rho = tr/k,
  * Cholesky, numerator GEMM, then up to admm_iter x (solve, prox, dual, residual test ao_admm.py:33-43)
  * with the early break decided on the device.  mailbox[0] = objective, [1] / [2] = inner iterations
  * completed without a break for H / W (== admm_iter when no break), [3] = not-PD flag. */
 int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_iter, float lambda_w,
                      int prox_w, float lambda_h, int prox_h, double* mailbox, void* stream);
+
+/* The pieces of nmfb_aoadmm_step, for sharded runs (side 0 = H update, 1 = W update):
+ *   side_begin  flags reset, Gram of the fixed factor, rho = tr/k, Cholesky inverse, numerator GEMM for the
+ *               rank's window (ao_admm.py:53-56); returns the number of partial slots
+ *   inner       one solve / prox / dual pass over the window (ao_admm.py:59-62) leaving the window's blocks of
+ *               the four norm partials in s->norm_partial; `first` != 0 reduces the GEMM slots into s->c64
+ *   inner_flag  the residual test of ao_admm.py:33-43 over ALL blocks of norm_partial (the caller all-gathers
+ *               the windows first), deciding the early break on the device
+ * After the inner loop the caller all-gathers the factor and re-derives its planes. */
+int nmfb_aoadmm_side_begin(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream);
+int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side, int first, int slots,
+                      float lambda, int prox, void* stream);
+int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream);
 
 #ifdef __cplusplus
 }

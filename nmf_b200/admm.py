@@ -27,8 +27,9 @@ def _raise_if_not_pd(i, vals):
 
 def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_iter=10,
          max_iter=100000, tol1=1e-3, tol2=1e-3, nndsvd_init=(True, 'zero'), save_dir='./results/',
-         w0=None, h0=None, verbose=True, engine=None):
-    """v: (m, n) data, k: components.  Extra (non-reference) keywords: w0 / h0, verbose, engine."""
+         w0=None, h0=None, verbose=True, engine=None, comm=None):
+    """v: (m, n) data, k: components.  Extra (non-reference) keywords: w0 / h0, verbose, engine, and
+    comm (True or a torch.distributed group: 1-D sharded run, one process per GPU)."""
     experiment = Experiment(method='admm', components=k, rho=rho, distance_type=distance_type,
                             nndsvd_init=nndsvd_init, min_iter=min_iter, max_iter=max_iter, tol1=tol1,
                             tol2=tol2, lambda_w=reg_w[0], prox_w=reg_w[1], lambda_h=reg_h[0],
@@ -42,6 +43,9 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
     v = np.asarray(v)
     m, n = v.shape
 
+    if comm is not None and engine is None:
+        engine = Engine.for_comm(m, n, k, comm)
+        verbose = verbose and engine.rank == 0
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:
         eng.upload_data(v, fixed=True)

@@ -58,7 +58,10 @@ chol_inverse_kernel(const double* __restrict__ gram, int k, int rho_mode, double
     }
     __syncthreads();
 
-    // right-looking Cholesky, lower triangle in place
+    // right-looking Cholesky, lower triangle in place.  The trailing update is tiled 32 x 32 over the
+    // 1024 threads (warp = row residue, lane = column residue): no index arithmetic in the loop, each
+    // thread touches at most (KP/32)^2 / 2 entries per step.
+    const int ty = tid >> 5, tx = tid & 31;
     for (int j = 0; j < KP; ++j) {
         const double d = a[j * lda + j];
         if (!(d > 0.0)) {                          // also catches NaN
@@ -69,13 +72,9 @@ chol_inverse_kernel(const double* __restrict__ gram, int k, int rho_mode, double
         __syncthreads();
         for (int i = j + tid; i < KP; i += 1024) a[i * lda + j] *= inv_s;     // a[j][j] -> sqrt(d)
         __syncthreads();
-        const int rem = KP - 1 - j;                // trailing block (j+1 .. KP-1)^2, lower part
-        for (int idx = tid; idx < rem * rem; idx += 1024) {
-            const int ii = idx / rem, cc = idx - ii * rem;
-            if (cc <= ii) {
-                const int i = j + 1 + ii, c = j + 1 + cc;
-                a[i * lda + c] -= a[i * lda + j] * a[c * lda + j];
-            }
+        for (int i = j + 1 + ty; i < KP; i += 32) {
+            const double lij = a[i * lda + j];
+            for (int c = j + 1 + tx; c <= i; c += 32) a[i * lda + c] -= lij * a[c * lda + j];
         }
         __syncthreads();
     }
@@ -299,7 +298,7 @@ admm_apply_kernel(const AdmmApplyArgs p) {
 }
 
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
-    const int grid = a.Lp / 64;
+    const int grid = (a.nrows_p > 0 ? a.nrows_p : a.Lp) / 64;
     const size_t smem = (static_cast<size_t>(a.KP) * 64 + 32 * static_cast<size_t>(a.KP)) * sizeof(double);
     static bool set[3] = {false, false, false};
     cudaError_t e = cudaSuccess;

@@ -27,7 +27,8 @@ struct AdmmApplyArgs {
     long x_rpl_plane;
     double* norm_partial;     // optional: [grid][4]  |x-aux|^2, |x|^2, |x-x_prev|^2, |u|^2
     const int* done_flag;     // optional: skip the launch's work when *done_flag != 0
-    int KP, k, L, Lp;
+    int KP, k, L, Lp;         // L = live rows of the window being updated, Lp = pitch of the factor
+    int nrows_p;              // padded rows of the window (grid = nrows_p / 64); 0 = Lp
 };
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream);
 

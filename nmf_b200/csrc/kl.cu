@@ -429,8 +429,8 @@ mur_kl_update_kernel(const float* __restrict__ part, int slots, const double* __
 
 cudaError_t mur_kl_update_launch(const float* part, int slots, const double* bsum, float* master,
                                  __nv_bfloat16* cpl, long cpl_plane, __nv_bfloat16* rpl, long rpl_plane,
-                                 int KP, int k, int L, int Lp, float lambda, cudaStream_t stream) {
-    const int grid = Lp / 64;
+                                 int KP, int k, int L, int Lp, int nrows_p, float lambda, cudaStream_t stream) {
+    const int grid = nrows_p / 64;
     if (KP == 64)
         mur_kl_update_kernel<4><<<grid, 256, 0, stream>>>(part, slots, bsum, master, cpl, cpl_plane, rpl, rpl_plane, k, L, Lp, lambda);
     else if (KP == 128)

@@ -29,6 +29,6 @@ cudaError_t factor_rowsum_launch(const float* master, int KP, int L, int Lp, dou
 // x <- 2a / (b + sqrt(b^2 + 4 lambda a)),  a = x * sum_slots(part),  b = bsum[c]     (mur.py:25-27, 41-43)
 cudaError_t mur_kl_update_launch(const float* part, int slots, const double* bsum, float* master,
                                  __nv_bfloat16* cpl, long cpl_plane, __nv_bfloat16* rpl, long rpl_plane,
-                                 int KP, int k, int L, int Lp, float lambda, cudaStream_t stream);
+                                 int KP, int k, int L, int Lp, int nrows_p, float lambda, cudaStream_t stream);
 
 }  // namespace nmfb

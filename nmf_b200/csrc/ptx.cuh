@@ -124,6 +124,13 @@ __device__ __forceinline__ void umma_commit_mcast(uint64_t* bar, uint16_t cta_ma
         "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
         ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
 }
+__device__ __forceinline__ void umma_commit_mcast_warp(uint64_t* bar, uint16_t cta_mask) {   // whole warp
+    asm volatile(
+        "{\n\t.reg .pred e;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}\n"
+        ::"r"(smem_u32(bar)), "h"(cta_mask) : "memory");
+}
 
 // ------------------------------------------------------------------ tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, uint32_t ncols) {   // whole warp
@@ -143,6 +150,35 @@ __device__ __forceinline__ void tc_fence_before() {
 __device__ __forceinline__ void tc_fence_after() {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
+// Warp index as a value the compiler KNOWS is warp-uniform (threadIdx.x >> 5 alone is not): needed for the
+// uniform-datapath code generation of the whole-warp MMA loops below.
+__device__ __forceinline__ int warp_idx_uniform() {
+    return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+}
+
+// Whole-warp forms of MMA issue and commit: EVERY lane of the (converged) MMA warp executes the call with
+// warp-uniform operands and one elected lane issues the instruction.  Issuing from inside an
+// `if (lane == 0)` region instead makes ptxas wrap every tcgen05.mma in an ELECT / R2UR.BROADCAST /
+// BRA.U.ANY waterfall loop (~11 SASS instructions and ~130 cycles per MMA, measured with ncu on the
+// residual kernel: the issuing thread, not the tensor pipe, set the pace at 49 % pipe activity).
+__device__ __forceinline__ void umma_bf16_warp(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                               uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_warp(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred e;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n"
+        ::"r"(smem_u32(bar)) : "memory");
+}
+
 // D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate; issued by ONE thread.
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
                                           uint32_t idesc, uint32_t accumulate) {
@@ -242,5 +278,23 @@ __device__ __forceinline__ void fixed_unit(unsigned int absmax_bits, float& unit
 __device__ __forceinline__ float fixed_slice(float x, float unit, float inv_unit) {
     return rintf(x * inv_unit) * unit;
 }
+
+// v*log(v/s) - v + s (utils.py:23-26; +inf / NaN of the log term map to 0) without the cancellation
+// of the naive form: with d = (v - s)/s the term is s*((1+d)*log1p(d) - d) = s*d^2*(1/2 - d/6 + ...).
+__device__ __forceinline__ float kl_term(float v, float s) {
+    const float d = __fdividef(v - s, s);
+    float r;
+    if (fabsf(d) < 0.125f) {
+        const float p = 0.5f + d * (-1.f / 6.f + d * (1.f / 12.f + d * (-1.f / 20.f + d * (1.f / 30.f +
+                        d * (-1.f / 42.f + d * (1.f / 56.f + d * (-1.f / 72.f)))))));
+        r = s * d * d * p;
+    } else {
+        r = v * __logf(__fdividef(v, s)) - v + s;  // no cancellation to speak of out here
+    }
+    if (v == 0.f) r = s;                           // 0*log(0/s) = NaN -> 0
+    if (s == 0.f) r = -v;                          // v*log(v/0) = +inf -> 0 (and 0/0 -> NaN -> 0)
+    return r;
+}
+
 
 }  // namespace nmfb

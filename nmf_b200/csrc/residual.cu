@@ -9,15 +9,19 @@
 //
 // One CTA walks a contiguous run of 128x128 tiles in row-major tile order.  The W planes of the
 // current tile row stay resident in shared memory; H^T planes stream through a ring of 64-wide
-// K-chunks; V tiles are double-buffered.  warp 0 = TMA producer, warp 1 = MMA issuer, warps
-// 2..9 = eight epilogue warps (two per TMEM lane quarter, 64 columns each).
+// K-chunks; V tiles are double-buffered.  warp 0 = TMA producer of the factor planes, warps 1 and 11 =
+// MMA issuers (even / odd tiles of the CTA's run, one TMEM accumulator each: two instruction streams,
+// because one stream needs ~50 issue cycles per 64-cycle MMA), warps 2..9 = eight epilogue warps (two
+// per TMEM lane quarter, 64 columns each), warp 10 = TMA producer of the V tiles.  The two producers are separate threads on purpose: a V buffer frees
+// only when the epilogue of tile t-2 is done, and a single producer waiting for it would also hold back
+// the H^T stages of tile t, i.e. stall the MMA pipe (measured: 49 % tensor-pipe activity).
 #include "kernels.cuh"
 #include "ptx.cuh"
 
 namespace nmfb {
 
 namespace {
-constexpr int kThreadsR = 320;
+constexpr int kThreadsR = 384;
 constexpr int kBox = 128 * 128;      // bytes of one [128 rows x 64 bf16] box
 constexpr int kPrefetchTiles = 6;    // L2 prefetch distance of the V stream, in 128 x 128 tiles
 
@@ -52,23 +56,6 @@ int residual_smem_bytes(int KP, int NV, int BN) {
 
 // Compile-time <KCH = KP / 64, NV>: the single MMA-issuing thread must not spend its time computing
 // loop bounds and descriptor fields (see panel_gemm.cu).
-// v*log(v/s) - v + s (utils.py:23-26; +inf / NaN of the log term map to 0) without the cancellation
-// of the naive form: with d = (v - s)/s the term is s*((1+d)*log1p(d) - d) = s*d^2*(1/2 - d/6 + ...).
-__device__ __forceinline__ float kl_term(float v, float s) {
-    const float d = __fdividef(v - s, s);
-    float r;
-    if (fabsf(d) < 0.125f) {
-        const float p = 0.5f + d * (-1.f / 6.f + d * (1.f / 12.f + d * (-1.f / 20.f + d * (1.f / 30.f +
-                        d * (-1.f / 42.f + d * (1.f / 56.f + d * (-1.f / 72.f)))))));
-        r = s * d * d * p;
-    } else {
-        r = v * __logf(__fdividef(v, s)) - v + s;  // no cancellation to speak of out here
-    }
-    if (v == 0.f) r = s;                           // 0*log(0/s) = NaN -> 0
-    if (s == 0.f) r = -v;                          // v*log(v/0) = +inf -> 0 (and 0/0 -> NaN -> 0)
-    return r;
-}
-
 template <int KCH, int NV>
 __global__ void __launch_bounds__(kThreadsR, 1)
 residual_kernel(const __grid_constant__ ResidualArgs args) {
@@ -93,7 +80,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
     double* red = reinterpret_cast<double*>(bars + 20);      // [8]
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
     // Clusters of CS CTAs walk "super rows" of CS adjacent row tiles in lockstep over the same column
     // tiles, so the H^T stage every one of them needs is fetched once per cluster (each CTA loads
     // 1/CS of it and multicasts): the kernel is bound by L2 output otherwise (3 x |V| of L2 reads).
@@ -115,7 +102,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
             mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8);
         }
         mbar_init(a_full, 1);
-        mbar_init(a_empty, 1);
+        mbar_init(a_empty, 2);
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
@@ -129,7 +116,6 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
         if (lane == 0) {
             const int srow = 128 / CS;
             int bs = 0; uint32_t bph = 0;
-            int vs = 0; uint32_t vph = 0;
             uint32_t aph = 0;
             int cur_i = -1;
             for (long t = t_begin; t < t_end; ++t) {
@@ -146,27 +132,6 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                     aph ^= 1;
                     cur_i = sr;
                 }
-                // pull the V tile of a later step into L2: only two V buffers fit in shared memory, far
-                // too few bytes in flight to cover HBM latency on their own
-                {
-                    const long tp = t + kPrefetchTiles;
-                    if (tp < t_end) {
-                        const int srp = static_cast<int>(tp / args.ntiles);
-                        const int tjp = static_cast<int>(tp - static_cast<long>(srp) * args.ntiles);
-                        const int tip = min(srp * CS + static_cast<int>(crank), args.mtiles - 1);
-                        for (int p = 0; p < NV; ++p)
-                            for (int hb = 0; hb < 2; ++hb)
-                                tma_prefetch_2d(&args.v[p], 0, (tjp * 2 + hb) * args.v_rows_p + tip * 128);
-                    }
-                }
-                // V tile
-                mbar_wait(&v_empty[vs], vph ^ 1);
-                mbar_expect_tx(&v_full[vs], L.v_buf_bytes);
-                for (int p = 0; p < NV; ++p)
-                    for (int hb = 0; hb < 2; ++hb)
-                        tma_load_2d_hint(v_smem + vs * L.v_buf_bytes + (p * 2 + hb) * kBox, &args.v[p],
-                                         &v_full[vs], 0, (tj * 2 + hb) * args.v_rows_p + ti * 128, kPolicyEvictFirst);
-                if (++vs == L.nvs) { vs = 0; vph ^= 1; }
                 // H^T chunks
                 for (int kc = 0; kc < kchunks; ++kc) {
                     mbar_wait(&b_empty[bs], bph ^ 1);
@@ -183,29 +148,38 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                 }
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
-            const uint64_t desc0 = umma_desc_k_sw128(0);
-            int bs = 0; uint32_t bph = 0;
-            int acc = 0; uint32_t accph = 0;
-            uint32_t aph = 0;
-            int cur_i = -1;
-            const uint64_t a_desc = desc0 + (smem_u32(a_smem) >> 4);
-            const uint32_t b_addr = smem_u32(b_smem);
-            const int b_stage = L.b_stage_bytes, nbs = L.nbs;
-            for (long t = t_begin; t < t_end; ++t) {
-                const int ti = static_cast<int>(t / args.ntiles);      // super row (same in every CTA)
-                if (ti != cur_i) {
-                    mbar_wait(a_full, aph);
-                    aph ^= 1;
-                    cur_i = ti;
-                }
-                mbar_wait(&acc_empty[acc], accph ^ 1);
+    } else if (warp == 1 || warp == 11) {
+        // Whole warp, converged: every operand below is warp-uniform, one elected lane issues (ptx.cuh).
+        // Both issuer warps walk ALL tiles so that their ring / row bookkeeping stays in step; each one
+        // waits, issues and commits only for the tiles of its own parity (= its own accumulator).
+        const int me = (warp == 1) ? 0 : 1;
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+        const uint64_t desc0 = umma_desc_k_sw128(0);
+        int bs = 0; uint32_t bph = 0;
+        uint32_t accph = 0;
+        uint32_t aph = 0;
+        const uint64_t a_desc = desc0 + (smem_u32(a_smem) >> 4);
+        const uint32_t b_addr = smem_u32(b_smem);
+        const int b_stage = L.b_stage_bytes, nbs = L.nbs;
+        const uint32_t d = tmem_base + me * 128;
+        int tj = static_cast<int>(t_begin % args.ntiles);
+        bool new_row = true;
+        int par = 0;
+        for (long t = t_begin; t < t_end; ++t, par ^= 1) {
+            const bool mine = (par == me);
+            if (new_row) {
+                mbar_wait(a_full, aph);
+                aph ^= 1;
+                new_row = false;
+            }
+            if (mine) {
+                mbar_wait(&acc_empty[me], accph ^ 1);
+                accph ^= 1;
                 tc_fence_after();
-                const uint32_t d = tmem_base + acc * 128;
+            }
 #pragma unroll
-                for (int kc = 0; kc < kchunks; ++kc) {
+            for (int kc = 0; kc < kchunks; ++kc) {
+                if (mine) {
                     mbar_wait(&b_full[bs], bph);
                     tc_fence_after();
                     const uint64_t b_desc = desc0 + ((b_addr + bs * b_stage) >> 4);
@@ -215,18 +189,48 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                         const uint64_t a_lo = a_desc + (((1 * kchunks + kc) * kBox + ks * 32) >> 4);
                         const uint64_t b_hi = b_desc + ((ks * 32) >> 4);
                         const uint64_t b_lo = b_desc + ((kBox + ks * 32) >> 4);
-                        umma_bf16(d, a_hi, b_hi, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
-                        umma_bf16(d, a_hi, b_lo, idesc, 1);
-                        umma_bf16(d, a_lo, b_hi, idesc, 1);
+                        umma_bf16_warp(d, a_hi, b_hi, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
+                        umma_bf16_warp(d, a_hi, b_lo, idesc, 1);
+                        umma_bf16_warp(d, a_lo, b_hi, idesc, 1);
                     }
-                    if (CS > 1) umma_commit_mcast(&b_empty[bs], cmask);
-                    else        umma_commit(&b_empty[bs]);
-                    if (++bs == nbs) { bs = 0; bph ^= 1; }
+                    if (CS > 1) umma_commit_mcast_warp(&b_empty[bs], cmask);
+                    else        umma_commit_warp(&b_empty[bs]);
                 }
-                umma_commit(&acc_full[acc]);
-                const long tn = t + 1;
-                if (tn >= t_end || static_cast<int>(tn / args.ntiles) != ti) umma_commit(a_empty);
-                if (++acc == 2) { acc = 0; accph ^= 1; }
+                if (++bs == nbs) { bs = 0; bph ^= 1; }
+            }
+            if (mine) umma_commit_warp(&acc_full[me]);
+            if (++tj == args.ntiles) { tj = 0; new_row = true; }
+            // end of this CTA's tiles of the row: both issuers release the W planes (count 2); a warp
+            // without MMAs in flight arrives at once
+            if (t + 1 >= t_end || new_row) umma_commit_warp(a_empty);
+        }
+    } else if (warp == 10) {
+        if (lane == 0) {
+            int vs = 0; uint32_t vph = 0;
+            for (long t = t_begin; t < t_end; ++t) {
+                const int sr = static_cast<int>(t / args.ntiles);
+                const int tj = static_cast<int>(t - static_cast<long>(sr) * args.ntiles);
+                const int ti = min(sr * CS + static_cast<int>(crank), args.mtiles - 1);
+                // pull the V tile of a later step into L2: only two V buffers fit in shared memory, far
+                // too few bytes in flight to cover HBM latency on their own
+                {
+                    const long tp = t + kPrefetchTiles;
+                    if (tp < t_end) {
+                        const int srp = static_cast<int>(tp / args.ntiles);
+                        const int tjp = static_cast<int>(tp - static_cast<long>(srp) * args.ntiles);
+                        const int tip = min(srp * CS + static_cast<int>(crank), args.mtiles - 1);
+                        for (int p = 0; p < NV; ++p)
+                            for (int hb = 0; hb < 2; ++hb)
+                                tma_prefetch_2d(&args.v[p], 0, (tjp * 2 + hb) * args.v_rows_p + tip * 128);
+                    }
+                }
+                mbar_wait(&v_empty[vs], vph ^ 1);
+                mbar_expect_tx(&v_full[vs], L.v_buf_bytes);
+                for (int p = 0; p < NV; ++p)
+                    for (int hb = 0; hb < 2; ++hb)
+                        tma_load_2d_hint(v_smem + vs * L.v_buf_bytes + (p * 2 + hb) * kBox, &args.v[p],
+                                         &v_full[vs], 0, (tj * 2 + hb) * args.v_rows_p + ti * 128, kPolicyEvictFirst);
+                if (++vs == L.nvs) { vs = 0; vph ^= 1; }
             }
         }
     } else {
@@ -241,16 +245,23 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
         for (long t = t_begin; t < t_end; ++t) {
             const bool live = static_cast<int>(t / args.ntiles) * CS + static_cast<int>(crank) < args.mtiles;
             mbar_wait(&acc_full[acc], accph);
-            mbar_wait(&v_full[vs], vph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + hb * 64;
+            // Both halves of this warp's 64 columns go to registers first and the accumulator is handed
+            // back at once: the issuer of tile t + 2 waits for the TMEM read-out only (64 B/cycle/SM, i.e.
+            // ~1000 cycles per tile), not for the arithmetic below.
+            uint32_t s[2][32];
+            tmem_ld32(taddr, s[0]);
+            tmem_ld32(taddr + 32, s[1]);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            mbar_wait(&v_full[vs], vph);
             const uint8_t* vrow = v_smem + vs * L.v_buf_bytes + hb * kBox + row * 128;
-            float tsum = 0.f;
+            float ts[4] = {0.f, 0.f, 0.f, 0.f};          // independent chains
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
-                uint32_t s[32];
-                tmem_ld32(taddr + g * 32, s);
-                tmem_ld_wait();
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     const int chunk = (g * 4 + c8) ^ (row & 7);          // SWIZZLE_128B
@@ -273,20 +284,19 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                     }
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        const float sv = __uint_as_float(s[c8 * 8 + e]);
+                        const float sv = __uint_as_float(s[g][c8 * 8 + e]);
                         if (args.kl == 0) {
                             const float dlt = vv[e] - sv;
-                            tsum = fmaf(dlt, dlt, tsum);
+                            ts[e & 3] = fmaf(dlt, dlt, ts[e & 3]);
                         } else {
-                            tsum += kl_term(vv[e], sv);
+                            ts[e & 3] += kl_term(vv[e], sv);
                         }
                     }
                 }
             }
-            if (live) total += static_cast<double>(tsum);
-            tc_fence_before();
+            if (live) total += static_cast<double>((ts[0] + ts[1]) + (ts[2] + ts[3]));
             __syncwarp();
-            if (lane == 0) { mbar_arrive(&acc_empty[acc]); mbar_arrive(&v_empty[vs]); }
+            if (lane == 0) mbar_arrive(&v_empty[vs]);
             if (++acc == 2) { acc = 0; accph ^= 1; }
             if (++vs == L.nvs) { vs = 0; vph ^= 1; }
         }

@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from ._lib import AdmmState, Data, Factor, Problem, check
-from .sharding import allgather_windows, allreduce_sum_, live_rows, shard_bounds
+from .sharding import allgather_flat, allgather_windows, allreduce_max_, allreduce_sum_, live_rows, shard_bounds
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -96,6 +96,14 @@ class Engine:
         self.vmin = None
         self._problem = None
 
+    @classmethod
+    def for_comm(cls, m: int, n: int, k: int, comm) -> "Engine":
+        """Engine of this rank in a sharded run: comm = True (the default process group) or a
+        torch.distributed group; one process per GPU, the current CUDA device is this rank's."""
+        import torch.distributed as dist
+        group = None if comm is True else comm
+        return cls(m, n, k, rank=dist.get_rank(group), world=dist.get_world_size(group), group=group)
+
     # ------------------------------------------------------------------ plumbing
     @property
     def stream(self) -> int:
@@ -109,37 +117,47 @@ class Engine:
         self.v_cols = torch.zeros((nv, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=self.device)
         self._problem = None
 
-    def store_block(self, blk: torch.Tensor, r0: int):
-        """Write rows [r0, r0+rows) of V (a device tensor (rows, n) whose values are bf16-exact) into
-        plane 0 of this rank's shards of both K-blocked copies.  Plumbing for on-device data."""
-        rows, n = blk.shape
-        if r0 % 64 or (rows % 64 and r0 + rows != self.m):
-            raise ValueError("store_block: row blocks must be 64-aligned")
-        b = blk.to(torch.bfloat16)
-        a, e = max(r0, self.row_range[0]), min(r0 + rows, self.row_range[1])
-        if a < e:                                             # rows of this block inside my row shard
-            br = b[a - r0:e - r0]
-            npad = (-n) % 64
-            if npad:
-                br = torch.nn.functional.pad(br, (0, npad))
-            lo = a - self.row_win[0]
-            self.v_rows[0, : br.shape[1] // 64, lo:lo + (e - a), :] = br.reshape(e - a, -1, 64).permute(1, 0, 2)
-        c0, c1 = self.col_range
-        if c0 < c1:                                           # my columns of this block -> rows of V^T
-            bt = b[:, c0:c1].t()
-            rpad = (-rows) % 64
-            if rpad:
-                bt = torch.nn.functional.pad(bt, (0, rpad))
-            self.v_cols[0, r0 // 64:(r0 + rows + rpad) // 64, :c1 - c0, :] = bt.reshape(c1 - c0, -1, 64).permute(1, 0, 2)
-
     # ------------------------------------------------------------------ sharded runs
-    def gather_factor(self, fac: "FactorBuffers"):
-        """All-gather the windows of a factor every rank just updated, then re-derive its bf16 planes."""
+    def gather_factor(self, fac: "FactorBuffers", refresh: bool = True, fixed: bool = False):
+        """All-gather the windows of a factor (or ADMM auxiliary) every rank just updated, then re-derive
+        its bf16 planes: `refresh` = floating cplanes + rplanes, `fixed` = fixed-point cplanes on top
+        (operand of the exact-hi contractions)."""
         if self.world == 1:
             return
-        allgather_windows(fac.master, self.per_m if fac is self.w else self.per_n, self.group)
+        allgather_windows(fac.master, fac.win_p, self.group)
         fs = fac.struct()
-        check(self.lib.nmfb_refresh_planes(self.KP, C.byref(fs), self.stream))
+        if refresh:
+            check(self.lib.nmfb_refresh_planes(self.KP, C.byref(fs), self.stream))
+        if fixed:
+            check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
+
+    def mur_kl_half_step(self, side: int, lam: float):
+        p = self.problem()
+        check(self.lib.nmfb_mur_kl_half_step(C.byref(p), int(side), float(lam), self.stream))
+
+    def admm_half_step(self, side: int, rho, lam, prox):
+        p = self.problem()
+        check(self.lib.nmfb_admm_half_step(C.byref(p), C.byref(self._admm), int(side), float(rho), float(lam),
+                                           int(prox), self.stream))
+
+    def admm_publish(self, ring_slot: int):
+        check(self.lib.nmfb_admm_publish(C.byref(self._admm), self.scalars.data_ptr() + 64 * ring_slot, self.stream))
+
+    def aoadmm_side(self, side: int, admm_iter: int, lam, prox):
+        """One factor update of AO-ADMM in a sharded run (ao_admm.py:46-68): the four norms of the residual
+        test are all-gathered per inner iteration so that every rank takes the same early break."""
+        p = self.problem()
+        fac = self.h if side == 0 else self.w
+        slots = check(self.lib.nmfb_aoadmm_side_begin(C.byref(p), C.byref(self._admm), side, self.stream))
+        nblk = fac.win_p // 64
+        for it in range(admm_iter):
+            check(self.lib.nmfb_aoadmm_inner(C.byref(p), C.byref(self._admm), side, 1 if it == 0 else 0, slots,
+                                             float(lam), int(prox), self.stream))
+            full = self.norm_partial[: 4 * (fac.Lp // 64)]
+            mine = full[4 * nblk * self.rank: 4 * nblk * (self.rank + 1)].clone()
+            allgather_flat(full, mine, self.group)
+            check(self.lib.nmfb_aoadmm_inner_flag(C.byref(p), C.byref(self._admm), side, self.stream))
+        self.gather_factor(fac, refresh=True, fixed=self.fixed)
 
     def mur_eu_half_step(self, side: int, lam: float):
         p = self.problem()
@@ -152,9 +170,9 @@ class Engine:
 
     def _data_structs(self) -> Tuple[Data, Data]:
         vr = Data(self.v_rows.data_ptr(), self.row_range[1] - self.row_range[0], self.n, self.per_m, self.Np,
-                  self.nv, 1, int(self.fixed))
+                  self.nv, 1, int(self.fixed), self.row_range[0] if self.world > 1 else 0)
         vc = Data(self.v_cols.data_ptr(), self.col_range[1] - self.col_range[0], self.m, self.per_n, self.Mp,
-                  self.nv, 1, int(self.fixed))
+                  self.nv, 1, int(self.fixed), self.col_range[0] if self.world > 1 else 0)
         return vr, vc
 
     def problem(self) -> Problem:
@@ -184,8 +202,6 @@ class Engine:
     # ------------------------------------------------------------------ data in
     # chunk-wise ingest (host arrays and on-device synthetic data share it)
     def begin_ingest(self, nv: int, fixed: bool = False):
-        if self.world != 1:
-            raise NotImplementedError("ingest kernels serve unsharded engines; shards use store_block")
         self.fixed = bool(fixed)
         self._alloc_data(max(nv, 2) if fixed else nv)
         self.stats.copy_(torch.tensor([-1, 0, 0, 0], dtype=torch.int32))
@@ -211,6 +227,8 @@ class Engine:
                                             C.byref(vr), C.byref(vc), self.stats.data_ptr(), self.stream))
 
     def finish_ingest(self):
+        if self.world > 1:                    # every rank walked all of V but judged only its shard's planes
+            allreduce_max_(self.stats[1:3], self.group)
         st = self.stats.cpu().numpy().view(np.uint32)
         return _key_to_float(int(st[0])), bool(st[1]), bool(st[2])
 
@@ -240,8 +258,6 @@ class Engine:
             v = v.astype(np.float64)
         if not v.flags.c_contiguous:
             v = np.ascontiguousarray(v)
-        if self.world > 1:
-            return self._upload_sharded(v)
         if fixed:
             vmin, inexact, bad = self._ingest_pass(v, 2, fixed=True)
             if not inexact:
@@ -254,24 +270,6 @@ class Engine:
             vmin, need_lo, bad = self._ingest_pass(v, 2)
         if bad:
             raise ValueError("data contains non-finite values")
-        self.vmin = vmin
-        return vmin
-
-    def _upload_sharded(self, v: np.ndarray) -> float:
-        """Sharded runs: every rank walks the host V in row chunks and keeps its row / column shard
-        (store_block).  This build needs bf16-exact data here (one lossless plane)."""
-        self._alloc_data(1)
-        vmin = float("inf")
-        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
-        for r0 in range(0, self.m, rows_per):
-            r1 = min(self.m, r0 + rows_per)
-            blk = torch.from_numpy(v[r0:r1]).to(self.device)
-            if not torch.isfinite(blk).all():
-                raise ValueError("data contains non-finite values")
-            if not torch.equal(blk.to(torch.bfloat16).to(blk.dtype), blk):
-                raise NotImplementedError("sharded runs need bfloat16-exact data in this build")
-            vmin = min(vmin, float(blk.min()))
-            self.store_block(blk, r0)
         self.vmin = vmin
         return vmin
 
@@ -347,8 +345,8 @@ class Engine:
         self.admm_flags = torch.zeros(8, dtype=torch.int32, device=dev)
         self.norm_partial = torch.zeros(4 * (Lmax // 64), dtype=torch.float64, device=dev)
         if with_aux:
-            self.w_aux = FactorBuffers(self.m, KP, dev)
-            self.h_aux = FactorBuffers(self.n, KP, dev)
+            self.w_aux = FactorBuffers(self.m, KP, dev, self.Mp, self.w.win0, self.w.win_p)
+            self.h_aux = FactorBuffers(self.n, KP, dev, self.Np, self.h.win0, self.h.win_p)
             for src, dst in ((self.w, self.w_aux), (self.h, self.h_aux)):
                 dst.master.copy_(src.master)
                 fs = dst.struct()

@@ -35,11 +35,7 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
     m, n = x.shape
 
     if comm is not None and engine is None:              # sharded over the ranks of a torch.distributed group
-        import torch.distributed as dist
-        group = None if comm is True else comm
-        engine = Engine(m, n, k, rank=dist.get_rank(group), world=dist.get_world_size(group), group=group)
-        if engine.world > 1 and distance_type != 'eu':
-            raise NotImplementedError("sharded runs provide method='mur', distance_type='eu' in this build")
+        engine = Engine.for_comm(m, n, k, comm)
         verbose = verbose and engine.rank == 0
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:

@@ -48,5 +48,22 @@ def allgather_windows(master: torch.Tensor, per: int, group=None) -> None:
     master.view(KP, world, per).copy_(recv.permute(1, 0, 2))
 
 
+def allgather_flat(full: torch.Tensor, mine: torch.Tensor, group=None) -> None:
+    """full: contiguous 1-D tensor of world * len(mine) elements; rank p contributes `mine` as its p-th
+    segment (the norm partials of the AO-ADMM residual test)."""
+    world = dist.get_world_size(group)
+    assert full.is_contiguous() and full.numel() == world * mine.numel()
+    try:
+        dist.all_gather_into_tensor(full, mine, group=group)
+    except (RuntimeError, NotImplementedError):
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        full.copy_(torch.cat(parts))
+
+
 def allreduce_sum_(t: torch.Tensor, group=None) -> None:
     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+
+
+def allreduce_max_(t: torch.Tensor, group=None) -> None:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)

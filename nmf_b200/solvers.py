@@ -72,17 +72,34 @@ class MurKlStepper:
 
     def prepare(self):
         self.eng.objective_kl(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot: int):
-        self.eng.mur_kl_step(self.lw, self.lh, obj_slot=ring_slot * 8)
+        e = self.eng
+        if e.world == 1:
+            e.mur_kl_step(self.lw, self.lh, obj_slot=ring_slot * 8)
+            return
+        e.mur_kl_half_step(0, self.lw)                    # my rows of W from my rows of V and the full H
+        e.gather_factor(e.w)
+        e.mur_kl_half_step(1, self.lh)                    # my columns of H from my columns of V and the new W
+        e.gather_factor(e.h)
+        e.objective_kl(slot=ring_slot * 8)
+        e.reduce_scalar(ring_slot * 8)
 
     def phase_names(self):
         return self.phases
+
+    def phase_pairs(self):
+        if self.eng.world == 1:
+            return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
+        return []
 
     def roofline(self, phase_ms, peaks):
         """Dominant kernel = the fused GEMM -> quotient -> GEMM kernel (one launch per side):
         algorithmic 4*m*n*k FLOP per launch (S tile + Q.Y^T), executed 3 MMAs per product."""
         e = self.eng
+        if "kl_w" not in phase_ms:
+            return None
         ms = 0.5 * (phase_ms["kl_w"] + phase_ms["kl_h"])
         tf = 4.0 * e.m * e.n * e.k / (ms * 1e-3) / 1e12
         gbs = 2.0 * e.m * e.n * e.nv / (ms * 1e-3) / 1e9
@@ -133,9 +150,28 @@ class AdmmStepper(_GemmRoofline):
     def prepare(self):
         self.eng.alloc_admm(with_aux=True)
         self.eng.objective_eu(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot):
-        self.eng.admm_step(self.rho, self.lw, self.pw, self.lh, self.ph, ring_slot)
+        e = self.eng
+        if e.world == 1:
+            e.admm_step(self.rho, self.lw, self.pw, self.lh, self.ph, ring_slot)
+            return
+        # sharded: my columns of h_aux / H / U_h, exchange, my rows of w_aux / W / U_w, exchange
+        e.admm_half_step(0, self.rho, self.lh, self.ph)
+        e.gather_factor(e.h_aux, refresh=not e.fixed, fixed=e.fixed)     # operand of the W-side Gram and GEMM
+        e.gather_factor(e.h)                                            # operand of the objective
+        e.admm_half_step(1, self.rho, self.lw, self.pw)
+        e.gather_factor(e.w_aux, refresh=not e.fixed, fixed=e.fixed)
+        e.gather_factor(e.w, refresh=False)                             # keeps the replicated W current
+        e.objective_eu(slot=ring_slot * 8)
+        e.reduce_scalar(ring_slot * 8)
+        e.admm_publish(ring_slot)
+
+    def phase_pairs(self):
+        if self.eng.world == 1:
+            return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
+        return [("gemm_h", 1, 2), ("gemm_w", 4, 5)]
 
     def phase_names(self):
         return self.phases
@@ -154,9 +190,23 @@ class AoAdmmStepper(_GemmRoofline):
     def prepare(self):
         self.eng.alloc_admm(with_aux=False)
         self.eng.objective_eu(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot):
-        self.eng.aoadmm_step(self.admm_iter, self.lw, self.pw, self.lh, self.ph, ring_slot)
+        e = self.eng
+        if e.world == 1:
+            e.aoadmm_step(self.admm_iter, self.lw, self.pw, self.lh, self.ph, ring_slot)
+            return
+        e.aoadmm_side(0, self.admm_iter, self.lh, self.ph)              # H update, ao_admm.py:261-264
+        e.aoadmm_side(1, self.admm_iter, self.lw, self.pw)              # W update, ao_admm.py:265-270
+        e.objective_eu(slot=ring_slot * 8)
+        e.reduce_scalar(ring_slot * 8)
+        e.admm_publish(ring_slot)
+
+    def phase_pairs(self):
+        if self.eng.world == 1:
+            return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
+        return [("gemm_h", 1, 2), ("gemm_w", 4, 5)]
 
     def phase_names(self):
         return self.phases
