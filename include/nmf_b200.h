@@ -179,8 +179,16 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream);
  * through the fused GEMM -> quotient -> GEMM kernel (W.H never reaches HBM), row / column sums by
  * shuffle reductions, then the objective of the new pair.  k <= 128 in this build. */
 int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream);
-/* One factor update of the iteration above (side 0 = W, 1 = H); window semantics as nmfb_mur_eu_half_step. */
-int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, void* stream);
+/* One factor update of the iteration above (side 0 = W, 1 = H); window semantics as nmfb_mur_eu_half_step.
+ * obj_start_out != NULL: the pass also writes the KL objective (utils.py:23-26) of the pair it STARTS from
+ * (this rank's rows / columns of V only in a sharded run) -- S = W.H and V are in registers anyway, so the
+ * objective of outer iteration i costs no sweep of its own when taken from the W pass of iteration i + 1. */
+int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, double* obj_start_out, void* stream);
+/* W update (emitting the objective of the incoming pair, i.e. of the previous outer iteration, into
+ * *obj_start_out) followed by the H update; no objective of the new pair.  The host loop reads objective
+ * i - 1 after enqueueing iteration i and calls nmfb_objective_kl once for the last iteration. */
+int nmfb_mur_kl_step_lagged(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_start_out,
+                            void* stream);
 
 /* ---- ADMM / AO-ADMM ------------------------------------------------------------------------- */
 typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1 } nmfb_prox;   /* admm.py:126-139 */

@@ -74,7 +74,8 @@ _SIGNATURES = {
     "nmfb_mur_eu_half_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
     "nmfb_objective_kl": (c_int, [P(Problem), c_void_p, c_void_p]),
     "nmfb_mur_kl_step": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
-    "nmfb_mur_kl_half_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
+    "nmfb_mur_kl_half_step": (c_int, [P(Problem), c_int, c_float, c_void_p, c_void_p]),
+    "nmfb_mur_kl_step_lagged": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
     "nmfb_admm_half_step": (c_int, [P(Problem), P(AdmmState), c_int, C.c_double, c_float, c_int, c_void_p]),
     "nmfb_admm_publish": (c_int, [P(AdmmState), c_void_p, c_void_p]),
     "nmfb_aoadmm_side_begin": (c_int, [P(Problem), P(AdmmState), c_int, c_void_p]),

@@ -30,9 +30,14 @@ class LoopResult:
 
 
 def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision, verbose=True,
-        on_extra=None):
+        on_extra=None, lagged=False, finish=None):
     """enqueue_step(slot) must enqueue one outer iteration that leaves the objective in
-    engine.scalars[slot*8] (and optional extras in [slot*8+1 : slot*8+8])."""
+    engine.scalars[slot*8] (and optional extras in [slot*8+1 : slot*8+8]).
+
+    lagged=True (MUR-KL): the objective of iteration i-1 is a by-product of the first kernel of iteration
+    i.  enqueue_step(slot, prev_slot, mid) then writes it to scalars[prev_slot*8] and calls mid() right
+    after that kernel; the host reads it while the rest of iteration i runs, and finish(slot) enqueues a
+    stand-alone objective for the very last iteration."""
     res = LoopResult()
     res.obj_history = [obj0]
     host = torch.zeros(RING * 8, dtype=torch.float64).pin_memory()
@@ -57,22 +62,33 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
             res.masters = snaps[i % 2]
             stopped = True
 
-    for i in range(max_iter):
-        slot = i % RING
-        enqueue_step(slot)
+    def publish(i_obj, slot):
         host[slot * 8: slot * 8 + 8].copy_(engine.scalars[slot * 8: slot * 8 + 8], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(engine.device))
+        pending.append((i_obj, slot, ev))
+
+    for i in range(max_iter):
+        slot = i % RING
+        if lagged:
+            prev = (i - 1) % RING if i > 0 else RING - 1          # i == 0: recomputes obj0 into a spare slot
+            enqueue_step(slot, prev, (lambda: publish(i - 1, prev)) if i > 0 else None)
+        else:
+            enqueue_step(slot)
+            publish(i, slot)
         if i > min_iter:
             if snaps[i % 2] is None:
                 snaps[i % 2] = (torch.empty_like(engine.w.master), torch.empty_like(engine.h.master))
             snaps[i % 2][0].copy_(engine.w.master, non_blocking=True)
             snaps[i % 2][1].copy_(engine.h.master, non_blocking=True)
-        pending.append((i, slot, ev))
-        while len(pending) > LAG and not stopped:
+        while len(pending) > (0 if lagged else LAG) and not stopped:
             process(pending.popleft())
         if stopped:
             break
+    if lagged and not stopped and max_iter > 0:
+        last = (max_iter - 1) % RING
+        finish(last)
+        publish(max_iter - 1, last)
     while pending and not stopped:
         process(pending.popleft())
     if not stopped:

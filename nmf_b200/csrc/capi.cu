@@ -445,7 +445,7 @@ namespace {
 // One side of the KL update: X (rows of `data`) <- KL rule with the other factor Y.  In a sharded run
 // `data` holds this rank's rows only and the window of X is updated.
 int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, const nmfb_factor* y,
-            double* ysum, float lambda, void* stream) {
+            double* ysum, float lambda, double* obj_start_out, void* stream) {
     const int KP = p->KP;
     const Window w = window_of(x);
     KlPlan pl;
@@ -467,6 +467,10 @@ int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, 
         if ((rc = make_map(&a.d[q], bf(data->planes) + static_cast<long>(q) * data->rows_p * data->ld,
                            static_cast<long>(data->ld / 64) * data->rows_p, 64, 128))) return rc;
     a.out = p->partial + w.w0;
+    if (obj_start_out) {
+        if (pl.grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "mur_kl: obj_partial too small");
+        a.obj_partial = p->obj_partial;
+    }
     a.KP = KP; a.Lp = x->Lp;
     a.npanels = pl.npanels; a.ntiles = pl.ntiles; a.nsplit = pl.nsplit; a.tiles_per_split = pl.tiles_per_split;
     a.d_rows_p = data->rows_p;
@@ -475,29 +479,40 @@ int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, 
     CUDA_TRY(mur_kl_update_launch(p->partial + w.w0, pl.slots, ysum, x->master + w.w0, bf(x->cplanes) + w.w0,
                                   256L * x->Lp, bf(x->rplanes) + static_cast<long>(w.w0) * KP,
                                   static_cast<long>(x->Lp) * KP, KP, p->k, w.live, x->Lp, w.wp, lambda, st(stream)));
+    if (obj_start_out) CUDA_TRY(sum_partials_launch(p->obj_partial, pl.grid, 1.0, obj_start_out, st(stream)));
     return 0;
 }
 }  // namespace
 
-int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+int nmfb_mur_kl_half_step(const nmfb_problem* p, int side, float lambda, double* obj_start_out, void* stream) {
     if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_kl_half_step: bad argument");
     if (!p->ksum) return fail(NMFB_ERR_ARG, "mur_kl_half_step: problem.ksum workspace missing");
-    return side == 0 ? kl_side(p, &p->v_rows, &p->w, &p->h, p->ksum, lambda, stream)             // mur.py:122
-                     : kl_side(p, &p->v_cols, &p->h, &p->w, p->ksum + p->KP, lambda, stream);    // mur.py:123
+    // phase events: 0 | W update (+ objective of the incoming pair) | 1, 2 | H update | 3
+    mark(p, 2 * side, stream);
+    const int rc = side == 0 ? kl_side(p, &p->v_rows, &p->w, &p->h, p->ksum, lambda, obj_start_out, stream)             // mur.py:122
+                             : kl_side(p, &p->v_cols, &p->h, &p->w, p->ksum + p->KP, lambda, obj_start_out, stream);    // mur.py:123
+    mark(p, 2 * side + 1, stream);
+    return rc;
+}
+
+int nmfb_mur_kl_step_lagged(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_start_out,
+                            void* stream) {
+    if (!p) return fail(NMFB_ERR_ARG, "mur_kl_step_lagged: null problem");
+    int rc;
+    if ((rc = nmfb_mur_kl_half_step(p, 0, lambda_w, obj_start_out, stream)) < 0) return rc;
+    if ((rc = nmfb_mur_kl_half_step(p, 1, lambda_h, nullptr, stream)) < 0) return rc;
+    return 0;
 }
 
 int nmfb_mur_kl_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {
     if (!p) return fail(NMFB_ERR_ARG, "mur_kl_step: null problem");
     if (!p->ksum) return fail(NMFB_ERR_ARG, "mur_kl_step: problem.ksum workspace missing");
     int rc;
-    // phase events: 0 start | 1 W update (V, old W.H) | 2 H update (V^T, new W) | 3 objective
-    mark(p, 0, stream);
-    if ((rc = nmfb_mur_kl_half_step(p, 0, lambda_w, stream)) < 0) return rc;
-    mark(p, 1, stream);
-    if ((rc = nmfb_mur_kl_half_step(p, 1, lambda_h, stream)) < 0) return rc;
-    mark(p, 2, stream);
+    // phase events: 0 | W update | 1, 2 | H update | 3 | objective | 4
+    if ((rc = nmfb_mur_kl_half_step(p, 0, lambda_w, nullptr, stream)) < 0) return rc;
+    if ((rc = nmfb_mur_kl_half_step(p, 1, lambda_h, nullptr, stream)) < 0) return rc;
     if (obj_out && (rc = nmfb_objective_kl(p, obj_out, stream)) < 0) return rc;                       // mur.py:127
-    mark(p, 3, stream);
+    mark(p, 4, stream);
     return 0;
 }
 

@@ -9,14 +9,27 @@
 // Out is the bracket of mur.py:25 / :41; the update itself (x * Out, the row / column sums and the
 // regularised quotient) is the small kernel at the end of this file.
 //
+// The same pass can also emit the generalised KL objective of the pair (X, Y) it STARTS from
+// (utils.py:23-26): S and D are in registers anyway, so the objective of iteration i costs no second
+// sweep over V when it is taken from the W-side pass of iteration i + 1 (OBJ = true).
+//
 // One shared-memory tile of Y's component-major planes ([c][t], 128 c x 64 t) serves both MMAs: as
 // the MN-major B operand of MMA1 (K = c runs over the rows, N = t is contiguous) and as the K-major
 // A operand of MMA2.  fp32-grade arithmetic comes from bf16 hi/lo planes: 3 MMAs per product.
 //
-// warp 0 = TMA producer, warp 1 = MMA issuer (software-pipelined: MMA1 of tile j+1 is issued before
-// MMA2 of tile j, so the quotient epilogue overlaps tensor work), warps 2..9 = epilogue.  Out is
-// accumulated in chunks of kOutChunk tiles that are drained into register sums (see panel_gemm.cu for
-// why), and written once per work item into a partial slot.
+// Warp roles (384 threads):
+//   warp 0       TMA producer of X (once per work item) and of the Y ring (NSY stages)
+//   warp 10      TMA producer of the D ring (2 stages) + L2 prefetch of the data stream
+//   warp 1       issues MMA1 (whole warp, one elected lane per instruction: ptx.cuh)
+//   warp 11      issues MMA2
+//   warps 2..9   quotient epilogue, objective terms, Out drain
+// Rings and issuers are separate on purpose.  The first version had one producer, one issuer and two
+// combined (Y, D) stages: a stage could be refilled only after MMA2 of its tile had retired, the lone
+// issuer sat in the wait for that refill while the next Q was already there, and every tcgen05.mma
+// issued from an `if (lane == 0)` region cost ~130 cycles of R2UR waterfall against 32 cycles of N = 64
+// tensor work: 32 % tensor-pipe activity (profiles/r01b_all_paths.md).
+// Out is accumulated in chunks of kOutChunk tiles that are drained into register sums (see
+// panel_gemm.cu for why), and written once per work item into a partial slot.
 #include "kernels.cuh"
 #include "kl.cuh"
 #include "ptx.cuh"
@@ -24,16 +37,23 @@
 namespace nmfb {
 
 namespace {
-constexpr int kThreadsK = 320;
+constexpr int kThreadsK = 384;
 constexpr int kBoxK = 128 * 128;       // bytes of one [128 rows x 64 bf16] box
 constexpr int kOutChunk = 8;           // t-tiles accumulated in TMEM before a drain
 constexpr int kPrefetchK = 6;          // L2 prefetch distance of the data stream, in t-tiles
+constexpr int kNSD = 2;                // D ring depth
+
+// Y ring depth: what is left of 224 KB after X (2 KCH boxes), the D ring and one Q buffer (hi + lo).
+__host__ __device__ constexpr int kl_nsy(int KCH, int NV) {
+    const int left = (224 * 1024 - 2 * KCH * kBoxK - kNSD * NV * kBoxK - 2 * kBoxK) / (2 * kBoxK);
+    return left > 4 ? 4 : left;
+}
 
 // MN-major SWIZZLE_128B descriptor template (N = 64 contiguous elements per row, 8 rows per 1024 B atom).
 __device__ __forceinline__ uint64_t desc_mn_sw128_base() { return umma_desc_mn_sw128(0, 16); }
 }  // namespace
 
-template <int KCH, int NV>
+template <int KCH, int NV, bool OBJ>
 __global__ void __launch_bounds__(kThreadsK, 1)
 kl_panel_kernel(const __grid_constant__ KlArgs args) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -41,27 +61,32 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                                                ~static_cast<uintptr_t>(1023));
     constexpr int KP = KCH * 64;
     constexpr int X_BYTES = 2 * KCH * kBoxK;
-    constexpr int STAGE = (2 + NV) * kBoxK;          // Y hi, Y lo, D planes
-    constexpr int NST = 2;
-    constexpr int NQ = (NV == 1) ? 2 : 1;            // Q buffers (hi + lo each)
+    constexpr int Y_STAGE = 2 * kBoxK;               // Y hi, Y lo
+    constexpr int D_STAGE = NV * kBoxK;
+    constexpr int NSY = kl_nsy(KCH, NV);
     constexpr int Q_BYTES = 2 * kBoxK;
+    static_assert(NSY >= 2, "Y ring too shallow");
     uint8_t* x_smem = smem;
-    uint8_t* st_smem = x_smem + X_BYTES;
-    uint8_t* q_smem = st_smem + NST * STAGE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(q_smem + NQ * Q_BYTES);
+    uint8_t* y_smem = x_smem + X_BYTES;
+    uint8_t* d_smem = y_smem + NSY * Y_STAGE;
+    uint8_t* q_smem = d_smem + kNSD * D_STAGE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(q_smem + Q_BYTES);
     uint64_t* x_full = bars + 0;
     uint64_t* x_empty = bars + 1;
-    uint64_t* st_full = bars + 2;      // [2]
-    uint64_t* st_empty = bars + 4;     // [2]
-    uint64_t* s_full = bars + 6;       // [2]  S tile in TMEM ready
-    uint64_t* s_empty = bars + 8;      // [2]
-    uint64_t* q_full = bars + 10;      // [2]
-    uint64_t* q_empty = bars + 12;     // [2]
-    uint64_t* o_full = bars + 14;      // [2]  Out chunk ready
-    uint64_t* o_empty = bars + 16;     // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+    uint64_t* y_full = bars + 2;       // [4]
+    uint64_t* y_empty = bars + 6;      // [4]
+    uint64_t* d_full = bars + 10;      // [2]
+    uint64_t* d_empty = bars + 12;     // [2]
+    uint64_t* s_full = bars + 14;      // [2]  S tile in TMEM ready
+    uint64_t* s_empty = bars + 16;     // [2]
+    uint64_t* q_full = bars + 18;
+    uint64_t* q_empty = bars + 19;
+    uint64_t* o_full = bars + 20;      // [2]  Out chunk ready
+    uint64_t* o_empty = bars + 22;     // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+    double* red = reinterpret_cast<double*>(bars + 26);      // [8]
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
     const int nitems = args.npanels * args.nsplit;
 
     if (warp == 0 && lane == 0) {
@@ -69,12 +94,14 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
         for (int p = 0; p < NV; ++p) tma_prefetch_desc(&args.d[p]);
         mbar_init(x_full, 1);
         mbar_init(x_empty, 1);
+        for (int s = 0; s < 4; ++s) { mbar_init(&y_full[s], 1); mbar_init(&y_empty[s], 1); }
         for (int s = 0; s < 2; ++s) {
-            mbar_init(&st_full[s], 1);  mbar_init(&st_empty[s], 1);
+            mbar_init(&d_full[s], 1);   mbar_init(&d_empty[s], 8);
             mbar_init(&s_full[s], 1);   mbar_init(&s_empty[s], 8);
-            mbar_init(&q_full[s], 8);   mbar_init(&q_empty[s], 1);
             mbar_init(&o_full[s], 1);   mbar_init(&o_empty[s], 8);
         }
+        mbar_init(q_full, 8);
+        mbar_init(q_empty, 1);
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -86,7 +113,7 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
     const uint32_t tm_o = tmem_base + 128;      // Out buffers: 2 x 128 columns
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------ TMA producer: X and the Y ring
         if (lane == 0) {
             uint32_t xph = 0;
             int stg = 0; uint32_t sph = 0;
@@ -105,46 +132,61 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                                          panel * 128, kPolicyEvictLast);
                 xph ^= 1;
                 for (int t = t0; t < t1; ++t) {
+                    mbar_wait(&y_empty[stg], sph ^ 1);
+                    uint8_t* st = y_smem + stg * Y_STAGE;
+                    mbar_expect_tx(&y_full[stg], Y_STAGE);
+#pragma unroll
+                    for (int p = 0; p < 2; ++p)
+                        tma_load_2d_hint(st + p * kBoxK, &args.yc[p], &y_full[stg], t * 64, 0, kPolicyEvictLast);
+                    if (++stg == NSY) { stg = 0; sph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 10) {
+        // ------------------------------------------------------------ TMA producer: the D ring
+        if (lane == 0) {
+            int ds = 0; uint32_t dph = 0;
+            for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+                const int split = item / args.npanels;
+                const int panel = item - split * args.npanels;
+                const int t0 = split * args.tiles_per_split;
+                const int t1 = min(t0 + args.tiles_per_split, args.ntiles);
+                for (int t = t0; t < t1; ++t) {
                     const int tp = t + kPrefetchK;
                     if (tp < t1)
                         for (int p = 0; p < NV; ++p)
                             tma_prefetch_2d(&args.d[p], 0, tp * args.d_rows_p + panel * 128);
-                    mbar_wait(&st_empty[stg], sph ^ 1);
-                    uint8_t* st = st_smem + stg * STAGE;
-                    mbar_expect_tx(&st_full[stg], STAGE);
-#pragma unroll
-                    for (int p = 0; p < 2; ++p)
-                        tma_load_2d_hint(st + p * kBoxK, &args.yc[p], &st_full[stg], t * 64, 0, kPolicyEvictLast);
+                    mbar_wait(&d_empty[ds], dph ^ 1);
+                    uint8_t* st = d_smem + ds * D_STAGE;
+                    mbar_expect_tx(&d_full[ds], D_STAGE);
 #pragma unroll
                     for (int p = 0; p < NV; ++p)
-                        tma_load_2d_hint(st + (2 + p) * kBoxK, &args.d[p], &st_full[stg], 0,
+                        tma_load_2d_hint(st + p * kBoxK, &args.d[p], &d_full[ds], 0,
                                          t * args.d_rows_p + panel * 128, kPolicyEvictFirst);
-                    if (++stg == NST) { stg = 0; sph ^= 1; }
+                    if (++ds == kNSD) { ds = 0; dph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc1 = umma_idesc_bf16(128, 64, 0, 1);     // B (Y tile) is MN-major
-            constexpr uint32_t idesc2 = umma_idesc_bf16(128, 128);
-            const uint64_t dk0 = umma_desc_k_sw128(0);
-            const uint64_t dmn0 = desc_mn_sw128_base();
-            const uint64_t x_desc = dk0 + (smem_u32(x_smem) >> 4);
-            const uint32_t st_addr = smem_u32(st_smem), q_addr = smem_u32(q_smem);
-            uint32_t xph = 0;
-            uint32_t st_ph[2] = {0, 0};          // parity of the next st_full wait, per stage
-            uint32_t se_ph[2] = {0, 0};          // parity bookkeeping of s_empty, per S buffer
-            uint32_t qf_ph[2] = {0, 0};
-            uint32_t oe_ph[2] = {0, 0};
-            long gt1 = 0, gt2 = 0;               // running tile counters of MMA1 / MMA2 (select buffers)
-            int ob = 0;
-            auto mma1 = [&](long g) {
-                const int stg = static_cast<int>(g & 1), sb = static_cast<int>(g & 1);
-                mbar_wait(&st_full[stg], st_ph[stg]); st_ph[stg] ^= 1;
-                mbar_wait(&s_empty[sb], se_ph[sb] ^ 1); se_ph[sb] ^= 1;
+        // ------------------------------------------------------------ MMA1 issuer: S = X . Y^T
+        constexpr uint32_t idesc1 = umma_idesc_bf16(128, 64, 0, 1);     // B (Y tile) is MN-major
+        const uint64_t dk0 = umma_desc_k_sw128(0);
+        const uint64_t dmn0 = desc_mn_sw128_base();
+        const uint64_t x_desc = dk0 + (smem_u32(x_smem) >> 4);
+        const uint32_t y_addr = smem_u32(y_smem);
+        uint32_t xph = 0;
+        int stg = 0; uint32_t yph = 0;
+        int sb = 0; uint32_t seph = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int split = item / args.npanels;
+            const int t0 = split * args.tiles_per_split;
+            const int t1 = min(t0 + args.tiles_per_split, args.ntiles);
+            mbar_wait(x_full, xph); xph ^= 1;
+            for (int t = t0; t < t1; ++t) {
+                mbar_wait(&y_full[stg], yph);
+                mbar_wait(&s_empty[sb], seph ^ 1);
                 tc_fence_after();
-                const uint32_t yb = st_addr + stg * STAGE;
+                const uint32_t yb = y_addr + stg * Y_STAGE;
                 const uint64_t y_hi = dmn0 + (yb >> 4), y_lo = dmn0 + ((yb + kBoxK) >> 4);
                 const uint32_t d = tm_s + sb * 64;
 #pragma unroll
@@ -154,45 +196,52 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                         const uint64_t a_hi = x_desc + (((0 * KCH + kc) * kBoxK + ks * 32) >> 4);
                         const uint64_t a_lo = x_desc + (((1 * KCH + kc) * kBoxK + ks * 32) >> 4);
                         const uint32_t roff = ((kc * 64 + ks * 16) * 128) >> 4;     // 16 component rows down
-                        umma_bf16(d, a_hi, y_hi + roff, idesc1, (kc == 0 && ks == 0) ? 0u : 1u);
-                        umma_bf16(d, a_hi, y_lo + roff, idesc1, 1u);
-                        umma_bf16(d, a_lo, y_hi + roff, idesc1, 1u);
+                        umma_bf16_warp(d, a_hi, y_hi + roff, idesc1, (kc == 0 && ks == 0) ? 0u : 1u);
+                        umma_bf16_warp(d, a_hi, y_lo + roff, idesc1, 1u);
+                        umma_bf16_warp(d, a_lo, y_hi + roff, idesc1, 1u);
                     }
-                umma_commit(&s_full[sb]);
-            };
-            for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-                const int split = item / args.npanels;
-                const int t0 = split * args.tiles_per_split;
-                const int t1 = min(t0 + args.tiles_per_split, args.ntiles);
-                const int nt = t1 - t0;
-                mbar_wait(x_full, xph); xph ^= 1;
-                mma1(gt1++);
-                for (int j = 0; j < nt; ++j) {
-                    if (j + 1 < nt) mma1(gt1++);
-                    const int stg = static_cast<int>(gt2 & 1);
-                    const int qb = static_cast<int>(gt2 % NQ);
-                    mbar_wait(&q_full[qb], qf_ph[qb]); qf_ph[qb] ^= 1;
-                    const int jc = j % kOutChunk;
-                    if (jc == 0) { mbar_wait(&o_empty[ob], oe_ph[ob] ^ 1); oe_ph[ob] ^= 1; }
-                    tc_fence_after();
-                    const uint32_t yb = st_addr + stg * STAGE;
-                    const uint64_t y_hi = dk0 + (yb >> 4), y_lo = dk0 + ((yb + kBoxK) >> 4);
-                    const uint64_t q_hi = dk0 + ((q_addr + qb * Q_BYTES) >> 4);
-                    const uint64_t q_lo = q_hi + (kBoxK >> 4);
-                    const uint32_t d = tm_o + ob * 128;
+                umma_commit_warp(&s_full[sb]);
+                if (++stg == NSY) { stg = 0; yph ^= 1; }
+                if (++sb == 2) { sb = 0; seph ^= 1; }
+            }
+            umma_commit_warp(x_empty);
+        }
+    } else if (warp == 11) {
+        // ------------------------------------------------------------ MMA2 issuer: Out += Y^T . Q^T
+        constexpr uint32_t idesc2 = umma_idesc_bf16(128, 128);
+        const uint64_t dk0 = umma_desc_k_sw128(0);
+        const uint32_t y_addr = smem_u32(y_smem);
+        const uint64_t q_hi = dk0 + (smem_u32(q_smem) >> 4);
+        const uint64_t q_lo = q_hi + (kBoxK >> 4);
+        int stg = 0; uint32_t yph = 0;
+        uint32_t qph = 0;
+        uint32_t oe_ph = 0;                        // bit b = parity of o_empty[b]
+        int ob = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int split = item / args.npanels;
+            const int t0 = split * args.tiles_per_split;
+            const int t1 = min(t0 + args.tiles_per_split, args.ntiles);
+            const int nt = t1 - t0;
+            int jc = 0;
+            for (int j = 0; j < nt; ++j) {
+                mbar_wait(&y_full[stg], yph);               // long complete; orders this warp after the TMA writes
+                mbar_wait(q_full, qph); qph ^= 1;
+                if (jc == 0) { mbar_wait(&o_empty[ob], ((oe_ph >> ob) & 1u) ^ 1u); oe_ph ^= 1u << ob; }
+                tc_fence_after();
+                const uint32_t yb = y_addr + stg * Y_STAGE;
+                const uint64_t y_hi = dk0 + (yb >> 4), y_lo = dk0 + ((yb + kBoxK) >> 4);
+                const uint32_t d = tm_o + ob * 128;
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint32_t o = (ks * 32) >> 4;
-                        umma_bf16(d, y_hi + o, q_hi + o, idesc2, (jc == 0 && ks == 0) ? 0u : 1u);
-                        umma_bf16(d, y_hi + o, q_lo + o, idesc2, 1u);
-                        umma_bf16(d, y_lo + o, q_hi + o, idesc2, 1u);
-                    }
-                    umma_commit(&st_empty[stg]);
-                    umma_commit(&q_empty[qb]);
-                    if (jc == kOutChunk - 1 || j == nt - 1) { umma_commit(&o_full[ob]); ob ^= 1; }
-                    ++gt2;
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint32_t o = (ks * 32) >> 4;
+                    umma_bf16_warp(d, y_hi + o, q_hi + o, idesc2, (jc == 0 && ks == 0) ? 0u : 1u);
+                    umma_bf16_warp(d, y_hi + o, q_lo + o, idesc2, 1u);
+                    umma_bf16_warp(d, y_lo + o, q_hi + o, idesc2, 1u);
                 }
-                umma_commit(x_empty);
+                umma_commit_warp(&y_empty[stg]);
+                umma_commit_warp(q_empty);
+                if (++jc == kOutChunk || j == nt - 1) { umma_commit_warp(&o_full[ob]); ob ^= 1; jc = 0; }
+                if (++stg == NSY) { stg = 0; yph ^= 1; }
             }
         }
     } else {
@@ -201,9 +250,11 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
         const int q = warp & 3;                      // TMEM lane quarter
         const int half = ew >> 2;
         const int row = q * 32 + lane;               // S lane = data row r; Out lane = component c
-        uint32_t sf_ph[2] = {0, 0}, df_ph[2] = {0, 0}, qe_ph[2] = {0, 0}, of_ph[2] = {0, 0};
-        long g = 0;
+        int sb = 0; uint32_t sfph = 0;               // S buffer / D stage walk together (both 2 deep)
+        uint32_t qeph = 1;                           // first wait on the fresh q_empty passes
+        uint32_t of_ph = 0;                          // bit b = parity of o_full[b]
         int ob = 0;
+        double total = 0.0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int split = item / args.npanels;
             const int panel = item - split * args.npanels;
@@ -213,17 +264,17 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
             float sums[64];
 #pragma unroll
             for (int e = 0; e < 64; ++e) sums[e] = 0.f;
-            for (int j = 0; j < nt; ++j, ++g) {
-                const int sb = static_cast<int>(g & 1), stg = sb, qb = static_cast<int>(g % NQ);
-                mbar_wait(&s_full[sb], sf_ph[sb]); sf_ph[sb] ^= 1;
-                mbar_wait(&st_full[stg], df_ph[stg]); df_ph[stg] ^= 1;
-                mbar_wait(&q_empty[qb], qe_ph[qb] ^ 1); qe_ph[qb] ^= 1;
+            int jc = 0;
+            for (int j = 0; j < nt; ++j) {
+                mbar_wait(&s_full[sb], sfph);
+                mbar_wait(&d_full[sb], sfph);
                 tc_fence_after();
                 uint32_t s[32];
                 tmem_ld32(tm_s + (static_cast<uint32_t>(q * 32) << 16) + sb * 64 + half * 32, s);
                 tmem_ld_wait();
-                const uint8_t* drow = st_smem + stg * STAGE + 2 * kBoxK + row * 128;
-                uint8_t* qrow = q_smem + qb * Q_BYTES + row * 128;
+                const uint8_t* drow = d_smem + sb * D_STAGE + row * 128;
+                uint32_t hi4[4][4], lo4[4][4];
+                float tsum = 0.f;
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     const int chunk = (half * 4 + c8) ^ (row & 7);          // SWIZZLE_128B
@@ -244,29 +295,45 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                             dv[2 * e + 1] += __uint_as_float(l4[e] & 0xFFFF0000u);
                         }
                     }
-                    uint32_t hi4[4], lo4[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
+                        const float s0 = __uint_as_float(s[c8 * 8 + 2 * e]);
+                        const float s1 = __uint_as_float(s[c8 * 8 + 2 * e + 1]);
                         // mur.py:25 / :41  x / (wh + 1e-9)
-                        const float q0 = __fdividef(dv[2 * e], __uint_as_float(s[c8 * 8 + 2 * e]) + 1e-9f);
-                        const float q1 = __fdividef(dv[2 * e + 1], __uint_as_float(s[c8 * 8 + 2 * e + 1]) + 1e-9f);
+                        const float q0 = __fdividef(dv[2 * e], s0 + 1e-9f);
+                        const float q1 = __fdividef(dv[2 * e + 1], s1 + 1e-9f);
+                        if (OBJ) tsum += kl_term(dv[2 * e], s0) + kl_term(dv[2 * e + 1], s1);
                         __nv_bfloat16 h0, l0, h1, l1;
                         split2(q0, h0, l0);
                         split2(q1, h1, l1);
-                        hi4[e] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) |
-                                 (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
-                        lo4[e] = static_cast<uint32_t>(__bfloat16_as_ushort(l0)) |
-                                 (static_cast<uint32_t>(__bfloat16_as_ushort(l1)) << 16);
+                        hi4[c8][e] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) |
+                                     (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
+                        lo4[c8][e] = static_cast<uint32_t>(__bfloat16_as_ushort(l0)) |
+                                     (static_cast<uint32_t>(__bfloat16_as_ushort(l1)) << 16);
                     }
-                    *reinterpret_cast<uint4*>(qrow + chunk * 16) = make_uint4(hi4[0], hi4[1], hi4[2], hi4[3]);
-                    *reinterpret_cast<uint4*>(qrow + kBoxK + chunk * 16) = make_uint4(lo4[0], lo4[1], lo4[2], lo4[3]);
                 }
-                fence_async_smem();                  // generic-proxy writes of Q -> visible to the MMA
+                if (OBJ) total += static_cast<double>(tsum);
+                // S and D are consumed: hand both back before waiting for the Q buffer
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) { mbar_arrive(&q_full[qb]); mbar_arrive(&s_empty[sb]); }
-                if ((j % kOutChunk) == kOutChunk - 1 || j == nt - 1) {
-                    mbar_wait(&o_full[ob], of_ph[ob]); of_ph[ob] ^= 1;
+                if (lane == 0) { mbar_arrive(&s_empty[sb]); mbar_arrive(&d_empty[sb]); }
+                mbar_wait(q_empty, qeph); qeph ^= 1;            // MMA2 of the previous tile has read Q
+                uint8_t* qrow = q_smem + row * 128;
+#pragma unroll
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    const int chunk = (half * 4 + c8) ^ (row & 7);
+                    *reinterpret_cast<uint4*>(qrow + chunk * 16) =
+                        make_uint4(hi4[c8][0], hi4[c8][1], hi4[c8][2], hi4[c8][3]);
+                    *reinterpret_cast<uint4*>(qrow + kBoxK + chunk * 16) =
+                        make_uint4(lo4[c8][0], lo4[c8][1], lo4[c8][2], lo4[c8][3]);
+                }
+                fence_async_smem();                  // generic-proxy writes of Q -> visible to the MMA
+                __syncwarp();
+                if (lane == 0) mbar_arrive(q_full);
+                if (++sb == 2) { sb = 0; sfph ^= 1; }
+                if (++jc == kOutChunk || j == nt - 1) {
+                    jc = 0;
+                    mbar_wait(&o_full[ob], (of_ph >> ob) & 1u); of_ph ^= 1u << ob;
                     tc_fence_after();
                     const uint32_t taddr = tm_o + (static_cast<uint32_t>(q * 32) << 16) + ob * 128 + half * 64;
 #pragma unroll
@@ -292,6 +359,10 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                         make_float4(sums[4 * v], sums[4 * v + 1], sums[4 * v + 2], sums[4 * v + 3]);
             }
         }
+        if (OBJ) {
+            for (int o = 16; o; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+            if (lane == 0) red[ew] = total;
+        }
     }
 
     tc_fence_before();
@@ -300,12 +371,16 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
+    if (OBJ && threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        args.obj_partial[blockIdx.x] = t;
+    }
 }
 
 int kl_smem_bytes(int KP, int NV) {
     const int kch = KP / 64;
-    const int nq = (NV == 1) ? 2 : 1;
-    return 2 * kch * kBoxK + 2 * (2 + NV) * kBoxK + nq * 2 * kBoxK + 1024 + 512;
+    return 2 * kch * kBoxK + kl_nsy(kch, NV) * 2 * kBoxK + kNSD * NV * kBoxK + 2 * kBoxK + 1024 + 512;
 }
 
 int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan) {
@@ -331,20 +406,25 @@ int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan) {
     plan->tiles_per_split = per;
     plan->slots = nsplit;
     plan->smem_bytes = kl_smem_bytes(KP, NV);
+    const int nitems = npanels * nsplit;
+    plan->grid = nitems < num_sms ? nitems : num_sms;
     return 0;
 }
 
 cudaError_t kl_panel_launch(const KlArgs& args, const KlPlan& plan, int NV, int num_sms, cudaStream_t stream) {
-    using Fn = void (*)(const KlArgs);
-    Fn fn = nullptr;
-    if (args.KP == 64) fn = (NV == 1) ? kl_panel_kernel<1, 1> : kl_panel_kernel<1, 2>;
-    else if (args.KP == 128) fn = (NV == 1) ? kl_panel_kernel<2, 1> : kl_panel_kernel<2, 2>;
+    (void)num_sms;
+    void (*fn)(const KlArgs) = nullptr;
+    const bool obj = args.obj_partial != nullptr;
+    if (args.KP == 64)
+        fn = (NV == 1) ? (obj ? kl_panel_kernel<1, 1, true> : kl_panel_kernel<1, 1, false>)
+                       : (obj ? kl_panel_kernel<1, 2, true> : kl_panel_kernel<1, 2, false>);
+    else if (args.KP == 128)
+        fn = (NV == 1) ? (obj ? kl_panel_kernel<2, 1, true> : kl_panel_kernel<2, 1, false>)
+                       : (obj ? kl_panel_kernel<2, 2, true> : kl_panel_kernel<2, 2, false>);
     else return cudaErrorInvalidValue;
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;
-    const int nitems = plan.npanels * plan.nsplit;
-    const int grid = nitems < num_sms ? nitems : num_sms;
-    fn<<<grid, kThreadsK, plan.smem_bytes, stream>>>(args);
+    fn<<<plan.grid, kThreadsK, plan.smem_bytes, stream>>>(args);
     count_launch();
     return cudaGetLastError();
 }

@@ -9,13 +9,14 @@ struct alignas(64) KlArgs {
     CUtensorMap yc[2];       // cplanes of the other factor [256][Tp], box {64, 128}
     CUtensorMap d[2];        // K-blocked data planes, box {64, 128}
     float* out;              // partial slots [nsplit][KP][Lp]
+    double* obj_partial;     // optional: one fp64 slot per CTA for the KL objective of the incoming pair
     int KP, Lp;
     int npanels, ntiles, nsplit, tiles_per_split;
     int d_rows_p;
 };
 
 struct KlPlan {
-    int npanels, ntiles, nsplit, tiles_per_split, slots, smem_bytes;
+    int npanels, ntiles, nsplit, tiles_per_split, slots, smem_bytes, grid;
 };
 
 int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan);

@@ -179,8 +179,11 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
             }
 #pragma unroll
             for (int kc = 0; kc < kchunks; ++kc) {
+                // BOTH issuers observe every phase of every stage, in ring order: a warp that skipped the
+                // other's stages could reach wait(parity p) on a barrier whose phase p^1 is still pending,
+                // which test_wait reports as "done" (parity aliasing) -> MMAs on a stage that is being filled
+                mbar_wait(&b_full[bs], bph);
                 if (mine) {
-                    mbar_wait(&b_full[bs], bph);
                     tc_fence_after();
                     const uint64_t b_desc = desc0 + ((b_addr + bs * b_stage) >> 4);
 #pragma unroll

@@ -131,9 +131,11 @@ class Engine:
         if fixed:
             check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
 
-    def mur_kl_half_step(self, side: int, lam: float):
+    def mur_kl_half_step(self, side: int, lam: float, obj_start_slot: Optional[int] = None):
+        """obj_start_slot: scalar slot that receives the KL objective of the pair this pass starts from."""
         p = self.problem()
-        check(self.lib.nmfb_mur_kl_half_step(C.byref(p), int(side), float(lam), self.stream))
+        out = None if obj_start_slot is None else self.scalars.data_ptr() + 8 * obj_start_slot
+        check(self.lib.nmfb_mur_kl_half_step(C.byref(p), int(side), float(lam), out, self.stream))
 
     def admm_half_step(self, side: int, rho, lam, prox):
         p = self.problem()

@@ -58,6 +58,7 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
 
     logging.info('Entering Main Loop.')
     lr = _loop.run(eng, step, obj0=obj0, min_iter=min_iter, max_iter=max_iter, tol1=tol1, tol2=tol2,
-                   precision=precision, verbose=verbose)
+                   precision=precision, verbose=verbose, lagged=getattr(stepper, 'lagged', False),
+                   finish=getattr(stepper, 'finish', None))
     w, h = eng.get_factors(masters=lr.masters)
     return Results(w=w, h=h, i=lr.i, obj_history=lr.obj_history, experiment=experiment)

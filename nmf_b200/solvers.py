@@ -65,7 +65,7 @@ class MurEuStepper:
 
 class MurKlStepper:
     """mur.py:122-127 with distance_type='kl' -> nmfb_mur_kl_step."""
-    phases = ["kl_w", "kl_h", "objective"]
+    phases = ["kl_w", "kl_h"]
 
     def __init__(self, eng, lambda_w=0.0, lambda_h=0.0):
         self.eng, self.lw, self.lh = eng, float(lambda_w), float(lambda_h)
@@ -74,25 +74,31 @@ class MurKlStepper:
         self.eng.objective_kl(slot=0)
         self.eng.reduce_scalar(0)
 
-    def step(self, ring_slot: int):
+    lagged = True       # _loop.run: the objective of iteration i-1 comes out of the W pass of iteration i
+
+    def step(self, ring_slot: int, prev_slot: int, mid=None):
+        """One outer iteration (mur.py:122-123).  The W pass also produces the objective (mur.py:127) of
+        the pair it starts from -- the previous iteration's -- into scalars[prev_slot*8]; `mid` is called
+        right after it so that the host can read that value while the H pass runs."""
         e = self.eng
-        if e.world == 1:
-            e.mur_kl_step(self.lw, self.lh, obj_slot=ring_slot * 8)
-            return
-        e.mur_kl_half_step(0, self.lw)                    # my rows of W from my rows of V and the full H
+        e.mur_kl_half_step(0, self.lw, obj_start_slot=prev_slot * 8)   # my rows of W (all of them unsharded)
+        e.reduce_scalar(prev_slot * 8)
+        if mid is not None:
+            mid()
         e.gather_factor(e.w)
-        e.mur_kl_half_step(1, self.lh)                    # my columns of H from my columns of V and the new W
+        e.mur_kl_half_step(1, self.lh)                                 # my columns of H with the new W
         e.gather_factor(e.h)
-        e.objective_kl(slot=ring_slot * 8)
-        e.reduce_scalar(ring_slot * 8)
+
+    def finish(self, ring_slot: int):
+        """Stand-alone objective of the current pair (after the last iteration)."""
+        self.eng.objective_kl(slot=ring_slot * 8)
+        self.eng.reduce_scalar(ring_slot * 8)
 
     def phase_names(self):
         return self.phases
 
     def phase_pairs(self):
-        if self.eng.world == 1:
-            return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
-        return []
+        return [("kl_w", 0, 1), ("kl_h", 2, 3)]
 
     def roofline(self, phase_ms, peaks):
         """Dominant kernel = the fused GEMM -> quotient -> GEMM kernel (one launch per side):
@@ -100,7 +106,7 @@ class MurKlStepper:
         e = self.eng
         if "kl_w" not in phase_ms:
             return None
-        ms = 0.5 * (phase_ms["kl_w"] + phase_ms["kl_h"])
+        ms = 0.5 * (phase_ms["kl_w"] + phase_ms["kl_h"])     # W pass carries the objective terms as well
         tf = 4.0 * e.m * e.n * e.k / (ms * 1e-3) / 1e12
         gbs = 2.0 * e.m * e.n * e.nv / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
