@@ -274,7 +274,7 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                 tmem_ld_wait();
                 const uint8_t* drow = d_smem + sb * D_STAGE + row * 128;
                 uint32_t hi4[4][4], lo4[4][4];
-                float tsum = 0.f;
+                float tsum[2] = {0.f, 0.f};                 // objective terms (OBJ), two chains
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     const int chunk = (half * 4 + c8) ^ (row & 7);          // SWIZZLE_128B
@@ -297,22 +297,25 @@ kl_panel_kernel(const __grid_constant__ KlArgs args) {
                     }
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const float s0 = __uint_as_float(s[c8 * 8 + 2 * e]);
-                        const float s1 = __uint_as_float(s[c8 * 8 + 2 * e + 1]);
-                        // mur.py:25 / :41  x / (wh + 1e-9)
-                        const float q0 = __fdividef(dv[2 * e], s0 + 1e-9f);
-                        const float q1 = __fdividef(dv[2 * e + 1], s1 + 1e-9f);
-                        if (OBJ) tsum += kl_term(dv[2 * e], s0) + kl_term(dv[2 * e + 1], s1);
+                        float qq[2];
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const float v = dv[2 * e + u];
+                            const float sv = __uint_as_float(s[c8 * 8 + 2 * e + u]);
+                            const float r = rcp_approx(sv + 1e-9f);          // mur.py:25 / :41  x / (wh + 1e-9)
+                            qq[u] = v * r;
+                            if (OBJ) tsum[u] += kl_term_r(v, sv, r);
+                        }
                         __nv_bfloat16 h0, l0, h1, l1;
-                        split2(q0, h0, l0);
-                        split2(q1, h1, l1);
+                        split2(qq[0], h0, l0);
+                        split2(qq[1], h1, l1);
                         hi4[c8][e] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) |
                                      (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
                         lo4[c8][e] = static_cast<uint32_t>(__bfloat16_as_ushort(l0)) |
                                      (static_cast<uint32_t>(__bfloat16_as_ushort(l1)) << 16);
                     }
                 }
-                if (OBJ) total += static_cast<double>(tsum);
+                if (OBJ) total += static_cast<double>(tsum[0] + tsum[1]);
                 // S and D are consumed: hand both back before waiting for the Q buffer
                 tc_fence_before();
                 __syncwarp();

@@ -279,22 +279,29 @@ __device__ __forceinline__ float fixed_slice(float x, float unit, float inv_unit
     return rintf(x * inv_unit) * unit;
 }
 
-// v*log(v/s) - v + s (utils.py:23-26; +inf / NaN of the log term map to 0) without the cancellation
-// of the naive form: with d = (v - s)/s the term is s*((1+d)*log1p(d) - d) = s*d^2*(1/2 - d/6 + ...).
-__device__ __forceinline__ float kl_term(float v, float s) {
-    const float d = __fdividef(v - s, s);
+__device__ __forceinline__ float rcp_approx(float x) {
     float r;
-    if (fabsf(d) < 0.125f) {
-        const float p = 0.5f + d * (-1.f / 6.f + d * (1.f / 12.f + d * (-1.f / 20.f + d * (1.f / 30.f +
-                        d * (-1.f / 42.f + d * (1.f / 56.f + d * (-1.f / 72.f)))))));
-        r = s * d * d * p;
-    } else {
-        r = v * __logf(__fdividef(v, s)) - v + s;  // no cancellation to speak of out here
-    }
-    if (v == 0.f) r = s;                           // 0*log(0/s) = NaN -> 0
-    if (s == 0.f) r = -v;                          // v*log(v/0) = +inf -> 0 (and 0/0 -> NaN -> 0)
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 
+// v*log(v/s) - v + s (utils.py:23-26; +inf / NaN of the log term map to 0), branch-free.  r = 1/(s + 1e-9).
+// Near v == s the naive form cancels: with d = (v - s)/s the term is s*((1+d)*log1p(d) - d) =
+// s*d^2*(1/2 - d/6 + d^2/12 - ...), used for |d| < 1/8 (six coefficients: truncation 1.4e-7 relative);
+// elsewhere v*ln(v/s) - (v - s) loses nothing.  Both are evaluated and selected -- a per-element branch
+// made the fused objective pass of kl_panel_kernel three times slower than the pass without it.
+__device__ __forceinline__ float kl_term_r(float v, float s, float r) {
+    const float e = v - s;
+    const float d = e * r;
+    const float p = fmaf(d, fmaf(d, fmaf(d, fmaf(d, fmaf(d, -1.f / 42.f, 1.f / 30.f), -1.f / 20.f), 1.f / 12.f),
+                                 -1.f / 6.f), 0.5f);
+    const float a = (s * d) * (d * p);
+    const float b = fmaf(v * 0.69314718f, __log2f(v * r), -e);
+    float t = fabsf(d) < 0.125f ? a : b;
+    t = (v == 0.f) ? s : t;                        // 0*log(0/s) = NaN -> 0
+    t = (s == 0.f) ? -v : t;                       // v*log(v/0) = +inf -> 0 (and 0/0 -> NaN -> 0)
+    return t;
+}
+__device__ __forceinline__ float kl_term(float v, float s) { return kl_term_r(v, s, rcp_approx(s + 1e-9f)); }
 
 }  // namespace nmfb

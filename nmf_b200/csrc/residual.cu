@@ -78,6 +78,7 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
     uint64_t* a_full = bars + 16;
     uint64_t* a_empty = bars + 17;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+    uint64_t* go_b = bars + 19;          // issuer A -> issuer B: "tile ready"
     double* red = reinterpret_cast<double*>(bars + 20);      // [8]
 
     const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
@@ -102,7 +103,8 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
             mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8);
         }
         mbar_init(a_full, 1);
-        mbar_init(a_empty, 2);
+        mbar_init(a_empty, args.ntiles < 2 ? 1 : 2);      // one column tile per row: issuer A works alone
+        mbar_init(go_b, 1);
         fence_mbar_init();
     }
     if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
@@ -148,42 +150,40 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                 }
             }
         }
-    } else if (warp == 1 || warp == 11) {
-        // Whole warp, converged: every operand below is warp-uniform, one elected lane issues (ptx.cuh).
-        // Both issuer warps walk ALL tiles so that their ring / row bookkeeping stays in step; each one
-        // waits, issues and commits only for the tiles of its own parity (= its own accumulator).
-        const int me = (warp == 1) ? 0 : 1;
+    } else if (warp == 1) {
+        // ---------------------------------------------------- MMA issuer A (even tiles) + dispatcher
+        // Whole warp, converged: every operand is warp-uniform, one elected lane issues (ptx.cuh).
+        // This warp performs ALL pipeline waits (W planes, accumulators, H^T stages) in ring order, for the
+        // odd tiles too, and then hands those to issuer B through go_b.  Every mbarrier therefore has
+        // exactly one waiter that sees every phase: with two independent waiters one of them skips the
+        // other's phases, and mbarrier.try_wait.parity cannot tell phase p from phase p + 2 (observed as
+        // MMAs on half-filled stages and, with both warps waiting on everything, as multi-tile stalls).
         constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
         const uint64_t desc0 = umma_desc_k_sw128(0);
         int bs = 0; uint32_t bph = 0;
-        uint32_t accph = 0;
+        uint32_t accph = 0;                     // bit b = parity of acc_empty[b]
         uint32_t aph = 0;
         const uint64_t a_desc = desc0 + (smem_u32(a_smem) >> 4);
         const uint32_t b_addr = smem_u32(b_smem);
         const int b_stage = L.b_stage_bytes, nbs = L.nbs;
-        const uint32_t d = tmem_base + me * 128;
         int tj = static_cast<int>(t_begin % args.ntiles);
         bool new_row = true;
         int par = 0;
+        const bool solo = args.ntiles < 2;      // rows of one tile would let B release a row before A is done
         for (long t = t_begin; t < t_end; ++t, par ^= 1) {
-            const bool mine = (par == me);
             if (new_row) {
                 mbar_wait(a_full, aph);
                 aph ^= 1;
                 new_row = false;
             }
-            if (mine) {
-                mbar_wait(&acc_empty[me], accph ^ 1);
-                accph ^= 1;
+            mbar_wait(&acc_empty[par], ((accph >> par) & 1u) ^ 1u);
+            accph ^= 1u << par;
+            if (par == 0 || solo) {
                 tc_fence_after();
-            }
+                const uint32_t d = tmem_base + par * 128;
 #pragma unroll
-            for (int kc = 0; kc < kchunks; ++kc) {
-                // BOTH issuers observe every phase of every stage, in ring order: a warp that skipped the
-                // other's stages could reach wait(parity p) on a barrier whose phase p^1 is still pending,
-                // which test_wait reports as "done" (parity aliasing) -> MMAs on a stage that is being filled
-                mbar_wait(&b_full[bs], bph);
-                if (mine) {
+                for (int kc = 0; kc < kchunks; ++kc) {
+                    mbar_wait(&b_full[bs], bph);
                     tc_fence_after();
                     const uint64_t b_desc = desc0 + ((b_addr + bs * b_stage) >> 4);
 #pragma unroll
@@ -198,14 +198,64 @@ residual_kernel(const __grid_constant__ ResidualArgs args) {
                     }
                     if (CS > 1) umma_commit_mcast_warp(&b_empty[bs], cmask);
                     else        umma_commit_warp(&b_empty[bs]);
+                    if (++bs == nbs) { bs = 0; bph ^= 1; }
                 }
-                if (++bs == nbs) { bs = 0; bph ^= 1; }
+                umma_commit_warp(&acc_full[par]);
+            } else {
+#pragma unroll
+                for (int kc = 0; kc < kchunks; ++kc) {
+                    mbar_wait(&b_full[bs], bph);
+                    if (++bs == nbs) { bs = 0; bph ^= 1; }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(go_b);       // tile t: operands landed, accumulator 1 free
             }
-            if (mine) umma_commit_warp(&acc_full[me]);
             if (++tj == args.ntiles) { tj = 0; new_row = true; }
             // end of this CTA's tiles of the row: both issuers release the W planes (count 2); a warp
             // without MMAs in flight arrives at once
             if (t + 1 >= t_end || new_row) umma_commit_warp(a_empty);
+        }
+    } else if (warp == 11) {
+        // ---------------------------------------------------- MMA issuer B (odd tiles): waits on go_b only
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+        const uint64_t desc0 = umma_desc_k_sw128(0);
+        int bs = 0;
+        uint32_t goph = 0;
+        const uint64_t a_desc = desc0 + (smem_u32(a_smem) >> 4);
+        const uint32_t b_addr = smem_u32(b_smem);
+        const int b_stage = L.b_stage_bytes, nbs = L.nbs;
+        const uint32_t d = tmem_base + 128;
+        int tj = static_cast<int>(t_begin % args.ntiles);
+        int par = 0;
+        for (long t = (args.ntiles < 2 ? t_end : t_begin); t < t_end; ++t, par ^= 1) {
+            if (par == 1) {
+                mbar_wait(go_b, goph);
+                goph ^= 1;
+                tc_fence_after();
+            }
+#pragma unroll
+            for (int kc = 0; kc < kchunks; ++kc) {
+                if (par == 1) {
+                    const uint64_t b_desc = desc0 + ((b_addr + bs * b_stage) >> 4);
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t a_hi = a_desc + (((0 * kchunks + kc) * kBox + ks * 32) >> 4);
+                        const uint64_t a_lo = a_desc + (((1 * kchunks + kc) * kBox + ks * 32) >> 4);
+                        const uint64_t b_hi = b_desc + ((ks * 32) >> 4);
+                        const uint64_t b_lo = b_desc + ((kBox + ks * 32) >> 4);
+                        umma_bf16_warp(d, a_hi, b_hi, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
+                        umma_bf16_warp(d, a_hi, b_lo, idesc, 1);
+                        umma_bf16_warp(d, a_lo, b_hi, idesc, 1);
+                    }
+                    if (CS > 1) umma_commit_mcast_warp(&b_empty[bs], cmask);
+                    else        umma_commit_warp(&b_empty[bs]);
+                }
+                if (++bs == nbs) bs = 0;
+            }
+            if (par == 1) umma_commit_warp(&acc_full[1]);
+            bool row_end = false;
+            if (++tj == args.ntiles) { tj = 0; row_end = true; }
+            if (t + 1 >= t_end || row_end) umma_commit_warp(a_empty);
         }
     } else if (warp == 10) {
         if (lane == 0) {
