@@ -291,7 +291,7 @@ def run_reference(args):
         "e2e": {"value": its, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -397,7 +397,7 @@ def run_b200(args):
         its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
         line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -447,8 +447,26 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
             "what": "NMF(V_host fp32 pinned, k).factorize(max_iter=steps): ingest + iterations + factor download"}
 
 
+_JSON_FD = None
+
+
+def emit(line: dict):
+    """The contract is ONE JSON line on stdout: libraries (NCCL prints its version banner there when
+    NCCL_DEBUG is set on the box) write to fd 2 for the duration of the run, the line goes to the real fd 1."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
     args = parse_args()
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -66,6 +66,9 @@ class Engine:
         self.row_win, self.col_win = mb[self.rank], nb[self.rank]
         self.row_range = (self.row_win[0], self.row_win[0] + live_rows(self.m, *self.row_win))
         self.col_range = (self.col_win[0], self.col_win[0] + live_rows(self.n, *self.col_win))
+        if self.row_range[1] <= self.row_range[0] or self.col_range[1] <= self.col_range[0]:
+            raise ValueError(f"{self.world} ranks leave rank {self.rank} without rows or columns of a "
+                             f"{self.m} x {self.n} problem (shards are multiples of 256); use fewer ranks")
         props = torch.cuda.get_device_properties(self.device)
         if props.major != 10:
             raise RuntimeError(f"nmf_b200 is built for sm_100a only; device is sm_{props.major}{props.minor}")

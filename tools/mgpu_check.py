@@ -43,7 +43,9 @@ def same_on_all_ranks(value):
     return [int(p) for p in parts]
 
 
-for (m, n, k, iters) in [(1000, 700, 10, 30), (2048, 1536, 64, 40), (1500, 2500, 128, 30)]:
+SHAPES = [(1000, 700, 10, 30), (2048, 1536, 64, 40), (1500, 2500, 128, 30)] if world <= 2 else \
+    [(3700, 3900, 10, 30), (4096, 6144, 64, 40), (7500, 3800, 128, 30)]      # every rank keeps live rows / columns
+for (m, n, k, iters) in SHAPES:
     v = orc.planted(m, n, k, 0).astype(np.float64)
     w0, h0 = orc.seeded_init(m, n, k, 1)
     shape = f"m={m} n={n} k={k}"
