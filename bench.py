@@ -45,6 +45,15 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "mur_eu_65536x65536_k128"
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the
+# `ncu --set full` captures of these workloads (profiles/r01b_all_paths.md); per launch, like `achieved`.
+NCU_TRAFFIC = {
+    ("panel_gemm_kernel", "mur_eu_65536x65536_k128"): 8.624068e9 + 85.743104e6,
+    ("kl_panel_kernel", "mur_kl_20000x50000_k128"): 2.061042e9 + 64.324352e6,
+    ("panel_gemm_kernel", "admm_65536x16384_k128"): 4.393657e9 + 188.351488e6,        # exact-hi variant
+    ("panel_gemm_kernel", "ao_admm_65536x16384_k128"): 4.393657e9 + 188.351488e6,
+}
+
 
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -369,6 +378,11 @@ def run_b200(args):
     phase_ms = {nm: float(np.mean([evs[i][a].elapsed_time(evs[i][b]) for i in range(steps)]))
                 for nm, a, b in pairs}
     roof = stepper.roofline(phase_ms, peaks)
+    if roof is not None and world == 1:
+        t = NCU_TRAFFIC.get((roof.get("kernel"), args.workload))
+        if t is not None:
+            roof["traffic"] = t
+            roof["traffic_source"] = "ncu --set full, one launch, profiles/r01b_all_paths.md"
 
     line = {
         "metric": "nmf_outer_iterations_per_second", "value": value, "unit": "it/s", "n_gpus": world,

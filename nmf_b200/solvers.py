@@ -45,13 +45,18 @@ class MurEuStepper:
         e = self.eng
         ms = 0.5 * (phase_ms["gemm_w"] + phase_ms["gemm_h"])
         mpp = getattr(self, "mma_per_product", 2)
+        if mpp == 3 and getattr(e, "fixed", False):
+            mpp = 5                                          # exact-hi contraction (panel_gemm_exact.cu)
         flops = 2.0 * e.m * e.n * e.k / e.world              # per rank (its shard of V)
         vbytes = 2.0 * e.m * e.n * e.nv / e.world
         tf = flops / (ms * 1e-3) / 1e12
         gbs = vbytes / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
         tensor_frac, hbm_frac = tf / peak, gbs / peaks["hbm_gbs"]
-        bound = "tensor" if tensor_frac * mpp >= hbm_frac else "hbm"   # mpp MMAs execute per product
+        # the binding roof is the one whose lower bound on the ALGORITHMIC work is larger (with
+        # 2-byte V read once these shapes sit on the ridge or on the HBM side); the executed-MMA fraction
+        # (mpp MMAs per algorithmic product) is reported next to it
+        bound = "tensor" if tensor_frac >= hbm_frac else "hbm"
         out = {"kernel": "panel_gemm_kernel", "bound": bound, "ms_per_launch": ms,
                "executed_mma_per_product": mpp, "traffic": None,
                "tensor": {"achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tensor_frac,
