@@ -19,6 +19,17 @@ RING = 8          # scalar mailbox ring (slots of 8 doubles each)
 LAG = 1
 
 
+class _NoEvent:
+    """Stand-in for torch.cuda.Event when the engine lives on the CPU (host-logic tests only: the
+    product engine refuses to exist without a CUDA device)."""
+
+    def record(self, stream=None):
+        pass
+
+    def synchronize(self):
+        pass
+
+
 class LoopResult:
     __slots__ = ("i", "obj_history", "masters", "extras")
 
@@ -40,7 +51,10 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
     stand-alone objective for the very last iteration."""
     res = LoopResult()
     res.obj_history = [obj0]
-    host = torch.zeros(RING * 8, dtype=torch.float64).pin_memory()
+    on_gpu = torch.device(engine.device).type == "cuda"
+    host = torch.zeros(RING * 8, dtype=torch.float64)
+    if on_gpu:
+        host = host.pin_memory()
     snaps = [None, None]
     pending = deque()
     stopped = False
@@ -64,8 +78,8 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
 
     def publish(i_obj, slot):
         host[slot * 8: slot * 8 + 8].copy_(engine.scalars[slot * 8: slot * 8 + 8], non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(engine.device))
+        ev = torch.cuda.Event() if on_gpu else _NoEvent()
+        ev.record(torch.cuda.current_stream(engine.device) if on_gpu else None)
         pending.append((i_obj, slot, ev))
 
     for i in range(max_iter):
@@ -93,5 +107,6 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
         process(pending.popleft())
     if not stopped:
         logging.info('Max iteration reached.')
-    torch.cuda.current_stream(engine.device).synchronize()
+    if on_gpu:
+        torch.cuda.current_stream(engine.device).synchronize()
     return res

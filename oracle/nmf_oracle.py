@@ -170,13 +170,26 @@ def mur_run(v, k, w0, h0, *, distance_type="kl", min_iter=100, max_iter=100000,
 # --------------------------------------------------------------------------- #
 # proximal operators shared by ADMM and AO-ADMM
 # --------------------------------------------------------------------------- #
+def tikhonov_system(kk: int, lam: float, rho: float) -> np.ndarray:
+    """admm.py:142-150: a = 1/rho * (lam * T^T T + rho * I) with T = tridiag(-1, 2, -1) of order kk
+    (the component axis: `n = mat_aux.shape[0]`, and prox is always handed k x cols arrays)."""
+    t = 2.0 * np.eye(kk) - np.eye(kk, k=1) - np.eye(kk, k=-1)
+    return (lam / rho) * (t.T @ t) + np.eye(kk)
+
+
 def prox(kind: str, aux, dual, rho, lam):
-    """admm.py:126-139 / ao_admm.py:113-124.  'l2n' with lam == 0 reduces to 'nn'
-    (admm.py:141-156: the Tikhonov system becomes the identity)."""
+    """admm.py:126-156 / ao_admm.py:113-135 on component-major (k x cols) arrays.
+    'l2n': solve the Tikhonov system along the component axis, then clip (admm.py:141-156; with
+    lam == 0 the system is the identity, i.e. 'nn').  The reference uses a sparse solve of the same
+    k x k pentadiagonal SPD matrix; ao_admm.py:128 builds it without dtype=object and therefore raises
+    on NumPy >= 1.24 -- for AO-ADMM this restates the intended arithmetic (parity unpinned there)."""
     if kind == "nn" or (kind == "l2n" and lam == 0):
         return np.maximum(aux - dual, 0.0)
     if kind == "l1n":
         return np.maximum(aux - dual - lam / rho, 0.0)
+    if kind == "l2n":
+        a = tikhonov_system(aux.shape[0], lam, rho)
+        return np.maximum(np.linalg.solve(a, aux - dual), 0.0)
     raise TypeError("Unknown prox_type.")
 
 
@@ -205,7 +218,7 @@ def admm_run(v, k, w0, h0, *, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n"), min_iter
         h_aux = admm_aux(h, dual_h, w_aux, v, rho)
         w_aux = admm_aux(w.T, dual_w.T, h_aux.T, v.T, rho).T
         h = prox(reg_h[1], h_aux, dual_h, rho, reg_h[0])
-        w = prox(reg_w[1], w_aux, dual_w, rho, reg_w[0])
+        w = prox(reg_w[1], w_aux.T, dual_w.T, rho, reg_w[0]).T      # admm.py:300-301
         dual_h = dual_h + h - h_aux
         dual_w = dual_w + w - w_aux
         hist.append(objective(v, w @ h))

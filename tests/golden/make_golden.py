@@ -68,6 +68,10 @@ CASES = {
         v=dict(kind="planted", m=200, n=160, k=6, seed=15), k=6, init_seed=16, method="admm",
         kw=dict(rho=10, reg_w=(0.05, "l1n"), reg_h=(0, "nn"), min_iter=100, max_iter=30,
                 tol1=1e-3, tol2=1e-3, nndsvd_init=(True, "zero"))),
+    "admm_l2n": dict(
+        v=dict(kind="planted", m=320, n=224, k=12, seed=21), k=12, init_seed=22, method="admm",
+        kw=dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"), min_iter=100, max_iter=40,
+                tol1=1e-3, tol2=1e-3, nndsvd_init=(False, "zero"))),
     "ao_admm_l1n": dict(
         v=dict(kind="planted", m=512, n=384, k=16, seed=17), k=16, init_seed=18, method="ao_admm",
         kw=dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), min_iter=100, max_iter=40, admm_iter=5,
@@ -80,7 +84,10 @@ CASES = {
 
 
 def main():
+    only = set(sys.argv[1:])
     for name, case in CASES.items():
+        if only and name not in only:
+            continue
         v = make_v(case["v"])
         np.random.seed(case["init_seed"])
         model = NMF(v.copy(), case["k"])
