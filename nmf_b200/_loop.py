@@ -41,14 +41,19 @@ class LoopResult:
 
 
 def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision, verbose=True,
-        on_extra=None, lagged=False, finish=None):
+        on_extra=None, lagged=False, finish=None, checkpoint_every=0, on_checkpoint=None):
     """enqueue_step(slot) must enqueue one outer iteration that leaves the objective in
     engine.scalars[slot*8] (and optional extras in [slot*8+1 : slot*8+8]).
 
     lagged=True (MUR-KL): the objective of iteration i-1 is a by-product of the first kernel of iteration
     i.  enqueue_step(slot, prev_slot, mid) then writes it to scalars[prev_slot*8] and calls mid() right
     after that kernel; the host reads it while the rest of iteration i runs, and finish(slot) enqueues a
-    stand-alone objective for the very last iteration."""
+    stand-alone objective for the very last iteration.
+
+    checkpoint_every=N > 0: the reference's commented hook (`if i % 100 == 0: save_results(...)`,
+    mur.py:138-140): the factors of every N-th iteration are snapshotted on the stream like those of a
+    possible stop, and on_checkpoint(i, (w_master, h_master), obj_history) is called once the objective of
+    that iteration has been read -- the device never waits for the file."""
     res = LoopResult()
     res.obj_history = [obj0]
     on_gpu = torch.device(engine.device).type == "cuda"
@@ -75,6 +80,8 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
             logging.warning('Converged.')
             res.masters = snaps[i % 2]
             stopped = True
+        if checkpoint_every and on_checkpoint is not None and i % checkpoint_every == 0 and not stopped:
+            on_checkpoint(i, snaps[i % 2], list(res.obj_history))
 
     def publish(i_obj, slot):
         host[slot * 8: slot * 8 + 8].copy_(engine.scalars[slot * 8: slot * 8 + 8], non_blocking=True)
@@ -90,7 +97,7 @@ def run(engine, enqueue_step, *, obj0, min_iter, max_iter, tol1, tol2, precision
         else:
             enqueue_step(slot)
             publish(i, slot)
-        if i > min_iter:
+        if i > min_iter or (checkpoint_every and i % checkpoint_every == 0):
             if snaps[i % 2] is None:
                 snaps[i % 2] = (torch.empty_like(engine.w.master), torch.empty_like(engine.h.master))
             snaps[i % 2][0].copy_(engine.w.master, non_blocking=True)

@@ -14,7 +14,7 @@ import numpy as np
 from . import _loop
 from .engine import Engine
 from .solvers import make_stepper, prox_code
-from .utils import tol_precision
+from .utils import make_checkpointer, tol_precision
 
 Experiment = namedtuple('Experiment', 'method components rho distance_type nndsvd_init min_iter max_iter tol1 tol2 lambda_w prox_w lambda_h prox_h')
 Results = namedtuple('Results', 'w h i obj_history experiment')
@@ -27,7 +27,8 @@ def _raise_if_not_pd(i, vals):
 
 def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_iter=10,
          max_iter=100000, tol1=1e-3, tol2=1e-3, nndsvd_init=(True, 'zero'), save_dir='./results/',
-         w0=None, h0=None, verbose=True, engine=None, comm=None):
+         w0=None, h0=None, verbose=True, engine=None, comm=None,
+      checkpoint_every=0, checkpoint_path=None):
     """v: (m, n) data, k: components.  Extra (non-reference) keywords: w0 / h0, verbose, engine, and
     comm (True or a torch.distributed group: 1-D sharded run, one process per GPU)."""
     experiment = Experiment(method='admm', components=k, rho=rho, distance_type=distance_type,
@@ -58,6 +59,8 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
     stepper.prepare()
     obj0 = eng.read_scalar(0)
     lr = _loop.run(eng, stepper.step, obj0=obj0, min_iter=min_iter, max_iter=max_iter, tol1=tol1, tol2=tol2,
-                   precision=precision, verbose=verbose, on_extra=_raise_if_not_pd)
+                   precision=precision, verbose=verbose, on_extra=_raise_if_not_pd,
+                   checkpoint_every=checkpoint_every,
+                   on_checkpoint=make_checkpointer(eng, experiment, checkpoint_every, checkpoint_path))
     w, h = eng.get_factors(masters=lr.masters)
     return Results(w=w, h=h, i=lr.i, obj_history=lr.obj_history, experiment=experiment)

@@ -14,7 +14,7 @@ import numpy as np
 from . import _loop
 from .engine import Engine
 from .solvers import make_stepper
-from .utils import tol_precision
+from .utils import make_checkpointer, tol_precision
 
 Experiment = namedtuple('Experiment', 'method components distance_type nndsvd_init max_iter tol1 tol2 lambda_w lambda_h')
 Results = namedtuple('Results', 'w h i obj_history experiment')
@@ -22,7 +22,8 @@ Results = namedtuple('Results', 'w h i obj_history experiment')
 
 def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, tol2=1e-5,
         lambda_w=0.0, lambda_h=0.0, nndsvd_init=(False, 'zero'), save_dir='./results/',
-        w0=None, h0=None, verbose=True, engine=None, comm=None):
+        w0=None, h0=None, verbose=True, engine=None, comm=None,
+        checkpoint_every=0, checkpoint_path=None):
     """x: (m, n) non-negative data, k: number of components.  Extra (non-reference) keywords:
     w0 / h0 = explicit initial factors, verbose = per-iteration print, engine = reuse device state."""
     experiment = Experiment(method='mur', components=k, distance_type=distance_type,
@@ -59,6 +60,7 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
     logging.info('Entering Main Loop.')
     lr = _loop.run(eng, step, obj0=obj0, min_iter=min_iter, max_iter=max_iter, tol1=tol1, tol2=tol2,
                    precision=precision, verbose=verbose, lagged=getattr(stepper, 'lagged', False),
-                   finish=getattr(stepper, 'finish', None))
+                   finish=getattr(stepper, 'finish', None), checkpoint_every=checkpoint_every,
+                   on_checkpoint=make_checkpointer(eng, experiment, checkpoint_every, checkpoint_path))
     w, h = eng.get_factors(masters=lr.masters)
     return Results(w=w, h=h, i=lr.i, obj_history=lr.obj_history, experiment=experiment)

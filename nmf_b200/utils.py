@@ -33,3 +33,20 @@ def save_results(save_str, w, h, i, obj_history, experiment):
     """np.savez with the reference's key set (utils.py:103): w, h, i, obj_history, experiment."""
     np.savez(save_str, w=w, h=h, i=i, obj_history=obj_history, experiment=experiment)
     print('Results saved in {}.'.format(save_str))
+
+
+def make_checkpointer(engine, experiment, checkpoint_every, checkpoint_path):
+    """on_checkpoint callback for _loop.run: downloads the snapshotted factors of iteration i and writes
+    them with the reference's key set (utils.py:103) to `checkpoint_path` (np.savez adds .npz).  A run is
+    resumed by passing the saved w / h as w0 / h0 (exact for `mur`, whose whole state they are; `admm` /
+    `ao_admm` restart their duals from zero, like a fresh reference run from that point)."""
+    if not checkpoint_every or checkpoint_path is None:
+        return None
+
+    def on_checkpoint(i, masters, obj_history):
+        if getattr(engine, "rank", 0) != 0:
+            return
+        w, h = engine.get_factors(masters=masters)
+        np.savez(checkpoint_path, w=w, h=h, i=i, obj_history=obj_history, experiment=experiment._asdict())
+
+    return on_checkpoint

@@ -109,3 +109,44 @@ def test_loop_prints_like_the_reference(capsys):
     lr = _loop.run(eng, step, obj0=eng.objective(), min_iter=100, max_iter=3, tol1=1e-5, tol2=1e-3, precision=5)
     out = capsys.readouterr().out.splitlines()
     assert out == ['[{}]: {:.5f}'.format(i, lr.obj_history[i + 1]) for i in range(3)]      # mur.py:128
+
+
+@pytest.mark.parametrize("lagged", [False, True])
+def test_checkpoints_hold_the_factors_of_their_iteration(lagged):
+    """mur.py:138-140 (the commented `if i % 100 == 0: save_results(...)` hook): every N-th iteration the
+    callback sees the factors OF that iteration although the device is already further along."""
+    kind = "kl" if lagged else "eu"
+    v, k, w0, h0 = _case(kind)
+    iters, every = 11, 4
+    want = orc.mur_run(v, k, w0, h0, distance_type=kind, min_iter=10**9, max_iter=iters,
+                       snap=lambda i: i % every == 0)
+    eng = StubEngine(v, w0, h0, kind)
+    seen = []
+
+    def on_checkpoint(i, masters, hist):
+        seen.append((i, masters[0].numpy().T.copy(), masters[1].numpy().copy(), len(hist)))
+
+    def step_plain(slot):
+        eng.update()
+        eng.scalars[slot * 8] = eng.objective()
+
+    def step_lagged(slot, prev, mid):
+        eng.scalars[prev * 8] = eng.objective()
+        if mid is not None:
+            mid()
+        eng.update()
+
+    def finish(slot):
+        eng.scalars[slot * 8] = eng.objective()
+
+    common = dict(obj0=eng.objective(), min_iter=10**9, max_iter=iters, tol1=1e-5, tol2=1e-5, precision=5,
+                  verbose=False, checkpoint_every=every, on_checkpoint=on_checkpoint)
+    if lagged:
+        _loop.run(eng, step_lagged, lagged=True, finish=finish, **common)
+    else:
+        _loop.run(eng, step_plain, **common)
+    assert [s[0] for s in seen] == [0, 4, 8]
+    for (i, w, h, nh), (j, w_ref, h_ref) in zip(seen, want.snaps):
+        assert i == j and nh == i + 2                       # obj_history up to and including iteration i
+        np.testing.assert_allclose(w, w_ref, rtol=1e-12)
+        np.testing.assert_allclose(h, h_ref, rtol=1e-12)
