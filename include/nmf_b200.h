@@ -191,7 +191,7 @@ int nmfb_mur_kl_step_lagged(const nmfb_problem* p, float lambda_w, float lambda_
                             void* stream);
 
 /* ---- ADMM / AO-ADMM ------------------------------------------------------------------------- */
-typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1 } nmfb_prox;   /* admm.py:126-139 */
+typedef enum nmfb_prox { NMFB_PROX_NN = 0, NMFB_PROX_L1N = 1, NMFB_PROX_L2N = 2 } nmfb_prox;   /* admm.py:126-156 */
 
 typedef struct nmfb_admm_state {
     nmfb_factor w_aux, h_aux;       /* ADMM only: signed auxiliaries (admm.py:27-28); cplanes hold 3 planes */
@@ -206,7 +206,15 @@ typedef struct nmfb_admm_state {
     double* norm_partial;           /* fp64 [4 * max(Mp,Np)/64]                                           */
     int exact;                      /* 1: V planes and factor cplanes are fixed-point; use the exact-hi   */
                                     /*    contractions (needs problem.v_rows.fixed / v_cols.fixed)        */
+    double* binv;                   /* fp64 [2][KP][KP] or NULL: inverse Tikhonov systems of prox l2n,    */
+                                    /* ((lambda/rho) T^T T + I)^-1, [0] H-side, [1] W-side (admm.py:141-156) */
+    double* tik_scratch;            /* fp64 [KP][KP] + [4] scratch for building them (NULL iff binv NULL) */
 } nmfb_admm_state;
+
+/* prox l2n with lambda > 0 (k <= 128): (re)build s->binv[side] from lambda and the rho of that side's system
+ * (s->scal[side], valid once the side's Cholesky has been enqueued).  nmfb_admm_half_step, nmfb_admm_step and
+ * nmfb_aoadmm_step call it themselves; a caller of nmfb_aoadmm_side_begin calls it right after that. */
+int nmfb_admm_prepare_l2n(const nmfb_problem* p, const nmfb_admm_state* s, int side, double lambda, void* stream);
 
 /* ainv = (gram + rho I)^-1 by a shared-memory Cholesky (fp64), rho = rho_in (rho_mode 0, admm.py:220)
  * or trace(gram)/k (rho_mode 1, ao_admm.py:54); *rho_out = rho.  flags[0] is raised when the matrix is

@@ -44,7 +44,8 @@ class Problem(C.Structure):         # struct nmfb_problem
 class AdmmState(C.Structure):       # struct nmfb_admm_state
     _fields_ = [("w_aux", Factor), ("h_aux", Factor), ("dual_w", c_void_p), ("dual_h", c_void_p),
                 ("ainv", c_void_p), ("chol_scratch", c_void_p), ("c64", c_void_p), ("scal", c_void_p),
-                ("flags", c_void_p), ("norm_partial", c_void_p), ("exact", c_int)]
+                ("flags", c_void_p), ("norm_partial", c_void_p), ("exact", c_int),
+                ("binv", c_void_p), ("tik_scratch", c_void_p)]
 
 
 _SIGNATURES = {
@@ -77,6 +78,7 @@ _SIGNATURES = {
     "nmfb_mur_kl_half_step": (c_int, [P(Problem), c_int, c_float, c_void_p, c_void_p]),
     "nmfb_mur_kl_step_lagged": (c_int, [P(Problem), c_float, c_float, c_void_p, c_void_p]),
     "nmfb_admm_half_step": (c_int, [P(Problem), P(AdmmState), c_int, C.c_double, c_float, c_int, c_void_p]),
+    "nmfb_admm_prepare_l2n": (c_int, [P(Problem), P(AdmmState), c_int, C.c_double, c_void_p]),
     "nmfb_admm_publish": (c_int, [P(AdmmState), c_void_p, c_void_p]),
     "nmfb_aoadmm_side_begin": (c_int, [P(Problem), P(AdmmState), c_int, c_void_p]),
     "nmfb_aoadmm_inner": (c_int, [P(Problem), P(AdmmState), c_int, c_int, c_int, c_float, c_int, c_void_p]),

@@ -39,7 +39,7 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
         raise NotImplementedError("admm with distance_type='kl' (admm.py:303-315) is not provided by the B200 build")
     if distance_type != 'eu':
         raise TypeError('Unknown loss type.')
-    prox_code(reg_w), prox_code(reg_h)                       # TypeError('Unknown prox_type.') up front
+    prox_code(reg_w, k), prox_code(reg_h, k)                 # TypeError('Unknown prox_type.') up front
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)
     m, n = v.shape

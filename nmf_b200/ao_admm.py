@@ -35,7 +35,7 @@ def ao_admm(v, k, *, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_
         raise NotImplementedError("ao_admm with distance_type='kl' (ao_admm.py:272-285) is not provided by the B200 build")
     if distance_type != 'eu':
         raise TypeError('Unknown loss type.')
-    prox_code(reg_w), prox_code(reg_h)
+    prox_code(reg_w, k), prox_code(reg_h, k)
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)
     m, n = v.shape

@@ -301,11 +301,184 @@ admm_apply_kernel(const AdmmApplyArgs p) {
     }
 }
 
+// ------------------------------------------------------------------ solve + l2n prox + dual
+// A separate kernel on purpose: the nn / l1n kernel above is the measured hot path and stays as it is.
+// L2N (admm.py:141-156): x' = max(Binv (aux - u), 0) with Binv = ((lambda/rho) T^T T + I)^-1 along the
+// component axis -- a second k x k apply of the same shape, on aux - u staged through the b tile.
+template <int CPT>
+__global__ void __launch_bounds__(256)
+admm_apply_l2n_kernel(const AdmmApplyArgs p) {
+    constexpr int KP = CPT * 16;
+    constexpr int TR = 64;
+    constexpr int CK = 32;
+    extern __shared__ double sm_d[];
+    double* bs = sm_d;                    // [KP][TR]
+    double* gs = sm_d + KP * TR;          // [CK][KP]
+    __shared__ double red[8][4];
+    if (p.done_flag != nullptr && *p.done_flag != 0) return;
+    const int tid = threadIdx.x;
+    const int tr = tid & 15, tc = tid >> 4;
+    const int r0 = blockIdx.x * TR;
+    const int Lp = p.Lp;
+    const double rho = *p.rho;
+    const double thr = (p.prox == 1) ? static_cast<double>(p.lambda) / rho : 0.0;
+
+    for (int i = tid; i < KP * TR; i += 256) {
+        const int c = i / TR, rr = i - c * TR;
+        const long off = static_cast<long>(c) * Lp + r0 + rr;
+        double cv;
+        if (p.part != nullptr) {
+            cv = 0.0;
+            for (int s = 0; s < p.slots; ++s)
+                cv += static_cast<double>(p.part[static_cast<long>(s) * KP * Lp + off]);
+            if (p.c64 != nullptr) p.c64[off] = cv;
+        } else {
+            cv = p.c64[off];
+        }
+        bs[i] = cv + rho * (static_cast<double>(p.x[off]) + static_cast<double>(p.u[off]));
+    }
+    // out[c][r] = sum_c' mat[c][c'] bs[c'][r]  (mat symmetric, streamed through gs in slabs of CK rows)
+    auto apply = [&](const double* __restrict__ mat, double (&out)[CPT][4]) {
+#pragma unroll
+        for (int a = 0; a < CPT; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) out[a][b] = 0.0;
+        for (int ck = 0; ck < KP; ck += CK) {
+            __syncthreads();
+            for (int i = tid; i < CK * KP / 2; i += 256)
+                reinterpret_cast<double2*>(gs)[i] =
+                    *reinterpret_cast<const double2*>(mat + static_cast<long>(ck) * KP + i * 2);
+            __syncthreads();
+#pragma unroll 2
+            for (int cc = 0; cc < CK; ++cc) {
+                const double2 x01 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4);
+                const double2 x23 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4 + 2);
+                const double* grow = gs + cc * KP + tc * CPT;         // symmetric: row (ck+cc)
+#pragma unroll
+                for (int a = 0; a < CPT; a += 2) {
+                    const double2 g = *reinterpret_cast<const double2*>(grow + a);
+                    out[a][0] = fma(g.x, x01.x, out[a][0]);     out[a][1] = fma(g.x, x01.y, out[a][1]);
+                    out[a][2] = fma(g.x, x23.x, out[a][2]);     out[a][3] = fma(g.x, x23.y, out[a][3]);
+                    out[a + 1][0] = fma(g.y, x01.x, out[a + 1][0]); out[a + 1][1] = fma(g.y, x01.y, out[a + 1][1]);
+                    out[a + 1][2] = fma(g.y, x23.x, out[a + 1][2]); out[a + 1][3] = fma(g.y, x23.y, out[a + 1][3]);
+                }
+            }
+        }
+    };
+    double acc[CPT][4];
+    apply(p.ainv, acc);
+    double zacc[CPT][4];
+    {
+        __syncthreads();                       // every thread is done reading b
+#pragma unroll
+        for (int a = 0; a < CPT; ++a) {
+            const int c = tc * CPT + a;
+            const float4 uo4 = *reinterpret_cast<const float4*>(p.u + static_cast<long>(c) * Lp + r0 + tr * 4);
+            const float uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
+                bs[c * TR + tr * 4 + b] = live ? acc[a][b] - static_cast<double>(uo[b]) : 0.0;
+            }
+        }
+        apply(p.binv, zacc);                   // starts with a __syncthreads()
+    }
+
+    double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
+    __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
+#pragma unroll
+    for (int a = 0; a < CPT; ++a) {
+        const int c = tc * CPT + a;
+        const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
+        const float4 xo4 = *reinterpret_cast<const float4*>(p.x + off);
+        const float4 uo4 = *reinterpret_cast<const float4*>(p.u + off);
+        const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
+        float xn[4], un[4], ax[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
+            const double aux = live ? acc[a][b] : 0.0;
+            double xv;
+            xv = zacc[a][b];
+            xv = (live && xv > 0.0) ? xv : 0.0;
+            const double uv = live ? static_cast<double>(uo[b]) + xv - aux : 0.0;
+            xn[b] = static_cast<float>(xv);
+            un[b] = static_cast<float>(uv);
+            ax[b] = static_cast<float>(aux);
+            const double d0 = xv - aux, d2 = xv - static_cast<double>(xo[b]);
+            n_ra = fma(d0, d0, n_ra); n_x = fma(xv, xv, n_x); n_dx = fma(d2, d2, n_dx); n_u = fma(uv, uv, n_u);
+        }
+        *reinterpret_cast<float4*>(p.x + off) = make_float4(xn[0], xn[1], xn[2], xn[3]);
+        *reinterpret_cast<float4*>(p.u + off) = make_float4(un[0], un[1], un[2], un[3]);
+        if (p.aux_master != nullptr)
+            *reinterpret_cast<float4*>(p.aux_master + off) = make_float4(ax[0], ax[1], ax[2], ax[3]);
+        if (p.aux_cpl != nullptr) {
+            __align__(8) __nv_bfloat16 p0[4], p1[4], p2[4];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) split3(ax[b], p0[b], p1[b], p2[b]);
+            *reinterpret_cast<uint2*>(p.aux_cpl + off) = *reinterpret_cast<const uint2*>(p0);
+            *reinterpret_cast<uint2*>(p.aux_cpl + p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p1);
+            *reinterpret_cast<uint2*>(p.aux_cpl + 2 * p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p2);
+        }
+        __align__(8) __nv_bfloat16 q0[4], q1[4], q2[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            split3(xn[b], q0[b], q1[b], q2[b]);
+            rh[b][a] = q0[b];
+            rl[b][a] = q1[b];
+        }
+        if (p.x_cpl != nullptr) {
+            *reinterpret_cast<uint2*>(p.x_cpl + off) = *reinterpret_cast<const uint2*>(q0);
+            *reinterpret_cast<uint2*>(p.x_cpl + p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q1);
+            *reinterpret_cast<uint2*>(p.x_cpl + 2 * p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q2);
+        }
+    }
+    if (p.x_rpl != nullptr) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const long ro = static_cast<long>(r0 + tr * 4 + b) * KP + tc * CPT;
+#pragma unroll
+            for (int a = 0; a < CPT; a += 4) {
+                *reinterpret_cast<uint2*>(p.x_rpl + ro + a) = *reinterpret_cast<const uint2*>(&rh[b][a]);
+                *reinterpret_cast<uint2*>(p.x_rpl + p.x_rpl_plane + ro + a) = *reinterpret_cast<const uint2*>(&rl[b][a]);
+            }
+        }
+    }
+    if (p.norm_partial != nullptr) {
+        for (int o = 16; o; o >>= 1) {
+            n_ra += __shfl_xor_sync(0xffffffffu, n_ra, o);
+            n_x += __shfl_xor_sync(0xffffffffu, n_x, o);
+            n_dx += __shfl_xor_sync(0xffffffffu, n_dx, o);
+            n_u += __shfl_xor_sync(0xffffffffu, n_u, o);
+        }
+        if ((tid & 31) == 0) {
+            red[tid >> 5][0] = n_ra; red[tid >> 5][1] = n_x; red[tid >> 5][2] = n_dx; red[tid >> 5][3] = n_u;
+        }
+        __syncthreads();
+        if (tid < 4) {
+            double t = 0.0;
+            for (int w = 0; w < 8; ++w) t += red[w][tid];
+            p.norm_partial[static_cast<long>(blockIdx.x) * 4 + tid] = t;
+        }
+    }
+}
+
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
     const int grid = (a.nrows_p > 0 ? a.nrows_p : a.Lp) / 64;
     const size_t smem = (static_cast<size_t>(a.KP) * 64 + 32 * static_cast<size_t>(a.KP)) * sizeof(double);
     static bool set[3] = {false, false, false};
     cudaError_t e = cudaSuccess;
+    if (a.binv != nullptr) {                      // prox l2n: the two-product kernel, k <= 128
+        void (*fn)(const AdmmApplyArgs) = nullptr;
+        if (a.KP == 64)       fn = admm_apply_l2n_kernel<4>;
+        else if (a.KP == 128) fn = admm_apply_l2n_kernel<8>;
+        else return cudaErrorInvalidValue;        // two 16 x 4 fp64 register tiles do not fit
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+        if (e != cudaSuccess) return e;
+        fn<<<grid, 256, smem, stream>>>(a);
+        count_launch();
+        return cudaGetLastError();
+    }
     if (a.KP == 64) {
         if (!set[0]) { e = cudaFuncSetAttribute(admm_apply_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); set[0] = true; }
         admm_apply_kernel<4><<<grid, 256, smem, stream>>>(a);
@@ -317,6 +490,30 @@ cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
         admm_apply_kernel<16><<<grid, 256, smem, stream>>>(a);
     }
     if (e != cudaSuccess) return e;
+    count_launch();
+    return cudaGetLastError();
+}
+
+// (lambda / rho) T^T T for the Tikhonov matrix T = tridiag(-1, 2, -1) of order k (admm.py:142-146): the
+// pentadiagonal 6 / -4 / 1 with 5 in the two corners; padded components are zero.  chol_inverse_kernel with
+// rho = 1 then yields ((lambda/rho) T^T T + I)^-1.
+__global__ void __launch_bounds__(256)
+tikhonov_gram_kernel(int k, int KP, double lambda, const double* __restrict__ rho, double* __restrict__ out) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= KP * KP) return;
+    const int i = idx / KP, j = idx - i * KP;
+    double v = 0.0;
+    if (i < k && j < k) {
+        const int d = i > j ? i - j : j - i;
+        if (d == 0) v = (k == 1) ? 4.0 : ((i == 0 || i == k - 1) ? 5.0 : 6.0);
+        else if (d == 1) v = -4.0;
+        else if (d == 2) v = 1.0;
+    }
+    out[idx] = v * (lambda / *rho);
+}
+
+cudaError_t tikhonov_gram_launch(int k, int KP, double lambda, const double* rho, double* out, cudaStream_t stream) {
+    tikhonov_gram_kernel<<<(KP * KP + 255) / 256, 256, 0, stream>>>(k, KP, lambda, rho, out);
     count_launch();
     return cudaGetLastError();
 }

@@ -15,7 +15,7 @@ struct AdmmApplyArgs {
     const double* ainv;       // fp64 [KP][KP]
     const double* rho;        // device scalar
     float lambda;
-    int prox;                 // 0 = nn, 1 = l1n
+    int prox;                 // 0 = nn, 1 = l1n, 2 = l2n (binv != nullptr)
     float* x;                 // fp32 master [KP][Lp] of the constrained factor (in/out)
     float* u;                 // fp32 dual [KP][Lp] (in/out)
     float* aux_master;        // optional: auxiliary master (ADMM)
@@ -29,8 +29,12 @@ struct AdmmApplyArgs {
     const int* done_flag;     // optional: skip the launch's work when *done_flag != 0
     int KP, k, L, Lp;         // L = live rows of the window being updated, Lp = pitch of the factor
     int nrows_p;              // padded rows of the window (grid = nrows_p / 64); 0 = Lp
+    const double* binv;       // fp64 [KP][KP] inverse Tikhonov system (prox l2n) or nullptr; LAST on purpose:
+                              // a field in the middle moved the hot kernel from 128 to 132 registers (one CTA/SM)
 };
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream);
+// out[KP][KP] = (lambda / *rho) * T^T T, T = tridiag(-1, 2, -1) of order k (admm.py:142-146)
+cudaError_t tikhonov_gram_launch(int k, int KP, double lambda, const double* rho, double* out, cudaStream_t stream);
 
 // Reduce norm partials, raise flags[1] (= inner loop done) and count the executed inner iterations
 // in flags[used_idx]; no-op when already done.

@@ -538,6 +538,11 @@ int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* par
     a.ainv = s->ainv + static_cast<size_t>(side) * p->KP * p->KP;
     a.rho = s->scal + side;
     a.lambda = lambda; a.prox = prox;
+    if (prox == NMFB_PROX_L2N && lambda != 0.f) {
+        if (!s->binv) return fail(NMFB_ERR_ARG, "prox l2n: admm_state.binv workspace missing");
+        if (p->KP > 128) return fail(NMFB_ERR_ARG, "prox l2n with lambda > 0 supports k <= 128 in this build");
+        a.binv = s->binv + static_cast<size_t>(side) * p->KP * p->KP;
+    }
     a.x = f->master + w.w0; a.u = u + w.w0;
     if (aux) {
         a.aux_master = aux->master + w.w0;
@@ -574,11 +579,23 @@ int admm_gemm(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_data* 
 }
 
 int check_prox(int prox) {
-    if (prox != NMFB_PROX_NN && prox != NMFB_PROX_L1N) return fail(NMFB_ERR_ARG, "unknown prox code %d", prox);
+    if (prox != NMFB_PROX_NN && prox != NMFB_PROX_L1N && prox != NMFB_PROX_L2N)
+        return fail(NMFB_ERR_ARG, "unknown prox code %d", prox);
     return 0;
 }
 
 }  // namespace
+
+int nmfb_admm_prepare_l2n(const nmfb_problem* p, const nmfb_admm_state* s, int side, double lambda, void* stream) {
+    if (!p || !s || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "admm_prepare_l2n: bad argument");
+    if (!s->binv || !s->tik_scratch) return fail(NMFB_ERR_ARG, "admm_prepare_l2n: binv / tik_scratch workspace missing");
+    if (p->KP > 128) return fail(NMFB_ERR_ARG, "prox l2n with lambda > 0 supports k <= 128 in this build");
+    const size_t gsz = static_cast<size_t>(p->KP) * p->KP;
+    // a = 1/rho (lambda T^T T + rho I) = (lambda/rho) T^T T + I                            admm.py:148
+    CUDA_TRY(tikhonov_gram_launch(p->k, p->KP, lambda, s->scal + side, s->tik_scratch, st(stream)));
+    return nmfb_chol_inverse(s->tik_scratch, p->k, p->KP, 0, 1.0, s->chol_scratch, s->binv + side * gsz,
+                             s->tik_scratch + gsz, s->flags, stream);
+}
 
 int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int side, double rho, float lambda,
                         int prox, void* stream) {
@@ -598,6 +615,7 @@ int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int sid
     if ((rc = admm_gram(p, s, other_aux, side, stream)) < 0) return rc;
     if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + side * gsz,
                                 s->scal + side, s->flags, stream)) < 0) return rc;
+    if (prox == NMFB_PROX_L2N && lambda != 0.f && (rc = nmfb_admm_prepare_l2n(p, s, side, lambda, stream)) < 0) return rc;
     mark(p, 1 + 3 * side, stream);
     const int slots = admm_gemm(p, s, data, other_aux, self, stream);
     if (slots < 0) return slots;
@@ -688,6 +706,11 @@ int nmfb_aoadmm_step(const nmfb_problem* p, const nmfb_admm_state* s, int admm_i
         const nmfb_factor* self = side == 0 ? &p->h : &p->w;
         const int slots = nmfb_aoadmm_side_begin(p, s, side, stream);
         if (slots < 0) return slots;
+        {
+            const float lam = side == 0 ? lambda_h : lambda_w;                      // rho = tr(G)/k is known now
+            if ((side == 0 ? prox_h : prox_w) == NMFB_PROX_L2N && lam != 0.f &&
+                (rc = nmfb_admm_prepare_l2n(p, s, side, lam, stream)) < 0) return rc;
+        }
         for (int it = 0; it < admm_iter; ++it) {
             if ((rc = nmfb_aoadmm_inner(p, s, side, it == 0, slots, side == 0 ? lambda_h : lambda_w,
                                         side == 0 ? prox_h : prox_w, stream)) < 0) return rc;

@@ -154,6 +154,8 @@ class Engine:
         p = self.problem()
         fac = self.h if side == 0 else self.w
         slots = check(self.lib.nmfb_aoadmm_side_begin(C.byref(p), C.byref(self._admm), side, self.stream))
+        if int(prox) == 2 and float(lam) != 0.0:             # l2n: the Tikhonov system needs this side's rho
+            check(self.lib.nmfb_admm_prepare_l2n(C.byref(p), C.byref(self._admm), side, float(lam), self.stream))
         nblk = fac.win_p // 64
         for it in range(admm_iter):
             check(self.lib.nmfb_aoadmm_inner(C.byref(p), C.byref(self._admm), side, 1 if it == 0 else 0, slots,
@@ -349,6 +351,8 @@ class Engine:
         self.admm_scal = torch.zeros(4, dtype=torch.float64, device=dev)
         self.admm_flags = torch.zeros(8, dtype=torch.int32, device=dev)
         self.norm_partial = torch.zeros(4 * (Lmax // 64), dtype=torch.float64, device=dev)
+        self.binv = torch.zeros((2, KP, KP), dtype=torch.float64, device=dev)          # prox l2n systems
+        self.tik_scratch = torch.zeros(KP * KP + 4, dtype=torch.float64, device=dev)
         if with_aux:
             self.w_aux = FactorBuffers(self.m, KP, dev, self.Mp, self.w.win0, self.w.win_p)
             self.h_aux = FactorBuffers(self.n, KP, dev, self.Np, self.h.win0, self.h.win_p)
@@ -367,7 +371,8 @@ class Engine:
                 self._fixed_planes(self.h)
         self._admm = AdmmState(wa, ha, self.dual_w.data_ptr(), self.dual_h.data_ptr(), self.ainv.data_ptr(),
                                self.chol_scratch.data_ptr(), self.c64.data_ptr(), self.admm_scal.data_ptr(),
-                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(self.fixed))
+                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(self.fixed),
+                               self.binv.data_ptr(), self.tik_scratch.data_ptr())
 
     def admm_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
         p = self.problem()
@@ -401,6 +406,6 @@ class Engine:
         self.v_rows = self.v_cols = None
         self.w = self.h = None
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
-        for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch'):
+        for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch'):
             setattr(self, name, None)
         self._problem = None

@@ -122,20 +122,23 @@ class MurKlStepper:
                 "peak_source": peaks["source"] + " (sustained bf16)"}
 
 
-PROX_CODES = {"nn": 0, "l1n": 1}
+PROX_CODES = {"nn": 0, "l1n": 1, "l2n": 2}
 
 
-def prox_code(reg):
+def prox_code(reg, k=None):
     """(lambda, name) -> (lambda, C-ABI prox code).  'l2n' with lambda == 0 is the identity system of
-    admm.py:141-156, i.e. plain non-negativity; other operators are not part of this build."""
+    admm.py:141-156, i.e. plain non-negativity; with lambda > 0 it is the Tikhonov solve along the
+    component axis (k <= 128 in this build).  'l1inf' / 'l1inf_transpose' are not part of this build."""
     lam, name = reg
     if name == "l2n" and lam == 0:
         name = "nn"
+    if name == "l2n" and k is not None and k > 128:
+        raise NotImplementedError("prox operator 'l2n' with lambda > 0 supports k <= 128 in the B200 build")
     if name in PROX_CODES:
         return float(lam), PROX_CODES[name]
-    if name in ("l2n", "l1inf", "l1inf_transpose"):
-        raise NotImplementedError(f"prox operator {name!r} with lambda={lam} is not provided by the B200 build "
-                                  "(available: 'nn', 'l1n', and 'l2n' with lambda=0)")
+    if name in ("l1inf", "l1inf_transpose"):
+        raise NotImplementedError(f"prox operator {name!r} is not provided by the B200 build "
+                                  "(available: 'nn', 'l1n', 'l2n')")
     raise TypeError('Unknown prox_type.')
 
 
@@ -155,8 +158,8 @@ class AdmmStepper(_GemmRoofline):
 
     def __init__(self, eng, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n")):
         self.eng, self.rho = eng, float(rho)
-        self.lw, self.pw = prox_code(reg_w)
-        self.lh, self.ph = prox_code(reg_h)
+        self.lw, self.pw = prox_code(reg_w, eng.k)
+        self.lh, self.ph = prox_code(reg_h, eng.k)
 
     def prepare(self):
         self.eng.alloc_admm(with_aux=True)
@@ -195,8 +198,8 @@ class AoAdmmStepper(_GemmRoofline):
 
     def __init__(self, eng, reg_w=(0, "nn"), reg_h=(0, "l2n"), admm_iter=10):
         self.eng, self.admm_iter = eng, int(admm_iter)
-        self.lw, self.pw = prox_code(reg_w)
-        self.lh, self.ph = prox_code(reg_h)
+        self.lw, self.pw = prox_code(reg_w, eng.k)
+        self.lh, self.ph = prox_code(reg_h, eng.k)
 
     def prepare(self):
         self.eng.alloc_admm(with_aux=False)

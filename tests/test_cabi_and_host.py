@@ -107,8 +107,11 @@ def test_prox_names():
     assert prox_code((0, 'l2n')) == (0.0, 0)                           # admm.py:150: identity system
     with pytest.raises(TypeError):
         prox_code((0.1, 'l1'))                                         # not a reference name (admm.py:213)
+    assert prox_code((0.5, 'l2n')) == (0.5, 2)                         # admm.py:141-156
     with pytest.raises(NotImplementedError):
-        prox_code((0.5, 'l2n'))
+        prox_code((0.5, 'l2n'), k=200)
+    with pytest.raises(NotImplementedError):
+        prox_code((0.5, 'l1inf'))
 
 
 def test_facade_dispatch_and_save_names(tmp_path, capsys):

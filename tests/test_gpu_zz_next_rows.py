@@ -1,0 +1,78 @@
+"""GPU parity of the SURVEY.md 8(f) "next" rows built so far -- the l2n (Tikhonov) prox with lambda > 0
+(admm.py:141-156) and periodic checkpoints / resume (the reference's commented hook, mur.py:138-140).
+Kept in a file that sorts last: these paths were written after the GPU budget of round 1 was spent and
+have not run on a B200 yet, so a failure here must not hide the results of the §8(a)-(e) tests."""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+
+from conftest import golden_v, load_golden, rel_fro
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+def test_admm_l2n_matches_reference_golden():
+    """Both factors with the l2n prox, through NMF.factorize, against the frozen reference run."""
+    from nmf_b200 import NMF
+    g = load_golden("admm_l2n")
+    r = g["recipe"]
+    v = golden_v(r["v"])
+    np.random.seed(r["init_seed"])
+    model = NMF(v.copy(), r["k"])
+    with contextlib.redirect_stdout(io.StringIO()):
+        model.factorize(method="admm", **r["kw"])
+    res = model.results
+    assert res.i == int(g["i"]) and len(res.obj_history) == len(g["obj_history"])
+    obj_err = np.max(np.abs(np.array(res.obj_history) - g["obj_history"]) / g["obj_history"])
+    assert obj_err < TOL
+    assert rel_fro(res.w, g["w"]) < TOL and rel_fro(res.h, g["h"]) < TOL
+    assert res.experiment.prox_h == "l2n" and res.experiment.lambda_h == 0.5
+
+
+@pytest.mark.parametrize("method", ["admm", "ao_admm"])
+def test_l2n_trajectory_vs_oracle_k64(method):
+    """k = 64 (KP = 64 kernel variant) and, for AO-ADMM, the data-dependent rho = tr(G)/k in the
+    Tikhonov system.  (ao_admm.py:128 itself raises on NumPy >= 1.24: the oracle restates the intended
+    arithmetic there, parity unpinned for that sub-case.)"""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.admm import admm
+    from nmf_b200.ao_admm import ao_admm
+    m, n, k, iters = 768, 640, 64, 30
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    if method == "admm":
+        kw = dict(rho=100, reg_w=(0, "nn"), reg_h=(0.4, "l2n"))
+        tr = orc.admm_run(v, k, w0, h0, min_iter=10**9, max_iter=iters, **kw)
+        res = admm(v, k, min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False,
+                   nndsvd_init=(False, "zero"), **kw)
+    else:
+        kw = dict(reg_w=(0.2, "l2n"), reg_h=(0.4, "l2n"), admm_iter=5)
+        tr = orc.ao_admm_run(v, k, w0, h0, min_iter=10**9, max_iter=iters, **kw)
+        res = ao_admm(v, k, min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False,
+                      nndsvd_init=(False, "zero"), **kw)
+    assert res.i == tr.i
+    obj_err = max(abs(a - b) / b for a, b in zip(res.obj_history, tr.obj_history))
+    assert obj_err < TOL and rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
+
+
+def test_checkpoint_and_resume(tmp_path):
+    """A checkpoint holds the factors of its iteration; MUR resumed from it retraces the original run."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.mur import mur
+    m, n, k = 512, 384, 16
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    path = str(tmp_path / "ckpt")
+    full = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=20, w0=w0, h0=h0, verbose=False,
+               checkpoint_every=8, checkpoint_path=path)
+    z = np.load(path + ".npz", allow_pickle=True)
+    assert int(z["i"]) == 16 and len(z["obj_history"]) == 18            # last multiple of 8 below 20
+    assert sorted(z.files) == ["experiment", "h", "i", "obj_history", "w"]
+    tr = orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=17)
+    assert rel_fro(z["w"], tr.w) < TOL and rel_fro(z["h"], tr.h) < TOL
+    rest = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=3, w0=z["w"], h0=z["h"], verbose=False)
+    assert rel_fro(rest.w, full.w) < 1e-5 and rel_fro(rest.h, full.h) < 1e-5
