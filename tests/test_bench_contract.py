@@ -1,0 +1,52 @@
+"""CPU: the parts of bench.py's contract that do not need a GPU -- the reference arm prints exactly one
+JSON line with the agreed keys, workload names follow BASELINE.json's configs, algorithmic FLOP counts
+match SURVEY.md 8(d), and the committed ncu traffic figures are keyed by existing workloads."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import bench  # noqa: E402
+
+
+def test_reference_arm_prints_one_json_line():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload",
+                          "mur_eu_4096x4096_k64", "--steps", "1", "--warmup", "0"],
+                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=300, check=True).stdout
+    lines = [ln for ln in out.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "nmf_outer_iterations_per_second" and d["unit"] == "it/s"
+    assert d["higher_is_better"] is True and d["value"] > 0 and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["workload"] == "mur_eu_4096x4096_k64"
+
+
+def test_workloads_cover_baseline_configs():
+    w = bench.WORKLOADS
+    assert bench.DEFAULT_WORKLOAD == "mur_eu_65536x65536_k128" and bench.DEFAULT_WORKLOAD in w
+    assert w["mur_eu_32768x32768_k64"][:5] == ("mur", "eu", 32768, 32768, 64)                  # configs[1]
+    assert w["mur_kl_20000x50000_k128"][:5] == ("mur", "kl", 20000, 50000, 128)                # configs[2]
+    assert w["admm_65536x16384_k128"][5]["reg_h"] == (0.1, "l1n")                              # configs[3]
+    assert w["ao_admm_65536x16384_k128"][5]["admm_iter"] == 5
+    assert w["mur_eu_262144x131072_k256"][2:5] == (262144, 131072, 256)                        # configs[4]
+    for (kernel, workload) in bench.NCU_TRAFFIC:
+        assert workload in w
+
+
+def test_algorithmic_flops_follow_the_survey():
+    m, n, k = 65536, 65536, 128
+    assert bench.alg_flops_per_iter("mur", "eu", m, n, k, {}) == 4.0 * m * n * k + 4.0 * (m + n) * k * k
+    assert bench.alg_flops_per_iter("mur", "kl", m, n, k, {}) == 8.0 * m * n * k
+    f = bench.alg_flops_per_iter("ao_admm", "eu", m, n, k, {"admm_iter": 5})
+    assert f == 4.0 * m * n * k + 12.0 * (m + n) * k * k + 4.0 / 3.0 * k ** 3
+
+
+def test_cpu_sample_is_a_block_of_the_workload():
+    ms, ns = bench.cpu_sample_shape(65536, 16384, 128, 1 << 26)
+    assert ms * ns <= 1 << 26 and 65536 % ms == 0 and 16384 % ns == 0
