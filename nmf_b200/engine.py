@@ -240,10 +240,26 @@ class Engine:
         return _key_to_float(int(st[0])), bool(st[1]), bool(st[2])
 
     def _host_chunks(self, v: np.ndarray):
+        """Row chunks of the host V on the device.  When HBM has room for the whole fp32/fp64 V next to its
+        bf16 planes, the chunks of the first pass are kept for the later ones (absmax -> ingest, or the
+        repeat with a second plane): V crosses PCIe once per upload_data, not once per pass."""
+        cache = getattr(self, "_chunk_cache", None)
+        if cache is not None and cache[0] is v:
+            yield from cache[1]
+            return
+        free, _total = torch.cuda.mem_get_info(self.device)
+        planes_bytes = 8 * self.m * self.n // self.world + (64 << 20)         # two copies x two bf16 planes
+        keep = getattr(self, "_keep_chunks", False) and v.nbytes + planes_bytes < 0.8 * free
+        kept = []
         rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
         for r0 in range(0, self.m, rows_per):
             r1 = min(self.m, r0 + rows_per)
-            yield r0, torch.from_numpy(v[r0:r1]).to(self.device, non_blocking=False)
+            chunk = torch.from_numpy(v[r0:r1]).to(self.device, non_blocking=False)
+            if keep:
+                kept.append((r0, chunk))
+            yield r0, chunk
+        if keep:
+            self._chunk_cache = (v, kept)
 
     def _ingest_pass(self, v: np.ndarray, nv: int, fixed: bool = False):
         self.begin_ingest(nv, fixed)
@@ -265,6 +281,13 @@ class Engine:
             v = v.astype(np.float64)
         if not v.flags.c_contiguous:
             v = np.ascontiguousarray(v)
+        self._chunk_cache, self._keep_chunks = None, True
+        try:
+            return self._upload_passes(v, planes, fixed)
+        finally:
+            self._chunk_cache, self._keep_chunks = None, False
+
+    def _upload_passes(self, v: np.ndarray, planes: Optional[int], fixed: bool) -> float:
         if fixed:
             vmin, inexact, bad = self._ingest_pass(v, 2, fixed=True)
             if not inexact:
