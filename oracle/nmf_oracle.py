@@ -204,24 +204,49 @@ def admm_aux(x, dual, other_aux, data, rho):
     return np.linalg.solve(a, b)
 
 
-def admm_run(v, k, w0, h0, *, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n"), min_iter=10,
+def admm_aux_kl(x, dual, other_aux, v_aux, dual_v, rho):
+    """admm.py:223-225,230 (kl): the data term is the auxiliary copy of V plus its dual."""
+    kk = other_aux.shape[1]
+    a = other_aux.T @ other_aux + rho * np.eye(kk)
+    b = other_aux.T @ (v_aux + dual_v) + rho * (x + dual)
+    return np.linalg.solve(a, b)
+
+
+def kl_v_aux(v, v_bar):
+    """admm.py:311 / ao_admm.py:90: closed-form minimiser of KL(v | v_aux) + 1/2 |v_aux - v_bar|^2."""
+    return 0.5 * ((v_bar - 1.0) + np.sqrt((v_bar - 1.0) ** 2 + 4.0 * v))
+
+
+def admm_run(v, k, w0, h0, *, rho=1, distance_type="eu", reg_w=(0, "nn"), reg_h=(0, "l2n"), min_iter=10,
              max_iter=100000, tol1=1e-3, tol2=1e-3,
              snap: Optional[Callable[[int], bool]] = None) -> Trace:
-    """admm.py:233-345, Euclidean branch (:294-301, duals :320-321, objective :324)."""
+    """admm.py:233-345: Euclidean branch (:294-301) or Kullback-Leibler branch (:303-315, with the m x n
+    auxiliary v_aux and its dual, both starting at zero :33-35); duals :320-321, objective :324."""
+    if distance_type not in ("eu", "kl"):
+        raise TypeError("Unknown loss type.")
     v = np.asarray(v, dtype=np.float64)
     w, h = np.array(w0, dtype=np.float64), np.array(h0, dtype=np.float64)
     w_aux, h_aux = w.copy(), h.copy()                     # admm.py:27-28
     dual_w, dual_h = np.zeros_like(w), np.zeros_like(h)   # admm.py:31-32
-    hist = [objective(v, w @ h)]
+    v_aux, dual_v = np.zeros_like(v), np.zeros_like(v)    # admm.py:33
+    hist = [objective(v, w @ h, distance_type)]
     out = Trace(w, h, -1, hist)
     for i in range(max_iter):
-        h_aux = admm_aux(h, dual_h, w_aux, v, rho)
-        w_aux = admm_aux(w.T, dual_w.T, h_aux.T, v.T, rho).T
+        if distance_type == "eu":
+            h_aux = admm_aux(h, dual_h, w_aux, v, rho)
+            w_aux = admm_aux(w.T, dual_w.T, h_aux.T, v.T, rho).T
+        else:
+            h_aux = admm_aux_kl(h, dual_h, w_aux, v_aux, dual_v, rho)
+            w_aux = admm_aux_kl(w.T, dual_w.T, h_aux.T, v_aux.T, dual_v.T, rho).T
         h = prox(reg_h[1], h_aux, dual_h, rho, reg_h[0])
         w = prox(reg_w[1], w_aux.T, dual_w.T, rho, reg_w[0]).T      # admm.py:300-301
+        if distance_type == "kl":
+            wh_aux = w_aux @ h_aux
+            v_aux = kl_v_aux(v, wh_aux - dual_v)                    # admm.py:310-311
+            dual_v = dual_v + v_aux - wh_aux                        # admm.py:313
         dual_h = dual_h + h - h_aux
         dual_w = dual_w + w - w_aux
-        hist.append(objective(v, w @ h))
+        hist.append(objective(v, w @ h, distance_type))
         out.i = i
         if snap is not None and snap(i):
             out.snaps.append((i, w.copy(), h.copy()))
@@ -264,24 +289,56 @@ def ao_factor_update(y, a, x, dual, k, prox_kind, lam, admm_iter):
     return x, dual, used
 
 
-def ao_admm_run(v, k, w0, h0, *, reg_w=(0, "nn"), reg_h=(0, "l2n"), min_iter=10,
+def ao_factor_update_kl(v, v_aux, dual_v, a, x, dual, k, prox_kind, lam, admm_iter):
+    """ao_admm.py:71-101 -- the Kullback-Leibler sub-problem: the right-hand side is rebuilt from
+    v_aux + dual_v in every inner iteration, v_aux / dual_v follow the closed form of :89-94."""
+    g = a.T @ a
+    rho = np.trace(g) / k
+    cho = sla.cholesky(g + rho * np.eye(g.shape[0]), lower=True)
+    used = admm_iter
+    for it in range(admm_iter):
+        aux = sla.cho_solve((cho, True), a.T @ (v_aux + dual_v) + rho * (x + dual))
+        x_prev = x
+        x = prox(prox_kind, aux, dual, rho, lam)
+        a_aux = a @ aux
+        v_aux = kl_v_aux(v, a_aux - dual_v)
+        dual = dual + x - aux
+        dual_v = dual_v + v_aux - a_aux
+        if inner_done(x, x_prev, aux, dual):
+            used = it
+            break
+    return x, dual, v_aux, dual_v, used
+
+
+def ao_admm_run(v, k, w0, h0, *, distance_type="eu", reg_w=(0, "nn"), reg_h=(0, "l2n"), min_iter=10,
                 max_iter=100000, admm_iter=10, tol1=1e-3, tol2=1e-3,
                 snap: Optional[Callable[[int], bool]] = None) -> Trace:
-    """ao_admm.py:201-311, Euclidean branch (:261-270); duals are warm-started across
-    outer iterations.  (`reg_h=(0,'l2n')`, the reference's own default, crashes the
-    reference on NumPy >= 1.24 at ao_admm.py:128; here it is the lam==0 identity.)"""
+    """ao_admm.py:201-311: Euclidean branch (:261-270) or Kullback-Leibler branch (:272-285); duals
+    (and, for kl, v_aux / dual_v, starting at zero :28-30) are warm-started across outer iterations.
+    (`reg_h=(0,'l2n')`, the reference's own default, crashes the reference on NumPy >= 1.24 at
+    ao_admm.py:128; here it is the lam==0 identity.)"""
+    if distance_type not in ("eu", "kl"):
+        raise TypeError("Unknown loss function type.")
     v = np.asarray(v, dtype=np.float64)
     w, h = np.array(w0, dtype=np.float64), np.array(h0, dtype=np.float64)
     dual_w, dual_h = np.zeros_like(w), np.zeros_like(h)
-    hist = [objective(v, w @ h)]
+    v_aux, dual_v = np.zeros_like(v), np.zeros_like(v)
+    hist = [objective(v, w @ h, distance_type)]
     out = Trace(w, h, -1, hist)
     for i in range(max_iter):
-        h, dual_h, used_h = ao_factor_update(v, w, h, dual_h, k, reg_h[1], reg_h[0], admm_iter)
-        wt, dwt, used_w = ao_factor_update(v.T, h.T, w.T, dual_w.T, k, reg_w[1], reg_w[0],
-                                           admm_iter)
+        if distance_type == "eu":
+            h, dual_h, used_h = ao_factor_update(v, w, h, dual_h, k, reg_h[1], reg_h[0], admm_iter)
+            wt, dwt, used_w = ao_factor_update(v.T, h.T, w.T, dual_w.T, k, reg_w[1], reg_w[0],
+                                               admm_iter)
+        else:
+            h, dual_h, v_aux, dual_v, used_h = ao_factor_update_kl(v, v_aux, dual_v, w, h, dual_h, k,
+                                                                   reg_h[1], reg_h[0], admm_iter)
+            wt, dwt, vat, dvt, used_w = ao_factor_update_kl(v.T, v_aux.T, dual_v.T, h.T, w.T, dual_w.T, k,
+                                                            reg_w[1], reg_w[0], admm_iter)
+            v_aux, dual_v = vat.T, dvt.T
         w, dual_w = wt.T, dwt.T
         out.inner_breaks.append((used_h, used_w))
-        hist.append(objective(v, w @ h))
+        hist.append(objective(v, w @ h, distance_type))
         out.i = i
         if snap is not None and snap(i):
             out.snaps.append((i, w.copy(), h.copy()))

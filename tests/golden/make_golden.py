@@ -72,6 +72,14 @@ CASES = {
         v=dict(kind="planted", m=320, n=224, k=12, seed=21), k=12, init_seed=22, method="admm",
         kw=dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"), min_iter=100, max_iter=40,
                 tol1=1e-3, tol2=1e-3, nndsvd_init=(False, "zero"))),
+    "admm_kl": dict(
+        v=dict(kind="planted", m=240, n=200, k=8, seed=23), k=8, init_seed=24, method="admm",
+        kw=dict(rho=20, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=100, max_iter=40,
+                tol1=1e-3, tol2=1e-3, nndsvd_init=(False, "zero"))),
+    "ao_admm_kl": dict(
+        v=dict(kind="planted", m=200, n=240, k=8, seed=25), k=8, init_seed=26, method="ao_admm",
+        kw=dict(distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=100, max_iter=25,
+                admm_iter=6, tol1=1e-3, tol2=1e-3, nndsvd_init=(False, "zero"))),
     "ao_admm_l1n": dict(
         v=dict(kind="planted", m=512, n=384, k=16, seed=17), k=16, init_seed=18, method="ao_admm",
         kw=dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), min_iter=100, max_iter=40, admm_iter=5,
