@@ -10,7 +10,7 @@ import json
 d=json.load(open('gpurun_out/bench_g$1_$2.json')); print('$2 x$1', round(d['value'],1),'it/s', round(d['ms_per_step'],3), d['phase_ms'])" || grep -v "^W0\|^\*\*\*\|OMP_NUM" gpurun_out/bench_g$1_$2.err | tail -12
 }
 TR8="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29512"
-timeout 600 $TR8 tools/mgpu_check.py > gpurun_out/mgpu_check_8.log 2>&1; echo "mgpu_check exit $?"
+timeout 420 $TR8 tools/mgpu_check.py > gpurun_out/mgpu_check_8.log 2>&1; echo "mgpu_check exit $?"
 grep -E "sharded|stop iteration|inner-iteration|MGPU|Error|error" gpurun_out/mgpu_check_8.log | head -40
 run 8 mur_eu_65536x65536_k128 30
 run 4 mur_eu_65536x65536_k128 30
