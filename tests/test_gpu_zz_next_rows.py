@@ -82,3 +82,57 @@ def test_checkpoint_and_resume(tmp_path):
     assert rel_fro(z["w"], tr.w) < TOL and rel_fro(z["h"], tr.h) < TOL
     rest = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=3, w0=z["w"], h0=z["h"], verbose=False)
     assert rel_fro(rest.w, full.w) < 1e-5 and rel_fro(rest.h, full.h) < 1e-5
+
+
+# ----------------------------------------------------------------------------------------------
+# BASELINE.json's full sizes through size-independent properties (the fp64 oracle needs minutes per
+# iteration there): Lee-Seung monotonicity of the MUR objective, non-negativity, finiteness, and the
+# agreement of the fused / stand-alone KL objective.  Data is generated on the device (bench.py).
+# ----------------------------------------------------------------------------------------------
+def _full_size_engine(m, n, k):
+    import bench
+    from nmf_b200.engine import Engine
+    eng = Engine(m, n, k)
+    bench.synth_fill_engine(eng, seed=0)
+    bench.synth_init(eng, seed=1)
+    return eng
+
+
+@first_run_pending
+def test_c2_mur_eu_full_size_is_monotone_and_non_negative():
+    """configs[1]: 32768 x 32768, k = 64."""
+    import torch
+    from nmf_b200 import solvers
+    eng = _full_size_engine(32768, 32768, 64)
+    st = solvers.make_stepper(eng, "mur", "eu")
+    st.prepare()
+    objs = [eng.read_scalar(0)]
+    for i in range(12):
+        st.step(i % 8)
+        objs.append(eng.read_scalar((i % 8) * 8))
+    assert all(np.isfinite(objs)) and all(b < a for a, b in zip(objs, objs[1:])), objs       # Lee & Seung
+    assert objs[-1] < 0.05 * objs[0]
+    for f in (eng.w, eng.h):
+        assert bool(torch.isfinite(f.master).all()) and float(f.master.min()) >= 0.0
+    eng.release()
+
+
+@first_run_pending
+def test_c3_mur_kl_full_size_is_monotone_and_objectives_agree():
+    """configs[2]: 20000 x 50000, k = 128; the objective that falls out of the W pass (lagged) must equal
+    the stand-alone objective kernel's value for the same pair."""
+    from nmf_b200 import solvers
+    eng = _full_size_engine(20000, 50000, 128)
+    st = solvers.make_stepper(eng, "mur", "kl")
+    st.prepare()
+    objs = [eng.read_scalar(0)]
+    fused = []
+    for i in range(8):
+        st.step(i % 8, (i - 1) % 8)                       # writes the objective of the incoming pair
+        fused.append(eng.read_scalar(((i - 1) % 8) * 8))
+        eng.objective_kl(slot=40)                         # stand-alone, pair after iteration i
+        objs.append(eng.read_scalar(40))
+    assert all(np.isfinite(objs)) and all(b < a for a, b in zip(objs, objs[1:])), objs
+    for got, want in zip(fused, objs[:-1]):               # fused[i] = objective before iteration i = objs[i]
+        assert abs(got - want) / want < 1e-5
+    eng.release()
