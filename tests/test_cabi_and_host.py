@@ -43,17 +43,60 @@ def test_pure_host_entry_points():
 
 
 def test_struct_layouts_match_header():
-    """sizeof of the ctypes mirrors == what a C compiler lays out (guards against drift)."""
+    """sizeof and every field's offsetof of the ctypes mirrors == what a C compiler lays out for the
+    header (guards against drift: same names, same order, same padding)."""
     import subprocess, tempfile
     from nmf_b200 import _lib
-    src = '#include <stdio.h>\n#include "nmf_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(nmfb_data), sizeof(nmfb_factor), sizeof(nmfb_problem), sizeof(nmfb_admm_state));return 0;}\n'
+    pairs = [("nmfb_data", _lib.Data), ("nmfb_factor", _lib.Factor), ("nmfb_problem", _lib.Problem),
+             ("nmfb_admm_state", _lib.AdmmState)]
+    lines, want = [], []
+    for cname, cls in pairs:
+        lines.append(f'printf("%zu\\n", sizeof({cname}));')
+        want.append(C.sizeof(cls))
+        for fname, _ in cls._fields_:
+            lines.append(f'printf("%zu\\n", offsetof({cname}, {fname}));')      # fails to compile on a renamed field
+            want.append(getattr(cls, fname).offset)
+    src = '#include <stdio.h>\n#include <stddef.h>\n#include "nmf_b200.h"\nint main(){' + "".join(lines) + 'return 0;}\n'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "t.c")
         open(c, "w").write(src)
         exe = os.path.join(d, "t")
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
-        sizes = [int(x) for x in subprocess.check_output([exe]).split()]
-    assert sizes == [C.sizeof(_lib.Data), C.sizeof(_lib.Factor), C.sizeof(_lib.Problem), C.sizeof(_lib.AdmmState)]
+        got = [int(x) for x in subprocess.check_output([exe]).split()]
+    assert got == want
+
+
+def test_ctypes_signatures_match_header_prototypes():
+    """Every prototype of the header, argument by argument, against the ctypes argtypes / restype."""
+    from nmf_b200 import _lib
+    text = open(os.path.join(ROOT, "include", "nmf_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    protos = re.findall(r"([A-Za-z_][\w \*]*?)\b(nmfb_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", text)
+    assert len(protos) == len(_lib.exported_symbols())
+    structs = {"nmfb_data": _lib.Data, "nmfb_factor": _lib.Factor, "nmfb_problem": _lib.Problem,
+               "nmfb_admm_state": _lib.AdmmState}
+    scalars = {"int": C.c_int, "long": C.c_long, "float": C.c_float, "double": C.c_double, "size_t": C.c_size_t,
+               "unsigned long long": C.c_ulonglong}
+
+    def to_ctypes(ctype):
+        ctype = ctype.replace("const", "").strip()
+        if ctype.endswith("*"):
+            base = ctype[:-1].strip()
+            if base == "char":
+                return C.c_char_p
+            return C.POINTER(structs[base]) if base in structs else C.c_void_p
+        return scalars[ctype]
+
+    for ret, name, args in protos:
+        res, argtypes = _lib._SIGNATURES[name]
+        want = []
+        for a in args.split(","):
+            a = a.strip()
+            if a and a != "void":
+                want.append(to_ctypes(re.match(r"(.*?)(\w+)$", a).group(1)))
+        assert want == list(argtypes), name
+        assert to_ctypes(ret) == res, name
 
 
 def test_no_cpu_fallback():
