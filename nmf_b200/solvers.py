@@ -112,8 +112,8 @@ class MurKlStepper:
         if "kl_w" not in phase_ms:
             return None
         ms = 0.5 * (phase_ms["kl_w"] + phase_ms["kl_h"])     # W pass carries the objective terms as well
-        tf = 4.0 * e.m * e.n * e.k / (ms * 1e-3) / 1e12
-        gbs = 2.0 * e.m * e.n * e.nv / (ms * 1e-3) / 1e9
+        tf = 4.0 * e.m * e.n * e.k / e.world / (ms * 1e-3) / 1e12      # per rank (its shard of V)
+        gbs = 2.0 * e.m * e.n * e.nv / e.world / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
         return {"kernel": "kl_panel_kernel", "bound": "tensor", "ms_per_launch": ms, "executed_mma_per_product": 3,
                 "traffic": None, "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,

@@ -50,3 +50,29 @@ def test_algorithmic_flops_follow_the_survey():
 def test_cpu_sample_is_a_block_of_the_workload():
     ms, ns = bench.cpu_sample_shape(65536, 16384, 128, 1 << 26)
     assert ms * ns <= 1 << 26 and 65536 % ms == 0 and 16384 % ns == 0
+
+
+def test_roofline_reports_are_per_rank_and_pick_the_binding_roof():
+    """solvers.*Stepper.roofline on a stand-in engine: algorithmic work of ONE launch on ONE rank's shard
+    (a sharded run must not report the whole job's FLOPs against one GPU's peak)."""
+    from types import SimpleNamespace
+    from nmf_b200 import solvers
+    peaks = dict(hbm_gbs=6500.0, bf16_tflops=1600.0, bf16_tflops_sustained=1400.0, source="measured")
+    m, n, k = 65536, 65536, 128
+    for world in (1, 8):
+        eng = SimpleNamespace(m=m, n=n, k=k, world=world, nv=1, fixed=False)
+        ms = 1.6 / world
+        r = solvers.MurEuStepper(eng).roofline({"gemm_w": ms, "gemm_h": ms}, peaks)
+        assert r["kernel"] == "panel_gemm_kernel" and r["bound"] == "hbm"          # 2-byte V read once: HBM side
+        assert abs(r["achieved"] - 2.0 * m * n / 1.6e-3 / 1e9) < 1e-6 * r["achieved"]
+        assert r["frac"] == r["achieved"] / r["peak"] and r["unit"] == "GB/s" and r["peak"] == 6500.0
+        assert 0 < r["frac"] < 1 and 0 < r["tensor"]["frac"] < 1
+        q = solvers.MurKlStepper(eng).roofline({"kl_w": ms, "kl_h": ms}, peaks)
+        assert q["kernel"] == "kl_panel_kernel" and q["unit"] == "TFLOP/s"
+        assert abs(q["achieved"] - 4.0 * m * n * k / 1.6e-3 / 1e12) < 1e-6 * q["achieved"]
+        assert 0 < q["frac"] < 1 and 0 < q["hbm"]["frac"] < 1
+    # exact-hi ADMM contraction: 5 executed MMAs per algorithmic product
+    eng = SimpleNamespace(m=m, n=16384, k=k, world=1, nv=2, fixed=True)
+    st = solvers.AdmmStepper(eng, rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))
+    r = st.roofline({"gemm_w": 1.0, "gemm_h": 1.0}, peaks)
+    assert r["executed_mma_per_product"] == 5 and (r["kernel"], "admm_65536x16384_k128") in bench.NCU_TRAFFIC
