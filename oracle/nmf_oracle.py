@@ -372,6 +372,17 @@ def planted(m: int, n: int, k: int, seed: int = 0) -> np.ndarray:
     return round_to_bf16_grid(v)
 
 
+def planted_with_zeros(m: int, n: int, k: int, seed: int = 0, frac: float = 0.3) -> np.ndarray:
+    """planted() with a fraction `frac` of the entries, row 3 and column 5 set to exactly zero: the data
+    for the 0 * log(0 / x) and x / 0 rules of utils.py:23-26 and for all-zero rows / columns."""
+    v = planted(m, n, k, seed)
+    mask = np.random.default_rng(seed + 7919).random((m, n)) < frac
+    v[mask] = 0.0
+    v[min(3, m - 1), :] = 0.0
+    v[:, min(5, n - 1)] = 0.0
+    return v
+
+
 def seeded_init(m: int, n: int, k: int, seed: int):
     """Reference-order init from a private seed (does not disturb the global RNG)."""
     st = np.random.get_state()

@@ -28,9 +28,11 @@ def load_golden(name):
 
 
 def golden_v(spec):
-    from oracle.nmf_oracle import planted
+    from oracle.nmf_oracle import planted, planted_with_zeros
     if spec["kind"] == "uniform":
         return np.random.default_rng(spec["seed"]).random((spec["m"], spec["n"]))
+    if spec["kind"] == "zeros":
+        return planted_with_zeros(spec["m"], spec["n"], spec["k"], spec["seed"]).astype(np.float64)
     return planted(spec["m"], spec["n"], spec["k"], spec["seed"]).astype(np.float64)
 
 

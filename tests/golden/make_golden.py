@@ -25,7 +25,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, "/root/reference")
 
 from nmf import NMF  # noqa: E402  (the reference)
-from oracle.nmf_oracle import planted  # noqa: E402
+from oracle.nmf_oracle import planted, planted_with_zeros  # noqa: E402
 
 
 def make_v(spec):
@@ -34,6 +34,8 @@ def make_v(spec):
         return np.random.default_rng(spec["seed"]).random((spec["m"], spec["n"]))
     if kind == "planted":
         return planted(spec["m"], spec["n"], spec["k"], spec["seed"]).astype(np.float64)
+    if kind == "zeros":              # exact zeros (30 %), an all-zero row and an all-zero column
+        return planted_with_zeros(spec["m"], spec["n"], spec["k"], spec["seed"]).astype(np.float64)
     raise ValueError(kind)
 
 
@@ -80,6 +82,27 @@ CASES = {
         v=dict(kind="planted", m=200, n=240, k=8, seed=25), k=8, init_seed=26, method="ao_admm",
         kw=dict(distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=100, max_iter=25,
                 admm_iter=6, tol1=1e-3, tol2=1e-3, nndsvd_init=(False, "zero"))),
+    # ---- edge cases: exact zeros in V, a single component, the other NNDSVD fill variants
+    "mur_kl_zeros": dict(
+        v=dict(kind="zeros", m=180, n=150, k=5, seed=27), k=5, init_seed=28, method="mur",
+        kw=dict(distance_type="kl", min_iter=100, max_iter=40, tol1=1e-5, tol2=1e-5)),
+    "mur_eu_zeros": dict(
+        v=dict(kind="zeros", m=150, n=180, k=5, seed=29), k=5, init_seed=30, method="mur",
+        kw=dict(distance_type="eu", min_iter=100, max_iter=40, tol1=1e-5, tol2=1e-5)),
+    "mur_eu_k1": dict(
+        v=dict(kind="uniform", m=37, n=23, seed=31), k=1, init_seed=32, method="mur",
+        kw=dict(distance_type="eu", min_iter=100, max_iter=30, tol1=1e-5, tol2=1e-5)),
+    "mur_kl_k1": dict(
+        v=dict(kind="uniform", m=23, n=37, seed=33), k=1, init_seed=34, method="mur",
+        kw=dict(distance_type="kl", min_iter=100, max_iter=30, tol1=1e-5, tol2=1e-5)),
+    "admm_nndsvd_mean": dict(
+        v=dict(kind="planted", m=160, n=120, k=5, seed=35), k=5, init_seed=36, method="admm",
+        kw=dict(rho=10, reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=100, max_iter=20,
+                tol1=1e-3, tol2=1e-3, nndsvd_init=(True, "mean"))),
+    "ao_admm_nndsvd_random": dict(
+        v=dict(kind="planted", m=120, n=160, k=5, seed=37), k=5, init_seed=38, method="ao_admm",
+        kw=dict(reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=100, max_iter=15, admm_iter=5,
+                tol1=1e-3, tol2=1e-3, nndsvd_init=(True, "random"))),
     "ao_admm_l1n": dict(
         v=dict(kind="planted", m=512, n=384, k=16, seed=17), k=16, init_seed=18, method="ao_admm",
         kw=dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), min_iter=100, max_iter=40, admm_iter=5,

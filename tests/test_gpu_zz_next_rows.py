@@ -136,3 +136,67 @@ def test_c3_mur_kl_full_size_is_monotone_and_objectives_agree():
     for got, want in zip(fused, objs[:-1]):               # fused[i] = objective before iteration i = objs[i]
         assert abs(got - want) / want < 1e-5
     eng.release()
+
+
+# ----------------------------------------------------------------------------------------------
+# Edge cases (written after the GPU budget of round 1 was spent, hence `first_run_pending`): exact zeros
+# in V with an all-zero row and column (the 0*log(0/x) and x/0 rules of utils.py:23-26), a single
+# component, the 'mean' / 'random' NNDSVD fills (utils.py:84-91), k = 200 (the KP = 256 kernels, C5's
+# width), very flat / very tall V, and the input dtypes / memory orders NumPy callers hand over.
+# ----------------------------------------------------------------------------------------------
+EDGE_GOLDENS = ["mur_kl_zeros", "mur_eu_zeros", "mur_eu_k1", "mur_kl_k1", "admm_nndsvd_mean",
+                "ao_admm_nndsvd_random"]
+
+
+@first_run_pending
+@pytest.mark.parametrize("name", EDGE_GOLDENS)
+def test_edge_case_matches_reference_golden(name):
+    from nmf_b200 import NMF
+    g = load_golden(name)
+    r = g["recipe"]
+    v = golden_v(r["v"])
+    np.random.seed(r["init_seed"])
+    model = NMF(v.copy(), r["k"])
+    with contextlib.redirect_stdout(io.StringIO()):
+        model.factorize(method=r["method"], **r["kw"])
+    res = model.results
+    assert res.i == int(g["i"]) and len(res.obj_history) == len(g["obj_history"])
+    obj_err = np.max(np.abs(np.array(res.obj_history) - g["obj_history"]) / g["obj_history"])
+    assert obj_err < TOL
+    assert rel_fro(res.w, g["w"]) < TOL and rel_fro(res.h, g["h"]) < TOL
+    assert np.all(res.w >= 0) and np.all(res.h >= 0)
+    if "zeros" in name:                                  # the all-zero row / column of V empties W's row / H's column
+        assert np.all(res.w[3] == 0) and np.all(res.h[:, 5] == 0)
+
+
+@first_run_pending
+@pytest.mark.parametrize("shape", [(640, 520, 200), (4096, 70, 8), (70, 4096, 8), (5, 7, 2)])
+def test_mur_eu_shapes_vs_oracle(shape):
+    """k = 200 runs the KP = 256 variants of every kernel; the flat / tall cases have a single 128-row
+    panel on one side and many on the other; 5 x 7 is smaller than any tile."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.mur import mur
+    m, n, k = shape
+    v = orc.planted(m, n, k, 40).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 41)
+    tr = orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=30)
+    res = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=30, w0=w0, h0=h0, verbose=False)
+    assert res.i == tr.i == 29
+    obj_err = max(abs(a - b) / b for a, b in zip(res.obj_history, tr.obj_history))
+    assert obj_err < TOL and rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
+
+
+@first_run_pending
+def test_input_dtype_and_memory_order_do_not_matter():
+    """fp32, Fortran-ordered and integer-valued V give the factors of the same V in C-ordered fp64."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.mur import mur
+    m, n, k = 300, 260, 6
+    v = np.round(orc.planted(m, n, k, 42).astype(np.float64) * 8)         # small integers, exact in every dtype
+    w0, h0 = orc.seeded_init(m, n, k, 43)
+    kw = dict(distance_type="eu", min_iter=10**9, max_iter=10, w0=w0, h0=h0, verbose=False)
+    base = mur(v.copy(), k, **kw)
+    for other in (v.astype(np.float32), np.asfortranarray(v), v.astype(np.int64), v[::1, ::1].T.copy().T):
+        res = mur(other, k, **kw)
+        assert np.array_equal(res.w, base.w) and np.array_equal(res.h, base.h)
+        assert res.obj_history == base.obj_history

@@ -14,6 +14,7 @@ def replay(g):
     nnd = kw.pop("nndsvd_init", (False, "zero"))
     m, n = v.shape
     if nnd[0]:
+        np.random.seed(r["init_seed"])               # the 'random' fill draws from the global RNG (utils.py:88-91)
         w0, h0 = orc.nndsvd(v, r["k"], nnd[1])
     else:
         w0, h0 = orc.seeded_init(m, n, r["k"], r["init_seed"])
