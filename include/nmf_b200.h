@@ -237,6 +237,17 @@ int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int sid
 /* mailbox[1], [2] = inner iterations used by the H / W update (AO-ADMM), mailbox[3] = not-PD flag. */
 int nmfb_admm_publish(const nmfb_admm_state* s, double* mailbox, void* stream);
 
+/* Kullback-Leibler branch of ADMM / AO-ADMM, the element-wise data step (admm.py:310-313,
+ * ao_admm.py:89-94).  prod [rows][ld] fp32 holds P = W_aux.H_aux (admm) or a.aux (ao_admm), rows =
+ * v_rows->rows of this rank; with V read from the planes of v_rows:  v_bar = P - dual_v,
+ * v_aux = ((v_bar - 1) + sqrt((v_bar - 1)^2 + 4 V)) / 2,  dual_v += v_aux - P,  d_out <- v_aux + dual_v
+ * (d_out may be prod): the data term a^T (v_aux + dual_v) of the next right-hand sides (admm.py:224,
+ * ao_admm.py:83).  Ingest d_out with nmfb_data_absmax + nmfb_ingest_data_fixed and run the half-steps on a
+ * problem whose v_rows / v_cols are those planes.  done_flag (device, may be NULL): nothing is touched
+ * when *done_flag != 0 (AO-ADMM: the inner loop has broken, ao_admm.py:96-98). */
+int nmfb_kl_vaux(const nmfb_data* v_rows, const float* prod, float* d_out, long ld, float* dual_v,
+                 const int* done_flag, void* stream);
+
 /* One outer iteration of AO-ADMM, Euclidean (ao_admm.py:261-270, 291): per factor Gram, rho = tr/k,
  * Cholesky, numerator GEMM, then up to admm_iter x (solve, prox, dual, residual test ao_admm.py:33-43)
  * with the early break decided on the device.  mailbox[0] = objective, [1] / [2] = inner iterations

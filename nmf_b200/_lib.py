@@ -80,6 +80,7 @@ _SIGNATURES = {
     "nmfb_admm_half_step": (c_int, [P(Problem), P(AdmmState), c_int, C.c_double, c_float, c_int, c_void_p]),
     "nmfb_admm_prepare_l2n": (c_int, [P(Problem), P(AdmmState), c_int, C.c_double, c_void_p]),
     "nmfb_admm_publish": (c_int, [P(AdmmState), c_void_p, c_void_p]),
+    "nmfb_kl_vaux": (c_int, [P(Data), c_void_p, c_void_p, c_long, c_void_p, c_void_p, c_void_p]),
     "nmfb_aoadmm_side_begin": (c_int, [P(Problem), P(AdmmState), c_int, c_void_p]),
     "nmfb_aoadmm_inner": (c_int, [P(Problem), P(AdmmState), c_int, c_int, c_int, c_float, c_int, c_void_p]),
     "nmfb_aoadmm_inner_flag": (c_int, [P(Problem), P(AdmmState), c_int, c_void_p]),

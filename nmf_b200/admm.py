@@ -1,8 +1,10 @@
-"""ADMM for NMF on B200 -- drop-in for the reference's `admm.admm` (nmf/admm.py:233-345), Euclidean
-branch: same keyword arguments, defaults, console output and `Results` / `Experiment` layout.
+"""ADMM for NMF on B200 -- drop-in for the reference's `admm.admm` (nmf/admm.py:233-345): same keyword
+arguments, defaults, console output and `Results` / `Experiment` layout.
 
-One C-ABI call per outer iteration (`nmfb_admm_step`): Gram -> fp64 Cholesky inverse -> split-bf16
-numerator GEMM -> fused solve / prox / dual kernel, for H then W, then the residual objective.
+Euclidean branch: one C-ABI call per outer iteration (`nmfb_admm_step`): Gram -> fp64 Cholesky inverse ->
+split-bf16 numerator GEMM -> fused solve / prox / dual kernel, for H then W, then the residual objective.
+Kullback-Leibler branch (admm.py:303-315, one GPU): the same half-steps on the data term v_aux + dual_v,
+followed by the element-wise v_aux / dual_v kernel (`Engine.admm_kl_step`).
 """
 from __future__ import annotations
 
@@ -35,10 +37,10 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
                             nndsvd_init=nndsvd_init, min_iter=min_iter, max_iter=max_iter, tol1=tol1,
                             tol2=tol2, lambda_w=reg_w[0], prox_w=reg_w[1], lambda_h=reg_h[0],
                             prox_h=reg_h[1])
-    if distance_type == 'kl':
-        raise NotImplementedError("admm with distance_type='kl' (admm.py:303-315) is not provided by the B200 build")
-    if distance_type != 'eu':
+    if distance_type not in ('eu', 'kl'):
         raise TypeError('Unknown loss type.')
+    if distance_type == 'kl' and comm is not None:
+        raise NotImplementedError("admm with distance_type='kl' (admm.py:303-315) runs on one GPU in this build")
     prox_code(reg_w, k), prox_code(reg_h, k)                 # TypeError('Unknown prox_type.') up front
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)
@@ -49,13 +51,13 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
         verbose = verbose and engine.rank == 0
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:
-        eng.upload_data(v, fixed=True)
+        eng.upload_data(v, fixed=(distance_type == 'eu'))     # kl: V is read by the objective and the v_aux step only
     if w0 is None or h0 is None:
         from .init import initial_factors
         w0, h0 = initial_factors(v, k, nndsvd_init)
     eng.set_factors(np.asarray(w0), np.asarray(h0))
 
-    stepper = make_stepper(eng, 'admm', 'eu', rho=rho, reg_w=reg_w, reg_h=reg_h)
+    stepper = make_stepper(eng, 'admm', distance_type, rho=rho, reg_w=reg_w, reg_h=reg_h)
     stepper.prepare()
     obj0 = eng.read_scalar(0)
     lr = _loop.run(eng, stepper.step, obj0=obj0, min_iter=min_iter, max_iter=max_iter, tol1=tol1, tol2=tol2,

@@ -1,9 +1,12 @@
-"""AO-ADMM for NMF on B200 -- drop-in for the reference's `ao_admm.ao_admm` (nmf/ao_admm.py:201-311),
-Euclidean branch: same keyword arguments, defaults, console output and `Results` / `Experiment` layout.
+"""AO-ADMM for NMF on B200 -- drop-in for the reference's `ao_admm.ao_admm` (nmf/ao_admm.py:201-311): same
+keyword arguments, defaults, console output and `Results` / `Experiment` layout.
 
-One C-ABI call per outer iteration (`nmfb_aoadmm_step`).  The inner ADMM loop of each factor
-(ao_admm.py:58-66) runs entirely on the device, early break included; the host only learns how many
+Euclidean branch: one C-ABI call per outer iteration (`nmfb_aoadmm_step`).  The inner ADMM loop of each
+factor (ao_admm.py:58-66) runs entirely on the device, early break included; the host only learns how many
 inner iterations ran (for the reference's 'ADMM break after N iterations.' line).
+Kullback-Leibler branch (ao_admm.py:71-101,272-285, one GPU): `Engine.aoadmm_kl_side` enqueues the inner
+iterations -- each with a fresh right-hand side from v_aux + dual_v and the element-wise data step --, the
+early break is still taken on the device (every kernel of a broken loop returns at its first instruction).
 """
 from __future__ import annotations
 
@@ -31,10 +34,10 @@ def ao_admm(v, k, *, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_
                             nndsvd_init=nndsvd_init, min_iter=min_iter, max_iter=max_iter,
                             admm_iter=admm_iter, tol1=tol1, tol2=tol2, lambda_w=reg_w[0], prox_w=reg_w[1],
                             lambda_h=reg_h[0], prox_h=reg_h[1])
-    if distance_type == 'kl':
-        raise NotImplementedError("ao_admm with distance_type='kl' (ao_admm.py:272-285) is not provided by the B200 build")
-    if distance_type != 'eu':
+    if distance_type not in ('eu', 'kl'):
         raise TypeError('Unknown loss type.')
+    if distance_type == 'kl' and comm is not None:
+        raise NotImplementedError("ao_admm with distance_type='kl' (ao_admm.py:272-285) runs on one GPU in this build")
     prox_code(reg_w, k), prox_code(reg_h, k)
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)
@@ -45,13 +48,13 @@ def ao_admm(v, k, *, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_
         verbose = verbose and engine.rank == 0
     eng = engine if engine is not None else Engine(m, n, k)
     if engine is None or eng.v_rows is None:
-        eng.upload_data(v, fixed=True)
+        eng.upload_data(v, fixed=(distance_type == 'eu'))     # kl: V is read by the objective and the v_aux step only
     if w0 is None or h0 is None:
         from .init import initial_factors
         w0, h0 = initial_factors(v, k, nndsvd_init)
     eng.set_factors(np.asarray(w0), np.asarray(h0))
 
-    stepper = make_stepper(eng, 'ao_admm', 'eu', reg_w=reg_w, reg_h=reg_h, admm_iter=admm_iter)
+    stepper = make_stepper(eng, 'ao_admm', distance_type, reg_w=reg_w, reg_h=reg_h, admm_iter=admm_iter)
     stepper.prepare()
     obj0 = eng.read_scalar(0)
     inner_used = []

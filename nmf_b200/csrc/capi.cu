@@ -629,6 +629,17 @@ int nmfb_admm_publish(const nmfb_admm_state* s, double* mailbox, void* stream) {
     return 0;
 }
 
+int nmfb_kl_vaux(const nmfb_data* v_rows, const float* prod, float* d_out, long ld, float* dual_v,
+                 const int* done_flag, void* stream) {
+    if (!v_rows || !v_rows->planes || !prod || !d_out || !dual_v) return fail(NMFB_ERR_ARG, "kl_vaux: null argument");
+    if (!v_rows->blocked || v_rows->nv < 1 || v_rows->nv > 2 || ld < v_rows->cols)
+        return fail(NMFB_ERR_ARG, "kl_vaux: needs K-blocked data planes (nv = 1 or 2) and ld >= cols");
+    CUDA_TRY(kl_vaux_launch(prod, d_out, dual_v, ld, v_rows->rows, v_rows->cols, bf(v_rows->planes),
+                            static_cast<long>(v_rows->rows_p) * v_rows->ld, v_rows->rows_p, v_rows->nv, done_flag,
+                            st(stream)));
+    return 0;
+}
+
 int nmfb_admm_step(const nmfb_problem* p, const nmfb_admm_state* s, double rho, float lambda_w, int prox_w,
                    float lambda_h, int prox_h, double* mailbox, void* stream) {
     if (!p || !s || !mailbox) return fail(NMFB_ERR_ARG, "admm_step: null argument");
@@ -683,8 +694,10 @@ int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side,
     if ((rc = check_prox(prox)) < 0) return rc;
     const nmfb_factor *other, *self; const nmfb_data* data; float* dual;
     ao_roles(p, s, side, &other, &self, &data, &dual);
-    return admm_apply(p, s, first ? p->partial : nullptr, slots, true, side, self, dual, nullptr, lambda, prox, true,
-                      true, stream);                                                  // ao_admm.py:59-62
+    // the auxiliary itself is kept only when the state carries buffers for it (KL branch: a.aux, ao_admm.py:88)
+    const nmfb_factor* aux = side == 0 ? &s->h_aux : &s->w_aux;
+    return admm_apply(p, s, first ? p->partial : nullptr, slots, true, side, self, dual,
+                      aux->master ? aux : nullptr, lambda, prox, true, true, stream);  // ao_admm.py:59-62
 }
 
 int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream) {

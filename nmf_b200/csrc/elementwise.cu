@@ -518,4 +518,59 @@ cudaError_t sum_partials_launch(const double* partial, int n, double scale, doub
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ KL-ADMM data step
+// admm.py:310-313 / ao_admm.py:89-94, element-wise over V:  with P = (W_aux H_aux)[i][j] in prod,
+//   v_bar = P - dual_v;  v_aux = ((v_bar - 1) + sqrt((v_bar - 1)^2 + 4 v)) / 2;  dual_v += v_aux - P
+// and d_out <- v_aux + dual_v, the data term of the next right-hand sides (admm.py:224; d_out may be prod
+// itself).  The root is taken in fp64, in the cancellation-free form 2v / (sqrt(.) - t) when
+// t = v_bar - 1 < 0.  A set done_flag (AO-ADMM: the inner loop has broken) leaves everything untouched.
+__global__ void __launch_bounds__(256)
+kl_vaux_kernel(const float* prod, float* d_out, float* __restrict__ dual_v, long ld, int rows, int cols,
+               const __nv_bfloat16* __restrict__ vpl, long v_plane, int v_rows_p, int nv,
+               const int* __restrict__ done_flag) {
+    if (done_flag != nullptr && *done_flag != 0) return;
+    const int r = blockIdx.x;                              // rows on x: gridDim.y stops at 65535
+    const int c0 = blockIdx.y * 1024 + threadIdx.x;
+    if (r >= rows) return;
+    float pv[4], dv[4], vv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int c = c0 + u * 256;
+        pv[u] = dv[u] = vv[u] = 0.f;
+        if (c < cols) {
+            const long o = static_cast<long>(r) * ld + c;
+            pv[u] = prod[o];
+            dv[u] = dual_v[o];
+            const long b = blocked_index(r, c, v_rows_p);
+            vv[u] = __bfloat162float(vpl[b]);
+            if (nv > 1) vv[u] += __bfloat162float(vpl[v_plane + b]);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int c = c0 + u * 256;
+        if (c < cols) {
+            const double P = static_cast<double>(pv[u]), v = static_cast<double>(vv[u]);
+            const double t = P - static_cast<double>(dv[u]) - 1.0;
+            const double root = sqrt(fma(t, t, 4.0 * v));
+            const double va = (t >= 0.0) ? 0.5 * (t + root) : (root - t > 0.0 ? 2.0 * v / (root - t) : 0.0);
+            const float dnew = static_cast<float>(static_cast<double>(dv[u]) + va - P);
+            const long o = static_cast<long>(r) * ld + c;
+            dual_v[o] = dnew;
+            d_out[o] = static_cast<float>(va + static_cast<double>(dnew));
+        }
+    }
+}
+
+cudaError_t kl_vaux_launch(const float* prod, float* d_out, float* dual_v, long ld, int rows, int cols,
+                           const __nv_bfloat16* vpl, long v_plane, int v_rows_p, int nv, const int* done_flag,
+                           cudaStream_t stream) {
+    if (rows <= 0 || cols <= 0) return cudaSuccess;
+    if ((cols + 1023) / 1024 > 65535) return cudaErrorInvalidValue;
+    dim3 grid(rows, (cols + 1023) / 1024);
+    kl_vaux_kernel<<<grid, 256, 0, stream>>>(prod, d_out, dual_v, ld, rows, cols, vpl, v_plane, v_rows_p, nv, done_flag);
+    count_launch();
+    return cudaGetLastError();
+}
+
 }  // namespace nmfb

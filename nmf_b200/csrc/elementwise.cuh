@@ -29,5 +29,8 @@ cudaError_t objective_simt_launch(const __nv_bfloat16* vpl, long v_plane, int v_
                                   int* nparts, cudaStream_t stream);
 cudaError_t sum_partials_launch(const double* partial, int n, double scale, double* out,
                                 cudaStream_t stream);
+cudaError_t kl_vaux_launch(const float* prod, float* d_out, float* dual_v, long ld, int rows, int cols,
+                           const __nv_bfloat16* vpl, long v_plane, int v_rows_p, int nv, const int* done_flag,
+                           cudaStream_t stream);
 
 }  // namespace nmfb

@@ -361,10 +361,12 @@ class Engine:
         fs = fac.struct()
         check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
 
-    def alloc_admm(self, with_aux: bool):
+    def alloc_admm(self, with_aux: bool, exact: Optional[bool] = None):
         """Duals (zero, admm.py:31-32 / ao_admm.py:26-27), the k x k inverse workspace and, for ADMM,
-        the signed auxiliaries initialised to copies of W and H (admm.py:27-28)."""
+        the signed auxiliaries initialised to copies of W and H (admm.py:27-28).  exact: contract in the
+        exact-hi arithmetic (default: whenever V was ingested as fixed-point planes)."""
         dev, KP = self.device, self.KP
+        exact = self.fixed if exact is None else bool(exact)
         Lmax = max(self.Mp, self.Np)
         self.dual_w = torch.zeros((KP, self.Mp), dtype=torch.float32, device=dev)
         self.dual_h = torch.zeros((KP, self.Np), dtype=torch.float32, device=dev)
@@ -383,19 +385,112 @@ class Engine:
                 dst.master.copy_(src.master)
                 fs = dst.struct()
                 check(self.lib.nmfb_refresh_planes(KP, C.byref(fs), self.stream))
-                if self.fixed:
+                if exact:
                     self._fixed_planes(dst)
             wa, ha = self.w_aux.struct(), self.h_aux.struct()
         else:
             self.w_aux = self.h_aux = None
             wa, ha = Factor(), Factor()
-            if self.fixed:                      # AO-ADMM contracts against W and H themselves
+            if exact:                           # AO-ADMM contracts against W and H themselves
                 self._fixed_planes(self.w)
                 self._fixed_planes(self.h)
         self._admm = AdmmState(wa, ha, self.dual_w.data_ptr(), self.dual_h.data_ptr(), self.ainv.data_ptr(),
                                self.chol_scratch.data_ptr(), self.c64.data_ptr(), self.admm_scal.data_ptr(),
-                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(self.fixed),
+                               self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(exact),
                                self.binv.data_ptr(), self.tik_scratch.data_ptr())
+
+    # ------------------------------------------------------------------ ADMM, Kullback-Leibler branch
+    def alloc_admm_kl(self, ao: bool = False):
+        """admm.py:33,303-315 / ao_admm.py:28-30,71-101: dual_v (zero) and, instead of v_aux itself, the data
+        term D = v_aux + dual_v of the right-hand sides (zero at the start), kept as fixed-point bf16 planes
+        in the layouts of V and V^T so that the contractions of the Euclidean branch run on it unchanged."""
+        if self.world != 1:
+            raise NotImplementedError("the Kullback-Leibler branch of admm / ao_admm is single-GPU in this build")
+        dev = self.device
+        self.alloc_admm(with_aux=True, exact=True)
+        if ao:                                   # AO-ADMM contracts against W and H themselves (ao_admm.py:83)
+            self._fixed_planes(self.w)
+            self._fixed_planes(self.h)
+        self.kl_dual_v = torch.zeros((self.m, self.n), dtype=torch.float32, device=dev)
+        self.kl_prod = torch.empty((self.m, self.n), dtype=torch.float32, device=dev)
+        self.kl_d = torch.zeros((self.m, self.n), dtype=torch.float32, device=dev)
+        self.d_rows = torch.zeros((2, self.Np // 64, self.per_m, 64), dtype=torch.bfloat16, device=dev)
+        self.d_cols = torch.zeros((2, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=dev)
+        self.d_rowmax = torch.zeros(self.Mp, dtype=torch.int32, device=dev)
+        self.d_colmax = torch.zeros(self.Np, dtype=torch.int32, device=dev)
+        self.d_stats = torch.zeros(4, dtype=torch.int32, device=dev)
+        vr, vc = self._data_structs()
+        self._d_structs = (Data(self.d_rows.data_ptr(), vr.rows, vr.cols, vr.rows_p, vr.ld, 2, 1, 1, 0),
+                           Data(self.d_cols.data_ptr(), vc.rows, vc.cols, vc.rows_p, vc.ld, 2, 1, 1, 0))
+        self._problem_d = Problem.from_buffer_copy(self.problem())
+        self._problem_d.v_rows, self._problem_d.v_cols = self._d_structs
+        self._problem_d.phase_events, self._problem_d.n_phase_events = None, 0
+
+    def kl_data_step(self, left: "FactorBuffers", right: "FactorBuffers", done_flag: Optional[int] = None):
+        """admm.py:309-313 / ao_admm.py:88-94: P = left^T-master @ right-master, i.e. (m x k) @ (k x n) -- a
+        plain fp32 library GEMM --, then one element-wise kernel for v_aux / dual_v that writes
+        D = v_aux + dual_v, then D -> fixed-point planes of both layouts.  done_flag: device address of the
+        AO-ADMM break flag; once it is set D, dual_v and therefore the planes stay what they are."""
+        k, m, n = self.k, self.m, self.n
+        torch.matmul(left.master[:k, :m].t(), right.master[:k, :n], out=self.kl_prod)
+        vr, _vc = self._data_structs()
+        d = self.kl_d
+        check(self.lib.nmfb_kl_vaux(C.byref(vr), self.kl_prod.data_ptr(), d.data_ptr(), d.stride(0),
+                                    self.kl_dual_v.data_ptr(), done_flag, self.stream))
+        self.d_rowmax.zero_()
+        self.d_colmax.zero_()
+        check(self.lib.nmfb_data_absmax(d.data_ptr(), 0, d.stride(0), 0, m, n, self.d_rowmax.data_ptr(),
+                                        self.d_colmax.data_ptr(), self.stream))
+        dr, dc = self._d_structs
+        check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, d.stride(0), 0, m, C.byref(dr), C.byref(dc),
+                                              self.d_stats.data_ptr(), self.d_rowmax.data_ptr(),
+                                              self.d_colmax.data_ptr(), self.stream))
+
+    def admm_kl_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
+        """One outer iteration of admm.py:303-324 with distance_type='kl'."""
+        pd, s = self._problem_d, self._admm
+        check(self.lib.nmfb_admm_half_step(C.byref(pd), C.byref(s), 0, float(rho), float(lambda_h), int(prox_h),
+                                           self.stream))                          # admm.py:304,308,320
+        self._fixed_planes(self.h_aux)
+        check(self.lib.nmfb_admm_half_step(C.byref(pd), C.byref(s), 1, float(rho), float(lambda_w), int(prox_w),
+                                           self.stream))                          # admm.py:305-306,309,321
+        self._fixed_planes(self.w_aux)
+        self.kl_data_step(self.w_aux, self.h_aux)                                 # admm.py:310-313
+        self.objective_kl(slot=ring_slot * 8)                                     # admm.py:324
+        self.admm_publish(ring_slot)
+
+    def aoadmm_kl_side(self, side: int, admm_iter: int, lam, prox):
+        """ao_admm.py:71-101 (admm_kl_update) for H (side 0: a = W) or W (side 1: a = H^T, everything
+        transposed, ao_admm.py:276-284): Gram, rho = tr/k and the Cholesky inverse once; per inner iteration
+        the right-hand side a^T (v_aux + dual_v) is contracted anew, then solve / prox / dual / norms, the data
+        step with P = a.aux and the break test (whose flag freezes the remaining iterations on the device)."""
+        pd, s, KP = self._problem_d, self._admm, self.KP
+        fac, other = (self.h, self.w) if side == 0 else (self.w, self.h)
+        data = self._d_structs[1] if side == 0 else self._d_structs[0]
+        slots = check(self.lib.nmfb_aoadmm_side_begin(C.byref(pd), C.byref(s), side, self.stream))
+        if int(prox) == 2 and float(lam) != 0.0:
+            check(self.lib.nmfb_admm_prepare_l2n(C.byref(pd), C.byref(s), side, float(lam), self.stream))
+        flag = self.admm_flags.data_ptr() + 4                                     # flags[1]: inner loop has broken
+        for it in range(admm_iter):
+            if it > 0:                                                            # ao_admm.py:83: fresh right-hand side
+                slots = check(self.lib.nmfb_panel_gemm_exact(C.byref(data), other.cplanes.data_ptr(), other.Lp, KP,
+                                                             self.partial.data_ptr(), self.partial.numel() * 4,
+                                                             fac.Lp, self.num_sms, self.stream))
+            check(self.lib.nmfb_aoadmm_inner(C.byref(pd), C.byref(s), side, 1, slots, float(lam), int(prox),
+                                             self.stream))                        # ao_admm.py:83-85,92
+            if side == 0:
+                self.kl_data_step(self.w, self.h_aux, flag)                       # ao_admm.py:88-90,94
+            else:
+                self.kl_data_step(self.w_aux, self.h, flag)
+            check(self.lib.nmfb_aoadmm_inner_flag(C.byref(pd), C.byref(s), side, self.stream))   # ao_admm.py:96
+        self._fixed_planes(fac)
+
+    def aoadmm_kl_step(self, admm_iter, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
+        """One outer iteration of ao_admm.py:272-291 with distance_type='kl'."""
+        self.aoadmm_kl_side(0, admm_iter, lambda_h, prox_h)
+        self.aoadmm_kl_side(1, admm_iter, lambda_w, prox_w)
+        self.objective_kl(slot=ring_slot * 8)
+        self.admm_publish(ring_slot)
 
     def admm_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
         p = self.problem()
@@ -429,6 +524,7 @@ class Engine:
         self.v_rows = self.v_cols = None
         self.w = self.h = None
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
-        for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch'):
+        for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch',
+                     'kl_dual_v', 'kl_prod', 'kl_d', 'd_rows', 'd_cols'):
             setattr(self, name, None)
         self._problem = None

@@ -191,6 +191,33 @@ class AdmmStepper(_GemmRoofline):
         return self.phases
 
 
+class AdmmKlStepper:
+    """admm.py:292-334 with distance_type='kl' (:303-315): the half-steps of the Euclidean branch on the data
+    term v_aux + dual_v, then the element-wise v_aux / dual_v step.  Single GPU."""
+    phases = []
+
+    def __init__(self, eng, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n")):
+        self.eng, self.rho = eng, float(rho)
+        self.lw, self.pw = prox_code(reg_w, eng.k)
+        self.lh, self.ph = prox_code(reg_h, eng.k)
+
+    def prepare(self):
+        self.eng.alloc_admm_kl()
+        self.eng.objective_kl(slot=0)
+
+    def step(self, ring_slot):
+        self.eng.admm_kl_step(self.rho, self.lw, self.pw, self.lh, self.ph, ring_slot)
+
+    def phase_names(self):
+        return self.phases
+
+    def phase_pairs(self):
+        return []
+
+    def roofline(self, phase_ms, peaks):
+        return None
+
+
 class AoAdmmStepper(_GemmRoofline):
     """ao_admm.py:259-301 (Euclidean) -> nmfb_aoadmm_step."""
     phases = ["gram_chol_h", "gemm_h", "inner_h", "gram_chol_w", "gemm_w", "inner_w", "objective"]
@@ -226,6 +253,23 @@ class AoAdmmStepper(_GemmRoofline):
         return self.phases
 
 
+class AoAdmmKlStepper(AdmmKlStepper):
+    """ao_admm.py:259-301 with distance_type='kl' (:272-285, admm_kl_update :71-101).  Single GPU; the inner
+    loop is enqueued from the host, its early break is taken on the device (flag-guarded kernels)."""
+
+    def __init__(self, eng, reg_w=(0, "nn"), reg_h=(0, "l2n"), admm_iter=10):
+        self.eng, self.admm_iter = eng, int(admm_iter)
+        self.lw, self.pw = prox_code(reg_w, eng.k)
+        self.lh, self.ph = prox_code(reg_h, eng.k)
+
+    def prepare(self):
+        self.eng.alloc_admm_kl(ao=True)
+        self.eng.objective_kl(slot=0)
+
+    def step(self, ring_slot):
+        self.eng.aoadmm_kl_step(self.admm_iter, self.lw, self.pw, self.lh, self.ph, ring_slot)
+
+
 def make_stepper(eng, method, distance_type="eu", **kw):
     if method == "mur" and distance_type == "eu":
         return MurEuStepper(eng, kw.get("lambda_w", 0.0), kw.get("lambda_h", 0.0))
@@ -233,6 +277,10 @@ def make_stepper(eng, method, distance_type="eu", **kw):
         return MurKlStepper(eng, kw.get("lambda_w", 0.0), kw.get("lambda_h", 0.0))
     if method == "admm" and distance_type == "eu":
         return AdmmStepper(eng, kw.get("rho", 1), kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")))
+    if method == "admm" and distance_type == "kl":
+        return AdmmKlStepper(eng, kw.get("rho", 1), kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")))
     if method == "ao_admm" and distance_type == "eu":
         return AoAdmmStepper(eng, kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")), kw.get("admm_iter", 10))
+    if method == "ao_admm" and distance_type == "kl":
+        return AoAdmmKlStepper(eng, kw.get("reg_w", (0, "nn")), kw.get("reg_h", (0, "l2n")), kw.get("admm_iter", 10))
     raise NotImplementedError(f"no stepper for method={method!r} distance_type={distance_type!r}")
