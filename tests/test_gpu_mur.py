@@ -89,3 +89,22 @@ def test_negative_data_is_shifted_in_place():
     res = mur(v_in, 5, distance_type="eu", min_iter=100, max_iter=5, verbose=False)
     assert np.isclose(v_in.min(), 0.0) and np.allclose(v_in, v - vmin)     # mur.py:99-102
     assert np.all(res.w >= 0) and np.all(res.h >= 0)
+
+
+def test_checkpoint_and_resume(tmp_path):
+    """A checkpoint holds the factors of its iteration; MUR resumed from it retraces the original run."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.mur import mur
+    m, n, k = 512, 384, 16
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    path = str(tmp_path / "ckpt")
+    full = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=20, w0=w0, h0=h0, verbose=False,
+               checkpoint_every=8, checkpoint_path=path)
+    z = np.load(path + ".npz", allow_pickle=True)
+    assert int(z["i"]) == 16 and len(z["obj_history"]) == 18            # last multiple of 8 below 20
+    assert sorted(z.files) == ["experiment", "h", "i", "obj_history", "w"]
+    tr = orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=17)
+    assert rel_fro(z["w"], tr.w) < TOL and rel_fro(z["h"], tr.h) < TOL
+    rest = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=3, w0=z["w"], h0=z["h"], verbose=False)
+    assert rel_fro(rest.w, full.w) < 1e-5 and rel_fro(rest.h, full.h) < 1e-5
