@@ -9,7 +9,8 @@ planted non-negative data.  Prints ONE JSON line (rank 0).
 
   value        iterations/s with V resident in HBM (CUDA events, max over ranks)
   e2e          iterations/s through NMF(V_host, k).factorize(...): upload of the host V, K
-               iterations, download of W and H -- all inside the timed region
+               iterations, download of W and H -- all inside the timed region (N > 1: the same call
+               with comm=True on every rank, barrier to slowest rank)
   roofline     dominant kernel (the split-bf16 tcgen05 panel GEMM) timed live with CUDA events
   cpu_baseline the oracle port of the reference loop (NumPy fp64) timed on this box's host cores
 
@@ -118,18 +119,15 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------
 # synthetic workload on the device: planted low-rank + 1% noise on the bf16 grid
 # ----------------------------------------------------------------------------------------------
-def synth_fill_engine(eng, seed: int, fixed: bool = False):
-    """Fill eng.v_rows / eng.v_cols (1 lossless bf16 plane) for the engine's row / column shard.
-    Every rank walks the same row chunks with the same per-chunk generator, so shards of
-    different ranks are slices of one and the same V."""
+def synth_blocks(dev, m: int, n: int, k: int, seed: int, chunk: int = 2048):
+    """Returns (wt, ht, blocks): blocks() yields (r0, rows r0.. of V as fp32 on the bf16 grid).  Every chunk
+    is drawn from its own counter (seed, r0), so any rank -- and the host rebuild of the end-to-end leg --
+    regenerates the same V chunk by chunk."""
     import torch
-    dev = eng.device
-    m, n, k = eng.m, eng.n, eng.k
     g = torch.Generator(device=dev)
     g.manual_seed(seed)
     wt = torch.rand((m, k), device=dev, generator=g)
     ht = torch.rand((k, n), device=dev, generator=g)
-    chunk = 2048
 
     def blocks():
         for r0 in range(0, m, chunk):
@@ -139,6 +137,14 @@ def synth_fill_engine(eng, seed: int, fixed: bool = False):
             blk.add_(torch.rand((r1 - r0, n), device=dev, generator=g), alpha=0.01)
             yield r0, blk.bfloat16().float()               # values on the bf16 grid, fp32 container
 
+    return wt, ht, blocks
+
+
+def synth_fill_engine(eng, seed: int, fixed: bool = False):
+    """Fill eng.v_rows / eng.v_cols (1 lossless bf16 plane) for the engine's row / column shard.
+    Every rank walks the same row chunks with the same per-chunk generator, so shards of
+    different ranks are slices of one and the same V."""
+    wt, ht, blocks = synth_blocks(eng.device, eng.m, eng.n, eng.k, seed)
     # through the library's ingest kernels; a sharded engine keeps its rows / columns of every chunk
     eng.begin_ingest(1, fixed=fixed)
     if fixed:
@@ -402,11 +408,21 @@ def run_b200(args):
         "peaks": peaks["source"],
     }
 
-    # ---- end to end through the public API with HOST buffers (N = 1) ----
+    # ---- end to end through the public API with HOST buffers ----
+    line["e2e"] = None
     if not args.no_e2e and world == 1:
         line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps)
-    else:
-        line["e2e"] = None
+    elif not args.no_e2e:
+        # a failure or a stall of this leg must not cost the device-timed line: after E2E_LIMIT_S seconds
+        # every rank prints / exits with what it has
+        guard = threading.Timer(E2E_LIMIT_S, _e2e_timed_out, args=(line, rank))
+        guard.daemon = True
+        guard.start()
+        try:
+            line["e2e"] = run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank)
+        except Exception as exc:                             # noqa: BLE001 -- reported in the line
+            line["e2e"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
+        guard.cancel()
     if not args.no_cpu and rank == 0 and world == 1:
         its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
         line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
@@ -459,6 +475,87 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
     return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
             "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps,
             "what": "NMF(V_host fp32 pinned, k).factorize(max_iter=steps): ingest + iterations + factor download"}
+
+
+E2E_LIMIT_S = 300.0
+
+
+def _e2e_timed_out(line, rank):
+    line["e2e"] = {"value": None, "error": f"end-to-end leg exceeded {E2E_LIMIT_S:.0f} s; device-timed fields are complete"}
+    if rank == 0:
+        emit(line)
+    os._exit(0)
+
+
+def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
+    """N > 1: the same call on every rank, NMF(V_host, k).factorize(..., comm=True) -- each rank is handed the
+    whole host V (that is the public API of a sharded run) and keeps its rows and
+    columns.  Timed from a barrier to the slowest rank's return (upload, `steps` iterations with the objective
+    read back every iteration, download of W and H on every rank)."""
+    import contextlib
+    import io
+
+    import psutil
+    import torch
+    import torch.distributed as dist
+    from nmf_b200 import NMF
+
+    dev = eng.device
+
+    def agreed(flag: bool) -> bool:                          # every rank takes the same branch
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    need = 4 * m * n
+    dist.barrier()
+    if not agreed(psutil.virtual_memory().available > 1.3 * need * world):
+        return {"value": None, "error": f"host memory: {world} ranks x {need / 2**30:.1f} GiB of V do not fit"}
+    w0 = eng.w.master[:k, :m].t().contiguous().cpu().numpy()     # current (replicated) factors as the start
+    h0 = eng.h.master[:k, :n].contiguous().cpu().numpy()
+    torch.cuda.synchronize(dev)
+    eng.release()
+    torch.cuda.empty_cache()
+    v_host, pinned = None, True
+    try:
+        v_host = torch.empty((m, n), dtype=torch.float32).pin_memory()
+    except Exception:                                        # noqa: BLE001 -- pageable memory is slower, not wrong
+        pinned = False
+        try:
+            v_host = torch.empty((m, n), dtype=torch.float32)
+        except Exception:                                    # noqa: BLE001
+            v_host = None
+    if not agreed(v_host is not None):
+        return {"value": None, "error": "host allocation of V failed on a rank"}
+    _wt, _ht, blocks = synth_blocks(dev, m, n, k, seed=0)
+    for r0, blk in blocks():
+        v_host[r0:r0 + blk.shape[0]].copy_(blk)
+    del _wt, _ht, blk
+    torch.cuda.empty_cache()
+    v_np = v_host.numpy()
+    kw = dict(extra)
+    if method == "mur":
+        kw["distance_type"] = dtype_
+    else:
+        kw["nndsvd_init"] = (False, "zero")
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    t0 = time.perf_counter()
+    model = NMF(v_np, k)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model.factorize(method=method, min_iter=10**9, max_iter=steps, w0=w0, h0=h0, verbose=False, comm=True, **kw)
+    torch.cuda.synchronize(dev)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    dt = float(dt.item())
+    res = model.results
+    assert res.i == steps - 1 and len(res.obj_history) == steps + 1
+    h2d = world * (v_np.nbytes + w0.nbytes + h0.nbytes)          # every rank walks the whole V and keeps its shards
+    d2h = world * (res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1))
+    return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
+            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps, "host_v_pinned": pinned,
+            "what": f"on each of {world} ranks NMF(V_host fp32, k).factorize(max_iter=steps, comm=True): "
+                    "ingest of the rank's rows and columns of V + iterations + factor download; slowest rank"}
 
 
 _JSON_FD = None
