@@ -12,6 +12,7 @@ planted non-negative data.  Prints ONE JSON line (rank 0).
                iterations, download of W and H -- all inside the timed region (N > 1: the same call
                with comm=True on every rank, barrier to slowest rank)
   roofline     dominant kernel (the split-bf16 tcgen05 panel GEMM) timed live with CUDA events
+  time_to_tol  seconds until the reference's stop test fires (tol2 = 1e-5 x initial objective), end to end
   cpu_baseline the oracle port of the reference loop (NumPy fp64) timed on this box's host cores
 
 `--impl reference` times the reference algorithm (oracle port; the reference is pure Python and
@@ -339,6 +340,7 @@ def run_b200(args):
     synth_init(eng, seed=1)
     stepper = solvers.make_stepper(eng, method, dtype_, **extra)
     stepper.prepare()
+    obj0 = eng.read_scalar(0)                                  # objective of the initial pair
     launches0 = eng.launch_count()
     lagged = getattr(stepper, "lagged", False)
 
@@ -411,7 +413,8 @@ def run_b200(args):
     # ---- end to end through the public API with HOST buffers ----
     line["e2e"] = None
     if not args.no_e2e and world == 1:
-        line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps)
+        line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0)
+        line["time_to_tol"] = line["e2e"].pop("time_to_tol", None)
     elif not args.no_e2e:
         # a failure or a stall of this leg must not cost the device-timed line: after E2E_LIMIT_S seconds
         # every rank prints / exits with what it has
@@ -432,7 +435,43 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
+TTT_MAX_ITER = 300
+
+
+def run_time_to_tol(v_np, method, dtype_, k, extra, obj0):
+    """End-to-end time to tolerance (BASELINE.json north_star) through the public API, host V in, host W / H
+    out, the reference's own stop test switched on (utils.py:4-15: stop when the objective falls by less than
+    tol2 in one iteration, or rises): tol2 = 1e-5 x the initial objective, tol1 = 0, min_iter = 10, the
+    reference's default random init from the seeded global RNG (mur.py:108-109), at most TTT_MAX_ITER."""
+    import contextlib
+    import io
+
+    import torch
+    from nmf_b200 import NMF
+
+    tol2 = 1e-5 * float(obj0)
+    kw = dict(extra)
+    if method == "mur":
+        kw["distance_type"] = dtype_
+    else:
+        kw["nndsvd_init"] = (False, "zero")
+    np.random.seed(1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    model = NMF(v_np, k)
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink):
+        model.factorize(method=method, min_iter=10, max_iter=TTT_MAX_ITER, tol1=0.0, tol2=tol2, verbose=False, **kw)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    res = model.results
+    return {"seconds": dt, "iterations": res.i + 1, "converged": "Algorithm converged" in sink.getvalue(),
+            "tol1": 0.0, "tol2": tol2, "min_iter": 10, "max_iter": TTT_MAX_ITER,
+            "objective_first": res.obj_history[0], "objective_last": res.obj_history[-1],
+            "rule": "reference stop test (utils.py:4-15) with tol2 = 1e-5 x initial objective; host V in, host W/H out"}
+
+
+def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0=None):
     """NMF(V_host, k).factorize(...) with V, W0, H0 in (pinned) host memory; the timed region
     covers upload, `steps` iterations (objective every iteration) and the download of W, H."""
     import contextlib
@@ -472,9 +511,15 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps):
     assert res.i == steps - 1 and len(res.obj_history) == steps + 1
     h2d = v_np.nbytes + w0.nbytes + h0.nbytes
     d2h = res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1)    # factors travel as fp32
-    return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
-            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps,
-            "what": "NMF(V_host fp32 pinned, k).factorize(max_iter=steps): ingest + iterations + factor download"}
+    out = {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
+           "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps,
+           "what": "NMF(V_host fp32 pinned, k).factorize(max_iter=steps): ingest + iterations + factor download"}
+    if obj0 is not None:
+        try:
+            out["time_to_tol"] = run_time_to_tol(v_np, method, dtype_, k, extra, obj0)
+        except Exception as exc:                             # noqa: BLE001 -- reported, never costs the line
+            out["time_to_tol"] = {"seconds": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
+    return out
 
 
 E2E_LIMIT_S = 300.0
