@@ -52,10 +52,7 @@ class Engine:
 
     def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None, rank: int = 0,
                  world: int = 1, group=None):
-        if not torch.cuda.is_available():
-            raise RuntimeError("nmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
-        self.lib = _lib.load()
-        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.lib, self.device, self.num_sms = self._open_device(device)
         self.m, self.n, self.k = int(m), int(n), int(k)
         self.rank, self.world = int(rank), int(world)
         self.group = group
@@ -69,11 +66,7 @@ class Engine:
         if self.row_range[1] <= self.row_range[0] or self.col_range[1] <= self.col_range[0]:
             raise ValueError(f"{self.world} ranks leave rank {self.rank} without rows or columns of a "
                              f"{self.m} x {self.n} problem (shards are multiples of 256); use fewer ranks")
-        props = torch.cuda.get_device_properties(self.device)
-        if props.major != 10:
-            raise RuntimeError(f"nmf_b200 is built for sm_100a only; device is sm_{props.major}{props.minor}")
-        self.num_sms = props.multi_processor_count
-        with torch.cuda.device(self.device):
+        with self._device_ctx():
             sharded = self.world > 1
             self.w = FactorBuffers(self.m, self.KP, self.device, self.Mp, self.row_win[0] if sharded else 0,
                                    self.per_m if sharded else 0)
@@ -98,6 +91,28 @@ class Engine:
         self.v_cols = None
         self.vmin = None
         self._problem = None
+
+    # The three places that touch the CUDA runtime directly (tests/softdev.py swaps them for a host stand-in
+    # of the device to run the orchestration on the CPU; the product always goes through these).
+    def _open_device(self, device):
+        """-> (C-ABI library, torch device, SM count); raises without a B200."""
+        if not torch.cuda.is_available():
+            raise RuntimeError("nmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+        lib = _lib.load()
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        props = torch.cuda.get_device_properties(dev)
+        if props.major != 10:
+            raise RuntimeError(f"nmf_b200 is built for sm_100a only; device is sm_{props.major}{props.minor}")
+        return lib, dev, props.multi_processor_count
+
+    def _device_ctx(self):
+        return torch.cuda.device(self.device)
+
+    def _sync_stream(self):
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def _hbm_free(self) -> int:
+        return torch.cuda.mem_get_info(self.device)[0]
 
     @classmethod
     def for_comm(cls, m: int, n: int, k: int, comm) -> "Engine":
@@ -247,7 +262,7 @@ class Engine:
         if cache is not None and cache[0] is v:
             yield from cache[1]
             return
-        free, _total = torch.cuda.mem_get_info(self.device)
+        free = self._hbm_free()
         planes_bytes = 8 * self.m * self.n // self.world + (64 << 20)         # two copies x two bf16 planes
         keep = getattr(self, "_keep_chunks", False) and v.nbytes + planes_bytes < 0.8 * free
         kept = []
@@ -329,7 +344,7 @@ class Engine:
             fs = fac.struct()
             check(self.lib.nmfb_import_factor(d.data_ptr(), 1 if a.dtype == np.float64 else 0, stride_l,
                                               stride_c, self.k, self.KP, C.byref(fs), self.stream))
-            torch.cuda.current_stream(self.device).synchronize()
+            self._sync_stream()
             del d
         self._problem = None
 

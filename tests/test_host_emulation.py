@@ -280,3 +280,81 @@ def test_inner_flag_kernel(emu):
     nan[:, 3] = 0.0
     nan[:, 2] = 0.0                                          # s = 0/0
     assert run(nan, [0] * 8)[1] == 0
+
+
+# ----------------------------------------------------------------------------------------------
+# tests/softdev.py runs the orchestration tests on NumPy restatements of the three data-path kernels (a host
+# thread per CUDA thread is too slow for a data term that is re-ingested every iteration): pin those
+# restatements to the kernel text, bit for bit.
+# ----------------------------------------------------------------------------------------------
+def _data_struct(planes, rows, cols, rows_p, ld, nv, fixed, origin):
+    from nmf_b200._lib import Data
+    return Data(planes.ctypes.data, rows, cols, rows_p, ld, nv, 1, fixed, origin)
+
+
+@pytest.mark.parametrize("fixed", [0, 1])
+@pytest.mark.parametrize("window", [None, (64, 70, 128, 60)])        # (row_lo, row_n, col_lo, col_n): a shard
+def test_numpy_ingest_equals_the_kernel(emu, fixed, window):
+    import softdev
+    m, n = 150, 200
+    rng = np.random.default_rng(17 + fixed)
+    v = (rng.standard_normal((m, n)) * np.exp(rng.standard_normal((m, 1)))).astype(np.float32)
+    if not fixed:
+        v = np.abs(v)
+    v[7] = 0
+    row_lo, row_n, col_lo, col_n = window or (0, m, 0, n)
+    ld_r, ld_c = 256, 256                                   # round_up(n, 256), round_up(m, 256)
+    rp_r, rp_c = 256, 256
+    nv = 2
+    out = []
+    for impl in ("kernel", "numpy"):
+        rowp = np.zeros((nv, ld_r // 64, rp_r, 64), np.uint16)
+        colp = np.zeros((nv, ld_c // 64, rp_c, 64), np.uint16)
+        stats = np.array([0xFFFFFFFF, 0, 0, 0], np.uint32)
+        rowmax, colmax = np.zeros(256, np.uint32), np.zeros(256, np.uint32)
+        for r0, r1 in ((0, 64), (64, 150)):                 # two chunks, like Engine.upload_data
+            chunk = np.ascontiguousarray(v[r0:r1])
+            if impl == "kernel":
+                emu.emu_data_absmax(ptr(chunk), C.c_long(n), r0, r1 - r0, n, ptr(rowmax), ptr(colmax))
+            else:
+                softdev.np_absmax(chunk, r0, rowmax, colmax)
+        for r0, r1 in ((0, 64), (64, 150)):
+            chunk = np.ascontiguousarray(v[r0:r1])
+            if impl == "kernel":
+                emu.emu_ingest(ptr(chunk), C.c_long(n), r0, r1 - r0, n, ptr(rowp), C.c_long(rowp[0].size), rp_r,
+                               ptr(colp), C.c_long(colp[0].size), rp_c, nv, ptr(stats),
+                               ptr(rowmax) if fixed else None, ptr(colmax) if fixed else None,
+                               row_lo, row_n, col_lo, col_n)
+            else:
+                vr = _data_struct(rowp, row_n, n, rp_r, ld_r, nv, fixed, row_lo)
+                vc = _data_struct(colp, col_n, m, rp_c, ld_c, nv, fixed, col_lo)
+                softdev.np_ingest(chunk, r0, vr, vc, stats, rowmax if fixed else None, colmax if fixed else None)
+        out.append((rowp, colp, stats, rowmax, colmax))
+    for a, b in zip(*out):
+        assert np.array_equal(a, b)
+    rowp, colp, stats = out[1][:3]
+    assert rowp.any() and colp.any() and stats[2] == 0
+    # and the decode the soft device uses gives back V (to the two planes' precision) for the rank's shard
+    got = softdev.SoftLib.decode(_data_struct(rowp, row_n, n, rp_r, ld_r, nv, fixed, row_lo))
+    np.testing.assert_allclose(got, v[row_lo:row_lo + row_n], rtol=2 ** -15, atol=np.abs(v).max() * 2 ** -15)
+    got = softdev.SoftLib.decode(_data_struct(colp, col_n, m, rp_c, ld_c, nv, fixed, col_lo))
+    np.testing.assert_allclose(got, v[:, col_lo:col_lo + col_n].T, rtol=2 ** -15, atol=np.abs(v).max() * 2 ** -15)
+
+
+def test_numpy_kl_vaux_equals_the_kernel(emu):
+    import softdev
+    rows, cols, rows_p, ld = 5, 300, 64, 320
+    rng = np.random.default_rng(23)
+    v = orc.round_to_bf16_grid(rng.random((rows, cols)).astype(np.float32) * 2)
+    planes = blocked(f32_to_bf16(v), rows_p)[None]
+    prod = np.zeros((rows, ld), np.float32)
+    prod[:, :cols] = rng.standard_normal((rows, cols)) * 30
+    dv = np.zeros((rows, ld), np.float32)
+    dv[:, :cols] = rng.standard_normal((rows, cols))
+    a = [prod.copy(), np.zeros_like(prod), dv.copy()]
+    b = [prod.copy(), np.zeros_like(prod), dv.copy()]
+    emu.emu_kl_vaux(ptr(a[0]), ptr(a[1]), ptr(a[2]), C.c_long(ld), rows, cols, ptr(planes), C.c_long(planes[0].size),
+                    rows_p, 1, None)
+    softdev.np_kl_vaux(b[0][:, :cols], b[1][:, :cols], b[2][:, :cols], v.astype(np.float64))
+    for x, y in zip(a, b):                                   # fma(t, t, 4v) vs t*t + 4v: at most an fp32 ulp apart
+        np.testing.assert_allclose(x, y, rtol=3e-7, atol=1e-7)

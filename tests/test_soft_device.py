@@ -1,0 +1,212 @@
+"""CPU: the whole host side of the product -- drivers, host loop, steppers, Engine, upload passes -- on the host
+stand-in of the device (tests/softdev.py): every frozen reference run is replayed through the PUBLIC API
+(`NMF(v, k).factorize(...)`), with V really living in K-blocked bf16 planes written by the (emulated) ingest
+kernels, the solver arithmetic restated in NumPy behind the C-ABI entry points, and the freshness of every bf16
+factor plane asserted at each consumer.  What this pins down is the orchestration: which buffer goes where, in
+which order, with which planes re-derived -- including the paths whose first GPU run is still pending (prox l2n,
+the Kullback-Leibler branch of admm / ao_admm, checkpoints)."""
+import contextlib
+import io
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from conftest import GOLDEN_NAMES, golden_v, load_golden, rel_fro  # noqa: E402
+from oracle import nmf_oracle as orc  # noqa: E402
+
+if not os.path.exists("/usr/local/cuda/include/cuda_bf16.h"):
+    pytest.skip("CUDA headers not found (host emulation of the ingest kernels)", allow_module_level=True)
+
+import softdev  # noqa: E402
+
+TOL = 1e-4
+
+
+@pytest.fixture
+def soft(monkeypatch):
+    import nmf_b200.init as init_mod
+    monkeypatch.setattr(init_mod, "nndsvd", orc.nndsvd)          # the product's NNDSVD needs cuSOLVER
+    with softdev.soft_device():
+        yield
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_public_api_on_the_soft_device_matches_reference_golden(soft, name):
+    from nmf_b200 import NMF
+    from nmf_b200.ao_admm import ao_admm
+    g = load_golden(name)
+    r = g["recipe"]
+    v = golden_v(r["v"])
+    np.random.seed(r["init_seed"])
+    model = NMF(v.copy(), r["k"])
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink):
+        model.factorize(method=r["method"], **r["kw"])
+    res = model.results
+    assert res.i == int(g["i"]), "stop iteration differs from the reference"
+    assert len(res.obj_history) == len(g["obj_history"])
+    obj_err = np.max(np.abs(np.array(res.obj_history) - g["obj_history"]) / g["obj_history"])
+    assert obj_err < TOL
+    assert rel_fro(res.w, g["w"]) < TOL and rel_fro(res.h, g["h"]) < TOL
+    assert res.w.dtype == np.float64 and res.w.shape == g["w"].shape
+    if r["method"] == "ao_admm":
+        assert sink.getvalue().count("ADMM break after") == int(g["n_inner_breaks"])
+        assert len(ao_admm.last_inner_iterations) == res.i + 1
+    assert "Factorization done." in sink.getvalue()
+
+
+# ----------------------------------------------------------------------------------------------
+# N > 1: the same drivers with comm=True on two gloo ranks, each with its own soft device holding only its rows
+# and columns of V (the sharded ingest, the window half-steps, the all-gathers of masters / norm partials, the
+# plane refreshes after every exchange, the all-reduced objective) against the unsharded oracle.
+# ----------------------------------------------------------------------------------------------
+def _sharded_worker(rank, world, port, ret):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from nmf_b200.admm import admm
+        from nmf_b200.ao_admm import ao_admm
+        from nmf_b200.mur import mur
+        m, n, k, iters = 600, 520, 6, 12                     # 2 ranks: windows of 512 rows / columns, the second one ragged
+        v = orc.planted(m, n, k, 0).astype(np.float64)
+        w0, h0 = orc.seeded_init(m, n, k, 1)
+        common = dict(min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False, comm=True)
+        out = {}
+        with softdev.soft_device():
+            for name, run, ref in (
+                ("mur_eu", lambda: mur(v, k, distance_type="eu", lambda_w=0.05, **common),
+                 lambda: orc.mur_run(v, k, w0, h0, distance_type="eu", lambda_w=0.05, min_iter=10**9, max_iter=iters)),
+                ("mur_kl", lambda: mur(v, k, distance_type="kl", **common),
+                 lambda: orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=iters)),
+                ("admm", lambda: admm(v, k, rho=20, reg_w=(0, "nn"), reg_h=(0.05, "l1n"),
+                                      nndsvd_init=(False, "zero"), **common),
+                 lambda: orc.admm_run(v, k, w0, h0, rho=20, reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=10**9,
+                                      max_iter=iters)),
+                ("ao_admm", lambda: ao_admm(v, k, reg_w=(0.1, "l2n"), reg_h=(0.05, "l1n"), admm_iter=4,
+                                            nndsvd_init=(False, "zero"), **common),
+                 lambda: orc.ao_admm_run(v, k, w0, h0, reg_w=(0.1, "l2n"), reg_h=(0.05, "l1n"), admm_iter=4,
+                                         min_iter=10**9, max_iter=iters)),
+            ):
+                res, tr = run(), ref()
+                oe = max(abs(a - b) / b for a, b in zip(res.obj_history, tr.obj_history))
+                out[name] = (res.i == tr.i, oe, rel_fro(res.w, tr.w), rel_fro(res.h, tr.h),
+                             float(np.abs(res.w).sum() + np.abs(res.h).sum()))
+                if name == "ao_admm":
+                    out["ao_breaks"] = [tuple(u) for u in ao_admm.last_inner_iterations] == \
+                        [tuple(u) for u in tr.inner_breaks]
+        ret[rank] = out
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_through_the_public_drivers_reproduce_the_unsharded_oracle():
+    import torch.multiprocessing as mp
+    softdev.emu_lib()                                        # build once, before the ranks race for it
+    world = 2
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 29900 + (os.getpid() % 90)
+    procs = [ctx.Process(target=_sharded_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(600)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    for name in ("mur_eu", "mur_kl", "admm", "ao_admm"):
+        for rank in range(world):
+            same_i, oe, ew, eh, _ = ret[rank][name]
+            assert same_i and oe < TOL and ew < TOL and eh < TOL, (name, rank, ret[rank][name])
+        assert ret[0][name][4] == ret[1][name][4], f"{name}: the ranks hold different factors"
+    assert ret[0]["ao_breaks"] and ret[1]["ao_breaks"]
+
+
+# ----------------------------------------------------------------------------------------------
+# Host behaviours around the solver loop, through the public API on the soft device
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["eu", "kl"])
+def test_stop_iteration_and_returned_factors_follow_the_reference_loop(soft, kind):
+    """A stop test that fires: same stop iteration, the factors OF that iteration (the device runs one iteration
+    ahead of the host; MUR-KL additionally reads its objective one iteration late), same history."""
+    from nmf_b200.mur import mur
+    m, n, k = 90, 70, 4
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    kw = dict(distance_type=kind, min_iter=3, max_iter=400, tol1=1e-3, tol2=0.05)
+    want = orc.mur_run(v, k, w0, h0, **kw)
+    assert 3 < want.i < 399
+    with contextlib.redirect_stdout(io.StringIO()) as sink:
+        res = mur(v, k, w0=w0, h0=h0, **kw)
+    assert res.i == want.i and len(res.obj_history) == want.i + 2
+    assert rel_fro(res.w, want.w) < 1e-5 and rel_fro(res.h, want.h) < 1e-5
+    out = sink.getvalue().splitlines()
+    assert out[0].startswith("[0]: ") and out[-1] == "Algorithm converged (2)."
+
+
+def test_checkpoints_and_resume_through_the_public_api(soft, tmp_path):
+    from nmf_b200.mur import mur
+    m, n, k = 120, 100, 5
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    path = str(tmp_path / "ckpt")
+    full = mur(v, k, distance_type="kl", min_iter=10**9, max_iter=20, w0=w0, h0=h0, verbose=False,
+               checkpoint_every=8, checkpoint_path=path)
+    z = np.load(path + ".npz", allow_pickle=True)
+    assert int(z["i"]) == 16 and len(z["obj_history"]) == 18
+    assert sorted(z.files) == ["experiment", "h", "i", "obj_history", "w"]
+    tr = orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=17)
+    assert rel_fro(z["w"], tr.w) < 1e-5 and rel_fro(z["h"], tr.h) < 1e-5
+    rest = mur(v, k, distance_type="kl", min_iter=10**9, max_iter=3, w0=z["w"], h0=z["h"], verbose=False)
+    assert np.array_equal(rest.w, full.w) and np.array_equal(rest.h, full.h)
+
+
+def test_negative_data_is_shifted_in_place_and_reuploaded(soft):
+    from nmf_b200.mur import mur
+    rng = np.random.default_rng(0)
+    v = rng.random((70, 50)) - 0.25
+    vmin, v_in = v.min(), v.copy()
+    w0, h0 = orc.seeded_init(70, 50, 3, 1)
+    res = mur(v_in, 3, distance_type="eu", min_iter=100, max_iter=5, w0=w0, h0=h0, verbose=False)
+    assert np.isclose(v_in.min(), 0.0) and np.allclose(v_in, v - vmin)              # mur.py:99-102
+    want = orc.mur_run(v - vmin, 3, w0, h0, distance_type="eu", min_iter=100, max_iter=5)
+    assert rel_fro(res.w, want.w) < TOL and rel_fro(res.h, want.h) < TOL
+
+
+@pytest.mark.parametrize("shape", [(5, 7, 2), (300, 70, 3), (70, 300, 3), (130, 260, 70)])
+def test_odd_shapes_pad_and_unpad_correctly(soft, shape):
+    """Smaller than a tile, flat, tall, and k = 70 (KP = 128): padding to 256 / KP must never leak into results."""
+    from nmf_b200.admm import admm
+    from nmf_b200.mur import mur
+    m, n, k = shape
+    v = orc.planted(m, n, k, 4).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 5)
+    res = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=6, w0=w0, h0=h0, verbose=False)
+    want = orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=6)
+    assert res.w.shape == (m, k) and res.h.shape == (k, n)
+    assert rel_fro(res.w, want.w) < TOL and rel_fro(res.h, want.h) < TOL
+    kw = dict(rho=5, reg_w=(0, "nn"), reg_h=(0.01, "l1n"))
+    res = admm(v, k, min_iter=10**9, max_iter=4, w0=w0, h0=h0, verbose=False, nndsvd_init=(False, "zero"), **kw)
+    want = orc.admm_run(v, k, w0, h0, min_iter=10**9, max_iter=4, **kw)
+    assert rel_fro(res.w, want.w) < TOL and rel_fro(res.h, want.h) < TOL
+
+
+def test_errors_surface_like_the_reference(soft):
+    from nmf_b200.admm import admm
+    from nmf_b200.ao_admm import ao_admm
+    v = np.random.default_rng(0).random((128, 96))
+    np.random.seed(1)
+    with pytest.raises(np.linalg.LinAlgError):             # H collapses to 0: rho = tr(0)/k = 0 (ao_admm.py:55)
+        ao_admm(v, 4, reg_w=(0, "nn"), reg_h=(500.0, "l1n"), admm_iter=5, min_iter=100, max_iter=50,
+                nndsvd_init=(False, "zero"), verbose=False)
+    with pytest.raises(TypeError):
+        admm(v, 4, reg_h=(0.1, "bogus"), nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
+    with pytest.raises(TypeError):
+        admm(v, 4, distance_type="xx", nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
+    with pytest.raises(NotImplementedError):
+        admm(v, 4, distance_type="kl", comm=True, nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
