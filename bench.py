@@ -534,8 +534,8 @@ def _e2e_timed_out(line, rank):
 
 def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
     """N > 1: the same call on every rank, NMF(V_host, k).factorize(..., comm=True) -- each rank is handed the
-    whole host V (that is the public API of a sharded run) and keeps its rows and
-    columns.  Timed from a barrier to the slowest rank's return (upload, `steps` iterations with the objective
+    whole host V (that is the public API of a sharded run), uploads its rows of it
+    and receives its columns from the other ranks' row shards over NVLink (Engine._ingest_pass_sharded).  Timed from a barrier to the slowest rank's return (upload, `steps` iterations with the objective
     read back every iteration, download of W and H on every rank)."""
     import contextlib
     import io
@@ -595,12 +595,14 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
     dt = float(dt.item())
     res = model.results
     assert res.i == steps - 1 and len(res.obj_history) == steps + 1
-    h2d = world * (v_np.nbytes + w0.nbytes + h0.nbytes)          # every rank walks the whole V and keeps its shards
+    # each rank uploads its rows of V (the column copy is assembled over NVLink) and both initial factors
+    h2d = v_np.nbytes + world * (w0.nbytes + h0.nbytes)
     d2h = world * (res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1))
     return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
             "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps, "host_v_pinned": pinned,
             "what": f"on each of {world} ranks NMF(V_host fp32, k).factorize(max_iter=steps, comm=True): "
-                    "ingest of the rank's rows and columns of V + iterations + factor download; slowest rank"}
+                    "upload of the rank's rows of V, all-to-all for its columns, iterations, factor download; "
+                    "slowest rank"}
 
 
 _JSON_FD = None

@@ -7,6 +7,7 @@ and nothing else: every arithmetic step is a kernel of libnmf_b200.so reached th
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Tuple
 
 import numpy as np
@@ -14,7 +15,8 @@ import torch
 
 from . import _lib
 from ._lib import AdmmState, Data, Factor, Problem, check
-from .sharding import allgather_flat, allgather_windows, allreduce_max_, allreduce_sum_, live_rows, shard_bounds
+from .sharding import (allgather_flat, allgather_windows, allreduce_max_, allreduce_min_key_, allreduce_sum_,
+                       exchange_blocks, live_rows, shard_bounds)
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -276,7 +278,70 @@ class Engine:
         if keep:
             self._chunk_cache = (v, kept)
 
+    # ---- sharded upload: every rank reads ONLY its rows of the host V; the column copy is assembled from the
+    # ranks' row shards by an all-to-all over NVLink (1/P of V over each PCIe link instead of all of it)
+    def _shard_and_panel(self, v: np.ndarray):
+        """(shard, panel): this rank's rows V[I_p, :] and columns V[:, J_p] as fp32 device tensors."""
+        cache = getattr(self, "_chunk_cache", None)
+        if cache is not None and cache[0] is v:
+            return cache[1]
+        r0, r1 = self.row_range
+        c0, c1 = self.col_range
+        shard = torch.empty((r1 - r0, self.n), dtype=torch.float32, device=self.device)
+        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
+        for a in range(r0, r1, rows_per):
+            b = min(r1, a + rows_per)
+            shard[a - r0:b - r0].copy_(torch.from_numpy(v[a:b]).to(self.device))      # casts fp64 -> fp32 on the device
+        mb = shard_bounds(self.m, self.world)[2]
+        nb = shard_bounds(self.n, self.world)[2]
+        rows_of = [(lo, lo + live_rows(self.m, lo, hi)) for lo, hi in mb]
+        cols_of = [(lo, lo + live_rows(self.n, lo, hi)) for lo, hi in nb]
+        send = [shard[:, a:b].contiguous() for a, b in cols_of]                          # my rows of rank q's columns
+        panel = torch.empty((self.m, c1 - c0), dtype=torch.float32, device=self.device)
+        recv = [panel[a:b] for a, b in rows_of]                                          # row slices are contiguous
+        exchange_blocks(send, recv, self.group)
+        del send
+        out = (shard, panel)
+        if getattr(self, "_keep_chunks", False):
+            self._chunk_cache = (v, out)
+        return out
+
+    def _ingest_pass_sharded(self, v: np.ndarray, nv: int, fixed: bool):
+        shard, panel = self._shard_and_panel(v)
+        self.begin_ingest(nv, fixed)
+        (r0, r1), (c0, c1) = self.row_range, self.col_range
+        vr, vc = self._data_structs()
+        # row pass: my rows, all columns -> v_rows only (empty column window); column pass: all rows of my columns,
+        # presented as a matrix with c1 - c0 columns -> v_cols only (empty row window)
+        vc_none = Data(vc.planes, 0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
+        vr_none = Data(vr.planes, 0, c1 - c0, vr.rows_p, vr.ld, vr.nv, 1, vr.fixed, 0)
+        vc_local = Data(vc.planes, c1 - c0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
+        st = self.stats.data_ptr()
+        if fixed:
+            scratch = torch.zeros(max(self.Mp, self.Np), dtype=torch.int32, device=self.device)
+            check(self.lib.nmfb_data_absmax(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, self.n,
+                                            self.rowmax.data_ptr(), scratch.data_ptr(), self.stream))
+            scratch.zero_()
+            check(self.lib.nmfb_data_absmax(panel.data_ptr(), 0, panel.stride(0), 0, self.m, c1 - c0,
+                                            scratch.data_ptr(), self.colmax.data_ptr() + 4 * c0, self.stream))
+            allreduce_max_(self.rowmax, self.group)          # the column pass judges exactness with every row's unit
+            check(self.lib.nmfb_ingest_data_fixed(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
+                                                  C.byref(vc_none), st, self.rowmax.data_ptr(),
+                                                  self.colmax.data_ptr(), self.stream))
+            check(self.lib.nmfb_ingest_data_fixed(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
+                                                  C.byref(vc_local), st, self.rowmax.data_ptr(),
+                                                  self.colmax.data_ptr() + 4 * c0, self.stream))
+        else:
+            check(self.lib.nmfb_ingest_data(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
+                                            C.byref(vc_none), st, self.stream))
+            check(self.lib.nmfb_ingest_data(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
+                                            C.byref(vc_local), st, self.stream))
+        allreduce_min_key_(self.stats[0:1], self.group)      # each rank saw its rows and its columns only
+        return self.finish_ingest()
+
     def _ingest_pass(self, v: np.ndarray, nv: int, fixed: bool = False):
+        if self.world > 1 and os.environ.get("NMFB_FULL_WALK_UPLOAD", "0") != "1":
+            return self._ingest_pass_sharded(v, nv, fixed)
         self.begin_ingest(nv, fixed)
         if fixed:
             for r0, chunk in self._host_chunks(v):

@@ -67,3 +67,29 @@ def allreduce_sum_(t: torch.Tensor, group=None) -> None:
 
 def allreduce_max_(t: torch.Tensor, group=None) -> None:
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+
+
+def allreduce_min_key_(key: torch.Tensor, group=None) -> None:
+    """MIN over ranks of order-preserving uint32 keys held in an int32 tensor (the min(V) slot of the ingest
+    statistics): flipping the top bit maps unsigned order onto the signed order all_reduce compares in."""
+    flipped = key ^ torch.tensor(-2 ** 31, dtype=torch.int32, device=key.device)
+    dist.all_reduce(flipped, op=dist.ReduceOp.MIN, group=group)
+    key.copy_(flipped ^ torch.tensor(-2 ** 31, dtype=torch.int32, device=key.device))
+
+
+def exchange_blocks(send: List[torch.Tensor], recv: List[torch.Tensor], group=None) -> None:
+    """All-to-all of unequal blocks: send[p] goes to rank p, recv[p] arrives from rank p (contiguous tensors;
+    the rank's own block is copied).  Point-to-point operations, so that it runs on NCCL (NVLink) and gloo."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    recv[rank].copy_(send[rank])
+    ops = []
+    for p in range(world):
+        if p == rank:
+            continue
+        peer = dist.get_global_rank(group, p) if group is not None else p
+        ops.append(dist.P2POp(dist.irecv, recv[p], peer, group))
+        ops.append(dist.P2POp(dist.isend, send[p], peer, group))
+    if ops:
+        for work in dist.batch_isend_irecv(ops):
+            work.wait()

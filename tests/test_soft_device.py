@@ -210,3 +210,62 @@ def test_errors_surface_like_the_reference(soft):
         admm(v, 4, distance_type="xx", nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
     with pytest.raises(NotImplementedError):
         admm(v, 4, distance_type="kl", comm=True, nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
+
+
+def _upload_worker(rank, world, port, ret):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        m, n, k = 700, 530, 4                                # ragged last windows in both directions
+        rng = np.random.default_rng(3)
+        cases = {
+            "bf16_exact": (orc.planted(m, n, k, 0), False),                       # one lossless plane
+            "two_planes": (rng.random((m, n)), False),                            # fp64 input, hi + lo
+            "negative": (rng.random((m, n)).astype(np.float32) - 0.5, False),     # min(V) < 0 must reach every rank
+            "fixed": (orc.planted(m, n, k, 1), True),                             # exact in two fixed-point planes
+            "fixed_fallback": (rng.random((m, n)), True),                         # not exact: floating planes again
+        }
+        out = {}
+        for name, (v, fixed) in cases.items():
+            got = []
+            for full_walk in ("1", "0"):
+                os.environ["NMFB_FULL_WALK_UPLOAD"] = full_walk
+                eng = softdev.SoftEngine.for_comm(m, n, k, True)
+                eng.ROW_CHUNK_BYTES = 64 * n * 8                                  # several chunks per shard
+                vmin = eng.upload_data(np.array(v), fixed=fixed)
+                got.append((vmin, eng.nv, eng.fixed, eng.v_rows.clone(), eng.v_cols.clone()))
+            a, b = got
+            out[name] = (a[0] == b[0], a[1] == b[1], a[2] == b[2], bool(torch.equal(a[3], b[3])),
+                         bool(torch.equal(a[4], b[4])), float(a[0]), int(a[1]), bool(a[2]),
+                         bool(b[3].any() and b[4].any()))
+        os.environ.pop("NMFB_FULL_WALK_UPLOAD", None)
+        ret[rank] = out
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_upload_reads_only_the_ranks_rows_and_builds_identical_planes():
+    """Engine._ingest_pass_sharded (each rank uploads its rows, the column copy comes from an all-to-all of the
+    row shards) against the full walk of V that ran on the GPUs in round 1: same planes bit for bit, same
+    min(V), same plane count and fixed / floating decision, on 3 ranks with ragged windows."""
+    import torch.multiprocessing as mp
+    softdev.emu_lib()
+    world = 3
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 29800 + (os.getpid() % 90)
+    procs = [ctx.Process(target=_upload_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(600)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    for rank in range(world):
+        for name, res in ret[rank].items():
+            assert all(res[:5]) and res[8], (rank, name, res)
+    r0 = ret[0]
+    assert r0["bf16_exact"][6] == 1 and r0["two_planes"][6] == 2 and r0["negative"][5] < 0
+    assert r0["fixed"][7] is True and r0["fixed_fallback"][7] is False
+    assert all(ret[r][nm][5] == r0[nm][5] for r in range(world) for nm in r0)     # every rank agrees on min(V)
