@@ -269,3 +269,74 @@ def test_sharded_upload_reads_only_the_ranks_rows_and_builds_identical_planes():
     assert r0["bf16_exact"][6] == 1 and r0["two_planes"][6] == 2 and r0["negative"][5] < 0
     assert r0["fixed"][7] is True and r0["fixed_fallback"][7] is False
     assert all(ret[r][nm][5] == r0[nm][5] for r in range(world) for nm in r0)     # every rank agrees on min(V)
+
+
+def test_bench_time_to_tol_leg_runs_the_public_api_with_the_stop_test_on(soft, monkeypatch):
+    """bench.run_time_to_tol (the north-star's end-to-end time-to-tol): reference stop rule with tol2 = 1e-5 x the
+    initial objective, seeded default init, bounded iteration count; all four bench methods."""
+    import torch
+    import bench
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setattr(bench, "TTT_MAX_ITER", 40)
+    m, n, k = 96, 80, 4
+    v = orc.planted(m, n, k, 0)
+    for method, dist_, extra in (("mur", "eu", {}), ("mur", "kl", {}),
+                                 ("admm", "eu", dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))),
+                                 ("ao_admm", "eu", dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5))):
+        np.random.seed(1)
+        w0, h0 = orc.reference_init(m, n, k)
+        obj0 = orc.objective(v.astype(np.float64), w0 @ h0, dist_)
+        t = bench.run_time_to_tol(v, method, dist_, k, extra, obj0)
+        assert t["seconds"] > 0 and 11 <= t["iterations"] <= 40 and t["tol2"] == pytest.approx(1e-5 * obj0)
+        assert t["converged"] == (t["iterations"] < 40)
+        assert t["objective_last"] < t["objective_first"] == pytest.approx(obj0, rel=1e-4)
+        fn = {"mur": orc.mur_run, "admm": orc.admm_run, "ao_admm": orc.ao_admm_run}[method]
+        kw = dict(extra, distance_type=dist_) if method == "mur" else dict(extra)
+        want = fn(v.astype(np.float64), k, w0, h0, min_iter=10, max_iter=40, tol1=0.0, tol2=1e-5 * obj0, **kw)
+        assert t["iterations"] == want.i + 1                 # stops where the reference stops
+
+
+def _bench_e2e_worker(rank, world, port, ret):
+    import torch
+    import torch.distributed as dist
+    import bench
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.cuda.synchronize = lambda *a, **k: None
+        torch.cuda.empty_cache = lambda *a, **k: None
+        m, n, k, steps = 600, 520, 6, 5
+        out = {}
+        with softdev.soft_device():
+            for method, dist_, extra in (("mur", "eu", {}),
+                                         ("admm", "eu", dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n")))):
+                eng = softdev.SoftEngine.for_comm(m, n, k, True)
+                bench.synth_fill_engine(eng, seed=0, fixed=(method == "admm"))
+                bench.synth_init(eng, seed=1)
+                e = bench.run_e2e_sharded(eng, method, dist_, m, n, k, extra, steps, world, rank)
+                out[method] = e
+        ret[rank] = out
+    finally:
+        dist.destroy_process_group()
+
+
+def test_bench_sharded_end_to_end_leg_on_two_ranks():
+    """bench.run_e2e_sharded (the N > 1 `e2e` figure): host V regenerated from the per-chunk counters, the public
+    call with comm=True on every rank, agreement protocol, byte accounting."""
+    import torch.multiprocessing as mp
+    softdev.emu_lib()
+    world = 2
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 29700 + (os.getpid() % 90)
+    procs = [ctx.Process(target=_bench_e2e_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(600)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    for method in ("mur", "admm"):
+        a, b = ret[0][method], ret[1][method]
+        assert "error" not in a and a["value"] > 0 and a["value"] == b["value"]          # max over ranks, agreed
+        assert a["h2d_bytes_per_step"] == (600 * 520 * 4 + 2 * (600 * 6 + 6 * 520) * 4) // 5
+        assert a["unit"] == "it/s" and a["host_v_pinned"] is False
