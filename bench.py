@@ -43,6 +43,11 @@ WORKLOADS = {
     "ao_admm_65536x16384_k128": ("ao_admm", "eu", 65536, 16384, 128,
                                  dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)),
     "mur_eu_262144x131072_k256": ("mur", "eu", 262144, 131072, 256, {}),
+    # Kullback-Leibler branch of admm / ao_admm (single GPU, first version; no roofline claim yet)
+    "admm_kl_65536x16384_k128": ("admm", "kl", 65536, 16384, 128,
+                                 dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))),
+    "ao_admm_kl_65536x16384_k128": ("ao_admm", "kl", 65536, 16384, 128,
+                                    dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)),
     "mur_eu_4096x4096_k64": ("mur", "eu", 4096, 4096, 64, {}),          # quick functional check
 }
 DEFAULT_WORKLOAD = "mur_eu_65536x65536_k128"
@@ -203,6 +208,34 @@ def cpu_step_fn(method, dist, ms, ns, k, extra, seed=0):
             st["wh"] = w @ h
             st["w"], st["h"] = w, h
             return orc.objective(v, st["wh"], dist)
+    elif method == "admm" and dist == "kl":      # loop body of admm.py:303-324
+        rho, reg_w, reg_h = extra["rho"], extra["reg_w"], extra["reg_h"]
+        st.update(w_aux=w0.copy(), h_aux=h0.copy(), dw=np.zeros_like(w0), dh=np.zeros_like(h0),
+                  va=np.zeros_like(v), dv=np.zeros_like(v))
+
+        def step():
+            h_aux = orc.admm_aux_kl(st["h"], st["dh"], st["w_aux"], st["va"], st["dv"], rho)
+            w_aux = orc.admm_aux_kl(st["w"].T, st["dw"].T, h_aux.T, st["va"].T, st["dv"].T, rho).T
+            h = orc.prox(reg_h[1], h_aux, st["dh"], rho, reg_h[0])
+            w = orc.prox(reg_w[1], w_aux.T, st["dw"].T, rho, reg_w[0]).T
+            wh_aux = w_aux @ h_aux
+            va = orc.kl_v_aux(v, wh_aux - st["dv"])
+            st["dv"] = st["dv"] + va - wh_aux
+            st["dh"] = st["dh"] + h - h_aux
+            st["dw"] = st["dw"] + w - w_aux
+            st.update(w=w, h=h, w_aux=w_aux, h_aux=h_aux, va=va)
+            return orc.objective(v, w @ h, "kl")
+    elif method == "ao_admm" and dist == "kl":   # loop body of ao_admm.py:272-291
+        reg_w, reg_h, inner = extra["reg_w"], extra["reg_h"], extra["admm_iter"]
+        st.update(dw=np.zeros_like(w0), dh=np.zeros_like(h0), va=np.zeros_like(v), dv=np.zeros_like(v))
+
+        def step():
+            h, dh, va, dv, _ = orc.ao_factor_update_kl(v, st["va"], st["dv"], st["w"], st["h"], st["dh"], k,
+                                                       reg_h[1], reg_h[0], inner)
+            wt, dwt, vat, dvt, _ = orc.ao_factor_update_kl(v.T, va.T, dv.T, h.T, st["w"].T, st["dw"].T, k,
+                                                           reg_w[1], reg_w[0], inner)
+            st.update(w=wt.T, h=h, dw=dwt.T, dh=dh, va=vat.T, dv=dvt.T)
+            return orc.objective(v, st["w"] @ h, "kl")
     elif method == "admm":                       # loop body of admm.py:294-301,320-324
         rho, reg_w, reg_h = extra["rho"], extra["reg_w"], extra["reg_h"]
         st.update(w_aux=w0.copy(), h_aux=h0.copy(), dw=np.zeros_like(w0), dh=np.zeros_like(h0))
@@ -336,7 +369,7 @@ def run_b200(args):
     peaks = load_peaks()
 
     eng = Engine(m, n, k, device=dev, rank=rank, world=world)
-    synth_fill_engine(eng, seed=0, fixed=(method in ('admm', 'ao_admm')))
+    synth_fill_engine(eng, seed=0, fixed=(method in ('admm', 'ao_admm') and dtype_ == 'eu'))
     synth_init(eng, seed=1)
     stepper = solvers.make_stepper(eng, method, dtype_, **extra)
     stepper.prepare()
@@ -450,10 +483,8 @@ def run_time_to_tol(v_np, method, dtype_, k, extra, obj0):
     from nmf_b200 import NMF
 
     tol2 = 1e-5 * float(obj0)
-    kw = dict(extra)
-    if method == "mur":
-        kw["distance_type"] = dtype_
-    else:
+    kw = dict(extra, distance_type=dtype_)
+    if method != "mur":
         kw["nndsvd_init"] = (False, "zero")
     np.random.seed(1)
     torch.cuda.synchronize()
@@ -495,10 +526,8 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0=None):
     eng.release()
     torch.cuda.empty_cache()
     v_np = v_host.numpy()
-    kw = dict(extra)
-    if method == "mur":
-        kw["distance_type"] = dtype_
-    else:
+    kw = dict(extra, distance_type=dtype_)
+    if method != "mur":
         kw["nndsvd_init"] = (False, "zero")
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
@@ -578,10 +607,8 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
     del _wt, _ht, blk
     torch.cuda.empty_cache()
     v_np = v_host.numpy()
-    kw = dict(extra)
-    if method == "mur":
-        kw["distance_type"] = dtype_
-    else:
+    kw = dict(extra, distance_type=dtype_)
+    if method != "mur":
         kw["nndsvd_init"] = (False, "zero")
     torch.cuda.synchronize(dev)
     dist.barrier()

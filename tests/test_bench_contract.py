@@ -76,3 +76,27 @@ def test_roofline_reports_are_per_rank_and_pick_the_binding_roof():
     st = solvers.AdmmStepper(eng, rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))
     r = st.roofline({"gemm_w": 1.0, "gemm_h": 1.0}, peaks)
     assert r["executed_mma_per_product"] == 5 and (r["kernel"], "admm_65536x16384_k128") in bench.NCU_TRAFFIC
+
+
+def test_cpu_arm_step_bodies_are_the_oracle_loops():
+    """bench.cpu_step_fn (the `--impl reference` / cpu_baseline arm) advances exactly like the oracle drivers, for
+    every workload family incl. the Kullback-Leibler branch of admm / ao_admm."""
+    import numpy as np
+    from oracle import nmf_oracle as orc
+    m, n, k = 60, 50, 4
+    v = orc.planted(m, n, k, 0).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 1)
+    admm_kw = dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))
+    ao_kw = dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)
+    for method, dist, extra, ref in (
+        ("mur", "eu", {}, lambda: orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=4)),
+        ("mur", "kl", {}, lambda: orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=4)),
+        ("admm", "eu", admm_kw, lambda: orc.admm_run(v, k, w0, h0, min_iter=10**9, max_iter=4, **admm_kw)),
+        ("admm", "kl", admm_kw, lambda: orc.admm_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=4, **admm_kw)),
+        ("ao_admm", "eu", ao_kw, lambda: orc.ao_admm_run(v, k, w0, h0, min_iter=10**9, max_iter=4, **ao_kw)),
+        ("ao_admm", "kl", ao_kw, lambda: orc.ao_admm_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=4, **ao_kw)),
+    ):
+        step, cores = bench.cpu_step_fn(method, dist, m, n, k, extra)
+        got = [step() for _ in range(4)]
+        np.testing.assert_allclose(got, ref().obj_history[1:], rtol=1e-10)
+        assert cores >= 1
