@@ -3,7 +3,7 @@ arguments, defaults, console output and `Results` / `Experiment` layout.
 
 Euclidean branch: one C-ABI call per outer iteration (`nmfb_admm_step`): Gram -> fp64 Cholesky inverse ->
 split-bf16 numerator GEMM -> fused solve / prox / dual kernel, for H then W, then the residual objective.
-Kullback-Leibler branch (admm.py:303-315, one GPU): the same half-steps on the data term v_aux + dual_v,
+Kullback-Leibler branch (admm.py:303-315): the same half-steps on the data term v_aux + dual_v,
 followed by the element-wise v_aux / dual_v kernel (`Engine.admm_kl_step`).
 """
 from __future__ import annotations
@@ -39,8 +39,6 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
                             prox_h=reg_h[1])
     if distance_type not in ('eu', 'kl'):
         raise TypeError('Unknown loss type.')
-    if distance_type == 'kl' and comm is not None:
-        raise NotImplementedError("admm with distance_type='kl' (admm.py:303-315) runs on one GPU in this build")
     prox_code(reg_w, k), prox_code(reg_h, k)                 # TypeError('Unknown prox_type.') up front
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)

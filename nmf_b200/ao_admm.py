@@ -4,7 +4,7 @@ keyword arguments, defaults, console output and `Results` / `Experiment` layout.
 Euclidean branch: one C-ABI call per outer iteration (`nmfb_aoadmm_step`).  The inner ADMM loop of each
 factor (ao_admm.py:58-66) runs entirely on the device, early break included; the host only learns how many
 inner iterations ran (for the reference's 'ADMM break after N iterations.' line).
-Kullback-Leibler branch (ao_admm.py:71-101,272-285, one GPU): `Engine.aoadmm_kl_side` enqueues the inner
+Kullback-Leibler branch (ao_admm.py:71-101,272-285): `Engine.aoadmm_kl_side` enqueues the inner
 iterations -- each with a fresh right-hand side from v_aux + dual_v and the element-wise data step --, the
 early break is still taken on the device (every kernel of a broken loop returns at its first instruction).
 """
@@ -36,8 +36,6 @@ def ao_admm(v, k, *, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), min_
                             lambda_h=reg_h[0], prox_h=reg_h[1])
     if distance_type not in ('eu', 'kl'):
         raise TypeError('Unknown loss type.')
-    if distance_type == 'kl' and comm is not None:
-        raise NotImplementedError("ao_admm with distance_type='kl' (ao_admm.py:272-285) runs on one GPU in this build")
     prox_code(reg_w, k), prox_code(reg_h, k)
     precision = tol_precision(tol1, tol2)
     v = np.asarray(v)

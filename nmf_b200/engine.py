@@ -292,50 +292,59 @@ class Engine:
         for a in range(r0, r1, rows_per):
             b = min(r1, a + rows_per)
             shard[a - r0:b - r0].copy_(torch.from_numpy(v[a:b]).to(self.device))      # casts fp64 -> fp32 on the device
-        mb = shard_bounds(self.m, self.world)[2]
-        nb = shard_bounds(self.n, self.world)[2]
-        rows_of = [(lo, lo + live_rows(self.m, lo, hi)) for lo, hi in mb]
-        cols_of = [(lo, lo + live_rows(self.n, lo, hi)) for lo, hi in nb]
-        send = [shard[:, a:b].contiguous() for a, b in cols_of]                          # my rows of rank q's columns
         panel = torch.empty((self.m, c1 - c0), dtype=torch.float32, device=self.device)
-        recv = [panel[a:b] for a, b in rows_of]                                          # row slices are contiguous
-        exchange_blocks(send, recv, self.group)
-        del send
+        self._panel_from_shards(shard, panel)
         out = (shard, panel)
         if getattr(self, "_keep_chunks", False):
             self._chunk_cache = (v, out)
         return out
 
-    def _ingest_pass_sharded(self, v: np.ndarray, nv: int, fixed: bool):
-        shard, panel = self._shard_and_panel(v)
-        self.begin_ingest(nv, fixed)
+    def _panel_from_shards(self, shard: torch.Tensor, panel: torch.Tensor):
+        """panel (m x my columns) <- every rank's rows of those columns: all-to-all of the row shards."""
+        mb = shard_bounds(self.m, self.world)[2]
+        nb = shard_bounds(self.n, self.world)[2]
+        rows_of = [(lo, lo + live_rows(self.m, lo, hi)) for lo, hi in mb]
+        cols_of = [(lo, lo + live_rows(self.n, lo, hi)) for lo, hi in nb]
+        send = [shard[:, a:b].contiguous() for a, b in cols_of]                          # my rows of rank q's columns
+        recv = [panel[a:b] for a, b in rows_of]                                          # row slices are contiguous
+        exchange_blocks(send, recv, self.group)
+
+    def _ingest_shard_and_panel(self, shard, panel, vr, vc, stats, rowmax, colmax, fixed: bool):
+        """Row pass: my rows, all columns -> the planes of `vr` only (empty column window).  Column pass: all rows
+        of my columns, presented as a matrix with that many columns -> the planes of `vc` only (empty row window).
+        fixed: |max| of my rows from the shard, of my columns from the panel; the row maxima are all-reduced
+        because the column pass judges exactness with every row's unit."""
         (r0, r1), (c0, c1) = self.row_range, self.col_range
-        vr, vc = self._data_structs()
-        # row pass: my rows, all columns -> v_rows only (empty column window); column pass: all rows of my columns,
-        # presented as a matrix with c1 - c0 columns -> v_cols only (empty row window)
         vc_none = Data(vc.planes, 0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
         vr_none = Data(vr.planes, 0, c1 - c0, vr.rows_p, vr.ld, vr.nv, 1, vr.fixed, 0)
         vc_local = Data(vc.planes, c1 - c0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
-        st = self.stats.data_ptr()
+        st = stats.data_ptr()
         if fixed:
             scratch = torch.zeros(max(self.Mp, self.Np), dtype=torch.int32, device=self.device)
             check(self.lib.nmfb_data_absmax(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, self.n,
-                                            self.rowmax.data_ptr(), scratch.data_ptr(), self.stream))
+                                            rowmax.data_ptr(), scratch.data_ptr(), self.stream))
             scratch.zero_()
             check(self.lib.nmfb_data_absmax(panel.data_ptr(), 0, panel.stride(0), 0, self.m, c1 - c0,
-                                            scratch.data_ptr(), self.colmax.data_ptr() + 4 * c0, self.stream))
-            allreduce_max_(self.rowmax, self.group)          # the column pass judges exactness with every row's unit
+                                            scratch.data_ptr(), colmax.data_ptr() + 4 * c0, self.stream))
+            allreduce_max_(rowmax, self.group)
             check(self.lib.nmfb_ingest_data_fixed(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
-                                                  C.byref(vc_none), st, self.rowmax.data_ptr(),
-                                                  self.colmax.data_ptr(), self.stream))
+                                                  C.byref(vc_none), st, rowmax.data_ptr(), colmax.data_ptr(),
+                                                  self.stream))
             check(self.lib.nmfb_ingest_data_fixed(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
-                                                  C.byref(vc_local), st, self.rowmax.data_ptr(),
-                                                  self.colmax.data_ptr() + 4 * c0, self.stream))
+                                                  C.byref(vc_local), st, rowmax.data_ptr(),
+                                                  colmax.data_ptr() + 4 * c0, self.stream))
         else:
             check(self.lib.nmfb_ingest_data(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
                                             C.byref(vc_none), st, self.stream))
             check(self.lib.nmfb_ingest_data(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
                                             C.byref(vc_local), st, self.stream))
+
+    def _ingest_pass_sharded(self, v: np.ndarray, nv: int, fixed: bool):
+        shard, panel = self._shard_and_panel(v)
+        self.begin_ingest(nv, fixed)
+        vr, vc = self._data_structs()
+        self._ingest_shard_and_panel(shard, panel, vr, vc, self.stats, getattr(self, "rowmax", None),
+                                     getattr(self, "colmax", None), fixed)
         allreduce_min_key_(self.stats[0:1], self.group)      # each rank saw its rows and its columns only
         return self.finish_ingest()
 
@@ -483,67 +492,89 @@ class Engine:
     def alloc_admm_kl(self, ao: bool = False):
         """admm.py:33,303-315 / ao_admm.py:28-30,71-101: dual_v (zero) and, instead of v_aux itself, the data
         term D = v_aux + dual_v of the right-hand sides (zero at the start), kept as fixed-point bf16 planes
-        in the layouts of V and V^T so that the contractions of the Euclidean branch run on it unchanged."""
-        if self.world != 1:
-            raise NotImplementedError("the Kullback-Leibler branch of admm / ao_admm is single-GPU in this build")
+        in the layouts of V and V^T so that the contractions of the Euclidean branch run on it unchanged.
+        Sharded runs hold the rank's rows of dual_v / D (the v step is element-wise) and re-build the column
+        copy of D by the all-to-all of the sharded upload."""
         dev = self.device
         self.alloc_admm(with_aux=True, exact=True)
         if ao:                                   # AO-ADMM contracts against W and H themselves (ao_admm.py:83)
             self._fixed_planes(self.w)
             self._fixed_planes(self.h)
-        self.kl_dual_v = torch.zeros((self.m, self.n), dtype=torch.float32, device=dev)
-        self.kl_prod = torch.empty((self.m, self.n), dtype=torch.float32, device=dev)
-        self.kl_d = torch.zeros((self.m, self.n), dtype=torch.float32, device=dev)
+        rows = self.row_range[1] - self.row_range[0]
+        self.kl_dual_v = torch.zeros((rows, self.n), dtype=torch.float32, device=dev)
+        self.kl_prod = torch.empty((rows, self.n), dtype=torch.float32, device=dev)
+        self.kl_d = torch.zeros((rows, self.n), dtype=torch.float32, device=dev)
+        self.kl_panel = (torch.empty((self.m, self.col_range[1] - self.col_range[0]), dtype=torch.float32, device=dev)
+                         if self.world > 1 else None)
         self.d_rows = torch.zeros((2, self.Np // 64, self.per_m, 64), dtype=torch.bfloat16, device=dev)
         self.d_cols = torch.zeros((2, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=dev)
         self.d_rowmax = torch.zeros(self.Mp, dtype=torch.int32, device=dev)
         self.d_colmax = torch.zeros(self.Np, dtype=torch.int32, device=dev)
         self.d_stats = torch.zeros(4, dtype=torch.int32, device=dev)
         vr, vc = self._data_structs()
-        self._d_structs = (Data(self.d_rows.data_ptr(), vr.rows, vr.cols, vr.rows_p, vr.ld, 2, 1, 1, 0),
-                           Data(self.d_cols.data_ptr(), vc.rows, vc.cols, vc.rows_p, vc.ld, 2, 1, 1, 0))
+        self._d_structs = (Data(self.d_rows.data_ptr(), vr.rows, vr.cols, vr.rows_p, vr.ld, 2, 1, 1, vr.origin),
+                           Data(self.d_cols.data_ptr(), vc.rows, vc.cols, vc.rows_p, vc.ld, 2, 1, 1, vc.origin))
         self._problem_d = Problem.from_buffer_copy(self.problem())
         self._problem_d.v_rows, self._problem_d.v_cols = self._d_structs
         self._problem_d.phase_events, self._problem_d.n_phase_events = None, 0
 
     def kl_data_step(self, left: "FactorBuffers", right: "FactorBuffers", done_flag: Optional[int] = None):
-        """admm.py:309-313 / ao_admm.py:88-94: P = left^T-master @ right-master, i.e. (m x k) @ (k x n) -- a
-        plain fp32 library GEMM --, then one element-wise kernel for v_aux / dual_v that writes
-        D = v_aux + dual_v, then D -> fixed-point planes of both layouts.  done_flag: device address of the
-        AO-ADMM break flag; once it is set D, dual_v and therefore the planes stay what they are."""
-        k, m, n = self.k, self.m, self.n
-        torch.matmul(left.master[:k, :m].t(), right.master[:k, :n], out=self.kl_prod)
+        """admm.py:309-313 / ao_admm.py:88-94 on this rank's rows: P = left^T-master[rows] @ right-master, i.e.
+        (rows x k) @ (k x n) -- a plain fp32 library GEMM --, then one element-wise kernel for v_aux / dual_v
+        that writes D = v_aux + dual_v, then D -> fixed-point planes of both layouts (sharded: the column copy
+        through the all-to-all).  done_flag: device address of the AO-ADMM break flag; once it is set D, dual_v
+        and therefore the planes stay what they are."""
+        k, n = self.k, self.n
+        r0, r1 = self.row_range
+        torch.matmul(left.master[:k, r0:r1].t(), right.master[:k, :n], out=self.kl_prod)
         vr, _vc = self._data_structs()
         d = self.kl_d
         check(self.lib.nmfb_kl_vaux(C.byref(vr), self.kl_prod.data_ptr(), d.data_ptr(), d.stride(0),
                                     self.kl_dual_v.data_ptr(), done_flag, self.stream))
         self.d_rowmax.zero_()
         self.d_colmax.zero_()
-        check(self.lib.nmfb_data_absmax(d.data_ptr(), 0, d.stride(0), 0, m, n, self.d_rowmax.data_ptr(),
-                                        self.d_colmax.data_ptr(), self.stream))
         dr, dc = self._d_structs
-        check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, d.stride(0), 0, m, C.byref(dr), C.byref(dc),
+        if self.world > 1:
+            self._panel_from_shards(d, self.kl_panel)
+            self._ingest_shard_and_panel(d, self.kl_panel, dr, dc, self.d_stats, self.d_rowmax, self.d_colmax, True)
+            return
+        check(self.lib.nmfb_data_absmax(d.data_ptr(), 0, d.stride(0), 0, self.m, n, self.d_rowmax.data_ptr(),
+                                        self.d_colmax.data_ptr(), self.stream))
+        check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, d.stride(0), 0, self.m, C.byref(dr), C.byref(dc),
                                               self.d_stats.data_ptr(), self.d_rowmax.data_ptr(),
                                               self.d_colmax.data_ptr(), self.stream))
 
+    def _publish_aux(self, fac: "FactorBuffers"):
+        """Exact-mode operand of the next contraction: all-gather the windows (sharded), fixed-point cplanes."""
+        if self.world == 1:
+            self._fixed_planes(fac)
+        else:
+            self.gather_factor(fac, refresh=False, fixed=True)
+
     def admm_kl_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
-        """One outer iteration of admm.py:303-324 with distance_type='kl'."""
+        """One outer iteration of admm.py:303-324 with distance_type='kl' (sharded: the window half-steps and
+        exchanges of the Euclidean branch, solvers.AdmmStepper, on the data term)."""
         pd, s = self._problem_d, self._admm
         check(self.lib.nmfb_admm_half_step(C.byref(pd), C.byref(s), 0, float(rho), float(lambda_h), int(prox_h),
                                            self.stream))                          # admm.py:304,308,320
-        self._fixed_planes(self.h_aux)
+        self._publish_aux(self.h_aux)
+        self.gather_factor(self.h)                                                # operand of the objective
         check(self.lib.nmfb_admm_half_step(C.byref(pd), C.byref(s), 1, float(rho), float(lambda_w), int(prox_w),
                                            self.stream))                          # admm.py:305-306,309,321
-        self._fixed_planes(self.w_aux)
+        self._publish_aux(self.w_aux)
+        self.gather_factor(self.w, refresh=False)                                 # keeps the replicated W current
         self.kl_data_step(self.w_aux, self.h_aux)                                 # admm.py:310-313
         self.objective_kl(slot=ring_slot * 8)                                     # admm.py:324
+        self.reduce_scalar(ring_slot * 8)
         self.admm_publish(ring_slot)
 
     def aoadmm_kl_side(self, side: int, admm_iter: int, lam, prox):
         """ao_admm.py:71-101 (admm_kl_update) for H (side 0: a = W) or W (side 1: a = H^T, everything
         transposed, ao_admm.py:276-284): Gram, rho = tr/k and the Cholesky inverse once; per inner iteration
         the right-hand side a^T (v_aux + dual_v) is contracted anew, then solve / prox / dual / norms, the data
-        step with P = a.aux and the break test (whose flag freezes the remaining iterations on the device)."""
+        step with P = a.aux and the break test (whose flag freezes the remaining iterations on the device).
+        Sharded: the rank's window of the factor; the norm partials (and, for the H side, the auxiliary that
+        P = W.h_aux needs in full) are all-gathered per inner iteration, like Engine.aoadmm_side."""
         pd, s, KP = self._problem_d, self._admm, self.KP
         fac, other = (self.h, self.w) if side == 0 else (self.w, self.h)
         data = self._d_structs[1] if side == 0 else self._d_structs[0]
@@ -551,25 +582,37 @@ class Engine:
         if int(prox) == 2 and float(lam) != 0.0:
             check(self.lib.nmfb_admm_prepare_l2n(C.byref(pd), C.byref(s), side, float(lam), self.stream))
         flag = self.admm_flags.data_ptr() + 4                                     # flags[1]: inner loop has broken
+        nblk = fac.win_p // 64
         for it in range(admm_iter):
             if it > 0:                                                            # ao_admm.py:83: fresh right-hand side
                 slots = check(self.lib.nmfb_panel_gemm_exact(C.byref(data), other.cplanes.data_ptr(), other.Lp, KP,
-                                                             self.partial.data_ptr(), self.partial.numel() * 4,
-                                                             fac.Lp, self.num_sms, self.stream))
+                                                             self.partial.data_ptr() + 4 * fac.win0,
+                                                             self.partial.numel() * 4, fac.Lp, self.num_sms,
+                                                             self.stream))
             check(self.lib.nmfb_aoadmm_inner(C.byref(pd), C.byref(s), side, 1, slots, float(lam), int(prox),
                                              self.stream))                        # ao_admm.py:83-85,92
+            if self.world > 1:
+                full = self.norm_partial[: 4 * (fac.Lp // 64)]
+                mine = full[4 * nblk * self.rank: 4 * nblk * (self.rank + 1)].clone()
+                allgather_flat(full, mine, self.group)
+                if side == 0:
+                    allgather_windows(self.h_aux.master, self.h_aux.win_p, self.group)
             if side == 0:
                 self.kl_data_step(self.w, self.h_aux, flag)                       # ao_admm.py:88-90,94
             else:
                 self.kl_data_step(self.w_aux, self.h, flag)
             check(self.lib.nmfb_aoadmm_inner_flag(C.byref(pd), C.byref(s), side, self.stream))   # ao_admm.py:96
-        self._fixed_planes(fac)
+        if self.world == 1:
+            self._fixed_planes(fac)
+        else:
+            self.gather_factor(fac, refresh=True, fixed=True)
 
     def aoadmm_kl_step(self, admm_iter, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
         """One outer iteration of ao_admm.py:272-291 with distance_type='kl'."""
         self.aoadmm_kl_side(0, admm_iter, lambda_h, prox_h)
         self.aoadmm_kl_side(1, admm_iter, lambda_w, prox_w)
         self.objective_kl(slot=ring_slot * 8)
+        self.reduce_scalar(ring_slot * 8)
         self.admm_publish(ring_slot)
 
     def admm_step(self, rho, lambda_w, prox_w, lambda_h, prox_h, ring_slot: int):
@@ -605,6 +648,6 @@ class Engine:
         self.w = self.h = None
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
         for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch',
-                     'kl_dual_v', 'kl_prod', 'kl_d', 'd_rows', 'd_cols'):
+                     'kl_dual_v', 'kl_prod', 'kl_d', 'kl_panel', 'd_rows', 'd_cols'):
             setattr(self, name, None)
         self._problem = None

@@ -193,7 +193,7 @@ class AdmmStepper(_GemmRoofline):
 
 class AdmmKlStepper:
     """admm.py:292-334 with distance_type='kl' (:303-315): the half-steps of the Euclidean branch on the data
-    term v_aux + dual_v, then the element-wise v_aux / dual_v step.  Single GPU."""
+    term v_aux + dual_v, then the element-wise v_aux / dual_v step on the rank's rows of V."""
     phases = []
 
     def __init__(self, eng, rho=1, reg_w=(0, "nn"), reg_h=(0, "l2n")):
@@ -204,6 +204,7 @@ class AdmmKlStepper:
     def prepare(self):
         self.eng.alloc_admm_kl()
         self.eng.objective_kl(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot):
         self.eng.admm_kl_step(self.rho, self.lw, self.pw, self.lh, self.ph, ring_slot)
@@ -254,8 +255,8 @@ class AoAdmmStepper(_GemmRoofline):
 
 
 class AoAdmmKlStepper(AdmmKlStepper):
-    """ao_admm.py:259-301 with distance_type='kl' (:272-285, admm_kl_update :71-101).  Single GPU; the inner
-    loop is enqueued from the host, its early break is taken on the device (flag-guarded kernels)."""
+    """ao_admm.py:259-301 with distance_type='kl' (:272-285, admm_kl_update :71-101).  The inner loop is
+    enqueued from the host, its early break is taken on the device (flag-guarded kernels)."""
 
     def __init__(self, eng, reg_w=(0, "nn"), reg_h=(0, "l2n"), admm_iter=10):
         self.eng, self.admm_iter = eng, int(admm_iter)
@@ -265,6 +266,7 @@ class AoAdmmKlStepper(AdmmKlStepper):
     def prepare(self):
         self.eng.alloc_admm_kl(ao=True)
         self.eng.objective_kl(slot=0)
+        self.eng.reduce_scalar(0)
 
     def step(self, ring_slot):
         self.eng.aoadmm_kl_step(self.admm_iter, self.lw, self.pw, self.lh, self.ph, ring_slot)

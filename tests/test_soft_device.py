@@ -89,6 +89,14 @@ def _sharded_worker(rank, world, port, ret):
                                       nndsvd_init=(False, "zero"), **common),
                  lambda: orc.admm_run(v, k, w0, h0, rho=20, reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=10**9,
                                       max_iter=iters)),
+                ("admm_kl", lambda: admm(v, k, rho=20, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"),
+                                         nndsvd_init=(False, "zero"), **common),
+                 lambda: orc.admm_run(v, k, w0, h0, rho=20, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"),
+                                      min_iter=10**9, max_iter=iters)),
+                ("ao_admm_kl", lambda: ao_admm(v, k, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"),
+                                               admm_iter=3, nndsvd_init=(False, "zero"), **common),
+                 lambda: orc.ao_admm_run(v, k, w0, h0, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"),
+                                         admm_iter=3, min_iter=10**9, max_iter=iters)),
                 ("ao_admm", lambda: ao_admm(v, k, reg_w=(0.1, "l2n"), reg_h=(0.05, "l1n"), admm_iter=4,
                                             nndsvd_init=(False, "zero"), **common),
                  lambda: orc.ao_admm_run(v, k, w0, h0, reg_w=(0.1, "l2n"), reg_h=(0.05, "l1n"), admm_iter=4,
@@ -119,7 +127,7 @@ def test_two_ranks_through_the_public_drivers_reproduce_the_unsharded_oracle():
     for p in procs:
         p.join(600)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
-    for name in ("mur_eu", "mur_kl", "admm", "ao_admm"):
+    for name in ("mur_eu", "mur_kl", "admm", "admm_kl", "ao_admm_kl", "ao_admm"):
         for rank in range(world):
             same_i, oe, ew, eh, _ = ret[rank][name]
             assert same_i and oe < TOL and ew < TOL and eh < TOL, (name, rank, ret[rank][name])
@@ -209,7 +217,7 @@ def test_errors_surface_like_the_reference(soft):
     with pytest.raises(TypeError):
         admm(v, 4, distance_type="xx", nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
     with pytest.raises(NotImplementedError):
-        admm(v, 4, distance_type="kl", comm=True, nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
+        admm(v, 4, reg_h=(0.1, "l1inf"), nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
 
 
 def _upload_worker(rank, world, port, ret):
