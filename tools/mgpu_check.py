@@ -77,6 +77,19 @@ for (m, n, k, iters) in SHAPES:
         same = [tuple(x) for x in inner] == [tuple(x) for x in tr.inner_breaks]
         ok &= same
         print(f"   inner-iteration pattern {'OK' if same else 'BAD'}", flush=True)
+    if os.environ.get("MGPU_CHECK_PENDING", "0") == "1":
+        # paths whose first GPU run was pending at the end of round 1: l2n prox, Kullback-Leibler branch
+        kw = dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"), min_iter=10**9, max_iter=iters)
+        if k <= 128:
+            res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
+            report("admm-l2n", res, orc.admm_run(v, k, w0, h0, **kw), shape)
+        kw = dict(rho=100, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=10**9, max_iter=iters)
+        res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
+        report("admm-kl", res, orc.admm_run(v, k, w0, h0, **kw), shape)
+        kw = dict(distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), admm_iter=4, min_iter=10**9,
+                  max_iter=iters)
+        res = ao_admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
+        report("ao-admm-kl", res, orc.ao_admm_run(v, k, w0, h0, **kw), shape)
 if rank == 0:
     print("MGPU CHECK", "PASS" if ok else "FAIL", flush=True)
 dist.barrier()
