@@ -192,3 +192,31 @@ def test_reference_order_initial_factors():
     np.random.seed(7)
     w_ref = np.abs(np.random.randn(5, 3)); h_ref = np.abs(np.random.randn(3, 4))   # mur.py:108-109
     assert np.array_equal(w, w_ref) and np.array_equal(h, h_ref)
+
+
+def test_nndsvd_from_the_gram_eigenvectors_matches_the_reference_svd():
+    """init.nndsvd takes the k leading triplets from the eigenvectors of the small Gram matrix (utils.py:44 takes
+    them from the full SVD): same W0 / H0 to ~1e-13 for tall, wide, planted and uniform data and every fill
+    variant, and through the full-SVD branch used above GRAM_LIMIT."""
+    from nmf_b200 import init
+    from oracle import nmf_oracle as orc
+    rng = np.random.default_rng(0)
+    rel = lambda a, b: np.linalg.norm(a - b) / np.linalg.norm(b)   # noqa: E731
+    cases = [(orc.planted(200, 160, 6, 15).astype(np.float64), 6), (rng.random((300, 120)), 10),
+             (rng.random((90, 400)), 8), (orc.planted(120, 160, 5, 37).astype(np.float64), 5)]
+    for x, k in cases:
+        for variant in ("zero", "mean", "random"):
+            np.random.seed(3)
+            w, h = init.nndsvd(x, k, variant, _device="cpu")
+            np.random.seed(3)
+            w_ref, h_ref = orc.nndsvd(x, k, variant)
+            assert rel(w, w_ref) < 1e-11 and rel(h, h_ref) < 1e-11
+            assert w.shape == (x.shape[0], k) and h.shape == (k, x.shape[1]) and w.min() >= 0 and h.min() >= 0
+    x, k = cases[1]
+    old, init.GRAM_LIMIT = init.GRAM_LIMIT, 64              # force the full-SVD branch
+    try:
+        w, h = init.nndsvd(x, k, "zero", _device="cpu")
+    finally:
+        init.GRAM_LIMIT = old
+    w_ref, h_ref = orc.nndsvd(x, k, "zero")
+    assert rel(w, w_ref) < 1e-11 and rel(h, h_ref) < 1e-11

@@ -31,7 +31,8 @@ TOL = 1e-4
 @pytest.fixture
 def soft(monkeypatch):
     import nmf_b200.init as init_mod
-    monkeypatch.setattr(init_mod, "nndsvd", orc.nndsvd)          # the product's NNDSVD needs cuSOLVER
+    real = init_mod.nndsvd                                       # the product's NNDSVD arithmetic, torch on the CPU
+    monkeypatch.setattr(init_mod, "nndsvd", lambda x, k, variant='zero': real(x, k, variant, _device='cpu'))
     with softdev.soft_device():
         yield
 
