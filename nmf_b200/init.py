@@ -33,7 +33,11 @@ def leading_triplets(xd, rank):
         return u[:, :rank], s[:rank], vt[:rank, :]
     small_is_n = n <= m
     g = xd.T @ xd if small_is_n else xd @ xd.T
-    lam, vec = torch.linalg.eigh(g)                       # ascending
+    try:
+        lam, vec = torch.linalg.eigh(g)                   # ascending
+    except RuntimeError:                                  # eigensolver did not converge: the SVD route (same device)
+        u, s, vt = torch.linalg.svd(xd, full_matrices=False)
+        return u[:, :rank], s[:rank], vt[:rank, :]
     lam, vec = lam.flip(0)[:rank], vec.flip(1)[:, :rank]
     s = lam.clamp(min=0).sqrt()
     safe = torch.where(s > 0, s, torch.ones_like(s))
