@@ -220,3 +220,72 @@ def test_nndsvd_from_the_gram_eigenvectors_matches_the_reference_svd():
         init.GRAM_LIMIT = old
     w_ref, h_ref = orc.nndsvd(x, k, "zero")
     assert rel(w, w_ref) < 1e-11 and rel(h, h_ref) < 1e-11
+
+
+SHAPES_FOR_PLANS = [(5, 7, 2), (37, 23, 1), (23, 37, 1), (4096, 70, 8), (70, 4096, 8), (640, 520, 200), (1000, 500, 10),
+                    (32768, 32768, 64), (20000, 50000, 128), (65536, 16384, 128), (65536, 65536, 128),
+                    (262144, 131072, 256)]
+
+
+@pytest.mark.parametrize("shape", SHAPES_FOR_PLANS)
+def test_argument_and_plan_stage_accepts_the_shape(shape):
+    """Without a driver every solver entry point must get as far as encoding its first TMA descriptor: tile plans,
+    workspace sizes and padded-extent checks (all host code of the library) accept the edge-case shapes of the GPU
+    tests and BASELINE.json's configurations.  (Dummy pointers: never run where a GPU could dereference them.)"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: the calls would launch on dummy pointers")
+    from nmf_b200 import _lib
+    from nmf_b200._lib import Data, Factor, Problem
+    lib = _lib.load()
+    m, n, k = shape
+    KP = lib.nmfb_padded_components(k)
+    Mp, Np = lib.nmfb_padded_length(m), lib.nmfb_padded_length(n)
+    buf = np.zeros(1 << 16, np.uint8)
+    base = buf.ctypes.data
+    pbytes = lib.nmfb_partial_bytes(Mp, Np, k, 148)
+    assert pbytes > 0
+
+    def problem(nv, fixed):
+        vr = Data(base, m, n, Mp, Np, nv, 1, fixed, 0)
+        vc = Data(base, n, m, Np, Mp, nv, 1, fixed, 0)
+        w, h = Factor(base, base, base, m, Mp, 0, 0), Factor(base, base, base, n, Np, 0, 0)
+        return Problem(m, n, k, KP, vr, vc, w, h, base, base, base, pbytes, base,
+                       lib.nmfb_obj_partial_len(m, n, 148), 148, None, 0, base)
+
+    def reached_the_driver(rc, what):
+        msg = lib.nmfb_last_error().decode()
+        assert rc == -2 and "cuTensorMapEncodeTiled" in msg, f"{what} {shape}: rc={rc} {msg}"
+
+    for nv in (1, 2):
+        p = problem(nv, 0)
+        for side in (0, 1):
+            reached_the_driver(lib.nmfb_mur_eu_half_step(C.byref(p), side, 0.0, None), f"mur_eu side {side} nv={nv}")
+            rc = lib.nmfb_mur_kl_half_step(C.byref(p), side, 0.0, None, None)
+            if KP <= 128:
+                reached_the_driver(rc, f"mur_kl side {side} nv={nv}")
+            else:
+                assert rc == -1 and b"k <= 128" in lib.nmfb_last_error()
+        if KP == 256 and nv == 2:
+            # no room for two V planes next to four A boxes of 256 components in 227 KB: the Euclidean objective
+            # takes the CUDA-core kernel (first launch fails here: no driver), the KL objective is refused
+            assert lib.nmfb_objective_eu(C.byref(p), 0, base, None) == -2
+            assert b"objective_simt_launch" in lib.nmfb_last_error()
+            assert lib.nmfb_objective_kl(C.byref(p), base, None) == -1
+        else:
+            reached_the_driver(lib.nmfb_objective_eu(C.byref(p), 0, base, None), "objective_eu")
+            reached_the_driver(lib.nmfb_objective_kl(C.byref(p), base, None), "objective_kl")
+    # the ADMM / AO-ADMM contractions, floating (3 factor planes) and exact-hi, on both copies of V
+    w, h = Factor(base, base, base, m, Mp, 0, 0), Factor(base, base, base, n, Np, 0, 0)
+    for fixed in (0, 1):
+        p = problem(2, fixed)
+        for data, other, self_ in ((p.v_cols, w, h), (p.v_rows, h, w)):
+            if fixed:
+                reached_the_driver(lib.nmfb_gram_exact(C.byref(other), KP, base, pbytes, base, base, 148, None),
+                                   "gram_exact")
+                reached_the_driver(lib.nmfb_panel_gemm_exact(C.byref(data), base, other.Lp, KP, base, pbytes,
+                                                             self_.Lp, 148, None), "panel_gemm_exact")
+            else:
+                reached_the_driver(lib.nmfb_gram(C.byref(other), KP, 3, base, pbytes, base, base, 148, None), "gram")
+                reached_the_driver(lib.nmfb_panel_gemm(C.byref(data), base, other.Lp, KP, 3, base, pbytes, self_.Lp,
+                                                       148, 0, 0, None), "panel_gemm nb=3")
