@@ -592,7 +592,7 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
     torch.cuda.empty_cache()
     v_host, pinned = None, True
     try:
-        v_host = torch.empty((m, n), dtype=torch.float32).pin_memory()
+        v_host = torch.empty((m, n), dtype=torch.float32, pin_memory=True)
     except Exception:                                        # noqa: BLE001 -- pageable memory is slower, not wrong
         pinned = False
         try:
