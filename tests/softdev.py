@@ -47,7 +47,7 @@ def emu_lib():
         os.makedirs(d, exist_ok=True)
         so = os.path.join(d, "libemu.so")
         srcs = [os.path.join(EMU_DIR, f) for f in ("harness.cpp", "cuda_on_host.h", "extract.py")]
-        srcs += [os.path.join(ROOT, "nmf_b200", "csrc", f) for f in ("admm.cu", "admm.cuh", "elementwise.cu",
+        srcs += [os.path.join(ROOT, "nmf_b200", "csrc", f) for f in ("admm.cu", "admm.cuh", "elementwise.cu", "kl.cu",
                                                                      "ptx.cuh", "kernels.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
             tmp = so + f".{os.getpid()}"

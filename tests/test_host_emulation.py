@@ -358,3 +358,92 @@ def test_numpy_kl_vaux_equals_the_kernel(emu):
     softdev.np_kl_vaux(b[0][:, :cols], b[1][:, :cols], b[2][:, :cols], v.astype(np.float64))
     for x, y in zip(a, b):                                   # fma(t, t, 4v) vs t*t + 4v: at most an fp32 ulp apart
         np.testing.assert_allclose(x, y, rtol=3e-7, atol=1e-7)
+
+
+# ----------------------------------------------------------------------------------------------
+# The CUDA-core kernels of the MUR paths (GPU-validated in round 1), through the emulator against the
+# reference formulas: the fused multiplicative updates, the row sums, the Gram slot reduction and the
+# CUDA-core objective.
+# ----------------------------------------------------------------------------------------------
+def _factor(KP, k, L, Lp, rng):
+    x = np.zeros((KP, Lp), np.float32)
+    x[:k, :L] = np.abs(rng.standard_normal((k, L))) + 0.01
+    return x
+
+
+def _check_planes(x, cpl, rpl, KP):
+    hi = orc.round_to_bf16_grid(x)
+    lo = orc.round_to_bf16_grid(x - hi)
+    assert np.array_equal(bf16_to_f32(cpl[0, :KP]), hi) and np.array_equal(bf16_to_f32(cpl[1, :KP]), lo)
+    assert np.array_equal(bf16_to_f32(rpl[0]), hi.T) and np.array_equal(bf16_to_f32(rpl[1]), lo.T)
+
+
+@pytest.mark.parametrize("KP,k", [(64, 10), (128, 128), (256, 200)])
+def test_mur_eu_update_kernel_is_the_lee_seung_rule(emu, KP, k):
+    """mur.py:29 / :45: x <- x * num / (G x + lambda x + 1e-9), G the Gram of the other factor."""
+    L, Lp, slots, lam = 150, 256, 2, 0.05
+    rng = np.random.default_rng(KP + k)
+    x = _factor(KP, k, L, Lp, rng)
+    y = np.zeros((KP, 300), np.float32)
+    y[:k] = np.abs(rng.standard_normal((k, 300)))
+    gram = (y.astype(np.float64) @ y.T.astype(np.float64)).astype(np.float32)
+    part = np.zeros((slots, KP, Lp), np.float32)
+    part[:, :k, :L] = np.abs(rng.standard_normal((slots, k, L))) * 20
+    x0 = x.copy()
+    cpl, rpl = np.zeros((3, 256, Lp), np.uint16), np.zeros((2, Lp, KP), np.uint16)
+    emu.emu_mur_eu_update(KP, ptr(part), slots, ptr(gram), ptr(x), ptr(cpl), ptr(rpl), k, L, Lp, Lp, C.c_float(lam))
+    xd, num = x0.astype(np.float64), part.astype(np.float64).sum(0)
+    want = xd * num / (gram.astype(np.float64) @ xd + lam * xd + 1e-9)
+    np.testing.assert_allclose(x[:k, :L], want[:k, :L], rtol=2e-5)
+    assert not x[k:].any() and not x[:, L:].any()
+    _check_planes(x, cpl, rpl, KP)
+
+
+@pytest.mark.parametrize("KP,k", [(64, 7), (128, 100)])
+@pytest.mark.parametrize("lam", [0.0, 0.3])
+def test_mur_kl_update_kernel_is_the_reference_rule(emu, KP, k, lam):
+    """mur.py:25-27 / :41-43: a = x * num, b = row sums of the other factor, x <- 2a / (b + sqrt(b^2 + 4 lambda a))."""
+    L, Lp, slots = 130, 192, 3
+    rng = np.random.default_rng(KP + k)
+    x = _factor(KP, k, L, Lp, rng)
+    other = _factor(KP, k, 333, 512, rng)
+    bsum = np.zeros(KP)
+    emu.emu_factor_rowsum(ptr(other), KP, 333, 512, ptr(bsum))
+    np.testing.assert_allclose(bsum, other.astype(np.float64).sum(1), rtol=1e-13)
+    part = np.zeros((slots, KP, Lp), np.float32)
+    part[:, :k, :L] = np.abs(rng.standard_normal((slots, k, L)))
+    x0 = x.copy()
+    cpl, rpl = np.zeros((3, 256, Lp), np.uint16), np.zeros((2, Lp, KP), np.uint16)
+    emu.emu_mur_kl_update(KP, ptr(part), slots, ptr(bsum), ptr(x), ptr(cpl), ptr(rpl), k, L, Lp, Lp, C.c_float(lam))
+    a = x0.astype(np.float64) * part.astype(np.float64).sum(0)
+    b = bsum[:, None]
+    with np.errstate(all="ignore"):
+        want = 2 * a / (b + np.sqrt(b * b + 4 * lam * a))
+    np.testing.assert_allclose(x[:k, :L], want[:k, :L], rtol=2e-5)
+    assert not x[k:].any() and not x[:, L:].any()
+    _check_planes(x, cpl, rpl, KP)
+
+
+def test_gram_reduce_and_cuda_core_objective(emu):
+    KP, Lp, slots = 64, 256, 5
+    rng = np.random.default_rng(9)
+    part = rng.standard_normal((slots, KP, Lp)).astype(np.float32)
+    g32, g64 = np.zeros((KP, KP), np.float32), np.zeros((KP, KP))
+    emu.emu_gram_reduce(ptr(part), slots, KP, Lp, ptr(g32), ptr(g64))
+    want = part[:, :, :KP].astype(np.float64).sum(0)
+    assert np.array_equal(g64, want) and np.array_equal(g32, want.astype(np.float32))
+    # utils.py:29 on a ragged 100 x 150 problem with two V planes
+    m, n, k, Mp, Np = 100, 150, 9, 256, 256
+    v = (rng.random((m, n)) * 3).astype(np.float32)
+    hi = orc.round_to_bf16_grid(v)
+    lo = orc.round_to_bf16_grid(v - hi)
+    planes = np.stack([blocked(f32_to_bf16(hi), Mp), blocked(f32_to_bf16(lo), Mp)])
+    wt = np.zeros((64, Mp), np.float32)
+    wt[:k, :m] = rng.random((k, m))
+    ht = np.zeros((64, Np), np.float32)
+    ht[:k, :n] = rng.random((k, n))
+    nparts = ((n + 63) // 64) * ((m + 63) // 64)
+    partial = np.zeros(nparts)
+    emu.emu_objective_simt(ptr(planes), C.c_long(planes[0].size), Mp, 2, ptr(wt), Mp, ptr(ht), Np, k, m, n, ptr(partial))
+    want = orc.objective((hi + lo).astype(np.float64), wt[:k, :m].T.astype(np.float64) @ ht[:k, :n].astype(np.float64))
+    assert abs(0.5 * partial.sum() - want) / want < 1e-5      # sum_partials_kernel applies the 1/2 of utils.py:29

@@ -73,4 +73,46 @@ void emu_fixed_planes(const float* master, int KP, int Lp, std::uint16_t* cpl, l
                 [&] { fixed_planes_kernel(master, Lp, reinterpret_cast<bf16*>(cpl), cpl_plane); });
 }
 
+// mur_eu_update_launch / mur_kl_update_launch: grid = window / 64, 256 threads
+void emu_mur_eu_update(int KP, const float* part, int slots, const float* gram, float* master, std::uint16_t* cpl,
+                       std::uint16_t* rpl, int k, int L, int Lp, int nrows_p, float lambda) {
+    const unsigned grid = static_cast<unsigned>(nrows_p / 64);
+    const size_t smem = (static_cast<size_t>(KP) * 64 + 32 * static_cast<size_t>(KP)) * sizeof(float);
+    bf16 *c = reinterpret_cast<bf16*>(cpl), *r = reinterpret_cast<bf16*>(rpl);
+    const long cp = 256L * Lp, rp = static_cast<long>(Lp) * KP;
+    std::function<void()> body;
+    if (KP == 64) body = [&] { mur_eu_update_kernel<4>(part, slots, gram, master, c, cp, r, rp, k, L, Lp, lambda); };
+    else if (KP == 128) body = [&] { mur_eu_update_kernel<8>(part, slots, gram, master, c, cp, r, rp, k, L, Lp, lambda); };
+    else body = [&] { mur_eu_update_kernel<16>(part, slots, gram, master, c, cp, r, rp, k, L, Lp, lambda); };
+    emu::launch({grid, 1, 1}, {256, 1, 1}, smem, body);
+}
+
+void emu_mur_kl_update(int KP, const float* part, int slots, const double* bsum, float* master, std::uint16_t* cpl,
+                       std::uint16_t* rpl, int k, int L, int Lp, int nrows_p, float lambda) {
+    const unsigned grid = static_cast<unsigned>(nrows_p / 64);
+    bf16 *c = reinterpret_cast<bf16*>(cpl), *r = reinterpret_cast<bf16*>(rpl);
+    const long cp = 256L * Lp, rp = static_cast<long>(Lp) * KP;
+    std::function<void()> body;
+    if (KP == 64) body = [&] { mur_kl_update_kernel<4>(part, slots, bsum, master, c, cp, r, rp, k, L, Lp, lambda); };
+    else if (KP == 128) body = [&] { mur_kl_update_kernel<8>(part, slots, bsum, master, c, cp, r, rp, k, L, Lp, lambda); };
+    else body = [&] { mur_kl_update_kernel<16>(part, slots, bsum, master, c, cp, r, rp, k, L, Lp, lambda); };
+    emu::launch({grid, 1, 1}, {256, 1, 1}, 0, body);
+}
+
+void emu_factor_rowsum(const float* master, int KP, int L, int Lp, double* sums) {
+    emu::launch({static_cast<unsigned>(KP), 1, 1}, {256, 1, 1}, 0, [&] { factor_rowsum_kernel(master, L, Lp, sums); });
+}
+
+void emu_gram_reduce(const float* part, int slots, int KP, int Lp, float* g32, double* g64) {
+    emu::launch({static_cast<unsigned>((KP * KP + 255) / 256), 1, 1}, {256, 1, 1}, 0,
+                [&] { gram_reduce_kernel(part, slots, KP, Lp, g32, g64); });
+}
+
+void emu_objective_simt(const std::uint16_t* vpl, long v_plane, int v_rows_p, int nv, const float* wt, int Mp,
+                        const float* ht, int Np, int k, int m, int n, double* partial) {
+    emu::launch({static_cast<unsigned>((n + 63) / 64), static_cast<unsigned>((m + 63) / 64), 1}, {256, 1, 1}, 0, [&] {
+        objective_simt_kernel(reinterpret_cast<const bf16*>(vpl), v_plane, v_rows_p, nv, wt, Mp, ht, Np, k, m, n, partial);
+    });
+}
+
 }  // extern "C"
