@@ -65,8 +65,12 @@ class Engine:
         self.row_win, self.col_win = mb[self.rank], nb[self.rank]
         self.row_range = (self.row_win[0], self.row_win[0] + live_rows(self.m, *self.row_win))
         self.col_range = (self.col_win[0], self.col_win[0] + live_rows(self.n, *self.col_win))
-        if self.row_range[1] <= self.row_range[0] or self.col_range[1] <= self.col_range[0]:
-            raise ValueError(f"{self.world} ranks leave rank {self.rank} without rows or columns of a "
+        # judged for ALL ranks on every rank, so that the whole group raises together instead of one rank
+        # leaving the others waiting in their first collective
+        empty = [p for p in range(self.world)
+                 if live_rows(self.m, *mb[p]) <= 0 or live_rows(self.n, *nb[p]) <= 0]
+        if empty:
+            raise ValueError(f"{self.world} ranks leave rank {empty[0]} without rows or columns of a "
                              f"{self.m} x {self.n} problem (shards are multiples of 256); use fewer ranks")
         with self._device_ctx():
             sharded = self.world > 1

@@ -349,3 +349,13 @@ def test_bench_sharded_end_to_end_leg_on_two_ranks():
         assert "error" not in a and a["value"] > 0 and a["value"] == b["value"]          # max over ranks, agreed
         assert a["h2d_bytes_per_step"] == (600 * 520 * 4 + 2 * (600 * 6 + 6 * 520) * 4) // 5
         assert a["unit"] == "it/s" and a["host_v_pinned"] is False
+
+
+def test_too_many_ranks_for_the_problem_is_refused_on_every_rank():
+    """Shards are multiples of 256 rows / columns: a rank without rows or columns would leave the others waiting
+    in their first collective, so every rank judges every rank's window and all of them raise."""
+    for rank in range(4):
+        with pytest.raises(ValueError, match="without rows or columns"):
+            softdev.SoftEngine(600, 5000, 4, rank=rank, world=4)       # 600 rows: ranks 3 has none
+    eng = softdev.SoftEngine(600, 5000, 4, rank=2, world=3)
+    assert eng.row_range == (512, 600) and eng.col_range[0] == 2 * eng.per_n
