@@ -447,3 +447,29 @@ def test_gram_reduce_and_cuda_core_objective(emu):
     emu.emu_objective_simt(ptr(planes), C.c_long(planes[0].size), Mp, 2, ptr(wt), Mp, ptr(ht), Np, k, m, n, ptr(partial))
     want = orc.objective((hi + lo).astype(np.float64), wt[:k, :m].T.astype(np.float64) @ ht[:k, :n].astype(np.float64))
     assert abs(0.5 * partial.sum() - want) / want < 1e-5      # sum_partials_kernel applies the 1/2 of utils.py:29
+
+
+@pytest.mark.parametrize("k,KP", [(10, 64), (64, 64), (100, 128), (200, 256)])
+def test_chol_inverse_kernel(emu, k, KP):
+    """admm.py:220,230 / ao_admm.py:54-55,59: (G + rho I)^-1 by the fp64 shared-memory Cholesky + substitution
+    kernel (1024 threads, warp-shuffle broadcasts), rho given or tr(G)/k, and the not-PD flag."""
+    rng = np.random.default_rng(k)
+    a = rng.standard_normal((k, 3 * k))
+    g = np.zeros((KP, KP))
+    g[:k, :k] = a @ a.T
+    for rho_mode, rho_in in ((0, 2.5), (1, 0.0)):
+        ainv, rho_out, flags = np.zeros((KP, KP)), np.zeros(4), np.zeros(8, np.int32)
+        scratch = np.zeros((KP, KP + 1))
+        emu.emu_chol_inverse(KP, ptr(g), k, rho_mode, C.c_double(rho_in), ptr(scratch), ptr(ainv), ptr(rho_out),
+                             ptr(flags))
+        rho = rho_in if rho_mode == 0 else np.trace(g[:k, :k]) / k
+        assert rho_out[0] == pytest.approx(rho, rel=1e-15) and flags[0] == 0
+        want = np.linalg.inv(g[:k, :k] + rho * np.eye(k))
+        np.testing.assert_allclose(ainv[:k, :k], want, rtol=1e-9, atol=1e-12 * np.abs(want).max())
+        assert np.allclose(ainv[:k, :k], ainv[:k, :k].T, rtol=0, atol=1e-12 * np.abs(want).max())   # the apply kernels read it as symmetric
+    bad = g.copy()
+    bad[:k, :k] -= (np.linalg.eigvalsh(g[:k, :k]).max() + 10) * np.eye(k)      # negative definite even with rho
+    ainv, rho_out, flags = np.zeros((KP, KP)), np.zeros(4), np.zeros(8, np.int32)
+    emu.emu_chol_inverse(KP, ptr(bad), k, 0, C.c_double(1.0), ptr(np.zeros((KP, KP + 1))), ptr(ainv), ptr(rho_out),
+                         ptr(flags))
+    assert flags[0] == 1                                      # scipy / numpy raise LinAlgError here

@@ -77,6 +77,22 @@ inline T __shfl_xor_sync(unsigned, T v, int lane_mask) {
     return out;
 }
 
+template <typename T>
+inline T __shfl_sync(unsigned, T v, int src_lane) {
+    static_assert(sizeof(T) <= 8, "shuffle of at most 8 bytes");
+    emu::Block& b = *emu::tl_block;
+    const int tid = emu::tl_tid, w = tid >> 5;
+    std::uint64_t bits = 0;
+    std::memcpy(&bits, &v, sizeof(T));
+    b.xchg[tid] = bits;
+    b.warp[w]->arrive_and_wait();
+    const std::uint64_t got = b.xchg[(tid & ~31) | (src_lane & 31)];
+    b.warp[w]->arrive_and_wait();
+    T out;
+    std::memcpy(&out, &got, sizeof(T));
+    return out;
+}
+
 inline unsigned atomicMax(unsigned* a, unsigned v) {
     unsigned old = __atomic_load_n(a, __ATOMIC_RELAXED);
     while (old < v && !__atomic_compare_exchange_n(a, &old, v, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
@@ -91,6 +107,7 @@ inline unsigned atomicOr(unsigned* a, unsigned v) { return __atomic_fetch_or(a, 
 
 inline unsigned __float_as_uint(float f) { unsigned u; std::memcpy(&u, &f, 4); return u; }
 inline float __uint_as_float(unsigned u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline int lane_id() { return emu::tl_tid & 31; }        // ptx.cuh reads %laneid
 using std::isfinite;
 using std::max;
 using std::min;

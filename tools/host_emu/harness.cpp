@@ -35,6 +35,17 @@ void emu_admm_apply(int l2n, int KP, int k, int L, int Lp, int nrows_p, const fl
     emu::launch({grid, 1, 1}, {256, 1, 1}, smem, body);
 }
 
+// chol_inverse_launch: one block of 1024 threads; the working matrix in shared memory up to KP = 128
+void emu_chol_inverse(int KP, const double* gram, int k, int rho_mode, double rho_in, double* gscratch, double* ainv,
+                      double* rho_out, int* flags) {
+    std::function<void()> body;
+    size_t smem = 0;
+    if (KP == 64) { smem = 64 * 65 * sizeof(double); body = [&] { chol_inverse_kernel<64>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags); }; }
+    else if (KP == 128) { smem = 128 * 129 * sizeof(double); body = [&] { chol_inverse_kernel<128>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags); }; }
+    else body = [&] { chol_inverse_kernel<256>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags); };
+    emu::launch({1, 1, 1}, {1024, 1, 1}, smem, body);
+}
+
 void emu_tikhonov_gram(int k, int KP, double lambda, const double* rho, double* out) {
     emu::launch({static_cast<unsigned>((KP * KP + 255) / 256), 1, 1}, {256, 1, 1}, 0,
                 [&] { tikhonov_gram_kernel(k, KP, lambda, rho, out); });
