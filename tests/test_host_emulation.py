@@ -473,3 +473,23 @@ def test_chol_inverse_kernel(emu, k, KP):
     emu.emu_chol_inverse(KP, ptr(bad), k, 0, C.c_double(1.0), ptr(np.zeros((KP, KP + 1))), ptr(ainv), ptr(rho_out),
                          ptr(flags))
     assert flags[0] == 1                                      # scipy / numpy raise LinAlgError here
+
+
+def test_fixed_planes_kernel_on_signed_factors(emu):
+    """Exact-mode operand planes of a (signed) ADMM auxiliary: plane 0 an integer of at most 128 units of
+    2^(E-6), E from the component row's |max|; planes 1-2 floating remainders; together x to ~2^-22 of that max."""
+    KP, Lp, k, L = 64, 512, 20, 400
+    rng = np.random.default_rng(4)
+    x = np.zeros((KP, Lp), np.float32)
+    x[:k, :L] = rng.standard_normal((k, L)) * np.exp(rng.standard_normal((k, 1)) * 3)
+    cpl = np.zeros((3, 256, Lp), np.uint16)
+    emu.emu_fixed_planes(ptr(x), KP, Lp, ptr(cpl), C.c_long(256 * Lp))
+    p = bf16_to_f32(cpl[:, :KP]).astype(np.float64)
+    mx = np.abs(x).max(1)
+    live = mx > 0
+    unit = np.ldexp(1.0, np.frexp(np.maximum(mx, 1e-30))[1] - 1 - 6)[:, None]
+    q = p[0][live] / unit[live]
+    assert np.array_equal(q, np.round(q)) and np.abs(q).max() <= 128
+    err = np.abs(p.sum(0) - x)
+    assert np.all(err[live] <= np.ldexp(mx[live], -21)[:, None])
+    assert not p[:, ~live].any()
