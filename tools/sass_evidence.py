@@ -38,7 +38,7 @@ def main(out_path):
             regs[fn] = m.groups()
     rows = []
     for k, c in counts.items():
-        if any(c[x] for x in ("UTCHMMA", "UTMALDG", "LDTM")) or any(t in k for t in ("admm_apply", "chol", "update")):
+        if any(c[x] for x in ("UTCHMMA", "UTMALDG", "LDTM")) or any(t in k for t in ("admm_apply", "chol", "update", "kl_vaux", "tikhonov", "ingest_data", "absmax")):
             r = regs.get(k, ("?", "?"))
             rows.append(f"| `{k}` | {r[0]} | {r[1]} | " + " | ".join(str(c[x]) for x in KEYS) + " |")
     with open(out_path, "w") as f:
