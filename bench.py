@@ -445,9 +445,13 @@ def run_b200(args):
 
     # ---- end to end through the public API with HOST buffers ----
     line["e2e"] = None
+    _install_term_handler(line, rank)                        # a killed run still prints its device-timed line
     if not args.no_e2e and world == 1:
-        line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0)
-        line["time_to_tol"] = line["e2e"].pop("time_to_tol", None)
+        try:
+            line["e2e"] = run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0)
+            line["time_to_tol"] = line["e2e"].pop("time_to_tol", None)
+        except Exception as exc:                             # noqa: BLE001 -- reported in the line
+            line["e2e"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
     elif not args.no_e2e:
         # a failure or a stall of this leg must not cost the device-timed line: after E2E_LIMIT_S seconds
         # every rank prints / exits with what it has
@@ -460,8 +464,12 @@ def run_b200(args):
             line["e2e"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
         guard.cancel()
     if not args.no_cpu and rank == 0 and world == 1:
-        its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
-        line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
+        try:
+            its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
+            line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
+        except Exception as exc:                             # noqa: BLE001 -- reported in the line
+            line["cpu_baseline"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
+    _EMITTED.set()
     if rank == 0:
         emit(line)
     if world > 1:
@@ -552,9 +560,34 @@ def run_e2e(eng, stepper, method, dtype_, m, n, k, extra, steps, obj0=None):
 
 
 E2E_LIMIT_S = 300.0
+_EMITTED = threading.Event()
+
+
+def _install_term_handler(line, rank):
+    """From here on the device-timed fields are complete: if the launcher tears the job down during one of the
+    later legs (another rank died, an outer time limit), rank 0 still prints them before it exits."""
+    import signal
+
+    def on_term(signum, _frame):
+        if not _EMITTED.is_set():
+            _EMITTED.set()
+            if line.get("e2e") is None:
+                line["e2e"] = {"value": None, "error": f"terminated by signal {signum} during a host-side leg; "
+                                                       "device-timed fields are complete"}
+            if rank == 0:
+                emit(line)
+        os._exit(0 if rank == 0 else 1)
+
+    try:
+        signal.signal(signal.SIGTERM, on_term)
+    except (ValueError, OSError):                            # not the main thread (tests drive run_b200 from one)
+        pass
 
 
 def _e2e_timed_out(line, rank):
+    if _EMITTED.is_set():
+        return
+    _EMITTED.set()
     line["e2e"] = {"value": None, "error": f"end-to-end leg exceeded {E2E_LIMIT_S:.0f} s; device-timed fields are complete"}
     if rank == 0:
         emit(line)
