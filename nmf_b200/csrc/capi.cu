@@ -346,7 +346,19 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
     const nmfb_data* v = &p->v_rows;            // the rows of V this rank holds == the window of W
     const Window ww = window_of(&p->w);
     int nparts = 0;
-    if (impl == 0 && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
+    // impl 2 = wide-tile variant (residual_n256.cu: opt-in, also through NMFB_RES_N256=1 for the objectives the
+    // solver steps enqueue themselves); KP = 64 / 128 with a single V plane only
+    bool wide = impl == 2;
+    if (impl == 0) {
+        const char* e = getenv("NMFB_RES_N256");
+        wide = e && atoi(e) == 1 && residual_n256_smem_bytes(p->KP, v->nv) > 0;
+    }
+    if (wide && residual_n256_smem_bytes(p->KP, v->nv) < 0)
+        return fail(NMFB_ERR_ARG, "objective: the wide-tile kernel needs KP = 64 or 128 and one V plane (KP=%d nv=%d)",
+                    p->KP, v->nv);
+    if (wide) impl = 0;
+    const int BN = wide ? 256 : 128;
+    if (impl == 0 && !wide && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
     if (impl == 1) {
         const long need = static_cast<long>((v->rows + 63) / 64) * ((p->n + 63) / 64);
         if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
@@ -357,7 +369,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         ResidualArgs a;
         memset(&a, 0, sizeof(a));
         a.mtiles = (v->rows + 127) / 128;
-        a.ntiles = (p->n + 127) / 128;
+        a.ntiles = (p->n + BN - 1) / BN;
         int cs = 2;
         if (const char* e = getenv("NMFB_RES_CLUSTER")) cs = atoi(e);
         if (cs != 1 && cs != 2 && cs != 4) cs = 1;
@@ -368,7 +380,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
                               p->KP, 128);
             if (rc) return rc;
             rc = make_map(&a.hr[q], bf(p->h.rplanes) + static_cast<long>(q) * p->h.Lp * p->KP, p->h.Lp, p->KP,
-                          128 / cs);
+                          BN / cs);
             if (rc) return rc;
         }
         for (int q = 0; q < v->nv; ++q) {
@@ -377,7 +389,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
             if (rc) return rc;
         }
         a.partial = p->obj_partial;
-        a.KP = p->KP; a.NV = v->nv; a.BN = 128;
+        a.KP = p->KP; a.NV = v->nv; a.BN = BN;
         a.m = p->m; a.n = p->n;
         a.kl = kl;
         a.v_rows_p = v->rows_p;
@@ -387,7 +399,8 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         const int grid = ncl * cs;
         if (grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
         nparts = grid;
-        CUDA_TRY(residual_launch(a, grid, st(stream)));
+        if (wide) { CUDA_TRY(residual_n256_launch(a, grid, st(stream))); }
+        else      { CUDA_TRY(residual_launch(a, grid, st(stream))); }
     }
     CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, kl ? 1.0 : 0.5, obj_out, st(stream)));
     return 0;

@@ -66,5 +66,8 @@ struct alignas(64) ResidualArgs {
 cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_smem_bytes(int KP, int NV, int BN);
 int residual_max_clusters(int cs, int num_sms);
+// wide-tile variant (residual_n256.cu; opt-in): 128 x 256 tiles, args.BN == 256, args.ntiles in 256-column tiles
+cudaError_t residual_n256_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
+int residual_n256_smem_bytes(int KP, int NV);
 
 }  // namespace nmfb

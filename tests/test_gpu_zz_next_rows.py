@@ -236,3 +236,33 @@ def test_kl_branch_trajectory_vs_oracle_k64(method):
     assert res.i == tr.i
     obj_err = max(abs(a - b) / b for a, b in zip(res.obj_history, tr.obj_history))
     assert obj_err < TOL and rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
+
+
+# ----------------------------------------------------------------------------------------------
+# Wide-tile objective kernel (residual_n256.cu: 128 x 256 tiles, N = 256 MMAs; opt-in through impl = 2 or
+# NMFB_RES_N256=1).  LAST in the file on purpose: it has never executed, and a faulting tcgen05 kernel
+# poisons the CUDA context of the process for every test after it.
+# ----------------------------------------------------------------------------------------------
+@first_run_pending
+@pytest.mark.parametrize("shape", [(1024, 1536, 128), (900, 1100, 48), (2304, 700, 100), (128, 256, 64),
+                                   (4096, 8192, 128)])
+def test_wide_tile_objective_agrees_with_the_default_kernel(shape):
+    """impl 2 against impl 0 (validated, r01c) and against the fp64 value: full and ragged tiles on both axes,
+    a single tile, KP = 64 and 128, enough tiles for every CTA to walk several rows of tiles."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.engine import Engine
+    m, n, k = shape
+    v = orc.planted(m, n, k, 50)
+    w0, h0 = orc.seeded_init(m, n, k, 51)
+    eng = Engine(m, n, k)
+    eng.upload_data(v)
+    eng.set_factors(w0, h0)
+    eng.objective_eu(slot=0, impl=0)
+    eng.objective_eu(slot=1, impl=2)
+    eng.objective_eu(slot=2, impl=2)                         # a second launch: barriers / TMEM left clean
+    a, b, c = eng.read_scalar(0), eng.read_scalar(1), eng.read_scalar(2)
+    want = orc.objective(v.astype(np.float64), w0.astype(np.float32).astype(np.float64)
+                         @ h0.astype(np.float32).astype(np.float64))
+    assert b == c
+    assert abs(b - a) / a < 1e-6 and abs(b - want) / want < 1e-5
+    eng.release()

@@ -283,6 +283,16 @@ def bench(m, n, k, what):
         ms = _time(f)
         print(f"bench objective tc m={m} n={n} k={k} {ms:.3f} ms alg {2.0*m*n*k/ms/1e9:.1f} TF/s "
               f"exec {6.0*m*n*k/ms/1e9:.1f} TF/s V {m*n*2/ms/1e6:.0f} GB/s", flush=True)
+        if KP <= 128 and eng.nv == 1 and os.environ.get("SELFTEST_WIDE", "1") == "1":
+            # wide-tile variant (residual_n256.cu, opt-in): same value first, then the time
+            eng.objective_eu(slot=1, impl=0)
+            eng.objective_eu(slot=2, impl=2)
+            a, b = eng.read_scalar(1), eng.read_scalar(2)
+            print(f"objective wide-tile vs default: {a:.9e} {b:.9e} rel {abs(a - b) / a:.2e}", flush=True)
+            f = lambda: eng.objective_eu(slot=2, impl=2)
+            ms = _time(f)
+            print(f"bench objective tc-wide m={m} n={n} k={k} {ms:.3f} ms alg {2.0*m*n*k/ms/1e9:.1f} TF/s "
+                  f"exec {6.0*m*n*k/ms/1e9:.1f} TF/s V {m*n*2/ms/1e6:.0f} GB/s", flush=True)
     if what in ("step", "all"):
         f = lambda: eng.mur_eu_step(0.0, 0.0, obj_slot=0)
         ms = _time(f, iters=5, warm=2)
