@@ -160,7 +160,8 @@ int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other,
 /* 0.5 * ||V - W H||_F^2 (utils.py:29) in residual form, fp64 accumulation, written to *obj_out
  * (device).  impl = 0: tcgen05 kernel, 1: CUDA-core kernel (cross-check / tiny problems), 2: wide-tile tcgen05
  * kernel (128 x 256 tiles; KP = 64 / 128 and one V plane, NMFB_ERR_ARG otherwise; experimental, also selected for
- * impl 0 when the environment has NMFB_RES_N256=1). */
+ * impl 0 when the environment has NMFB_RES_N256=1), 3: tcgen05 kernel with the W planes as the TMEM-resident A
+ * operand (experimental; NMFB_RES_TS=1 selects it for impl 0). */
 int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream);
 
 /* ---- solver steps --------------------------------------------------------------------------- */

@@ -357,8 +357,17 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         return fail(NMFB_ERR_ARG, "objective: the wide-tile kernel needs KP = 64 or 128 and one V plane (KP=%d nv=%d)",
                     p->KP, v->nv);
     if (wide) impl = 0;
+    // impl 3 = TS variant (residual_ts.cu: W planes as the TMEM-resident A operand; opt-in, NMFB_RES_TS=1)
+    bool ts = impl == 3;
+    if (impl == 0 && !wide) {
+        const char* e = getenv("NMFB_RES_TS");
+        ts = e && atoi(e) == 1 && residual_ts_smem_bytes(p->KP, v->nv) > 0;
+    }
+    if (ts && residual_ts_smem_bytes(p->KP, v->nv) < 0)
+        return fail(NMFB_ERR_ARG, "objective: the TS kernel does not fit KP=%d nv=%d", p->KP, v->nv);
+    if (ts) impl = 0;
     const int BN = wide ? 256 : 128;
-    if (impl == 0 && !wide && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
+    if (impl == 0 && !wide && !ts && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
     if (impl == 1) {
         const long need = static_cast<long>((v->rows + 63) / 64) * ((p->n + 63) / 64);
         if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
@@ -379,6 +388,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
             int rc = make_map(&a.wr[q], bf(p->w.rplanes) + (static_cast<long>(q) * p->w.Lp + ww.w0) * p->KP, ww.wp,
                               p->KP, 128);
             if (rc) return rc;
+            a.w_rpl[q] = bf(p->w.rplanes) + (static_cast<long>(q) * p->w.Lp + ww.w0) * p->KP;
             rc = make_map(&a.hr[q], bf(p->h.rplanes) + static_cast<long>(q) * p->h.Lp * p->KP, p->h.Lp, p->KP,
                           BN / cs);
             if (rc) return rc;
@@ -399,8 +409,9 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         const int grid = ncl * cs;
         if (grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
         nparts = grid;
-        if (wide) { CUDA_TRY(residual_n256_launch(a, grid, st(stream))); }
-        else      { CUDA_TRY(residual_launch(a, grid, st(stream))); }
+        if (wide)    { CUDA_TRY(residual_n256_launch(a, grid, st(stream))); }
+        else if (ts) { CUDA_TRY(residual_ts_launch(a, grid, st(stream))); }
+        else         { CUDA_TRY(residual_launch(a, grid, st(stream))); }
     }
     CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, kl ? 1.0 : 0.5, obj_out, st(stream)));
     return 0;

@@ -62,6 +62,7 @@ struct alignas(64) ResidualArgs {
     int kl;                  // 0: sum (v-s)^2 ; 1: generalised KL terms
     int v_rows_p;            // rows per K-block of the blocked V planes
     int cluster;             // CTAs per cluster (H^T stages are multicast across it)
+    const __nv_bfloat16* w_rpl[2];   // TS variant only: the W row planes [rows][KP] themselves (same base as wr[])
 };
 cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_smem_bytes(int KP, int NV, int BN);
@@ -69,5 +70,8 @@ int residual_max_clusters(int cs, int num_sms);
 // wide-tile variant (residual_n256.cu; opt-in): 128 x 256 tiles, args.BN == 256, args.ntiles in 256-column tiles
 cudaError_t residual_n256_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_n256_smem_bytes(int KP, int NV);
+// TS variant (residual_ts.cu; opt-in): W planes of the tile row as the TMEM-resident A operand, args.BN == 128
+cudaError_t residual_ts_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
+int residual_ts_smem_bytes(int KP, int NV);
 
 }  // namespace nmfb

@@ -239,30 +239,48 @@ def test_kl_branch_trajectory_vs_oracle_k64(method):
 
 
 # ----------------------------------------------------------------------------------------------
-# Wide-tile objective kernel (residual_n256.cu: 128 x 256 tiles, N = 256 MMAs; opt-in through impl = 2 or
-# NMFB_RES_N256=1).  LAST in the file on purpose: it has never executed, and a faulting tcgen05 kernel
-# poisons the CUDA context of the process for every test after it.
+# Experimental objective kernels, opt-in through `impl` (or NMFB_RES_N256=1 / NMFB_RES_TS=1):
+#   impl 2 = residual_n256.cu (128 x 256 tiles, N = 256 MMAs), impl 3 = residual_ts.cu (W planes as the TMEM-resident
+#   A operand).  LAST in the file on purpose: neither has ever executed, and a faulting tcgen05 kernel poisons the
+#   CUDA context of the process for every test after it (impl 2 first: it uses only instruction forms that the
+#   validated kernels use).
 # ----------------------------------------------------------------------------------------------
+def _objective_variant_agrees(impl, m, n, k, exact_data=True):
+    from oracle import nmf_oracle as orc
+    from nmf_b200.engine import Engine
+    if exact_data:
+        v = orc.planted(m, n, k, 50)                         # on the bf16 grid: one V plane
+    else:
+        v = np.random.default_rng(52).random((m, n)).astype(np.float32)      # needs the hi + lo planes
+    w0, h0 = orc.seeded_init(m, n, k, 51)
+    eng = Engine(m, n, k)
+    eng.upload_data(np.asarray(v))
+    assert eng.nv == (1 if exact_data else 2)
+    eng.set_factors(w0, h0)
+    eng.objective_eu(slot=0, impl=0)
+    eng.objective_eu(slot=1, impl=impl)
+    eng.objective_eu(slot=2, impl=impl)                      # a second launch: barriers / TMEM left clean
+    a, b, c = eng.read_scalar(0), eng.read_scalar(1), eng.read_scalar(2)
+    want = orc.objective(np.asarray(v, np.float64), w0.astype(np.float32).astype(np.float64)
+                         @ h0.astype(np.float32).astype(np.float64))
+    eng.release()
+    assert b == c
+    assert abs(b - a) / a < 1e-6 and abs(b - want) / want < 1e-5
+
+
 @first_run_pending
 @pytest.mark.parametrize("shape", [(1024, 1536, 128), (900, 1100, 48), (2304, 700, 100), (128, 256, 64),
                                    (4096, 8192, 128)])
 def test_wide_tile_objective_agrees_with_the_default_kernel(shape):
     """impl 2 against impl 0 (validated, r01c) and against the fp64 value: full and ragged tiles on both axes,
     a single tile, KP = 64 and 128, enough tiles for every CTA to walk several rows of tiles."""
-    from oracle import nmf_oracle as orc
-    from nmf_b200.engine import Engine
-    m, n, k = shape
-    v = orc.planted(m, n, k, 50)
-    w0, h0 = orc.seeded_init(m, n, k, 51)
-    eng = Engine(m, n, k)
-    eng.upload_data(v)
-    eng.set_factors(w0, h0)
-    eng.objective_eu(slot=0, impl=0)
-    eng.objective_eu(slot=1, impl=2)
-    eng.objective_eu(slot=2, impl=2)                         # a second launch: barriers / TMEM left clean
-    a, b, c = eng.read_scalar(0), eng.read_scalar(1), eng.read_scalar(2)
-    want = orc.objective(v.astype(np.float64), w0.astype(np.float32).astype(np.float64)
-                         @ h0.astype(np.float32).astype(np.float64))
-    assert b == c
-    assert abs(b - a) / a < 1e-6 and abs(b - want) / want < 1e-5
-    eng.release()
+    _objective_variant_agrees(2, *shape)
+
+
+@first_run_pending
+@pytest.mark.parametrize("shape,exact", [((1024, 1536, 128), True), ((900, 1100, 48), True), ((640, 520, 200), True),
+                                         ((128, 128, 64), True), ((4096, 8192, 128), True), ((1100, 900, 100), False)])
+def test_tmem_operand_objective_agrees_with_the_default_kernel(shape, exact):
+    """impl 3 against impl 0 and the fp64 value: KP = 64 / 128 / 256 (k = 200: the planes fill all 512 TMEM
+    columns next to the accumulators), one tile, several rows of tiles per CTA, two V planes."""
+    _objective_variant_agrees(3, *shape, exact_data=exact)

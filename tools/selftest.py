@@ -283,15 +283,19 @@ def bench(m, n, k, what):
         ms = _time(f)
         print(f"bench objective tc m={m} n={n} k={k} {ms:.3f} ms alg {2.0*m*n*k/ms/1e9:.1f} TF/s "
               f"exec {6.0*m*n*k/ms/1e9:.1f} TF/s V {m*n*2/ms/1e6:.0f} GB/s", flush=True)
-        if KP <= 128 and eng.nv == 1 and os.environ.get("SELFTEST_WIDE", "1") == "1":
-            # wide-tile variant (residual_n256.cu, opt-in): same value first, then the time
+        # experimental variants (opt-in): 2 = wide tiles (residual_n256.cu), 3 = W planes in TMEM (residual_ts.cu);
+        # same value first, then the time.  SELFTEST_VARIANTS="2,3" (default) / "" to skip.
+        for impl in [int(x) for x in os.environ.get("SELFTEST_VARIANTS", "2,3").split(",") if x]:
+            if impl == 2 and not (KP <= 128 and eng.nv == 1):
+                continue
+            name = {2: "tc-wide", 3: "tc-tmemA"}[impl]
             eng.objective_eu(slot=1, impl=0)
-            eng.objective_eu(slot=2, impl=2)
+            eng.objective_eu(slot=2, impl=impl)
             a, b = eng.read_scalar(1), eng.read_scalar(2)
-            print(f"objective wide-tile vs default: {a:.9e} {b:.9e} rel {abs(a - b) / a:.2e}", flush=True)
-            f = lambda: eng.objective_eu(slot=2, impl=2)
+            print(f"objective {name} vs default: {a:.9e} {b:.9e} rel {abs(a - b) / a:.2e}", flush=True)
+            f = lambda: eng.objective_eu(slot=2, impl=impl)
             ms = _time(f)
-            print(f"bench objective tc-wide m={m} n={n} k={k} {ms:.3f} ms alg {2.0*m*n*k/ms/1e9:.1f} TF/s "
+            print(f"bench objective {name} m={m} n={n} k={k} {ms:.3f} ms alg {2.0*m*n*k/ms/1e9:.1f} TF/s "
                   f"exec {6.0*m*n*k/ms/1e9:.1f} TF/s V {m*n*2/ms/1e6:.0f} GB/s", flush=True)
     if what in ("step", "all"):
         f = lambda: eng.mur_eu_step(0.0, 0.0, obj_slot=0)
