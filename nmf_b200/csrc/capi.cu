@@ -485,6 +485,7 @@ int kl_side(const nmfb_problem* p, const nmfb_data* data, const nmfb_factor* x, 
     int rc;
     for (int q = 0; q < 2; ++q) {
         if ((rc = make_map(&a.xr[q], bf(x->rplanes) + (static_cast<long>(q) * x->Lp + w.w0) * KP, w.wp, KP, 128))) return rc;
+        a.x_rpl[q] = bf(x->rplanes) + (static_cast<long>(q) * x->Lp + w.w0) * KP;
         if ((rc = make_map(&a.yc[q], bf(y->cplanes) + static_cast<long>(q) * 256 * y->Lp, 256, y->Lp, 128))) return rc;
     }
     for (int q = 0; q < data->nv; ++q)

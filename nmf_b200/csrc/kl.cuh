@@ -13,6 +13,7 @@ struct alignas(64) KlArgs {
     int KP, Lp;
     int npanels, ntiles, nsplit, tiles_per_split;
     int d_rows_p;
+    const __nv_bfloat16* x_rpl[2];   // TS variant only: the row planes of X themselves (same base as xr[])
 };
 
 struct KlPlan {
@@ -22,6 +23,8 @@ struct KlPlan {
 int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan);
 int kl_smem_bytes(int KP, int NV);
 cudaError_t kl_panel_launch(const KlArgs& args, const KlPlan& plan, int NV, int num_sms, cudaStream_t stream);
+// TS variant (kl_ts.cu; opt-in through NMFB_KL_TS=1): X as the TMEM-resident A operand of MMA1; same plan
+cudaError_t kl_panel_ts_launch(const KlArgs& args, const KlPlan& plan, int NV, cudaStream_t stream);
 
 // sums[c] = sum over the first L entries of master row c (fp64): `np.ones_like(x) @ h.T` (mur.py:26)
 // and `w.T @ np.ones_like(x)` (mur.py:42) collapse to these k-vectors.

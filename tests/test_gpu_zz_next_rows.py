@@ -284,3 +284,25 @@ def test_tmem_operand_objective_agrees_with_the_default_kernel(shape, exact):
     """impl 3 against impl 0 and the fp64 value: KP = 64 / 128 / 256 (k = 200: the planes fill all 512 TMEM
     columns next to the accumulators), one tile, several rows of tiles per CTA, two V planes."""
     _objective_variant_agrees(3, *shape, exact_data=exact)
+
+
+@first_run_pending
+@pytest.mark.parametrize("shape", [(768, 640, 100), (512, 2048, 24), (2000, 5000, 128)])
+def test_kl_pass_with_tmem_operand_agrees_with_the_default_kernel(shape, monkeypatch):
+    """NMFB_KL_TS=1 (kl_ts.cu: X as the TMEM-resident A operand of MMA1) against the default fused kernel and the
+    oracle: KP = 64 / 128, fused objective included, several work items per CTA at the last shape."""
+    from oracle import nmf_oracle as orc
+    from nmf_b200.mur import mur
+    m, n, k = shape
+    v = orc.planted(m, n, k, 60).astype(np.float64)
+    w0, h0 = orc.seeded_init(m, n, k, 61)
+    kw = dict(distance_type="kl", min_iter=10**9, max_iter=6, w0=w0, h0=h0, verbose=False)
+    monkeypatch.setenv("NMFB_KL_TS", "0")
+    base = mur(v, k, **kw)
+    monkeypatch.setenv("NMFB_KL_TS", "1")
+    res = mur(v, k, **kw)
+    monkeypatch.setenv("NMFB_KL_TS", "0")
+    assert rel_fro(res.w, base.w) < 1e-6 and rel_fro(res.h, base.h) < 1e-6
+    assert max(abs(a - b) / abs(b) for a, b in zip(res.obj_history, base.obj_history)) < 1e-6
+    tr = orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=6)
+    assert rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
