@@ -416,8 +416,11 @@ int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan) {
 
 cudaError_t kl_panel_launch(const KlArgs& args, const KlPlan& plan, int NV, int num_sms, cudaStream_t stream) {
     (void)num_sms;
-    if (const char* e = getenv("NMFB_KL_TS"))        // opt-in experimental variant (kl_ts.cu)
-        if (atoi(e) == 1) return kl_panel_ts_launch(args, plan, NV, stream);
+    if (const char* e = getenv("NMFB_KL_TS")) {      // opt-in experimental variants (kl_ts.cu, kl_ts2.cu)
+        const int v = atoi(e);
+        if (v == 2 && args.KP == 128) return kl_panel_ts2_launch(args, plan, NV, stream);
+        if (v == 1 || v == 2) return kl_panel_ts_launch(args, plan, NV, stream);
+    }
     void (*fn)(const KlArgs) = nullptr;
     const bool obj = args.obj_partial != nullptr;
     if (args.KP == 64)

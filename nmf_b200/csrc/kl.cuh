@@ -25,6 +25,8 @@ int kl_smem_bytes(int KP, int NV);
 cudaError_t kl_panel_launch(const KlArgs& args, const KlPlan& plan, int NV, int num_sms, cudaStream_t stream);
 // TS variant (kl_ts.cu; opt-in through NMFB_KL_TS=1): X as the TMEM-resident A operand of MMA1; same plan
 cudaError_t kl_panel_ts_launch(const KlArgs& args, const KlPlan& plan, int NV, cudaStream_t stream);
+// second TS variant (kl_ts2.cu; NMFB_KL_TS=2, KP = 128): the quotient Q too, stored over S, as the A operand of MMA2
+cudaError_t kl_panel_ts2_launch(const KlArgs& args, const KlPlan& plan, int NV, cudaStream_t stream);
 
 // sums[c] = sum over the first L entries of master row c (fp64): `np.ones_like(x) @ h.T` (mur.py:26)
 // and `w.T @ np.ones_like(x)` (mur.py:42) collapse to these k-vectors.

@@ -287,10 +287,12 @@ def test_tmem_operand_objective_agrees_with_the_default_kernel(shape, exact):
 
 
 @first_run_pending
-@pytest.mark.parametrize("shape", [(768, 640, 100), (512, 2048, 24), (2000, 5000, 128)])
-def test_kl_pass_with_tmem_operand_agrees_with_the_default_kernel(shape, monkeypatch):
-    """NMFB_KL_TS=1 (kl_ts.cu: X as the TMEM-resident A operand of MMA1) against the default fused kernel and the
-    oracle: KP = 64 / 128, fused objective included, several work items per CTA at the last shape."""
+@pytest.mark.parametrize("variant,shape", [("1", (768, 640, 100)), ("1", (512, 2048, 24)), ("1", (2000, 5000, 128)),
+                                           ("2", (768, 640, 100)), ("2", (2000, 5000, 128))])
+def test_kl_pass_with_tmem_operand_agrees_with_the_default_kernel(variant, shape, monkeypatch):
+    """NMFB_KL_TS=1 (kl_ts.cu: X as the TMEM-resident A operand of MMA1) and =2 (kl_ts2.cu: the quotient too,
+    stored over S, as the A operand of MMA2; KP = 128) against the default fused kernel and the oracle: KP = 64 /
+    128, fused objective included, several work items per CTA at the last shape."""
     from oracle import nmf_oracle as orc
     from nmf_b200.mur import mur
     m, n, k = shape
@@ -299,7 +301,7 @@ def test_kl_pass_with_tmem_operand_agrees_with_the_default_kernel(shape, monkeyp
     kw = dict(distance_type="kl", min_iter=10**9, max_iter=6, w0=w0, h0=h0, verbose=False)
     monkeypatch.setenv("NMFB_KL_TS", "0")
     base = mur(v, k, **kw)
-    monkeypatch.setenv("NMFB_KL_TS", "1")
+    monkeypatch.setenv("NMFB_KL_TS", variant)
     res = mur(v, k, **kw)
     monkeypatch.setenv("NMFB_KL_TS", "0")
     assert rel_fro(res.w, base.w) < 1e-6 and rel_fro(res.h, base.h) < 1e-6

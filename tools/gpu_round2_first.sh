@@ -29,7 +29,7 @@ for ln in open('gpurun_out/bench_headline_$var.json'):
         print('  value', round(d['value'], 1), 'it/s  phase_ms', d.get('phase_ms'), ' objective_last', d.get('objective_last'))
 PY
 done
-for ts in 0 1; do
+for ts in 0 1 2; do
   NMFB_KL_TS=$ts timeout 900 python bench.py --workload mur_kl_20000x50000_k128 --steps 30 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_kl_ts$ts.json 2> gpurun_out/bench_kl_ts$ts.err
   echo "bench mur_kl NMFB_KL_TS=$ts exit $?" >> $S
   python - <<PY >> $S
@@ -52,5 +52,6 @@ full NMFB_RES_N256=1 mur_eu_65536x65536_k128 "residual_n256_kernel" 3 residual_n
 full NMFB_RES_TS=1 mur_eu_65536x65536_k128 "residual_ts_kernel" 3 residual_ts_r02
 full NMFB_KL_TS=0 mur_kl_20000x50000_k128 "kl_panel_kernel" 4 kl_panel_r02
 full NMFB_KL_TS=1 mur_kl_20000x50000_k128 "kl_panel_ts_kernel" 4 kl_panel_ts_r02
+full NMFB_KL_TS=2 mur_kl_20000x50000_k128 "kl_panel_ts2_kernel" 4 kl_panel_ts2_r02
 python tools/ncu_summary.py > gpurun_out/ncu_summary_r02.md 2>/dev/null
 cat $S
