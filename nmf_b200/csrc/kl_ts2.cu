@@ -326,7 +326,9 @@ kl_panel_ts2_kernel(const __grid_constant__ KlArgs args) {
                 // this lane quarter reads its S from, so the pair meets first (named barrier 1 + q, 64 threads).
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&d_empty[sb]);
+                tc_fence_before();                   // my tcgen05.ld of S before the other warp's tcgen05.st
                 asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+                tc_fence_after();
                 const uint32_t qaddr = tm_s + (static_cast<uint32_t>(q * 32) << 16) + sb * 64 + half * 16;
                 tmem_st16(qaddr, hi4);
                 tmem_st16(qaddr + 32, lo4);
