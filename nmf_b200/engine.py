@@ -31,6 +31,19 @@ def _key_to_float(key: int) -> float:
     return float(np.array([bits], dtype=np.uint32).view(np.float32)[0])
 
 
+def _sample_needs_lo_plane(v: np.ndarray) -> bool:
+    """True when a strided sample of the host V (<= 32 rows x <= 8192 columns) holds a value that one bf16
+    plane cannot represent exactly (NaN / inf count as such: the full pass reports them)."""
+    m, n = v.shape
+    rows = np.unique(np.linspace(0, m - 1, num=min(m, 32)).astype(np.int64))
+    a = v[rows][:, ::max(1, n // 8192)]
+    a32 = a.astype(np.float32, copy=False)
+    exact = (np.ascontiguousarray(a32).view(np.uint32) & np.uint32(0xFFFF)) == 0
+    if a.dtype != np.float32:
+        exact &= a32.astype(a.dtype) == a
+    return not bool(exact.all())
+
+
 class FactorBuffers:
     """master / cplanes / rplanes of one factor (layouts in include/nmf_b200.h)."""
 
@@ -261,9 +274,10 @@ class Engine:
         return _key_to_float(int(st[0])), bool(st[1]), bool(st[2])
 
     def _host_chunks(self, v: np.ndarray):
-        """Row chunks of the host V on the device.  When HBM has room for the whole fp32/fp64 V next to its
-        bf16 planes, the chunks of the first pass are kept for the later ones (absmax -> ingest, or the
-        repeat with a second plane): V crosses PCIe once per upload_data, not once per pass."""
+        """Row chunks of the host V on the device.  A fixed-point upload walks V twice (|max|, then the planes):
+        when HBM has room for the whole fp32/fp64 V next to its bf16 planes, the chunks of the first walk are kept
+        for the later ones, so V crosses PCIe once.  A floating upload is one walk (the plane count comes from a
+        host sample, _upload_passes) and keeps nothing."""
         cache = getattr(self, "_chunk_cache", None)
         if cache is not None and cache[0] is v:
             yield from cache[1]
@@ -374,7 +388,9 @@ class Engine:
             v = v.astype(np.float64)
         if not v.flags.c_contiguous:
             v = np.ascontiguousarray(v)
-        self._chunk_cache, self._keep_chunks = None, True
+        # device copies of the chunks are kept only where a second pass over V is certain (fixed-point ingest:
+        # |max| pass, then the planes); a floating upload is one pass (see _upload_passes)
+        self._chunk_cache, self._keep_chunks = None, bool(fixed)
         try:
             return self._upload_passes(v, planes, fixed)
         finally:
@@ -388,8 +404,13 @@ class Engine:
                     raise ValueError("data contains non-finite values")
                 self.vmin = vmin
                 return vmin
-        vmin, need_lo, bad = self._ingest_pass(v, planes or 1)
-        if need_lo and planes is None:
+        # How many bf16 planes V needs is decided by the ingest kernel over ALL of V; a small sample read on the host
+        # first lets the common cases take ONE pass over PCIe: a sample that is not bf16-exact goes straight to
+        # hi + lo planes, an exact one to the single plane (and only a V that is exact in the sample but not
+        # everywhere pays the second pass).
+        first = planes or (2 if _sample_needs_lo_plane(v) else 1)
+        vmin, need_lo, bad = self._ingest_pass(v, first)
+        if need_lo and planes is None and first == 1:
             vmin, need_lo, bad = self._ingest_pass(v, 2)
         if bad:
             raise ValueError("data contains non-finite values")

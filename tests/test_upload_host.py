@@ -61,11 +61,26 @@ def counting_transfers(monkeypatch):
 
 
 def _v(m=200, n=40):
+    """Not bf16-exact (values up to 7999): the host sample sends it straight to hi + lo planes."""
     return np.arange(m * n, dtype=np.float64).reshape(m, n)
 
 
+def _v_exact(m=200, n=40):
+    """Every value fits one bf16 plane."""
+    return (np.arange(m * n, dtype=np.float64) % 128).reshape(m, n)
+
+
+def _v_exact_in_the_sample_only(m=200, n=40):
+    """bf16-exact in every row the host sample reads, not in one row it skips."""
+    sampled = set(np.unique(np.linspace(0, m - 1, num=min(m, 32)).astype(np.int64)).tolist())
+    hidden = next(r for r in range(m) if r not in sampled)
+    v = _v_exact(m, n)
+    v[hidden, 3] = 1000.5
+    return v
+
+
 def test_single_plane_upload_is_one_pass_in_64_row_chunks(counting_transfers):
-    v = _v()
+    v = _v_exact()
     eng = HostOnlyEngine(200, 40, [(0.0, False, False)], 0)
     assert eng.upload_data(v) == 0.0 and eng.vmin == 0.0
     assert [e for e in eng.log if e[0] == "begin"] == [("begin", 1, False)]
@@ -76,23 +91,37 @@ def test_single_plane_upload_is_one_pass_in_64_row_chunks(counting_transfers):
     assert eng._chunk_cache is None and eng._keep_chunks is False      # nothing outlives the call
 
 
-def test_second_plane_pass_reuses_the_chunks_when_hbm_has_room(counting_transfers):
+def test_inexact_data_goes_straight_to_two_planes(counting_transfers):
+    """The host sample sees values one bf16 plane cannot hold: one pass with hi + lo planes, V crosses PCIe once."""
     v = _v()
+    eng = HostOnlyEngine(200, 40, [(1.0, False, False)], 0)
+    assert eng.upload_data(v) == 1.0
+    assert [e for e in eng.log if e[0] == "begin"] == [("begin", 2, False)]
+    assert counting_transfers["n"] == 4 and len(eng.seen) == 4
+
+
+def test_a_sample_that_misses_the_inexact_value_costs_a_second_pass(counting_transfers):
+    v = _v_exact_in_the_sample_only()
     eng = HostOnlyEngine(200, 40, [(1.0, True, False), (1.0, False, False)], 0)
     assert eng.upload_data(v) == 1.0
     assert [e for e in eng.log if e[0] == "begin"] == [("begin", 1, False), ("begin", 2, False)]
-    assert counting_transfers["n"] == 4                                  # not 8
-    first, second = eng.seen[:4], eng.seen[4:]
-    assert all(a[0] == b[0] and a[1] is b[1] for a, b in zip(first, second))
+    assert counting_transfers["n"] == 8                                  # floating uploads keep no device chunks
+    assert len(eng.seen) == 8 and [s[0] for s in eng.seen] == [0, 64, 128, 192] * 2
 
 
-def test_no_room_means_every_pass_transfers_again(counting_transfers):
+def test_explicit_plane_count_is_obeyed(counting_transfers):
+    eng = HostOnlyEngine(200, 40, [(1.0, True, False)], 0)
+    eng.upload_data(_v(), planes=1)                                      # caller insists on one (lossy) plane
+    assert [e for e in eng.log if e[0] == "begin"] == [("begin", 1, False)]
+
+
+def test_fixed_point_fallback_without_room_transfers_every_pass(counting_transfers):
     counting_transfers["free"] = 1 << 10
     v = _v()
-    eng = HostOnlyEngine(200, 40, [(1.0, True, False), (1.0, False, False)], 0)
-    eng.upload_data(v)
-    assert counting_transfers["n"] == 8
-    assert len(eng.seen) == 8 and [s[0] for s in eng.seen] == [0, 64, 128, 192] * 2
+    eng = HostOnlyEngine(200, 40, [(2.0, True, False), (2.0, False, False)], 0)
+    eng.upload_data(v, fixed=True)
+    # |max| pass + fixed ingest + the floating fallback (straight to two planes): three walks, nothing kept
+    assert counting_transfers["n"] == 12
 
 
 def test_fixed_point_upload_passes_and_fallback(counting_transfers):
@@ -103,11 +132,17 @@ def test_fixed_point_upload_passes_and_fallback(counting_transfers):
     kinds = [e[0] for e in eng.log]
     assert kinds == ["begin"] + ["absmax"] * 4 + ["ingest"] * 4 and eng.log[0] == ("begin", 2, True)
     assert counting_transfers["n"] == 4
-    # not exact: falls back to floating planes (1, then 2), still one transfer
+    # not exact: falls back to floating planes (the sample says two), still one transfer
     counting_transfers["n"] = 0
-    eng = HostOnlyEngine(200, 40, [(2.0, True, False), (2.0, True, False), (2.0, False, False)], 0)
+    eng = HostOnlyEngine(200, 40, [(2.0, True, False), (2.0, False, False)], 0)
     eng.upload_data(v, fixed=True)
-    assert [e for e in eng.log if e[0] == "begin"] == [("begin", 2, True), ("begin", 1, False), ("begin", 2, False)]
+    assert [e for e in eng.log if e[0] == "begin"] == [("begin", 2, True), ("begin", 2, False)]
+    assert eng.fixed is False and counting_transfers["n"] == 4
+    # same with data the sample finds exact: one floating plane
+    counting_transfers["n"] = 0
+    eng = HostOnlyEngine(200, 40, [(2.0, True, False), (2.0, False, False)], 0)
+    eng.upload_data(_v_exact(), fixed=True)
+    assert [e for e in eng.log if e[0] == "begin"] == [("begin", 2, True), ("begin", 1, False)]
     assert eng.fixed is False and counting_transfers["n"] == 4
 
 
