@@ -443,6 +443,11 @@ def run_b200(args):
         "peaks": peaks["source"],
     }
 
+    variants = {v: os.environ[v] for v in ("NMFB_RES_N256", "NMFB_RES_TS", "NMFB_KL_TS")
+                if os.environ.get(v, "0") not in ("", "0")}
+    if variants:                                             # opt-in experimental kernels
+        line["config"]["experimental_kernels"] = variants
+
     # ---- end to end through the public API with HOST buffers ----
     line["e2e"] = None
     _install_term_handler(line, rank)                        # a killed run still prints its device-timed line
