@@ -9,7 +9,7 @@
 //   2. MMA1 in the [d], [a_tmem], b_desc form.  Its N = 64 instructions fetched 4 KB of A + 2 KB of B per 32
 //      cycles from shared memory (192 B/cycle against a port of 128 B/cycle); now 2 KB (64 B/cycle).  Per 128 x 64
 //      tile the kernel moved 336 KB through the shared-memory port (MMA1 144, MMA2 96, Q stores 32, Y / D fills 48,
-//      D reads 16) = 2625 cycles at best -- the 1.39 ms of the H-side pass at 20000 x 50000 (827 tiles per SM at
+//      D reads 16) = 2690 cycles at best -- the 1.39 ms of the H-side pass at 20000 x 50000 (827 tiles per SM at
 //      1965 MHz) are ~3300 cycles per tile against 1536 cycles of MMA work: the default kernel runs at ~80 % of
 //      the port limit, not of the tensor pipe (profiles/r01e_smem_operand_model.md); this variant moves 240 KB.
 //   3. The 64 KB of shared memory X took go to the Y ring (4 stages).

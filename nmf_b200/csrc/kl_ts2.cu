@@ -11,7 +11,7 @@
 //      hi / lo planes of one warp land in columns the other one reads);
 //   3. Out^T: lanes = data rows, columns = components; the drain writes out[c][r] with the lanes along r.
 // Shared-memory port per 128 x 64 tile: MMA1 48 KB + MMA2 48 KB (B operands only) + Y / D fills 48 KB + D reads
-// 16 KB = 160 KB = 1250 cycles, below the 1536 cycles of MMA work (kl.cu: 336 KB = 2625 cycles).
+// 16 KB = 160 KB = 1280 cycles, below the 1536 cycles of MMA work (kl.cu: 336 KB = 2690 cycles).
 //
 #include "kernels.cuh"
 #include "kl.cuh"
