@@ -33,7 +33,7 @@ def _key_to_float(key: int) -> float:
 
 def _sample_needs_lo_plane(v: np.ndarray) -> bool:
     """True when a strided sample of the host V (<= 32 rows x <= 8192 columns) holds a value that one bf16
-    plane cannot represent exactly (NaN / inf count as such: the full pass reports them)."""
+    plane cannot represent exactly (non-finite values may fall either way: the full pass over V rejects them)."""
     m, n = v.shape
     rows = np.unique(np.linspace(0, m - 1, num=min(m, 32)).astype(np.int64))
     a = v[rows][:, ::max(1, n // 8192)]

@@ -157,3 +157,24 @@ def test_upload_rejects_bad_input(counting_transfers):
     eng = HostOnlyEngine(200, 40, [(0.0, False, False)], 0)
     eng.upload_data(np.asfortranarray(_v().astype(np.int64)))
     assert all(c.dtype == torch.float64 and c.is_contiguous() for _, c in eng.seen)
+
+
+def test_host_sample_for_the_plane_count():
+    """engine._sample_needs_lo_plane: bf16-exact data of either dtype -> one plane; anything one bf16 plane cannot
+    hold -> two (non-finite values may fall either way, the ingest pass rejects them); wide matrices are sampled
+    with a column stride, tiny ones entirely."""
+    from nmf_b200.engine import _sample_needs_lo_plane as needs_lo
+    from oracle import nmf_oracle as orc
+    exact = orc.planted(300, 200, 8, 0)                                  # float32 on the bf16 grid
+    assert not needs_lo(exact) and not needs_lo(exact.astype(np.float64))
+    assert needs_lo(np.random.default_rng(0).random((300, 200)))
+    assert needs_lo(np.random.default_rng(0).random((300, 200)).astype(np.float32))
+    assert needs_lo(np.full((5, 7), np.nan)) and needs_lo(np.full((5, 7), np.inf, dtype=np.float32)) is False
+    assert not needs_lo(np.zeros((1, 1)))
+    wide = np.zeros((4, 40000), dtype=np.float32)
+    wide[:, ::4] = 1.0 + 2.0 ** -12                                      # column stride 4 hits these
+    assert needs_lo(wide)
+    wide[:] = 0.0
+    wide[:, 1::4] = 1.0 + 2.0 ** -12                                     # ... and misses these: the kernel's verdict decides
+    assert not needs_lo(wide)
+    assert needs_lo(np.array([[1e-45]], dtype=np.float64))               # not representable in fp32 at all
