@@ -1,5 +1,5 @@
 #!/bin/bash
-# First gpurun call of round 2 (1 GPU, ~15 min): everything written after round 1's GPU budget was spent.
+# First gpurun call of round 2 (1 GPU, ~18 min): everything written after round 1's GPU budget was spent.
 #   1. pytest -m gpu with per-test outcomes (-rA): which first_run_pending tests XPASS / XFAIL
 #   2. experimental objective kernels (residual_n256.cu, residual_ts.cu): value + time against the default kernel
 #      at the headline and C2 shapes (tools/selftest.py), then the headline bench with NMFB_RES_N256=1 / NMFB_RES_TS=1
@@ -28,6 +28,19 @@ for ln in open('gpurun_out/bench_headline_$var.json'):
         d = json.loads(ln)
         print('  value', round(d['value'], 1), 'it/s  phase_ms', d.get('phase_ms'), ' objective_last', d.get('objective_last'))
 PY
+done
+for ts in 0 1; do   # ADMM / AO-ADMM objective reads two V planes (fixed-point ingest): residual_ts_kernel<2,2>
+  for w in admm_65536x16384_k128 ao_admm_65536x16384_k128; do
+    NMFB_RES_TS=$ts timeout 900 python bench.py --workload $w --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_${w}_ts$ts.json 2> gpurun_out/bench_${w}_ts$ts.err
+    echo "bench $w NMFB_RES_TS=$ts exit $?" >> $S
+    python - <<PY >> $S
+import json
+for ln in open('gpurun_out/bench_${w}_ts$ts.json'):
+    if ln.startswith('{'):
+        d = json.loads(ln)
+        print('  value', round(d['value'], 1), 'it/s  phase_ms', d.get('phase_ms'), ' objective_last', d.get('objective_last'))
+PY
+  done
 done
 for ts in 0 1 2; do
   NMFB_KL_TS=$ts timeout 900 python bench.py --workload mur_kl_20000x50000_k128 --steps 30 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_kl_ts$ts.json 2> gpurun_out/bench_kl_ts$ts.err
