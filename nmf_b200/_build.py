@@ -8,7 +8,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libnmf_b200.so")
-SOURCES = ["capi.cu", "panel_gemm.cu", "panel_gemm_exact.cu", "residual.cu", "residual_n256.cu", "residual_ts.cu", "elementwise.cu", "admm.cu", "kl.cu", "kl_ts.cu", "kl_ts2.cu"]
+SOURCES = ["capi.cu", "panel_gemm.cu", "panel_gemm_exact.cu", "residual_n256.cu", "residual_ts.cu", "elementwise.cu", "admm.cu", "kl.cu", "kl_ts.cu", "kl_ts2.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
@@ -17,11 +17,15 @@ NVCC_FLAGS = [
 ]
 
 
+class NvccMissing(RuntimeError):
+    """No compiler on this machine (the one build failure a prebuilt in-tree .so may stand in for)."""
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
             return cand
-    raise RuntimeError("nvcc not found: libnmf_b200.so cannot be built")
+    raise NvccMissing("nvcc not found: libnmf_b200.so cannot be built")
 
 
 def sources():
@@ -42,9 +46,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB_PATH
     nvcc = _nvcc()
-    objs = []
     build_dir = os.path.join(PKG_DIR, "build")
     os.makedirs(build_dir, exist_ok=True)
+    # one builder at a time (N torchrun ranks starting on a stale library): the others wait for the lock and
+    # then find the library fresh
+    import fcntl
+    with open(os.path.join(build_dir, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not is_stale():
+                return LIB_PATH
+            return _build_locked(nvcc, build_dir, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(nvcc: str, build_dir: str, verbose: bool) -> str:
+    objs = []
     procs = []
     for src in sources():
         obj = os.path.join(build_dir, os.path.basename(src)[:-3] + ".o")
@@ -59,7 +77,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError("nvcc failed: " + " ".join(cmd) + "\n" + out)
         if verbose and out:
             print(out)
-    tmp = LIB_PATH + ".tmp"
+    tmp = f"{LIB_PATH}.{os.getpid()}.tmp"
     link = [nvcc, "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(link, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:

@@ -111,9 +111,13 @@ def load(build_if_needed: bool = True):
     if build_if_needed and _build.is_stale():
         try:
             _build.build()
-        except Exception as exc:       # no nvcc on the box: use the prebuilt .so if there is one
+        except _build.NvccMissing as exc:       # no compiler on the box: the prebuilt .so stands in, loudly
             if not os.path.exists(path):
                 raise RuntimeError(f"libnmf_b200.so is missing and could not be built: {exc}") from exc
+            import warnings
+            warnings.warn("nmf_b200: sources are newer than libnmf_b200.so and there is no nvcc to rebuild it; "
+                          "using the prebuilt library", RuntimeWarning)
+        # compile and link errors propagate: a stale binary must never stand in for an edit that does not build
     if not os.path.exists(path):
         raise RuntimeError("libnmf_b200.so not found; run `python -c 'import __graft_entry__ as g; g.build()'`")
     lib = C.CDLL(path)

@@ -52,7 +52,7 @@ def admm(v, k, *, rho=1, distance_type='eu', reg_w=(0, 'nn'), reg_h=(0, 'l2n'), 
         eng.upload_data(v, fixed=(distance_type == 'eu'))     # kl: V is read by the objective and the v_aux step only
     if w0 is None or h0 is None:
         from .init import initial_factors
-        w0, h0 = initial_factors(v, k, nndsvd_init)
+        w0, h0 = initial_factors(v, k, nndsvd_init, engine=eng)
     eng.set_factors(np.asarray(w0), np.asarray(h0))
 
     stepper = make_stepper(eng, 'admm', distance_type, rho=rho, reg_w=reg_w, reg_h=reg_h)

@@ -143,13 +143,10 @@ cudaError_t chol_inverse_launch(const double* gram, int KP, int k, int rho_mode,
         chol_inverse_kernel<64><<<1, 1024, sm, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
     } else if (KP == 128) {
         const size_t sm = 128 * 129 * sizeof(double);
-        static bool set = false;
-        if (!set) {
-            e = cudaFuncSetAttribute(chol_inverse_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(sm));
-            if (e != cudaSuccess) return e;
-            set = true;
-        }
+        // per device, not per process: set on every launch (a host-side table write, no device work)
+        e = cudaFuncSetAttribute(chol_inverse_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(sm));
+        if (e != cudaSuccess) return e;
         chol_inverse_kernel<128><<<1, 1024, sm, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
     } else {
         chol_inverse_kernel<256><<<1, 1024, 0, stream>>>(gram, k, rho_mode, rho_in, gscratch, ainv, rho_out, flags);
@@ -466,8 +463,7 @@ admm_apply_l2n_kernel(const AdmmApplyArgs p) {
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
     const int grid = (a.nrows_p > 0 ? a.nrows_p : a.Lp) / 64;
     const size_t smem = (static_cast<size_t>(a.KP) * 64 + 32 * static_cast<size_t>(a.KP)) * sizeof(double);
-    static bool set[3] = {false, false, false};
-    cudaError_t e = cudaSuccess;
+    cudaError_t e = cudaSuccess;        // the opt-in attribute is per device: set on every launch
     if (a.binv != nullptr) {                      // prox l2n: the two-product kernel, k <= 128
         void (*fn)(const AdmmApplyArgs) = nullptr;
         if (a.KP == 64)       fn = admm_apply_l2n_kernel<4>;
@@ -480,13 +476,16 @@ cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
         return cudaGetLastError();
     }
     if (a.KP == 64) {
-        if (!set[0]) { e = cudaFuncSetAttribute(admm_apply_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); set[0] = true; }
+        e = cudaFuncSetAttribute(admm_apply_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e != cudaSuccess) return e;
         admm_apply_kernel<4><<<grid, 256, smem, stream>>>(a);
     } else if (a.KP == 128) {
-        if (!set[1]) { e = cudaFuncSetAttribute(admm_apply_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024); set[1] = true; }
+        e = cudaFuncSetAttribute(admm_apply_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+        if (e != cudaSuccess) return e;
         admm_apply_kernel<8><<<grid, 256, smem, stream>>>(a);
     } else {
-        if (!set[2]) { e = cudaFuncSetAttribute(admm_apply_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); set[2] = true; }
+        e = cudaFuncSetAttribute(admm_apply_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
         admm_apply_kernel<16><<<grid, 256, smem, stream>>>(a);
     }
     if (e != cudaSuccess) return e;

@@ -346,28 +346,21 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
     const nmfb_data* v = &p->v_rows;            // the rows of V this rank holds == the window of W
     const Window ww = window_of(&p->w);
     int nparts = 0;
-    // impl 2 = wide-tile variant (residual_n256.cu: opt-in, also through NMFB_RES_N256=1 for the objectives the
-    // solver steps enqueue themselves); KP = 64 / 128 with a single V plane only
-    bool wide = impl == 2;
-    if (impl == 0) {
-        const char* e = getenv("NMFB_RES_N256");
-        wide = e && atoi(e) == 1 && residual_n256_smem_bytes(p->KP, v->nv) > 0;
-    }
+    // impl 0 = the product's choice: wide tiles (residual_n256.cu) for KP <= 128 with one V plane, the TS form
+    // (residual_ts.cu) for everything else it fits, the CUDA-core kernel as the last resort.  impl 1 / 2 / 3 force
+    // the CUDA-core / wide / TS kernel (cross-checks in the tests).
+    bool wide = impl == 2, ts = impl == 3;
     if (wide && residual_n256_smem_bytes(p->KP, v->nv) < 0)
         return fail(NMFB_ERR_ARG, "objective: the wide-tile kernel needs KP = 64 or 128 and one V plane (KP=%d nv=%d)",
                     p->KP, v->nv);
-    if (wide) impl = 0;
-    // impl 3 = TS variant (residual_ts.cu: W planes as the TMEM-resident A operand; opt-in, NMFB_RES_TS=1)
-    bool ts = impl == 3;
-    if (impl == 0 && !wide) {
-        const char* e = getenv("NMFB_RES_TS");
-        ts = e && atoi(e) == 1 && residual_ts_smem_bytes(p->KP, v->nv) > 0;
-    }
     if (ts && residual_ts_smem_bytes(p->KP, v->nv) < 0)
         return fail(NMFB_ERR_ARG, "objective: the TS kernel does not fit KP=%d nv=%d", p->KP, v->nv);
-    if (ts) impl = 0;
+    if (impl == 0) {
+        wide = residual_n256_smem_bytes(p->KP, v->nv) > 0;
+        ts = !wide && residual_ts_smem_bytes(p->KP, v->nv) > 0;
+        if (!wide && !ts) impl = 1;
+    }
     const int BN = wide ? 256 : 128;
-    if (impl == 0 && !wide && !ts && residual_smem_bytes(p->KP, v->nv, 128) < 0) impl = 1;
     if (impl == 1) {
         const long need = static_cast<long>((v->rows + 63) / 64) * ((p->n + 63) / 64);
         if (need > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
@@ -379,9 +372,7 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         memset(&a, 0, sizeof(a));
         a.mtiles = (v->rows + 127) / 128;
         a.ntiles = (p->n + BN - 1) / BN;
-        int cs = 2;
-        if (const char* e = getenv("NMFB_RES_CLUSTER")) cs = atoi(e);
-        if (cs != 1 && cs != 2 && cs != 4) cs = 1;
+        int cs = 2;                                   // H^T stages are multicast across a CTA pair
         while (cs > 1 && a.mtiles < 2 * cs) cs >>= 1;
         a.cluster = cs;
         for (int q = 0; q < 2; ++q) {
@@ -409,9 +400,8 @@ int objective_common(const nmfb_problem* p, int impl, int kl, double* obj_out, v
         const int grid = ncl * cs;
         if (grid > p->obj_partial_len) return fail(NMFB_ERR_WORKSPACE, "objective: obj_partial too small");
         nparts = grid;
-        if (wide)    { CUDA_TRY(residual_n256_launch(a, grid, st(stream))); }
-        else if (ts) { CUDA_TRY(residual_ts_launch(a, grid, st(stream))); }
-        else         { CUDA_TRY(residual_launch(a, grid, st(stream))); }
+        if (wide) { CUDA_TRY(residual_n256_launch(a, grid, st(stream))); }
+        else      { CUDA_TRY(residual_ts_launch(a, grid, st(stream))); }
     }
     CUDA_TRY(sum_partials_launch(p->obj_partial, nparts, kl ? 1.0 : 0.5, obj_out, st(stream)));
     return 0;
@@ -423,7 +413,7 @@ int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* st
 }
 
 int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
-    if (p && residual_smem_bytes(p->KP, p->v_rows.nv, 128) < 0)
+    if (p && residual_n256_smem_bytes(p->KP, p->v_rows.nv) < 0 && residual_ts_smem_bytes(p->KP, p->v_rows.nv) < 0)
         return fail(NMFB_ERR_ARG, "objective_kl: unsupported shape");
     return objective_common(p, 0, 1, obj_out, stream);
 }

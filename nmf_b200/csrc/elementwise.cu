@@ -328,13 +328,13 @@ cudaError_t mur_eu_update_launch(const float* part, int slots, const float* gram
         mur_eu_update_kernel<4><<<grid, 256, smem, stream>>>(part, slots, gram, master, cpl, cpl_plane, rpl,
                                                              rpl_plane, k, L, Lp, lambda);
     } else if (KP == 128) {
-        static bool set = false;
-        if (!set) { e = cudaFuncSetAttribute(mur_eu_update_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); set = true; }
+        e = cudaFuncSetAttribute(mur_eu_update_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        if (e != cudaSuccess) return e;
         mur_eu_update_kernel<8><<<grid, 256, smem, stream>>>(part, slots, gram, master, cpl, cpl_plane, rpl,
                                                              rpl_plane, k, L, Lp, lambda);
     } else {
-        static bool set = false;
-        if (!set) { e = cudaFuncSetAttribute(mur_eu_update_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024); set = true; }
+        e = cudaFuncSetAttribute(mur_eu_update_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        if (e != cudaSuccess) return e;
         mur_eu_update_kernel<16><<<grid, 256, smem, stream>>>(part, slots, gram, master, cpl, cpl_plane, rpl,
                                                               rpl_plane, k, L, Lp, lambda);
     }

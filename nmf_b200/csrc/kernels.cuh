@@ -50,7 +50,7 @@ cudaError_t panel_gemm_launch(const PanelGemmArgs& args, const PanelGemmPlan& pl
 int panel_gemm_exact_plan(int KP, int NA, int L, int R, int blocked, int num_sms, PanelGemmPlan* plan);
 cudaError_t panel_gemm_exact_launch(const PanelGemmArgs& args, const PanelGemmPlan& plan, cudaStream_t stream);
 
-// ------------------------------------------------------------------ residual objective (residual.cu)
+// ------------------------------------------------------------------ residual objective (residual_n256.cu, residual_ts.cu)
 struct alignas(64) ResidualArgs {
     CUtensorMap wr[2];       // W row-major planes [Mp][KP], box {64, 128}
     CUtensorMap hr[2];       // H^T row-major planes [Np][KP], box {64, BN}
@@ -62,15 +62,13 @@ struct alignas(64) ResidualArgs {
     int kl;                  // 0: sum (v-s)^2 ; 1: generalised KL terms
     int v_rows_p;            // rows per K-block of the blocked V planes
     int cluster;             // CTAs per cluster (H^T stages are multicast across it)
-    const __nv_bfloat16* w_rpl[2];   // TS variant only: the W row planes [rows][KP] themselves (same base as wr[])
+    const __nv_bfloat16* w_rpl[2];   // TS form only: the W row planes [rows][KP] themselves (same base as wr[])
 };
-cudaError_t residual_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
-int residual_smem_bytes(int KP, int NV, int BN);
 int residual_max_clusters(int cs, int num_sms);
-// wide-tile variant (residual_n256.cu; opt-in): 128 x 256 tiles, args.BN == 256, args.ntiles in 256-column tiles
+// wide tiles (residual_n256.cu): 128 x 256 tiles, args.BN == 256, args.ntiles in 256-column tiles; KP <= 128, one V plane
 cudaError_t residual_n256_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_n256_smem_bytes(int KP, int NV);
-// TS variant (residual_ts.cu; opt-in): W planes of the tile row as the TMEM-resident A operand, args.BN == 128
+// TS form (residual_ts.cu): W planes of the tile row as the TMEM-resident A operand, args.BN == 128; every KP, 1-2 V planes
 cudaError_t residual_ts_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_ts_smem_bytes(int KP, int NV);
 

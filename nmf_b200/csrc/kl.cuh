@@ -13,7 +13,7 @@ struct alignas(64) KlArgs {
     int KP, Lp;
     int npanels, ntiles, nsplit, tiles_per_split;
     int d_rows_p;
-    const __nv_bfloat16* x_rpl[2];   // TS variant only: the row planes of X themselves (same base as xr[])
+    const __nv_bfloat16* x_rpl[2];   // the row planes of X themselves (same base as xr[])
 };
 
 struct KlPlan {
@@ -21,11 +21,10 @@ struct KlPlan {
 };
 
 int kl_plan(int KP, int NV, int R, int T, int num_sms, KlPlan* plan);
-int kl_smem_bytes(int KP, int NV);
 cudaError_t kl_panel_launch(const KlArgs& args, const KlPlan& plan, int NV, int num_sms, cudaStream_t stream);
-// TS variant (kl_ts.cu; opt-in through NMFB_KL_TS=1): X as the TMEM-resident A operand of MMA1; same plan
+// kl_ts.cu (KP = 64): X as the TMEM-resident A operand of MMA1
 cudaError_t kl_panel_ts_launch(const KlArgs& args, const KlPlan& plan, int NV, cudaStream_t stream);
-// second TS variant (kl_ts2.cu; NMFB_KL_TS=2, KP = 128): the quotient Q too, stored over S, as the A operand of MMA2
+// kl_ts2.cu (KP = 128): the quotient Q too, stored over S, as the A operand of MMA2
 cudaError_t kl_panel_ts2_launch(const KlArgs& args, const KlPlan& plan, int NV, cudaStream_t stream);
 
 // sums[c] = sum over the first L entries of master row c (fp64): `np.ones_like(x) @ h.T` (mur.py:26)

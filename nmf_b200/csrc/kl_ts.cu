@@ -1,8 +1,8 @@
 // Fused GEMM -> quotient -> GEMM kernel of the Kullback-Leibler updates, "TS" variant: the factor being updated
 // (X, the resident 128-row panel) lives in TENSOR MEMORY and is the A operand of MMA1 (S = X . Y^T).
 //
-// STATUS: opt-in (NMFB_KL_TS=1).  Written after the GPU budget of round 1 was spent: compiled for sm_100a, NOT
-// yet executed on a B200.  The default stays kl_panel_kernel (kl.cu), of which the kernel below is a copy with:
+// STATUS: the KP = 64 kernel of the product (KP = 128 takes kl_ts2.cu).  Parity on B200: GPUTEST_r01, round-2 A/B in
+// profiles/r02a_*.  Relative to the SS-form kernel of round 1 (deleted):
 //   1. TMEM: S buffers 2 x 64 columns, Out buffers 2 x 128, and -- new -- the X planes in the last 128 columns
 //      (128 lanes = rows of the panel, two bf16 K-values per column, hi then lo, KP / 2 columns each).  The eight
 //      epilogue warps store them with tcgen05.st at the start of every work item, gated by x_empty / x_full.

@@ -3,8 +3,8 @@
 // the quotient Q as the A operand of MMA2, written by the epilogue warps over the S tile they have just read
 // (FlashAttention-4's P over S).  MMA2 therefore computes the transpose, Out^T[r][c] += Q[r][t] . Y[t][c].
 //
-// STATUS: opt-in (NMFB_KL_TS=2, KP = 128 only).  Written after the GPU budget of round 1 was spent: compiled for
-// sm_100a, NOT yet executed on a B200.  Differences from kl_ts.cu:
+// STATUS: the KP = 128 kernel of the product (304 it/s at 20000 x 50000 against 256 for the SS-form kernel of round 1,
+// profiles/r02a_*).  Differences from kl_ts.cu:
 //   1. no Q buffer in shared memory, no q_empty barrier; q_full[2] (one per S buffer, eight arrivals);
 //      s_empty[b] is committed by the MMA2 issuer (Q in buffer b has been read), not by the epilogue;
 //   2. the two epilogue warps of a lane quarter meet at a named barrier between reading S and storing Q (the

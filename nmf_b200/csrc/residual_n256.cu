@@ -1,17 +1,18 @@
 // Residual-form objective, wide-tile variant: 128 x 256 tiles, i.e. tcgen05.mma with N = 256.
 //
-// STATUS: opt-in (impl = 2 of nmfb_objective_eu, or NMFB_RES_N256=1 for every objective the library enqueues).
-// Written after the GPU budget of round 1 was spent: compiled for sm_100a, NOT yet executed on a B200.  The
-// default objective kernel stays residual_kernel (residual.cu); nothing selects this file unless asked to.
+// STATUS: the objective kernel of the product for KP <= 128 with one V plane (MUR-eu / MUR-KL on bf16-exact data);
+// everything else takes residual_ts.cu.  Round-2 A/B at 65536^2 k=128: 2.86 ms against 3.10 ms for the 128 x 128
+// SS-form kernel of round 1 (deleted) and 2.95 ms for the TS form; ncu: tensor pipe 84.6 % active at the 1.36 GHz
+// the power cap leaves, i.e. the kernel sits at the power-limited MMA rate (profiles/r02a_ncu_full_variants.md).
 //
-// Why: the ncu capture of residual_kernel<2,1> (profiles/r01b_all_paths.md) shows l1tex throughput 48.6 % at
+// Why: the ncu capture of the round-1 kernel residual_kernel<2,1> (profiles/r01b_all_paths.md) shows l1tex throughput 48.6 % at
 // 49.3 % tensor-pipe activity, and the panel GEMM (N = 256 MMAs) 62-66 % at 85 %.  Both ratios are what the
 // operand fetch of an SS-mode MMA predicts: an M = 128, N = 128, K = 16 instruction reads 4 KB of A and 4 KB of B
 // from shared memory per 64 cycles = 128 B/cycle, the whole shared-memory bandwidth of an SM, so that kernel can
 // never run its tensor pipe much above ~75 % (TMA fills and the epilogue's V reads need the same port); with
 // N = 256 it is 4 + 8 KB per 128 cycles = 96 B/cycle.  The wide tile also halves the number of MMA instructions
 // per FLOP (128-cycle MMAs against ~50 issue cycles each), so ONE issuing warp is enough and the dispatcher /
-// second-issuer hand-off of residual.cu is not needed.
+// second-issuer hand-off of the 128 x 128 kernels (residual_ts.cu) is not needed.
 //
 // Shared memory (KP = 128): W planes of the tile row 64 KB + two H^T stages of 64 KB ([256 rows x 64] x 2 planes)
 // + two 16 KB V boxes = 224 KB.  V therefore streams through ONE [128 x 64] box per column half (the four

@@ -1,9 +1,19 @@
-// Residual-form objective, "TS" variant: the resident operand (the W planes of the tile row) lives in TENSOR
-// MEMORY and is the A operand of tcgen05.mma; only the streamed H^T stages are read from shared memory.
+// Residual-form objective on tcgen05:  sum_{i,j} f(V_ij, S_ij),  S = W.H formed tile by tile in TMEM and never
+// written to HBM.
+//   mode 0 (eu):  f = (v - s)^2                         -> 0.5 * sum = utils.py:29
+//   mode 1 (kl):  f = v*log(v/s) - v + s  (+inf/NaN of the log term -> 0, utils.py:23-26)
+// S needs fp32-grade accuracy because the residual is ~1e-4 of |V| on low-rank data (the trace form
+// ||V||^2 - 2<W^T V,H> + <W^T W,H H^T> cancels catastrophically), so each 128x128 tile is three bf16 MMA chains:
+// Whi.Hhi + Whi.Hlo + Wlo.Hhi.
 //
-// STATUS: opt-in (impl = 3 of nmfb_objective_eu, or NMFB_RES_TS=1).  Written after the GPU budget of round 1
-// was spent: compiled for sm_100a, NOT yet executed on a B200.  The default stays residual_kernel (residual.cu),
-// of which this file is a copy with three changes:
+// "TS" form: the resident operand (the W planes of the tile row) lives in TENSOR MEMORY and is the A operand of
+// tcgen05.mma; only the streamed H^T stages are read from shared memory.  This kernel serves every shape the
+// wide-tile kernel (residual_n256.cu) does not: KP = 256, two V planes (hi + lo, or the fixed-point planes of
+// ADMM / AO-ADMM).  Round-2 A/B at 65536^2 k=128 (profiles/r02a_*): SS-form 128x128 kernel 3.10 ms (deleted),
+// this kernel 2.95 ms, wide tiles 2.86 ms; ADMM objective (two V planes) 1.07 -> 0.97 ms.
+// One CTA walks a contiguous run of 128x128 tiles in row-major tile order; warp 0 = TMA producer of the H^T
+// stages, warps 1 and 11 = MMA issuers (even / odd tiles, one TMEM accumulator each), warps 2..9 = epilogue
+// warps, warp 10 = TMA producer of the V tiles.  Relative to a plain SS-form tile loop:
 //   1. TMEM holds two 128-column S accumulators (columns 0..255) AND the W planes (columns 256..): 128 lanes =
 //      the 128 rows of the tile, two bf16 K-values per 32-bit column, hi plane then lo plane, KP/2 columns each
 //      (KP = 256: 2 x 128 columns, 512 in all).  The eight epilogue warps write them with tcgen05.st at the first
@@ -15,8 +25,6 @@
 //      profiles/r01e_smem_operand_model.md derives from the r01b captures.
 //   3. The 64 KB of shared memory the W planes used to take go to the H^T ring (4 stages at every KP).
 //
-// Everything else -- tile order, clusters with multicast H^T stages, the dispatcher / second issuer, the V
-// producer, the epilogue arithmetic -- is residual.cu's.
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -391,6 +399,31 @@ residual_ts_kernel(const __grid_constant__ ResidualArgs args) {
         for (int w = 0; w < 8; ++w) t += red[w];
         args.partial[blockIdx.x] = t;
     }
+}
+
+// Resident clusters of `cs` CTAs for this kernel (one CTA per SM); cached per cluster size.
+int residual_max_clusters(int cs, int num_sms) {
+    static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (cs == 1) return num_sms;
+    if (cache[cs] > 0) return cache[cs];
+    void (*fn)(const ResidualArgs) = residual_ts_kernel<2, 1>;
+    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(num_sms / cs * cs);
+    cfg.blockDim = dim3(kThreadsT);
+    cfg.dynamicSmemBytes = 200 * 1024;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = num_sms / cs * 3 / 4;
+    }
+    if (n > num_sms / cs) n = num_sms / cs;
+    cache[cs] = n;
+    return n;
 }
 
 cudaError_t residual_ts_launch(const ResidualArgs& args, int grid, cudaStream_t stream) {

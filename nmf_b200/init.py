@@ -6,7 +6,22 @@ from __future__ import annotations
 import numpy as np
 
 
-def initial_factors(x, k, nndsvd_init=(False, 'zero')):
+def initial_factors(x, k, nndsvd_init=(False, 'zero'), engine=None):
+    """engine: the Engine of a sharded run (world > 1).  Rank 0 alone then draws from its global RNG (or runs
+    NNDSVD) and the result is broadcast, so that every rank starts from the SAME replicated factors whatever
+    the other ranks' RNG states are -- the start of a sharded run equals that of the single-GPU run seeded
+    like rank 0."""
+    m, n = x.shape
+    if engine is not None and getattr(engine, "world", 1) > 1:
+        from .sharding import broadcast_from_rank0
+        pair = _draw(x, k, nndsvd_init) if engine.rank == 0 else (None, None)
+        w = broadcast_from_rank0(pair[0], (m, k), engine.device, engine.group)
+        h = broadcast_from_rank0(pair[1], (k, n), engine.device, engine.group)
+        return w, h
+    return _draw(x, k, nndsvd_init)
+
+
+def _draw(x, k, nndsvd_init):
     m, n = x.shape
     if nndsvd_init[0]:
         return nndsvd(x, k, nndsvd_init[1])

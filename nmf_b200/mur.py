@@ -49,7 +49,7 @@ def mur(x, k, *, distance_type='kl', min_iter=100, max_iter=100000, tol1=1e-5, t
 
     if w0 is None or h0 is None:
         from .init import initial_factors
-        w0, h0 = initial_factors(x, k, nndsvd_init)
+        w0, h0 = initial_factors(x, k, nndsvd_init, engine=eng)
     eng.set_factors(np.asarray(w0), np.asarray(h0))
 
     stepper = make_stepper(eng, 'mur', distance_type, lambda_w=lambda_w, lambda_h=lambda_h)

@@ -61,6 +61,21 @@ def allgather_flat(full: torch.Tensor, mine: torch.Tensor, group=None) -> None:
         full.copy_(torch.cat(parts))
 
 
+def broadcast_from_rank0(arr, shape, device, group=None):
+    """fp64 host array of `shape`, the one rank 0 passes (the others pass None), on every rank.  The transfer
+    runs on `device` tensors (NCCL needs CUDA memory, gloo takes the CPU)."""
+    import numpy as np
+    rank = dist.get_rank(group)
+    src = dist.get_global_rank(group, 0) if group is not None else 0
+    if rank == 0:
+        t = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64)).to(device)
+        assert tuple(t.shape) == tuple(shape)
+    else:
+        t = torch.empty(tuple(shape), dtype=torch.float64, device=device)
+    dist.broadcast(t, src=src, group=group)
+    return t.cpu().numpy()
+
+
 def allreduce_sum_(t: torch.Tensor, group=None) -> None:
     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
 

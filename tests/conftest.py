@@ -40,4 +40,13 @@ def rel_fro(a, b):
     return float(np.linalg.norm(np.asarray(a, np.float64) - b) / np.linalg.norm(b))
 
 
-GOLDEN_NAMES = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+def golden_subset(length, stride):
+    """Lines of a factor frozen in the mid_* / full_* goldens (tests/golden/make_golden_mid.py)."""
+    return np.union1d(np.arange(0, length, stride), np.arange(max(0, length - 256), length))
+
+
+_ALL = sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+# SURVEY 8d sizes (make_golden_mid.py: obj_history + a row / column subset of the final factors)
+MID_GOLDEN_NAMES = [nm for nm in _ALL if nm.startswith("mid_")]
+FULL_GOLDEN_NAMES = [nm for nm in _ALL if nm.startswith("full_")]
+GOLDEN_NAMES = [nm for nm in _ALL if nm not in MID_GOLDEN_NAMES and nm not in FULL_GOLDEN_NAMES]

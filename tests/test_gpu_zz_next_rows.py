@@ -1,8 +1,7 @@
 """GPU parity of the SURVEY.md 8(f) "next" rows -- the l2n (Tikhonov) prox with lambda > 0 (admm.py:141-156),
 the Kullback-Leibler branch of admm / ao_admm --, of BASELINE.json's full-size configurations through
 size-independent properties, and of edge cases (zeros in V, one component, odd shapes, input dtypes).
-Kept in a file that sorts last: all of it was written after the GPU budget of round 1 was spent and has
-not run on a B200 yet, so a failure here must not hide the results of the section 8(a)-(e) tests.
+All of it passed on the driver's B200 at the end of round 1 (GPUTEST_r01.json); no test here may fail silently.
 (The checkpoint / resume test lives in test_gpu_mur.py: it only adds host logic to validated kernels.)"""
 import contextlib
 import io
@@ -15,13 +14,8 @@ from conftest import golden_v, load_golden, rel_fro
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-4
-# The l2n kernel has compiled for sm_100a but never executed (see the module docstring): until its first GPU
-# run it may fail without turning the suite red; a pass shows up as XPASS.
-first_run_pending = pytest.mark.xfail(reason="written after the round-1 GPU budget was spent; first B200 run pending",
-                                      strict=False)
 
 
-@first_run_pending
 def test_admm_l2n_matches_reference_golden():
     """Both factors with the l2n prox, through NMF.factorize, against the frozen reference run."""
     from nmf_b200 import NMF
@@ -40,7 +34,6 @@ def test_admm_l2n_matches_reference_golden():
     assert res.experiment.prox_h == "l2n" and res.experiment.lambda_h == 0.5
 
 
-@first_run_pending
 @pytest.mark.parametrize("method", ["admm", "ao_admm"])
 def test_l2n_trajectory_vs_oracle_k64(method):
     """k = 64 (KP = 64 kernel variant) and, for AO-ADMM, the data-dependent rho = tr(G)/k in the
@@ -81,7 +74,6 @@ def _full_size_engine(m, n, k):
     return eng
 
 
-@first_run_pending
 def test_c2_mur_eu_full_size_is_monotone_and_non_negative():
     """configs[1]: 32768 x 32768, k = 64."""
     import torch
@@ -100,7 +92,6 @@ def test_c2_mur_eu_full_size_is_monotone_and_non_negative():
     eng.release()
 
 
-@first_run_pending
 def test_c3_mur_kl_full_size_is_monotone_and_objectives_agree():
     """configs[2]: 20000 x 50000, k = 128; the objective that falls out of the W pass (lagged) must equal
     the stand-alone objective kernel's value for the same pair."""
@@ -122,7 +113,7 @@ def test_c3_mur_kl_full_size_is_monotone_and_objectives_agree():
 
 
 # ----------------------------------------------------------------------------------------------
-# Edge cases (written after the GPU budget of round 1 was spent, hence `first_run_pending`): exact zeros
+# Edge cases: exact zeros
 # in V with an all-zero row and column (the 0*log(0/x) and x/0 rules of utils.py:23-26), a single
 # component, the 'mean' / 'random' NNDSVD fills (utils.py:84-91), k = 200 (the KP = 256 kernels, C5's
 # width), very flat / very tall V, and the input dtypes / memory orders NumPy callers hand over.
@@ -131,7 +122,6 @@ EDGE_GOLDENS = ["mur_kl_zeros", "mur_eu_zeros", "mur_eu_k1", "mur_kl_k1", "admm_
                 "ao_admm_nndsvd_random"]
 
 
-@first_run_pending
 @pytest.mark.parametrize("name", EDGE_GOLDENS)
 def test_edge_case_matches_reference_golden(name):
     from nmf_b200 import NMF
@@ -152,7 +142,6 @@ def test_edge_case_matches_reference_golden(name):
         assert np.all(res.w[3] == 0) and np.all(res.h[:, 5] == 0)
 
 
-@first_run_pending
 @pytest.mark.parametrize("shape", [(640, 520, 200), (4096, 70, 8), (70, 4096, 8), (5, 7, 2)])
 def test_mur_eu_shapes_vs_oracle(shape):
     """k = 200 runs the KP = 256 variants of every kernel; the flat / tall cases have a single 128-row
@@ -169,7 +158,6 @@ def test_mur_eu_shapes_vs_oracle(shape):
     assert obj_err < TOL and rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
 
 
-@first_run_pending
 def test_input_dtype_and_memory_order_do_not_matter():
     """fp32, Fortran-ordered and integer-valued V give the factors of the same V in C-ordered fp64."""
     from oracle import nmf_oracle as orc
@@ -187,9 +175,8 @@ def test_input_dtype_and_memory_order_do_not_matter():
 
 # ----------------------------------------------------------------------------------------------
 # Kullback-Leibler branch of admm (admm.py:303-315) and ao_admm (ao_admm.py:71-101,
-# 272-285), single GPU.  Written after the GPU budget of round 1 was spent: first run pending.
+# 272-285), single GPU.
 # ----------------------------------------------------------------------------------------------
-@first_run_pending
 @pytest.mark.parametrize("name", ["admm_kl", "ao_admm_kl"])
 def test_kl_branch_matches_reference_golden(name):
     from nmf_b200 import NMF
@@ -213,7 +200,6 @@ def test_kl_branch_matches_reference_golden(name):
         assert len(ao_admm.last_inner_iterations) == res.i + 1
 
 
-@first_run_pending
 @pytest.mark.parametrize("method", ["admm", "ao_admm"])
 def test_kl_branch_trajectory_vs_oracle_k64(method):
     from oracle import nmf_oracle as orc
@@ -239,11 +225,9 @@ def test_kl_branch_trajectory_vs_oracle_k64(method):
 
 
 # ----------------------------------------------------------------------------------------------
-# Experimental objective kernels, opt-in through `impl` (or NMFB_RES_N256=1 / NMFB_RES_TS=1):
-#   impl 2 = residual_n256.cu (128 x 256 tiles, N = 256 MMAs), impl 3 = residual_ts.cu (W planes as the TMEM-resident
-#   A operand).  LAST in the file on purpose: neither has ever executed, and a faulting tcgen05 kernel poisons the
-#   CUDA context of the process for every test after it (impl 2 first: it uses only instruction forms that the
-#   validated kernels use).
+# The two tcgen05 objective kernels against the CUDA-core kernel (impl 1) and the fp64 value:
+#   impl 2 = residual_n256.cu (128 x 256 tiles; the product's choice for KP <= 128 with one V plane),
+#   impl 3 = residual_ts.cu (W planes as the TMEM-resident A operand; every other shape), impl 0 = the product's choice.
 # ----------------------------------------------------------------------------------------------
 def _objective_variant_agrees(impl, m, n, k, exact_data=True):
     from oracle import nmf_oracle as orc
@@ -257,54 +241,45 @@ def _objective_variant_agrees(impl, m, n, k, exact_data=True):
     eng.upload_data(np.asarray(v))
     assert eng.nv == (1 if exact_data else 2)
     eng.set_factors(w0, h0)
-    eng.objective_eu(slot=0, impl=0)
+    eng.objective_eu(slot=0, impl=1)
     eng.objective_eu(slot=1, impl=impl)
     eng.objective_eu(slot=2, impl=impl)                      # a second launch: barriers / TMEM left clean
-    a, b, c = eng.read_scalar(0), eng.read_scalar(1), eng.read_scalar(2)
+    eng.objective_eu(slot=3, impl=0)
+    a, b, c, d = (eng.read_scalar(i) for i in range(4))
     want = orc.objective(np.asarray(v, np.float64), w0.astype(np.float32).astype(np.float64)
                          @ h0.astype(np.float32).astype(np.float64))
     eng.release()
     assert b == c
-    assert abs(b - a) / a < 1e-6 and abs(b - want) / want < 1e-5
+    assert abs(b - a) / a < 1e-5 and abs(b - want) / want < 1e-5 and abs(d - want) / want < 1e-5
 
 
-@first_run_pending
 @pytest.mark.parametrize("shape", [(1024, 1536, 128), (900, 1100, 48), (2304, 700, 100), (128, 256, 64),
                                    (4096, 8192, 128)])
-def test_wide_tile_objective_agrees_with_the_default_kernel(shape):
-    """impl 2 against impl 0 (validated, r01c) and against the fp64 value: full and ragged tiles on both axes,
-    a single tile, KP = 64 and 128, enough tiles for every CTA to walk several rows of tiles."""
+def test_wide_tile_objective_agrees_with_the_cuda_core_kernel(shape):
+    """Full and ragged tiles on both axes, a single tile, KP = 64 and 128, enough tiles for every CTA to walk
+    several rows of tiles."""
     _objective_variant_agrees(2, *shape)
 
 
-@first_run_pending
 @pytest.mark.parametrize("shape,exact", [((1024, 1536, 128), True), ((900, 1100, 48), True), ((640, 520, 200), True),
-                                         ((128, 128, 64), True), ((4096, 8192, 128), True), ((1100, 900, 100), False)])
-def test_tmem_operand_objective_agrees_with_the_default_kernel(shape, exact):
-    """impl 3 against impl 0 and the fp64 value: KP = 64 / 128 / 256 (k = 200: the planes fill all 512 TMEM
-    columns next to the accumulators), one tile, several rows of tiles per CTA, two V planes."""
+                                         ((128, 128, 64), True), ((4096, 8192, 128), True), ((1100, 900, 100), False),
+                                         ((640, 520, 200), False)])
+def test_tmem_operand_objective_agrees_with_the_cuda_core_kernel(shape, exact):
+    """KP = 64 / 128 / 256 (k = 200: the planes fill all 512 TMEM columns next to the accumulators), one tile,
+    several rows of tiles per CTA, two V planes (also at KP = 256)."""
     _objective_variant_agrees(3, *shape, exact_data=exact)
 
 
-@first_run_pending
-@pytest.mark.parametrize("variant,shape", [("1", (768, 640, 100)), ("1", (512, 2048, 24)), ("1", (2000, 5000, 128)),
-                                           ("2", (768, 640, 100)), ("2", (2000, 5000, 128))])
-def test_kl_pass_with_tmem_operand_agrees_with_the_default_kernel(variant, shape, monkeypatch):
-    """NMFB_KL_TS=1 (kl_ts.cu: X as the TMEM-resident A operand of MMA1) and =2 (kl_ts2.cu: the quotient too,
-    stored over S, as the A operand of MMA2; KP = 128) against the default fused kernel and the oracle: KP = 64 /
-    128, fused objective included, several work items per CTA at the last shape."""
+@pytest.mark.parametrize("shape", [(768, 640, 100), (512, 2048, 24), (2000, 5000, 128), (2000, 5000, 64)])
+def test_kl_pass_with_tmem_operands_matches_the_oracle(shape):
+    """kl_ts2.cu (KP = 128: X and the quotient as TMEM-resident A operands) and kl_ts.cu (KP = 64: X only) against
+    the oracle, fused objective included, several work items per CTA at the last shapes."""
     from oracle import nmf_oracle as orc
     from nmf_b200.mur import mur
     m, n, k = shape
     v = orc.planted(m, n, k, 60).astype(np.float64)
     w0, h0 = orc.seeded_init(m, n, k, 61)
-    kw = dict(distance_type="kl", min_iter=10**9, max_iter=6, w0=w0, h0=h0, verbose=False)
-    monkeypatch.setenv("NMFB_KL_TS", "0")
-    base = mur(v, k, **kw)
-    monkeypatch.setenv("NMFB_KL_TS", variant)
-    res = mur(v, k, **kw)
-    monkeypatch.setenv("NMFB_KL_TS", "0")
-    assert rel_fro(res.w, base.w) < 1e-6 and rel_fro(res.h, base.h) < 1e-6
-    assert max(abs(a - b) / abs(b) for a, b in zip(res.obj_history, base.obj_history)) < 1e-6
+    res = mur(v, k, distance_type="kl", min_iter=10**9, max_iter=6, w0=w0, h0=h0, verbose=False)
     tr = orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=6)
     assert rel_fro(res.w, tr.w) < TOL and rel_fro(res.h, tr.h) < TOL
+    assert max(abs(a - b) / abs(b) for a, b in zip(res.obj_history, tr.obj_history)) < TOL

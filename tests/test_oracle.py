@@ -3,7 +3,7 @@ unmodified reference (tests/golden/*.npz, made by tests/golden/make_golden.py)."
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_NAMES, golden_v, load_golden, rel_fro
+from conftest import GOLDEN_NAMES, MID_GOLDEN_NAMES, golden_v, load_golden, rel_fro
 from oracle import nmf_oracle as orc
 
 
@@ -35,6 +35,17 @@ def test_oracle_matches_reference_golden(name):
         used = sum((a < g["recipe"]["kw"]["admm_iter"]) + (b < g["recipe"]["kw"]["admm_iter"])
                    for a, b in t.inner_breaks)
         assert used == int(g["n_inner_breaks"])
+
+
+@pytest.mark.parametrize("name", MID_GOLDEN_NAMES)
+def test_oracle_first_iterations_match_mid_size_golden(name):
+    """SURVEY 8d sizes (8192^2 k=64, 4000x10000 k=128, 16384x4096 k=128): the first three iterations of the oracle
+    against the reference's frozen objective history (the whole 100-iteration runs are the GPU tests' business;
+    three iterations keep the CPU suite short)."""
+    g = load_golden(name)
+    g["recipe"]["kw"] = dict(g["recipe"]["kw"], max_iter=3, min_iter=10**9)
+    t = replay(g)
+    np.testing.assert_allclose(t.obj_history, g["obj_history"][:4], rtol=1e-9)
 
 
 def test_c1_known_answers():
