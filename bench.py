@@ -13,10 +13,11 @@ planted non-negative data.  Prints ONE JSON line (rank 0).
                with comm=True on every rank, barrier to slowest rank)
   roofline     dominant kernel (the split-bf16 tcgen05 panel GEMM) timed live with CUDA events
   time_to_tol  seconds until the reference's stop test fires (tol2 = 1e-5 x initial objective), end to end
-  cpu_baseline the oracle port of the reference loop (NumPy fp64) timed on this box's host cores
+  cpu_baseline the reference's NMF.factorize (oracle/_ref; else the oracle port) timed on this box's host cores
 
-`--impl reference` times the reference algorithm (oracle port; the reference is pure Python and
-cannot travel to the GPU box) on the host cores, on a bounded sample of the same workload.
+`--impl reference` times the reference's own NMF.factorize (vendored into oracle/_ref by
+__graft_entry__.build(); the oracle port when that is absent) on the host cores, on a bounded block of the
+same workload, scaled to the full size.
 """
 from __future__ import annotations
 
@@ -266,9 +267,93 @@ def cpu_step_fn(method, dist, ms, ns, k, extra, seed=0):
     return step, cores
 
 
+def use_all_host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1; the CPU arm is supposed to use the box's cores."""
+    n = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=n)
+    except Exception:                                        # noqa: BLE001
+        pass
+    return n
+
+
+def blas_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        return max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
+    except Exception:                                        # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+def load_reference():
+    """The UNMODIFIED reference package, vendored by __graft_entry__.build() from /root/reference/nmf into
+    oracle/_ref/nmf (git-ignored, travels to the GPU box), imported under a private name so that it cannot be
+    mistaken for the drop-in shim `nmf/`.  None when it is not there."""
+    import importlib.util
+    pkg = os.path.join(ROOT, "oracle", "_ref", "nmf")
+    init = os.path.join(pkg, "__init__.py")
+    if not os.path.exists(init):
+        return None
+    name = "_nmf_reference"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, init, submodule_search_locations=[pkg])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def reference_run_seconds(ref, v, k, method, dist, extra, max_iter):
+    """Wall time of NMF(V, k).factorize(method, max_iter=...) of the reference: stop test off, stdout dropped."""
+    import contextlib
+    kw = dict(extra, distance_type=dist, min_iter=10**9, max_iter=max_iter)
+    if method != "mur":
+        kw["nndsvd_init"] = (False, "zero")
+    np.random.seed(1)
+    model = ref.NMF(v, k)
+    t0 = time.perf_counter()
+    with open(os.devnull, "w") as sink, contextlib.redirect_stdout(sink):
+        model.factorize(method=method, **kw)
+    return time.perf_counter() - t0
+
+
+def time_reference(ref, method, dist, m, n, k, extra, steps, warmup, budget_s):
+    """The reference's own NMF.factorize on a block of the workload, by the two-run difference of BASELINE.md
+    section 3: t(max_iter = warmup + steps) - t(max_iter = warmup) excludes the initialisation and the first
+    `warmup` iterations.  The block is the largest power-of-two fraction of V whose two runs fit budget_s (the
+    reference needs ~8 fp64 copies of V; 65536^2 does not fit this host at all); work is proportional to m*n, so
+    the full-size rate is the block's rate divided by the area ratio -- the line says so."""
+    from oracle import nmf_oracle as orc                     # data generator only
+    warmup = max(1, warmup)
+    pm, pn = cpu_sample_shape(m, n, k, 1 << 20)
+    pv = orc.planted(pm, pn, k, 0).astype(np.float64)
+    reference_run_seconds(ref, pv, k, method, dist, extra, 1)
+    per_elem = (reference_run_seconds(ref, pv, k, method, dist, extra, 3)
+                - reference_run_seconds(ref, pv, k, method, dist, extra, 1)) / 2 / (pm * pn)
+    total_iters = 2 * warmup + steps + 2                     # both runs + roughly one iteration per init
+    budget_elems = max(1 << 22, int(budget_s / max(per_elem, 1e-12) / total_iters))
+    budget_elems = min(budget_elems, 1 << 28)                # <= 2 GiB of fp64 V (x ~8 temporaries)
+    ms, ns = cpu_sample_shape(m, n, k, budget_elems)
+    v = orc.planted(ms, ns, k, 0).astype(np.float64)
+    t_a = reference_run_seconds(ref, v, k, method, dist, extra, warmup)
+    t_b = reference_run_seconds(ref, v, k, method, dist, extra, warmup + steps)
+    dt = max(t_b - t_a, 1e-9) / steps
+    scale = (m * n) / (ms * ns)
+    desc = (f"reference NMF.factorize (oracle/_ref) on a {ms}x{ns} block of the {m}x{n} workload (1/{scale:g} of V), "
+            f"k={k}: t(max_iter={warmup + steps}) - t(max_iter={warmup}) = {t_b - t_a:.2f} s over {steps} iterations "
+            f"= {dt * 1e3:.1f} ms each; SCALED by {scale:g} to the full size (work is proportional to m*n)")
+    return 1.0 / (dt * scale), dt * 1e3, blas_threads(), desc
+
+
 def time_cpu(method, dist, m, n, k, extra, steps, warmup, budget_s):
-    """Times `steps` oracle iterations on a sample sized so that the run fits budget_s; returns
-    (full-size iterations/s, ms per sample step, cores, description)."""
+    """-> (full-size iterations/s, ms per sample step, cores, description, kind).  kind = "reference": the vendored
+    reference itself (time_reference); "port": the oracle port, when oracle/_ref is absent."""
+    use_all_host_threads()
+    ref = load_reference()
+    if ref is not None:
+        return (*time_reference(ref, method, dist, m, n, k, extra, steps, warmup, budget_s), "reference")
     # calibrate on a small block, then pick the sample size
     probe_m, probe_n = cpu_sample_shape(m, n, k, 1 << 20)
     step, cores = cpu_step_fn(method, dist, probe_m, probe_n, k, extra)
@@ -288,9 +373,9 @@ def time_cpu(method, dist, m, n, k, extra, steps, warmup, budget_s):
         step()
     dt = (time.perf_counter() - t0) / steps
     scale = (m * n) / (ms * ns)
-    desc = (f"{ms}x{ns} block of the {m}x{n} workload (1/{scale:g} of V), k={k}, {steps} oracle iterations "
-            f"at {dt * 1e3:.1f} ms each, time scaled by {scale:g} (work is proportional to m*n)")
-    return 1.0 / (dt * scale), dt * 1e3, cores, desc
+    desc = (f"oracle port on a {ms}x{ns} block of the {m}x{n} workload (1/{scale:g} of V), k={k}, {steps} iterations "
+            f"at {dt * 1e3:.1f} ms each; SCALED by {scale:g} to the full size (work is proportional to m*n)")
+    return 1.0 / (dt * scale), dt * 1e3, blas_threads(), desc, "port"
 
 
 # ----------------------------------------------------------------------------------------------
@@ -328,7 +413,7 @@ def run_reference(args):
     method, dist, m, n, k, extra = WORKLOADS[args.workload]
     steps, warmup = max(1, args.steps), max(0, args.warmup)
     budget = min(150.0, 4.0 * (steps + warmup))
-    its, ms_step, cores, desc = time_cpu(method, dist, m, n, k, extra, steps, warmup, budget)
+    its, ms_step, cores, desc, kind = time_cpu(method, dist, m, n, k, extra, steps, warmup, budget)
     line = {
         "impl": "reference", "metric": "nmf_outer_iterations_per_second", "value": its, "unit": "it/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 / its,
@@ -336,7 +421,8 @@ def run_reference(args):
         "data": "synthetic",
         "config": {"workload": args.workload, "method": method, "distance": dist, "m": m, "n": n, "k": k,
                    **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
-        "cpu_baseline": {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc},
+        "cpu_baseline": {"value": its, "unit": "it/s", "cores": cores, "kind": kind, "sample": desc,
+                         "scaled_from_sample": True},
         "e2e": {"value": its, "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -433,6 +519,9 @@ def run_b200(args):
         "config": {"workload": args.workload, "method": method, "distance": dtype_, "m": m, "n": n, "k": k,
                    "v_storage": "bf16 (lossless, V and V^T resident)", "l2": "inputs_exceed_l2",
                    "objective_every_iteration": True, "parallelism": f"rows/cols x{world}",
+                   "exchange": ("none" if world == 1 else
+                                "peer-memory stores + device barrier (csrc/peer.cu), k x k Gram terms reduced in the "
+                                "same exchange" if getattr(eng, "peer", None) is not None else "torch.distributed"),
                    **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
         "clocks": clk.summary(),
         "gpu_launches": int(launches_per_step * steps),
@@ -464,14 +553,16 @@ def run_b200(args):
         guard.daemon = True
         guard.start()
         try:
-            line["e2e"] = run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank)
+            line["e2e"] = run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank, obj0)
+            line["time_to_tol"] = line["e2e"].pop("time_to_tol", None)
         except Exception as exc:                             # noqa: BLE001 -- reported in the line
             line["e2e"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
         guard.cancel()
     if not args.no_cpu and rank == 0 and world == 1:
         try:
-            its, ms_cpu, cores, desc = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
-            line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": "port", "sample": desc}
+            its, ms_cpu, cores, desc, kind = time_cpu(method, dtype_, m, n, k, extra, 3, 1, args.cpu_budget)
+            line["cpu_baseline"] = {"value": its, "unit": "it/s", "cores": cores, "kind": kind, "sample": desc,
+                                    "scaled_from_sample": True}
         except Exception as exc:                             # noqa: BLE001 -- reported in the line
             line["cpu_baseline"] = {"value": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
     _EMITTED.set()
@@ -599,11 +690,14 @@ def _e2e_timed_out(line, rank):
     os._exit(0)
 
 
-def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
+def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank, obj0=None):
     """N > 1: the same call on every rank, NMF(V_host, k).factorize(..., comm=True) -- each rank is handed the
-    whole host V (that is the public API of a sharded run), uploads its rows of it
-    and receives its columns from the other ranks' row shards over NVLink (Engine._ingest_pass_sharded).  Timed from a barrier to the slowest rank's return (upload, `steps` iterations with the objective
-    read back every iteration, download of W and H on every rank)."""
+    whole host V (the public API of a sharded run) and reads ONLY its rows and its
+    columns of it (Engine._shard_and_panel: 2/P of V per PCIe link, nothing between the GPUs).  Timed from a
+    barrier to the slowest rank's return (engine set-up incl. the peer arena, upload, `steps` iterations with the
+    objective read back every iteration, download of W and H on every rank); `breakdown` = the slowest rank's
+    wall seconds per leg.  The host V is ONE shared-memory file that rank 0 fills and every rank maps, so the node
+    holds one copy instead of N pinned ones."""
     import contextlib
     import io
 
@@ -611,6 +705,7 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
     import torch
     import torch.distributed as dist
     from nmf_b200 import NMF
+    from nmf_b200.engine import Engine
 
     dev = eng.device
 
@@ -621,53 +716,100 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank):
 
     need = 4 * m * n
     dist.barrier()
-    if not agreed(psutil.virtual_memory().available > 1.3 * need * world):
-        return {"value": None, "error": f"host memory: {world} ranks x {need / 2**30:.1f} GiB of V do not fit"}
+    if not agreed(psutil.virtual_memory().available > 1.3 * need):
+        return {"value": None, "error": f"host memory: {need / 2**30:.1f} GiB of V do not fit"}
     w0 = eng.w.master[:k, :m].t().contiguous().cpu().numpy()     # current (replicated) factors as the start
     h0 = eng.h.master[:k, :n].contiguous().cpu().numpy()
     torch.cuda.synchronize(dev)
     eng.release()
     torch.cuda.empty_cache()
-    v_host, pinned = None, True
+    import shutil
+    path = f"/dev/shm/nmfb_bench_v_{os.environ.get('MASTER_PORT', '0')}.npy"
+    v_np, pinned = None, False
+    shared = agreed(os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > 1.1 * need)
     try:
-        v_host = torch.empty((m, n), dtype=torch.float32, pin_memory=True)
-    except Exception:                                        # noqa: BLE001 -- pageable memory is slower, not wrong
-        pinned = False
-        try:
-            v_host = torch.empty((m, n), dtype=torch.float32)
-        except Exception:                                    # noqa: BLE001
-            v_host = None
-    if not agreed(v_host is not None):
-        return {"value": None, "error": "host allocation of V failed on a rank"}
-    _wt, _ht, blocks = synth_blocks(dev, m, n, k, seed=0)
-    for r0, blk in blocks():
-        v_host[r0:r0 + blk.shape[0]].copy_(blk)
-    del _wt, _ht, blk
+        if shared and rank == 0:
+            v_np = np.lib.format.open_memmap(path, mode="w+", dtype=np.float32, shape=(m, n))
+        elif not shared:                                     # no room in /dev/shm: a private copy per rank
+            v_np = np.empty((m, n), dtype=np.float32)
+        if v_np is not None:
+            _wt, _ht, blocks = synth_blocks(dev, m, n, k, seed=0)
+            for r0, blk in blocks():
+                v_np[r0:r0 + blk.shape[0]] = blk.cpu().numpy()
+            del _wt, _ht, blk
+            if shared:
+                v_np.flush()
+        dist.barrier()
+        if shared and rank != 0:
+            v_np = np.load(path, mmap_mode="r+")
+        # page-lock the mapping in this process (every rank maps the same physical pages)
+        rc = torch.cuda.cudart().cudaHostRegister(v_np.ctypes.data, v_np.nbytes, 0)
+        pinned = int(rc) == 0
+    except Exception as exc:                                 # noqa: BLE001
+        v_np = None
+        err = f"{type(exc).__name__}: {exc}"[:200]
+    if not agreed(v_np is not None):
+        return {"value": None, "error": "host V (shared memory) could not be set up on a rank"}
     torch.cuda.empty_cache()
-    v_np = v_host.numpy()
     kw = dict(extra, distance_type=dtype_)
     if method != "mur":
         kw["nndsvd_init"] = (False, "zero")
-    torch.cuda.synchronize(dev)
-    dist.barrier()
-    t0 = time.perf_counter()
-    model = NMF(v_np, k)
-    with contextlib.redirect_stdout(io.StringIO()):
-        model.factorize(method=method, min_iter=10**9, max_iter=steps, w0=w0, h0=h0, verbose=False, comm=True, **kw)
-    torch.cuda.synchronize(dev)
-    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    dt = float(dt.item())
-    res = model.results
+
+    def timed(**run_kw):
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        t0 = time.perf_counter()
+        engine = Engine.for_comm(m, n, k, True)
+        t_engine = time.perf_counter() - t0
+        model = NMF(v_np, k)
+        sink = io.StringIO()
+        with contextlib.redirect_stdout(sink):
+            model.factorize(method=method, verbose=False, comm=True, engine=engine, **run_kw, **kw)
+        torch.cuda.synchronize(dev)
+        total = time.perf_counter() - t0
+        legs = [total, t_engine, engine.timings.get("upload_s", 0.0), engine.timings.get("download_s", 0.0)]
+        t = torch.tensor(legs, dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total, t_engine, t_up, t_down = (float(x) for x in t.tolist())
+        engine.release()
+        bd = {"engine_and_peer_arena_s": round(t_engine, 4), "upload_s": round(t_up, 4),
+              "iterations_s": round(max(total - t_engine - t_up - t_down, 0.0), 4), "download_s": round(t_down, 4)}
+        return model.results, total, bd, sink.getvalue()
+
+    res, dt, breakdown, _ = timed(min_iter=10**9, max_iter=steps, w0=w0, h0=h0)
     assert res.i == steps - 1 and len(res.obj_history) == steps + 1
-    # each rank uploads its rows of V (the column copy is assembled over NVLink) and both initial factors
-    h2d = v_np.nbytes + world * (w0.nbytes + h0.nbytes)
+    # each rank uploads its rows and its columns of V (2/P of V) and both initial factors
+    h2d = 2 * v_np.nbytes + world * (w0.nbytes + h0.nbytes)
     d2h = world * (res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1))
-    return {"value": steps / dt, "unit": "it/s", "seconds_total": dt,
-            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps, "host_v_pinned": pinned,
-            "what": f"on each of {world} ranks NMF(V_host fp32, k).factorize(max_iter=steps, comm=True): "
-                    "upload of the rank's rows of V, all-to-all for its columns, iterations, factor download; "
-                    "slowest rank"}
+    out = {"value": steps / dt, "unit": "it/s", "seconds_total": dt, "breakdown": breakdown,
+           "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps, "host_v_pinned": pinned,
+           "what": f"on each of {world} ranks NMF(V_host fp32 in shared memory, k).factorize(max_iter=steps, comm=True): "
+                   "engine + peer arena, upload of the rank's rows and columns of V, iterations, factor download; "
+                   "slowest rank"}
+    if obj0 is not None:
+        try:
+            tol2 = 1e-5 * float(obj0)
+            np.random.seed(1)
+            r2, dt2, bd2, text = timed(min_iter=10, max_iter=TTT_MAX_ITER, tol1=0.0, tol2=tol2)
+            out["time_to_tol"] = {"seconds": dt2, "iterations": r2.i + 1, "converged": "Algorithm converged" in text
+                                  or r2.i + 1 < TTT_MAX_ITER, "tol1": 0.0, "tol2": tol2, "min_iter": 10,
+                                  "max_iter": TTT_MAX_ITER, "breakdown": bd2,
+                                  "objective_first": r2.obj_history[0], "objective_last": r2.obj_history[-1],
+                                  "rule": "reference stop test (utils.py:4-15) with tol2 = 1e-5 x initial objective; "
+                                          "host V in, host W/H out, slowest rank"}
+        except Exception as exc:                             # noqa: BLE001 -- reported, never costs the line
+            out["time_to_tol"] = {"seconds": None, "error": f"{type(exc).__name__}: {exc}"[:300]}
+    try:
+        torch.cuda.cudart().cudaHostUnregister(v_np.ctypes.data)
+    except Exception:                                        # noqa: BLE001
+        pass
+    del v_np
+    dist.barrier()
+    if rank == 0 and shared:
+        with contextlib.suppress(OSError):
+            os.remove(path)
+    out["host_v_shared"] = shared
+    return out
 
 
 _JSON_FD = None

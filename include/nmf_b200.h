@@ -158,10 +158,10 @@ int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other,
                        int k, int KP, float lambda, void* stream);
 
 /* 0.5 * ||V - W H||_F^2 (utils.py:29) in residual form, fp64 accumulation, written to *obj_out
- * (device).  impl = 0: tcgen05 kernel, 1: CUDA-core kernel (cross-check / tiny problems), 2: wide-tile tcgen05
- * kernel (128 x 256 tiles; KP = 64 / 128 and one V plane, NMFB_ERR_ARG otherwise; experimental, also selected for
- * impl 0 when the environment has NMFB_RES_N256=1), 3: tcgen05 kernel with the W planes as the TMEM-resident A
- * operand (experimental; NMFB_RES_TS=1 selects it for impl 0). */
+ * (device).  impl = 0: the library's choice -- the wide-tile tcgen05 kernel (128 x 256 tiles) for KP = 64 / 128 with
+ * one V plane, the tcgen05 kernel with the W planes as the TMEM-resident A operand for every other shape;
+ * 1: CUDA-core kernel (cross-check); 2 / 3: force the wide-tile / TMEM-operand kernel (NMFB_ERR_ARG when the shape
+ * does not fit it). */
 int nmfb_objective_eu(const nmfb_problem* p, int impl, double* obj_out, void* stream);
 
 /* ---- solver steps --------------------------------------------------------------------------- */
@@ -171,7 +171,7 @@ int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, doub
                      void* stream);
 /* One factor update of the iteration above (side 0 = W, 1 = H).  In a sharded run (factor windows set,
  * v_rows / v_cols holding this rank's rows / columns) it updates the window only; the caller then
- * all-gathers the factor across ranks and calls nmfb_refresh_planes before the next half step. */
+ * exchanges the windows (nmfb_peer_push / nmfb_peer_barrier / nmfb_adopt_exchange) before the next half step. */
 int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* stream);
 
 /* Generalised Kullback-Leibler objective sum(v log(v/wh) - v + wh) with the reference's special values
@@ -270,6 +270,40 @@ int nmfb_aoadmm_side_begin(const nmfb_problem* p, const nmfb_admm_state* s, int 
 int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side, int first, int slots,
                       float lambda, int prox, void* stream);
 int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream);
+
+/* ---- sharded runs: exchange over NVLink peer memory ------------------------------------------- */
+/* SURVEY.md 8e (1-D MPI-FAUN layout): after a half step every rank owns fresh rows [win0, win0 + win_p) of the
+ * factor; the reference has no counterpart (it is single-process).  The exchange is done by the ranks' own
+ * kernels on peer pointers -- `peers_host[p]` is the device address, valid on THIS device, of rank p's exchange
+ * arena (symmetric memory or CUDA IPC, opened by the caller; index `rank` is the local arena) --, never by a
+ * collective library:
+ *   peer_push       copies `rows` rows of `row_bytes` bytes from src (pitch src_pitch) to byte offset dst_off of
+ *                   EVERY rank's arena (pitch dst_pitch): the window of a master, a Gram term, a scalar
+ *   peer_barrier    cross-GPU barrier on the stream: publishes `seq` (a counter the callers advance together) to
+ *                   every rank's flag array and waits until all ranks have published >= seq; the stores of
+ *                   earlier kernels on the stream are visible to the peers that pass it
+ *   sum_rank_slots  out[i] = sum_p slots[p * stride + i] in rank order (bit-identical on all ranks): the k x k
+ *                   Gram all-reduce (`w.T @ w` ao_admm.py:53, the re-associated Grams of mur.py:29,45) and the
+ *                   objective sum (utils.py:29 over the ranks' rows)
+ *   adopt_exchange  the factor's master <- the exchange buffer ([KP][Lp] like the master, all windows current);
+ *                   refresh != 0 also re-derives cplanes / rplanes in the same pass
+ * Buffers must be double-buffered by the caller (see nmf_b200/csrc/peer.cu for the ordering argument). */
+int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
+                   long dst_pitch, int rows, long row_bytes, void* stream);
+int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int seq, void* stream);
+int nmfb_sum_rank_slots(const double* slots, int world, long stride, int n, double* out64, float* out32,
+                        void* stream);
+int nmfb_adopt_exchange(int KP, const nmfb_factor* f, const float* xchg, int refresh, void* stream);
+/* This rank's term of the Gram matrix: nmfb_gram over the rows of the factor's window only. */
+int nmfb_gram_window(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes,
+                     float* gram32, double* gram64, int num_sms, void* stream);
+/* nmfb_mur_eu_half_step without its Gram launch: gram32 already holds the Gram of the other factor (reduced from
+ * the ranks' window terms during that factor's exchange). */
+int nmfb_mur_eu_window_step(const nmfb_problem* p, int side, float lambda, void* stream);
+/* Strided host -> device copy (cudaMemcpy2DAsync) of a column panel of the caller's host V: a sharded upload reads
+ * the rank's rows AND its columns straight from host memory (2/P of V per PCIe link, no inter-GPU step). */
+int nmfb_upload_2d(void* dst, long dst_pitch, const void* src_host, long src_pitch, long width_bytes, long height,
+                   void* stream);
 
 #ifdef __cplusplus
 }

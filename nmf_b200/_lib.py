@@ -92,6 +92,16 @@ _SIGNATURES = {
                                  c_void_p]),
 }
 
+_SIGNATURES.update({
+    "nmfb_peer_push": (c_int, [c_void_p, c_long, c_void_p, c_int, c_long, c_long, c_int, c_long, c_void_p]),
+    "nmfb_peer_barrier": (c_int, [c_void_p, c_int, c_int, C.c_uint, c_void_p]),
+    "nmfb_sum_rank_slots": (c_int, [c_void_p, c_int, c_long, c_int, c_void_p, c_void_p, c_void_p]),
+    "nmfb_adopt_exchange": (c_int, [c_int, P(Factor), c_void_p, c_int, c_void_p]),
+    "nmfb_gram_window": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
+    "nmfb_mur_eu_window_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
+    "nmfb_upload_2d": (c_int, [c_void_p, c_long, c_void_p, c_long, c_long, c_long, c_void_p]),
+})
+
 _OPTIONAL = set()
 
 _lib = None

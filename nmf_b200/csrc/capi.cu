@@ -8,6 +8,7 @@
 #include "elementwise.cuh"
 #include "kernels.cuh"
 #include "kl.cuh"
+#include "peer.cuh"
 
 using namespace nmfb;
 
@@ -186,8 +187,54 @@ int nmfb_fixed_planes(int KP, const nmfb_factor* f, void* stream) {
 }
 
 int nmfb_refresh_planes(int KP, const nmfb_factor* f, void* stream) {
-    CUDA_TRY(refresh_planes_launch(f->master, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
+    CUDA_TRY(refresh_planes_launch(f->master, nullptr, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
                                    static_cast<long>(f->Lp) * KP, st(stream)));
+    return 0;
+}
+
+int nmfb_adopt_exchange(int KP, const nmfb_factor* f, const float* xchg, int refresh, void* stream) {
+    if (!f || !xchg) return fail(NMFB_ERR_ARG, "adopt_exchange: null argument");
+    if (refresh) {
+        CUDA_TRY(refresh_planes_launch(xchg, f->master, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
+                                       static_cast<long>(f->Lp) * KP, st(stream)));
+    } else {
+        CUDA_TRY(cudaMemcpyAsync(f->master, xchg, static_cast<size_t>(KP) * f->Lp * 4, cudaMemcpyDeviceToDevice,
+                                 st(stream)));
+    }
+    return 0;
+}
+
+int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
+                   long dst_pitch, int rows, long row_bytes, void* stream) {
+    if (!src || !peers_host) return fail(NMFB_ERR_ARG, "peer_push: null argument");
+    if (world < 1 || world > kMaxPeers || rows < 1 || (row_bytes & 15) || (dst_off & 15) || (src_pitch & 15) ||
+        (dst_pitch & 15))
+        return fail(NMFB_ERR_ARG, "peer_push: world in [1, %d], 16-byte multiples (world=%d rows=%d row_bytes=%ld)",
+                    kMaxPeers, world, rows, row_bytes);
+    CUDA_TRY(peer_push_launch(src, src_pitch, peers_host, world, dst_off, dst_pitch, rows, row_bytes, st(stream)));
+    return 0;
+}
+
+int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int seq, void* stream) {
+    if (!flags_host || world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
+        return fail(NMFB_ERR_ARG, "peer_barrier: bad argument");
+    CUDA_TRY(peer_barrier_launch(flags_host, rank, world, seq, st(stream)));
+    return 0;
+}
+
+int nmfb_sum_rank_slots(const double* slots, int world, long stride, int n, double* out64, float* out32,
+                        void* stream) {
+    if (!slots || world < 1 || n < 1 || (!out64 && !out32)) return fail(NMFB_ERR_ARG, "sum_rank_slots: bad argument");
+    CUDA_TRY(sum_rank_slots_launch(slots, world, stride, n, out64, out32, st(stream)));
+    return 0;
+}
+
+int nmfb_upload_2d(void* dst, long dst_pitch, const void* src_host, long src_pitch, long width_bytes, long height,
+                   void* stream) {
+    if (!dst || !src_host || width_bytes < 1 || height < 1) return fail(NMFB_ERR_ARG, "upload_2d: bad argument");
+    CUDA_TRY(cudaMemcpy2DAsync(dst, static_cast<size_t>(dst_pitch), src_host, static_cast<size_t>(src_pitch),
+                               static_cast<size_t>(width_bytes), static_cast<size_t>(height),
+                               cudaMemcpyHostToDevice, st(stream)));
     return 0;
 }
 
@@ -331,6 +378,25 @@ Window window_of(const nmfb_factor* f) {
 }
 }  // namespace
 
+int nmfb_gram_window(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
+                     double* gram64, int num_sms, void* stream) {
+    // This rank's term of the Gram matrix: the contraction runs over the rows of its window only.  The padded
+    // rows of a window ([L, Lp)) hold zeros, so whole 64-row contraction blocks may be read.
+    if (!f) return fail(NMFB_ERR_ARG, "gram_window: null factor");
+    if (nplanes != 2 && nplanes != 3) return fail(NMFB_ERR_ARG, "gram_window: nplanes must be 2 or 3");
+    if (KP == 256) nplanes = 2;
+    const Window w = window_of(f);
+    if (w.live <= 0) return fail(NMFB_ERR_ARG, "gram_window: empty window");
+    nmfb_data d;
+    d.planes = bf(f->cplanes) + w.w0;
+    d.rows = KP; d.cols = w.live; d.rows_p = 256; d.ld = f->Lp; d.nv = nplanes; d.blocked = 0; d.fixed = 0; d.origin = 0;
+    const int slots = nmfb_panel_gemm(&d, bf(f->cplanes) + w.w0, f->Lp, KP, nplanes, partial, partial_bytes, 256,
+                                      num_sms, 128, 0, stream);
+    if (slots < 0) return slots;
+    CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
+    return 0;
+}
+
 int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other, const nmfb_factor* f,
                        int k, int KP, float lambda, void* stream) {
     const Window w = window_of(f);
@@ -418,7 +484,8 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
     return objective_common(p, 0, 1, obj_out, stream);
 }
 
-int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+namespace {
+int mur_eu_half(const nmfb_problem* p, int side, float lambda, bool with_gram, void* stream) {
     if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_eu_half_step: bad argument");
     const int KP = p->KP;
     const size_t gsz = static_cast<size_t>(KP) * KP;
@@ -430,7 +497,10 @@ int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* s
     float* g32 = p->gram32 + (side == 0 ? gsz : 0);
     double* g64 = p->gram64 + (side == 0 ? gsz : 0);
     int rc;
-    if ((rc = nmfb_gram(other, KP, 2, p->partial, p->partial_bytes, g32, g64, p->num_sms, stream)) < 0) return rc;
+    // with_gram = false: the Gram of the other factor is already in gram32 (sharded runs reduce the ranks' window
+    // terms during the exchange of that factor, nmfb_gram_window + nmfb_sum_rank_slots)
+    if (with_gram && (rc = nmfb_gram(other, KP, 2, p->partial, p->partial_bytes, g32, g64, p->num_sms, stream)) < 0)
+        return rc;
     mark(p, 1 + 3 * side, stream);
     // sharded runs: this rank's rows of the product land at its window of the full-pitch partial
     const int slots = nmfb_panel_gemm(data, other->cplanes, other->Lp, KP, 2, p->partial + window_of(self).w0,
@@ -440,6 +510,15 @@ int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* s
     if ((rc = nmfb_mur_eu_update(p->partial, slots, g32, self, p->k, KP, lambda, stream)) < 0) return rc;
     mark(p, 3 + 3 * side, stream);
     return 0;
+}
+}  // namespace
+
+int nmfb_mur_eu_half_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+    return mur_eu_half(p, side, lambda, true, stream);
+}
+
+int nmfb_mur_eu_window_step(const nmfb_problem* p, int side, float lambda, void* stream) {
+    return mur_eu_half(p, side, lambda, false, stream);
 }
 
 int nmfb_mur_eu_step(const nmfb_problem* p, float lambda_w, float lambda_h, double* obj_out, void* stream) {

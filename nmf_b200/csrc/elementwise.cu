@@ -119,9 +119,12 @@ cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row
 // ------------------------------------------------------------------ factor planes from master
 // Re-derives every bf16 plane from the fp32 master (used after ingest of an initial factor and
 // by solvers whose update kernel does not write planes itself).
+// adopt != nullptr: the values come from `master` (an exchange buffer of the same [KP][Lp] layout that the ranks'
+// windows were stored into, peer.cu) and are also written to `adopt`, the factor's own master.
 __global__ void __launch_bounds__(256)
-refresh_planes_kernel(const float* __restrict__ master, int KP, int Lp, __nv_bfloat16* __restrict__ cpl,
-                      long cpl_plane, __nv_bfloat16* __restrict__ rpl, long rpl_plane) {
+refresh_planes_kernel(const float* __restrict__ master, float* __restrict__ adopt, int KP, int Lp,
+                      __nv_bfloat16* __restrict__ cpl, long cpl_plane, __nv_bfloat16* __restrict__ rpl,
+                      long rpl_plane) {
     const int r = blockIdx.x * 256 + threadIdx.x;
     if (r >= Lp) return;
     for (int c0 = 0; c0 < KP; c0 += 8) {
@@ -129,6 +132,7 @@ refresh_planes_kernel(const float* __restrict__ master, int KP, int Lp, __nv_bfl
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
             const float x = master[static_cast<long>(c0 + q) * Lp + r];
+            if (adopt) adopt[static_cast<long>(c0 + q) * Lp + r] = x;
             __nv_bfloat16 p0, p1, p2;
             split3(x, p0, p1, p2);
             const long o = static_cast<long>(c0 + q) * Lp + r;
@@ -144,9 +148,9 @@ refresh_planes_kernel(const float* __restrict__ master, int KP, int Lp, __nv_bfl
     }
 }
 
-cudaError_t refresh_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
-                                  __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream) {
-    refresh_planes_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, KP, Lp, cpl, cpl_plane, rpl,
+cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int Lp, __nv_bfloat16* cpl,
+                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream) {
+    refresh_planes_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, adopt, KP, Lp, cpl, cpl_plane, rpl,
                                                                rpl_plane);
     count_launch();
     return cudaGetLastError();

@@ -13,8 +13,8 @@ cudaError_t data_absmax_launch(const void* src, int is_f64, long src_ld, int row
                                unsigned int* rowmax, unsigned int* colmax, cudaStream_t stream);
 cudaError_t fixed_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
                                 cudaStream_t stream);
-cudaError_t refresh_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
-                                  __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream);
+cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int Lp, __nv_bfloat16* cpl,
+                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream);
 cudaError_t import_factor_launch(const void* src, int is_f64, long stride_l, long stride_c, int L, int k,
                                  float* master, int KP, int Lp, cudaStream_t stream);
 cudaError_t export_factor_launch(const float* master, int KP, int Lp, void* dst, int is_f64, long stride_l,

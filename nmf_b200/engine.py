@@ -54,6 +54,9 @@ class FactorBuffers:
         self.master = torch.zeros((KP, self.Lp), dtype=torch.float32, device=device)
         self.cplanes = torch.zeros((3, 256, self.Lp), dtype=torch.bfloat16, device=device)
         self.rplanes = torch.zeros((2, self.Lp, KP), dtype=torch.bfloat16, device=device)
+        # sharded runs on GPUs: the peer arena and region the windows of this factor are exchanged through
+        # (Engine._attach_exchange), and how many exchanges it has seen (parity = which of the two buffers)
+        self.arena, self.xname, self.xcount = None, None, 0
 
     def struct(self) -> Factor:
         return Factor(self.master.data_ptr(), self.cplanes.data_ptr(), self.rplanes.data_ptr(),
@@ -68,6 +71,7 @@ class Engine:
     def __init__(self, m: int, n: int, k: int, device: Optional[torch.device] = None, rank: int = 0,
                  world: int = 1, group=None):
         self.lib, self.device, self.num_sms = self._open_device(device)
+        self.timings = {}                     # wall seconds of the host-side legs (upload_s, download_s): bench e2e
         self.m, self.n, self.k = int(m), int(n), int(k)
         self.rank, self.world = int(rank), int(world)
         self.group = group
@@ -104,6 +108,9 @@ class Engine:
             self.stats = torch.zeros(4, dtype=torch.int32, device=self.device)
             self.scalars = torch.zeros(64, dtype=torch.float64, device=self.device)
             self.ksum = torch.zeros((2, self.KP), dtype=torch.float64, device=self.device)
+            self.peer = None
+            if self.world > 1 and torch.device(self.device).type == "cuda":
+                self._open_peer()
         self.nv = 0
         self.fixed = False                    # plane 0 of V is the fixed-point slice (exact-mode ADMM)
         self.v_rows = None
@@ -155,18 +162,105 @@ class Engine:
         self._problem = None
 
     # ------------------------------------------------------------------ sharded runs
-    def gather_factor(self, fac: "FactorBuffers", refresh: bool = True, fixed: bool = False):
-        """All-gather the windows of a factor (or ADMM auxiliary) every rank just updated, then re-derive
-        its bf16 planes: `refresh` = floating cplanes + rplanes, `fixed` = fixed-point cplanes on top
-        (operand of the exact-hi contractions)."""
+    def _open_peer(self):
+        """Peer-memory arena of this rank (peer.py): barrier flags, the ranks' objective / norm partials, their
+        terms of the two Gram matrices, and the exchange buffers of W and H -- everything peers write is
+        double-buffered ([2] leading)."""
+        from .peer import PeerArena
+        KP, g, w = self.KP, self.KP * self.KP * 8, self.world
+        self._norm_bytes = 4 * (max(self.Mp, self.Np) // 64) * 8
+        layout = [("scal", 2 * w * 64), ("gram", 2 * 2 * w * g), ("norm", 2 * self._norm_bytes),
+                  ("xw", 2 * KP * self.Mp * 4), ("xh", 2 * KP * self.Np * 4)]
+        self.peer = PeerArena(self.lib, layout, self.device, self.rank, self.world, self.group)
+        self._attach_exchange(self.w, self.peer, "xw")
+        self._attach_exchange(self.h, self.peer, "xh")
+        self.gram_term = torch.zeros((KP, KP), dtype=torch.float64, device=self.device)
+        self.gram_term32 = torch.zeros((KP, KP), dtype=torch.float32, device=self.device)
+        self._scal_count = self._norm_count = self._gram_count = 0
+
+    @staticmethod
+    def _attach_exchange(fac: "FactorBuffers", arena, name: str):
+        fac.arena, fac.xname, fac.xcount = arena, name, 0
+
+    def _push_window(self, fac: "FactorBuffers") -> int:
+        """Store this rank's rows of the master into every rank's exchange buffer; returns the device address of
+        the LOCAL buffer that holds all windows once the barrier has been passed."""
+        KP, par = self.KP, fac.xcount & 1
+        fac.xcount += 1
+        base = par * KP * fac.Lp * 4
+        fac.arena.push(fac.master.data_ptr() + 4 * fac.win0, 4 * fac.Lp, fac.xname, base + 4 * fac.win0, 4 * fac.Lp,
+                       KP, 4 * fac.win_p, self.stream)
+        return fac.arena.local.data_ptr() + fac.arena.offsets[fac.xname] + base
+
+    def gather_factor(self, fac: "FactorBuffers", refresh: bool = True, fixed: bool = False, gram_index=None):
+        """Exchange the windows of a factor (or ADMM auxiliary) every rank just updated, then re-derive its bf16
+        planes: `refresh` = floating cplanes + rplanes, `fixed` = fixed-point cplanes on top (operand of the
+        exact-hi contractions).  On GPUs the window goes straight into the peers' exchange buffers (peer.cu), one
+        cross-GPU barrier later every rank adopts all windows; gram_index = 0 (W^T W) / 1 (H H^T) also reduces the
+        ranks' window terms of that Gram matrix in the same exchange (k x k all-reduce in rank order).  Without
+        peer memory (host stand-in of the CPU tests) the windows are all-gathered by torch.distributed."""
         if self.world == 1:
             return
-        allgather_windows(fac.master, fac.win_p, self.group)
         fs = fac.struct()
-        if refresh:
-            check(self.lib.nmfb_refresh_planes(self.KP, C.byref(fs), self.stream))
+        if self.peer is None:
+            allgather_windows(fac.master, fac.win_p, self.group)
+            if refresh:
+                check(self.lib.nmfb_refresh_planes(self.KP, C.byref(fs), self.stream))
+            if fixed:
+                check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
+            return
+        KP, w = self.KP, self.world
+        g = KP * KP * 8
+        if gram_index is not None:
+            check(self.lib.nmfb_gram_window(C.byref(fs), KP, 2, self.partial.data_ptr(), self.partial.numel() * 4,
+                                            self.gram_term32.data_ptr(), self.gram_term.data_ptr(), self.num_sms,
+                                            self.stream))
+            gpar = self._gram_count & 1
+            self._gram_count += 1
+            goff = (gpar * 2 + gram_index) * w * g
+            self.peer.push(self.gram_term.data_ptr(), g, "gram", goff + self.rank * g, g, 1, g, self.stream)
+        xptr = self._push_window(fac)
+        fac.arena.barrier(self.stream)
+        check(self.lib.nmfb_adopt_exchange(KP, C.byref(fs), xptr, 1 if refresh else 0, self.stream))
         if fixed:
-            check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
+            check(self.lib.nmfb_fixed_planes(KP, C.byref(fs), self.stream))
+        if gram_index is not None:
+            slots = self.peer.local.data_ptr() + self.peer.offsets["gram"] + goff
+            check(self.lib.nmfb_sum_rank_slots(slots, w, KP * KP, KP * KP, self.gram64.data_ptr() + gram_index * g,
+                                               self.gram32.data_ptr() + gram_index * (g // 2), self.stream))
+
+    def full_grams(self):
+        """W^T W and H H^T of the (replicated) factors into gram32 / gram64: start of a sharded MUR-eu run; from
+        then on the exchanges keep them current."""
+        p = self.problem()
+        g = self.KP * self.KP
+        for idx, fac in ((0, self.w), (1, self.h)):
+            fs = fac.struct()
+            check(self.lib.nmfb_gram(C.byref(fs), self.KP, 2, self.partial.data_ptr(), self.partial.numel() * 4,
+                                     self.gram32.data_ptr() + 4 * idx * g, self.gram64.data_ptr() + 8 * idx * g,
+                                     self.num_sms, self.stream))
+        del p
+
+    def mur_eu_window_step(self, side: int, lam: float):
+        p = self.problem()
+        check(self.lib.nmfb_mur_eu_window_step(C.byref(p), int(side), float(lam), self.stream))
+
+    def gather_norm_partials(self, fac: "FactorBuffers"):
+        """AO-ADMM residual test (ao_admm.py:33-43): every rank needs all blocks of the four norm partials."""
+        nblk = fac.win_p // 64
+        full = self.norm_partial[: 4 * (fac.Lp // 64)]
+        if self.peer is None:
+            mine = full[4 * nblk * self.rank: 4 * nblk * (self.rank + 1)].clone()
+            allgather_flat(full, mine, self.group)
+            return
+        par = self._norm_count & 1
+        self._norm_count += 1
+        seg = 4 * nblk * 8
+        base = par * self._norm_bytes
+        self.peer.push(full.data_ptr() + seg * self.rank, seg, "norm", base + seg * self.rank, seg, 1, seg, self.stream)
+        self.peer.barrier(self.stream)
+        got = self.peer.view("norm", (2, self._norm_bytes // 8), torch.float64)[par, : full.numel()]
+        full.copy_(got, non_blocking=True)
 
     def mur_kl_half_step(self, side: int, lam: float, obj_start_slot: Optional[int] = None):
         """obj_start_slot: scalar slot that receives the KL objective of the pair this pass starts from."""
@@ -190,13 +284,10 @@ class Engine:
         slots = check(self.lib.nmfb_aoadmm_side_begin(C.byref(p), C.byref(self._admm), side, self.stream))
         if int(prox) == 2 and float(lam) != 0.0:             # l2n: the Tikhonov system needs this side's rho
             check(self.lib.nmfb_admm_prepare_l2n(C.byref(p), C.byref(self._admm), side, float(lam), self.stream))
-        nblk = fac.win_p // 64
         for it in range(admm_iter):
             check(self.lib.nmfb_aoadmm_inner(C.byref(p), C.byref(self._admm), side, 1 if it == 0 else 0, slots,
                                              float(lam), int(prox), self.stream))
-            full = self.norm_partial[: 4 * (fac.Lp // 64)]
-            mine = full[4 * nblk * self.rank: 4 * nblk * (self.rank + 1)].clone()
-            allgather_flat(full, mine, self.group)
+            self.gather_norm_partials(fac)
             check(self.lib.nmfb_aoadmm_inner_flag(C.byref(p), C.byref(self._admm), side, self.stream))
         self.gather_factor(fac, refresh=True, fixed=self.fixed)
 
@@ -206,8 +297,22 @@ class Engine:
 
     def reduce_scalar(self, index: int):
         """Sum a mailbox scalar over ranks (each rank's objective covers its own rows of V)."""
-        if self.world > 1:
+        if self.world == 1:
+            return
+        if self.peer is None:
             allreduce_sum_(self.scalars[index:index + 1], self.group)
+            return
+        # every rank stores its partial into slot `rank` of every rank's table; summed in rank order after the
+        # barrier, so that all ranks hold the bit-identical objective (and take the same stop decision)
+        par = self._scal_count & 1
+        self._scal_count += 1
+        base = par * self.world * 64
+        assert index % 2 == 0                                       # 16-byte granules
+        self.peer.push(self.scalars.data_ptr() + 8 * index, 16, "scal", base + 64 * self.rank, 64, 1, 16, self.stream)
+        self.peer.barrier(self.stream)
+        slots = self.peer.local.data_ptr() + self.peer.offsets["scal"] + base
+        check(self.lib.nmfb_sum_rank_slots(slots, self.world, 8, 1, self.scalars.data_ptr() + 8 * index, None,
+                                           self.stream))
 
     def _data_structs(self) -> Tuple[Data, Data]:
         vr = Data(self.v_rows.data_ptr(), self.row_range[1] - self.row_range[0], self.n, self.per_m, self.Np,
@@ -299,19 +404,24 @@ class Engine:
     # ---- sharded upload: every rank reads ONLY its rows of the host V; the column copy is assembled from the
     # ranks' row shards by an all-to-all over NVLink (1/P of V over each PCIe link instead of all of it)
     def _shard_and_panel(self, v: np.ndarray):
-        """(shard, panel): this rank's rows V[I_p, :] and columns V[:, J_p] as fp32 device tensors."""
+        """(shard, panel): this rank's rows V[I_p, :] and columns V[:, J_p] on the device, in the host dtype.
+        Both come straight from host memory -- the rows as one contiguous run, the columns as a strided 2-D copy
+        (cudaMemcpy2DAsync, 1/P of every row) -- so each PCIe link carries 2/P of V and no inter-GPU step, no
+        staging copy and no lazily-built point-to-point channels are involved (round 1 assembled the columns by
+        an all-to-all of the row shards: 7.4 s at 8 GPUs, mostly NCCL channel setup)."""
         cache = getattr(self, "_chunk_cache", None)
         if cache is not None and cache[0] is v:
             return cache[1]
-        r0, r1 = self.row_range
-        c0, c1 = self.col_range
-        shard = torch.empty((r1 - r0, self.n), dtype=torch.float32, device=self.device)
-        rows_per = max(64, int(self.ROW_CHUNK_BYTES // max(1, v.shape[1] * v.itemsize)) // 64 * 64)
-        for a in range(r0, r1, rows_per):
-            b = min(r1, a + rows_per)
-            shard[a - r0:b - r0].copy_(torch.from_numpy(v[a:b]).to(self.device))      # casts fp64 -> fp32 on the device
-        panel = torch.empty((self.m, c1 - c0), dtype=torch.float32, device=self.device)
-        self._panel_from_shards(shard, panel)
+        (r0, r1), (c0, c1) = self.row_range, self.col_range
+        tdt = torch.float64 if v.dtype == np.float64 else torch.float32
+        es, n = v.itemsize, self.n
+        shard = torch.empty((r1 - r0, n), dtype=tdt, device=self.device)
+        panel = torch.empty((self.m, c1 - c0), dtype=tdt, device=self.device)
+        host = v.ctypes.data
+        check(self.lib.nmfb_upload_2d(shard.data_ptr(), n * es, host + r0 * n * es, n * es, n * es, r1 - r0,
+                                      self.stream))
+        check(self.lib.nmfb_upload_2d(panel.data_ptr(), (c1 - c0) * es, host + c0 * es, n * es, (c1 - c0) * es,
+                                      self.m, self.stream))
         out = (shard, panel)
         if getattr(self, "_keep_chunks", False):
             self._chunk_cache = (v, out)
@@ -333,28 +443,29 @@ class Engine:
         fixed: |max| of my rows from the shard, of my columns from the panel; the row maxima are all-reduced
         because the column pass judges exactness with every row's unit."""
         (r0, r1), (c0, c1) = self.row_range, self.col_range
+        is64 = 1 if shard.dtype == torch.float64 else 0
         vc_none = Data(vc.planes, 0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
         vr_none = Data(vr.planes, 0, c1 - c0, vr.rows_p, vr.ld, vr.nv, 1, vr.fixed, 0)
         vc_local = Data(vc.planes, c1 - c0, vc.cols, vc.rows_p, vc.ld, vc.nv, 1, vc.fixed, 0)
         st = stats.data_ptr()
         if fixed:
             scratch = torch.zeros(max(self.Mp, self.Np), dtype=torch.int32, device=self.device)
-            check(self.lib.nmfb_data_absmax(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, self.n,
+            check(self.lib.nmfb_data_absmax(shard.data_ptr(), is64, shard.stride(0), r0, r1 - r0, self.n,
                                             rowmax.data_ptr(), scratch.data_ptr(), self.stream))
             scratch.zero_()
-            check(self.lib.nmfb_data_absmax(panel.data_ptr(), 0, panel.stride(0), 0, self.m, c1 - c0,
+            check(self.lib.nmfb_data_absmax(panel.data_ptr(), is64, panel.stride(0), 0, self.m, c1 - c0,
                                             scratch.data_ptr(), colmax.data_ptr() + 4 * c0, self.stream))
             allreduce_max_(rowmax, self.group)
-            check(self.lib.nmfb_ingest_data_fixed(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
+            check(self.lib.nmfb_ingest_data_fixed(shard.data_ptr(), is64, shard.stride(0), r0, r1 - r0, C.byref(vr),
                                                   C.byref(vc_none), st, rowmax.data_ptr(), colmax.data_ptr(),
                                                   self.stream))
-            check(self.lib.nmfb_ingest_data_fixed(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
+            check(self.lib.nmfb_ingest_data_fixed(panel.data_ptr(), is64, panel.stride(0), 0, self.m, C.byref(vr_none),
                                                   C.byref(vc_local), st, rowmax.data_ptr(),
                                                   colmax.data_ptr() + 4 * c0, self.stream))
         else:
-            check(self.lib.nmfb_ingest_data(shard.data_ptr(), 0, shard.stride(0), r0, r1 - r0, C.byref(vr),
+            check(self.lib.nmfb_ingest_data(shard.data_ptr(), is64, shard.stride(0), r0, r1 - r0, C.byref(vr),
                                             C.byref(vc_none), st, self.stream))
-            check(self.lib.nmfb_ingest_data(panel.data_ptr(), 0, panel.stride(0), 0, self.m, C.byref(vr_none),
+            check(self.lib.nmfb_ingest_data(panel.data_ptr(), is64, panel.stride(0), 0, self.m, C.byref(vr_none),
                                             C.byref(vc_local), st, self.stream))
 
     def _ingest_pass_sharded(self, v: np.ndarray, nv: int, fixed: bool):
@@ -382,6 +493,15 @@ class Engine:
         Default: the single lossless plane when V is bf16-exact, hi + lo planes otherwise.
         fixed=True (ADMM / AO-ADMM): fixed-point plane + remainder for the exact-hi contractions; falls
         back to the floating planes when two planes cannot hold the data exactly.  Returns min(V)."""
+        import time
+        t_up = time.perf_counter()
+        try:
+            return self._upload_data(v, planes, fixed)
+        finally:
+            self._sync_stream()
+            self.timings["upload_s"] = self.timings.get("upload_s", 0.0) + time.perf_counter() - t_up
+
+    def _upload_data(self, v: np.ndarray, planes: Optional[int] = None, fixed: bool = False) -> float:
         if v.ndim != 2 or v.shape != (self.m, self.n):
             raise ValueError(f"data must be a 2-D array of shape {(self.m, self.n)}")
         if v.dtype not in (np.float32, np.float64):
@@ -449,6 +569,14 @@ class Engine:
 
     def get_factors(self, dtype=np.float64, masters=None) -> Tuple[np.ndarray, np.ndarray]:
         """Download W (m, k) and H (k, n) as host arrays."""
+        import time
+        t_dn = time.perf_counter()
+        try:
+            return self._get_factors(dtype, masters)
+        finally:
+            self.timings["download_s"] = self.timings.get("download_s", 0.0) + time.perf_counter() - t_dn
+
+    def _get_factors(self, dtype=np.float64, masters=None) -> Tuple[np.ndarray, np.ndarray]:
         tdt = torch.float64 if dtype == np.float64 else torch.float32
         w_d = torch.empty((self.m, self.k), dtype=tdt, device=self.device)
         h_d = torch.empty((self.k, self.n), dtype=tdt, device=self.device)
@@ -495,6 +623,12 @@ class Engine:
         if with_aux:
             self.w_aux = FactorBuffers(self.m, KP, dev, self.Mp, self.w.win0, self.w.win_p)
             self.h_aux = FactorBuffers(self.n, KP, dev, self.Np, self.h.win0, self.h.win_p)
+            if self.peer is not None:               # exchange buffers of the auxiliaries: a second arena
+                from .peer import PeerArena
+                self.peer_aux = PeerArena(self.lib, [("xwa", 2 * KP * self.Mp * 4), ("xha", 2 * KP * self.Np * 4)],
+                                          self.device, self.rank, self.world, self.group)
+                self._attach_exchange(self.w_aux, self.peer_aux, "xwa")
+                self._attach_exchange(self.h_aux, self.peer_aux, "xha")
             for src, dst in ((self.w, self.w_aux), (self.h, self.h_aux)):
                 dst.master.copy_(src.master)
                 fs = dst.struct()
@@ -607,7 +741,6 @@ class Engine:
         if int(prox) == 2 and float(lam) != 0.0:
             check(self.lib.nmfb_admm_prepare_l2n(C.byref(pd), C.byref(s), side, float(lam), self.stream))
         flag = self.admm_flags.data_ptr() + 4                                     # flags[1]: inner loop has broken
-        nblk = fac.win_p // 64
         for it in range(admm_iter):
             if it > 0:                                                            # ao_admm.py:83: fresh right-hand side
                 slots = check(self.lib.nmfb_panel_gemm_exact(C.byref(data), other.cplanes.data_ptr(), other.Lp, KP,
@@ -617,11 +750,9 @@ class Engine:
             check(self.lib.nmfb_aoadmm_inner(C.byref(pd), C.byref(s), side, 1, slots, float(lam), int(prox),
                                              self.stream))                        # ao_admm.py:83-85,92
             if self.world > 1:
-                full = self.norm_partial[: 4 * (fac.Lp // 64)]
-                mine = full[4 * nblk * self.rank: 4 * nblk * (self.rank + 1)].clone()
-                allgather_flat(full, mine, self.group)
+                self.gather_norm_partials(fac)
                 if side == 0:
-                    allgather_windows(self.h_aux.master, self.h_aux.win_p, self.group)
+                    self.gather_factor(self.h_aux, refresh=False)
             if side == 0:
                 self.kl_data_step(self.w, self.h_aux, flag)                       # ao_admm.py:88-90,94
             else:
@@ -672,6 +803,7 @@ class Engine:
         self.v_rows = self.v_cols = None
         self.w = self.h = None
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
+        self.peer = self.peer_aux = None
         for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch',
                      'kl_dual_v', 'kl_prod', 'kl_d', 'kl_panel', 'd_rows', 'd_cols'):
             setattr(self, name, None)

@@ -14,19 +14,30 @@ class MurEuStepper:
         self.eng, self.lw, self.lh = eng, float(lambda_w), float(lambda_h)
 
     def prepare(self):
-        self.eng.objective_eu(slot=0)
-        self.eng.reduce_scalar(0)
+        e = self.eng
+        if e.world > 1 and e.peer is not None:
+            e.full_grams()                               # from here on the exchanges keep both Grams current
+        e.objective_eu(slot=0)
+        e.reduce_scalar(0)
 
     def step(self, ring_slot: int):
         e = self.eng
         if e.world == 1:
             e.mur_eu_step(self.lw, self.lh, obj_slot=ring_slot * 8)
             return
-        # sharded: update my window of W, all-gather W, my window of H, all-gather H, partial objective
-        e.mur_eu_half_step(0, self.lw)
-        e.gather_factor(e.w)
-        e.mur_eu_half_step(1, self.lh)
-        e.gather_factor(e.h)
+        if e.peer is None:
+            # host stand-in of the CPU tests: update my window of W, all-gather W, my window of H, all-gather H
+            e.mur_eu_half_step(0, self.lw)
+            e.gather_factor(e.w)
+            e.mur_eu_half_step(1, self.lh)
+            e.gather_factor(e.h)
+        else:
+            # GPUs: my window of W (GEMM on my rows of V + update), then ONE exchange that stores the window and
+            # my term of W^T W into the peers' memory (k x k Gram all-reduce, north_star); the same for H
+            e.mur_eu_window_step(0, self.lw)
+            e.gather_factor(e.w, gram_index=0)
+            e.mur_eu_window_step(1, self.lh)
+            e.gather_factor(e.h, gram_index=1)
         e.objective_eu(slot=ring_slot * 8)
         e.reduce_scalar(ring_slot * 8)
 

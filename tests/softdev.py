@@ -285,6 +285,15 @@ class SoftLib:
         self.launches += 1
         return 0
 
+    def nmfb_upload_2d(self, dst, dst_pitch, src_host, src_pitch, width_bytes, height, stream):
+        """cudaMemcpy2DAsync stand-in: `height` rows of `width_bytes` bytes between pitched buffers."""
+        src = mem(src_host, np.uint8, (height - 1) * src_pitch + width_bytes)
+        out = mem(dst, np.uint8, (height - 1) * dst_pitch + width_bytes)
+        s2 = np.lib.stride_tricks.as_strided(src, (height, width_bytes), (src_pitch, 1))
+        d2 = np.lib.stride_tricks.as_strided(out, (height, width_bytes), (dst_pitch, 1))
+        d2[...] = s2
+        return 0
+
     def nmfb_kl_vaux(self, vr, prod, d_out, ld, dual_v, done_flag, stream):
         vr = _obj(vr)
         assert vr.blocked and 1 <= vr.nv <= 2 and ld >= vr.cols

@@ -77,7 +77,7 @@ def test_ctypes_signatures_match_header_prototypes():
     structs = {"nmfb_data": _lib.Data, "nmfb_factor": _lib.Factor, "nmfb_problem": _lib.Problem,
                "nmfb_admm_state": _lib.AdmmState}
     scalars = {"int": C.c_int, "long": C.c_long, "float": C.c_float, "double": C.c_double, "size_t": C.c_size_t,
-               "unsigned long long": C.c_ulonglong}
+               "unsigned long long": C.c_ulonglong, "unsigned int": C.c_uint}
 
     def to_ctypes(ctype):
         ctype = ctype.replace("const", "").strip()
@@ -284,3 +284,12 @@ def test_argument_and_plan_stage_accepts_the_shape(shape):
                 reached_the_driver(lib.nmfb_gram(C.byref(other), KP, 3, base, pbytes, base, base, 148, None), "gram")
                 reached_the_driver(lib.nmfb_panel_gemm(C.byref(data), base, other.Lp, KP, 3, base, pbytes, self_.Lp,
                                                        148, 0, 0, None), "panel_gemm nb=3")
+
+
+def test_reference_package_name_resolves_to_the_b200_build():
+    """`from nmf import NMF` (reference nmf/__init__.py:1, README.md:18-22) is the drop-in facade."""
+    import nmf
+    import nmf_b200
+    from nmf import NMF
+    from nmf.mur import mur
+    assert NMF is nmf_b200.NMF and mur is nmf_b200.mur.mur and nmf.admm.admm is nmf_b200.admm.admm

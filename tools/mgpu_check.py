@@ -14,6 +14,11 @@ import torch.distributed as dist
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+try:                                   # torchrun sets OMP_NUM_THREADS=1: the fp64 oracle on rank 0 wants the cores
+    from threadpoolctl import threadpool_limits
+    threadpool_limits(max(1, (os.cpu_count() or 1) // world))
+except Exception:                      # noqa: BLE001
+    pass
 from oracle import nmf_oracle as orc
 from nmf_b200.admm import admm
 from nmf_b200.ao_admm import ao_admm
@@ -77,8 +82,8 @@ for (m, n, k, iters) in SHAPES:
         same = [tuple(x) for x in inner] == [tuple(x) for x in tr.inner_breaks]
         ok &= same
         print(f"   inner-iteration pattern {'OK' if same else 'BAD'}", flush=True)
-    if os.environ.get("MGPU_CHECK_PENDING", "0") == "1":
-        # paths whose first GPU run was pending at the end of round 1: l2n prox, Kullback-Leibler branch
+    if os.environ.get("MGPU_CHECK_QUICK", "0") != "1":
+        # SURVEY 8(f) rows sharded: l2n prox, Kullback-Leibler branch of admm / ao_admm
         kw = dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"), min_iter=10**9, max_iter=iters)
         if k <= 128:
             res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
@@ -90,7 +95,34 @@ for (m, n, k, iters) in SHAPES:
                   max_iter=iters)
         res = ao_admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
         report("ao-admm-kl", res, orc.ao_admm_run(v, k, w0, h0, **kw), shape)
+
+
+# ---- the sharded upload (each rank reads its rows and its columns of the host V) must build the very planes the
+# full walk (every rank is shown every chunk and keeps its share) builds: one plane, hi + lo, fixed-point
+def planes_of(v, fixed, full_walk):
+    from nmf_b200.engine import Engine
+    os.environ["NMFB_FULL_WALK_UPLOAD"] = "1" if full_walk else "0"
+    eng = Engine.for_comm(v.shape[0], v.shape[1], 16, True)
+    eng.upload_data(v, fixed=fixed)
+    out = (eng.nv, eng.fixed, eng.v_rows.clone(), eng.v_cols.clone())
+    os.environ["NMFB_FULL_WALK_UPLOAD"] = "0"
+    return out
+
+
+for tag, v, fixed in (("exact fp32", orc.planted(1800, 2300, 16, 3), False),
+                      ("inexact fp64", np.random.default_rng(4).random((1800, 2300)), False),
+                      ("fixed-point", orc.planted(2300, 1800, 16, 5).astype(np.float64), True)):
+    a, b = planes_of(v, fixed, False), planes_of(v, fixed, True)
+    same = a[0] == b[0] and a[1] == b[1] and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
+    flags = same_on_all_ranks(int(same))
+    if rank == 0:
+        ok &= all(flags)
+        print(f"   sharded upload == full walk ({tag}, nv={a[0]}): {'OK' if all(flags) else 'BAD'} {flags}", flush=True)
+
+verdict = torch.tensor([1 if ok else 0], device="cuda")
+dist.broadcast(verdict, src=0)
 if rank == 0:
     print("MGPU CHECK", "PASS" if ok else "FAIL", flush=True)
 dist.barrier()
 dist.destroy_process_group()
+sys.exit(0 if int(verdict.item()) else 1)
