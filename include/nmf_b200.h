@@ -271,6 +271,19 @@ int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side,
                       float lambda, int prox, void* stream);
 int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream);
 
+/* ---- Kullback-Leibler branch of ADMM / AO-ADMM: the data step ----------------------------------- */
+/* planes3 [3][Lp][KP] <- three row-major bf16 planes (24-bit significands) of the factor's master. */
+int nmfb_row_planes3(int KP, const nmfb_factor* f, void* planes3, void* stream);
+/* admm.py:309-313 (`w_aux @ h_aux`, v_aux, dual_v) and ao_admm.py:88-94 (`a @ aux`, ...) fused on this rank's rows
+ * of V: P = A.B is formed tile by tile in tensor memory from the planes of nmfb_row_planes3 (A: rows a_row0.. of the
+ * left factor, B: the right factor) and never written; dual_v is updated in place, d_out = v_aux + dual_v (both fp32
+ * [v_rows->rows_p][ld], ld >= round_up(cols, 128)); rowmax [origin + rows] / colmax [cols] receive the |max| bit
+ * patterns of D for the fixed-point re-ingest (nmfb_ingest_data_fixed).  *done_flag != 0: nothing is touched.
+ * k <= 128.  Replaces the cuBLAS SGEMM + element-wise kernel + |max| pass of round 1. */
+int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, int a_row0, const void* b_planes3,
+                      int b_Lp, int KP, float* dual_v, float* d_out, long ld, uint32_t* rowmax, uint32_t* colmax,
+                      const int* done_flag, int num_sms, void* stream);
+
 /* ---- sharded runs: exchange over NVLink peer memory ------------------------------------------- */
 /* SURVEY.md 8e (1-D MPI-FAUN layout): after a half step every rank owns fresh rows [win0, win0 + win_p) of the
  * factor; the reference has no counterpart (it is single-process).  The exchange is done by the ranks' own

@@ -8,7 +8,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libnmf_b200.so")
-SOURCES = ["capi.cu", "panel_gemm.cu", "panel_gemm_exact.cu", "residual_n256.cu", "residual_ts.cu", "elementwise.cu", "admm.cu", "kl.cu", "kl_ts.cu", "kl_ts2.cu", "peer.cu"]
+SOURCES = ["capi.cu", "panel_gemm.cu", "panel_gemm_exact.cu", "residual_n256.cu", "residual_ts.cu", "elementwise.cu", "admm.cu", "kl.cu", "kl_ts.cu", "kl_ts2.cu", "peer.cu", "kl_data.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",

@@ -109,13 +109,14 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
                 const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
                 if (b > best) best = b;
             }
-    for (int side = 0; side < 2; ++side) {           // exact-hi ADMM contractions (2 data planes)
-        PanelGemmPlan xp;
-        const int R = side == 0 ? m : n, T = side == 0 ? n : m;
-        if (panel_gemm_exact_plan(KP, 2, R, T, 1, num_sms, &xp) != 0) continue;
-        const size_t b = static_cast<size_t>(xp.slots) * KP * nmfb_padded_length(R) * 4;
-        if (b > best) best = b;
-    }
+    for (int side = 0; side < 2; ++side)             // exact-hi ADMM contractions (2 data planes; 3 for the KL data term)
+        for (int na = 2; na <= 3; ++na) {
+            PanelGemmPlan xp;
+            const int R = side == 0 ? m : n, T = side == 0 ? n : m;
+            if (panel_gemm_exact_plan(KP, na, R, T, 1, num_sms, &xp) != 0) continue;
+            const size_t b = static_cast<size_t>(xp.slots) * KP * nmfb_padded_length(R) * 4;
+            if (b > best) best = b;
+        }
     {
         PanelGemmPlan xp;                            // exact Gram: data = the factor's own three planes
         if (panel_gemm_exact_plan(KP, 3, KP, m > n ? m : n, 0, num_sms, &xp) == 0) {
@@ -168,8 +169,8 @@ int nmfb_ingest_data_fixed(const void* src, int src_is_f64, long src_ld, int row
                            const nmfb_data* vc, uint32_t* stats, const uint32_t* rowmax, const uint32_t* colmax,
                            void* stream) {
     if (!rowmax || !colmax) return fail(NMFB_ERR_ARG, "ingest_data_fixed: row / column maxima missing");
-    if (!vr || !vc || vr->nv < 2 || !vr->fixed || !vc->fixed)
-        return fail(NMFB_ERR_ARG, "ingest_data_fixed: needs two fixed-point planes");
+    if (!vr || !vc || vr->nv < 2 || vr->nv > 3 || !vr->fixed || !vc->fixed)
+        return fail(NMFB_ERR_ARG, "ingest_data_fixed: needs two or three fixed-point planes");
     return ingest_common(src, src_is_f64, src_ld, row0, nrows, vr, vc, stats, rowmax, colmax, stream);
 }
 
@@ -731,6 +732,52 @@ int nmfb_kl_vaux(const nmfb_data* v_rows, const float* prod, float* d_out, long 
     CUDA_TRY(kl_vaux_launch(prod, d_out, dual_v, ld, v_rows->rows, v_rows->cols, bf(v_rows->planes),
                             static_cast<long>(v_rows->rows_p) * v_rows->ld, v_rows->rows_p, v_rows->nv, done_flag,
                             st(stream)));
+    return 0;
+}
+
+int nmfb_row_planes3(int KP, const nmfb_factor* f, void* planes3, void* stream) {
+    if (!f || !planes3) return fail(NMFB_ERR_ARG, "row_planes3: null argument");
+    CUDA_TRY(row_planes3_launch(f->master, KP, f->Lp, bf(planes3), st(stream)));
+    return 0;
+}
+
+int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, int a_row0, const void* b_planes3,
+                      int b_Lp, int KP, float* dual_v, float* d_out, long ld, uint32_t* rowmax, uint32_t* colmax,
+                      const int* done_flag, int num_sms, void* stream) {
+    if (!v_rows || !v_rows->planes || !a_planes3 || !b_planes3 || !dual_v || !d_out || !rowmax || !colmax)
+        return fail(NMFB_ERR_ARG, "kl_data_step: null argument");
+    if (!v_rows->blocked || v_rows->nv < 1 || v_rows->nv > 2)
+        return fail(NMFB_ERR_ARG, "kl_data_step: needs K-blocked data planes (nv = 1 or 2)");
+    if (kl_data_smem_bytes(KP, v_rows->nv) < 0)
+        return fail(NMFB_ERR_ARG, "kl_data_step: k <= 128 in this build (KP=%d)", KP);
+    KlDataArgs a;
+    memset(&a, 0, sizeof(a));
+    a.mtiles = (v_rows->rows + 127) / 128;
+    a.ntiles = (v_rows->cols + 127) / 128;
+    if (a.mtiles < 1 || a.ntiles < 1) return fail(NMFB_ERR_ARG, "kl_data_step: empty shard");
+    if (ld < static_cast<long>(a.ntiles) * 128 || (ld & 3) || a.mtiles * 128 > v_rows->rows_p ||
+        a.ntiles * 128 > b_Lp || a_row0 + a.mtiles * 128 > a_Lp)
+        return fail(NMFB_ERR_ARG, "kl_data_step: padded extents too small (ld=%ld rows_p=%d)", ld, v_rows->rows_p);
+    int cs = 2;
+    while (cs > 1 && a.mtiles < 2 * cs) cs >>= 1;
+    a.cluster = cs;
+    int rc;
+    for (int q = 0; q < 3; ++q) {
+        a.a_rpl[q] = bf(a_planes3) + (static_cast<long>(q) * a_Lp + a_row0) * KP;
+        if ((rc = make_map(&a.br[q], bf(b_planes3) + static_cast<long>(q) * b_Lp * KP, b_Lp, KP, 128 / cs))) return rc;
+    }
+    for (int q = 0; q < v_rows->nv; ++q)
+        if ((rc = make_map(&a.v[q], bf(v_rows->planes) + static_cast<long>(q) * v_rows->rows_p * v_rows->ld,
+                           static_cast<long>(v_rows->ld / 64) * v_rows->rows_p, 64, 128))) return rc;
+    a.dual_v = dual_v; a.d_out = d_out; a.ld = ld;
+    a.rowmax = rowmax; a.colmax = colmax; a.done_flag = done_flag; a.row_origin = v_rows->origin;
+    a.KP = KP; a.NV = v_rows->nv; a.v_rows_p = v_rows->rows_p;
+    const long ntot = static_cast<long>((a.mtiles + cs - 1) / cs) * a.ntiles;
+    int ncl = residual_max_clusters(cs, num_sms);
+    if (ntot < ncl) ncl = static_cast<int>(ntot);
+    CUDA_TRY(zero_words_guarded_launch(rowmax + v_rows->origin, v_rows->rows, colmax, v_rows->cols, done_flag,
+                                       st(stream)));
+    CUDA_TRY(kl_data_launch(a, ncl * cs, st(stream)));
     return 0;
 }
 

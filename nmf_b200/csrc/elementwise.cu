@@ -38,14 +38,19 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
             x = static_cast<float>(src[static_cast<long>(r) * src_ld + c]);
             vmin = fminf(vmin, x);
             if (!isfinite(x)) bad = 1;
-            __nv_bfloat16 hi, lo;
-            if (rowmax != nullptr) {                       // fixed-point plane 0 + floating remainder
+            __nv_bfloat16 hi, lo, lo2 = __float2bfloat16_rn(0.f);
+            if (rowmax != nullptr) {                       // fixed-point plane 0 + floating remainder(s)
                 float u, iu;
                 fixed_unit(rowmax[row0 + r], u, iu);
                 const float v0 = fixed_slice(x, u, iu), rem = x - v0;
                 hi = __float2bfloat16_rn(v0);
                 lo = __float2bfloat16_rn(rem);
-                if (__bfloat162float(lo) != rem) need_lo = 1;          // two planes do not hold x exactly
+                float left = rem - __bfloat162float(lo);
+                if (nv > 2) {                              // third plane (KL data term of ADMM: arbitrary fp32 values)
+                    lo2 = __float2bfloat16_rn(left);
+                    left -= __bfloat162float(lo2);
+                }
+                if (left != 0.f) need_lo = 1;              // the planes do not hold x exactly
             } else {
                 split2(x, hi, lo);
                 if (__bfloat162float(lo) != 0.f) need_lo = 1;
@@ -55,6 +60,7 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
                 const long o = blocked_index(lr, c, rowp_rows_p);
                 rowp[o] = hi;
                 if (nv > 1) rowp[rowp_plane + o] = lo;
+                if (nv > 2) rowp[2 * rowp_plane + o] = lo2;
             }
         }
         tile[rr][tx] = x;
@@ -63,7 +69,7 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
     for (int cc = ty; cc < 64; cc += 4) {
         const int c = c0 + cc, r = r0 + tx;
         if (r < nrows && c < ncols && c >= col_lo && c < col_lo + col_n) {
-            __nv_bfloat16 hi, lo;
+            __nv_bfloat16 hi, lo, lo2 = __float2bfloat16_rn(0.f);
             const float x = tile[tx][cc];
             if (colmax != nullptr) {
                 float u, iu;
@@ -71,13 +77,19 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
                 const float v0 = fixed_slice(x, u, iu), rem = x - v0;
                 hi = __float2bfloat16_rn(v0);
                 lo = __float2bfloat16_rn(rem);
-                if (__bfloat162float(lo) != rem) need_lo = 1;
+                float left = rem - __bfloat162float(lo);
+                if (nv > 2) {
+                    lo2 = __float2bfloat16_rn(left);
+                    left -= __bfloat162float(lo2);
+                }
+                if (left != 0.f) need_lo = 1;
             } else {
                 split2(x, hi, lo);
             }
             const long o = blocked_index(c - col_lo, row0 + r, colp_rows_p);
             colp[o] = hi;
             if (nv > 1) colp[colp_plane + o] = lo;
+            if (nv > 2) colp[2 * colp_plane + o] = lo2;
         }
     }
     // block-level fold
@@ -152,6 +164,48 @@ cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int
                                   long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream) {
     refresh_planes_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, adopt, KP, Lp, cpl, cpl_plane, rpl,
                                                                rpl_plane);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// Three row-major bf16 planes [3][Lp][KP] of a master (24-bit significands): operands of the KL data step of
+// ADMM / AO-ADMM (kl_data.cu), whose product has to be fp32-grade.
+__global__ void __launch_bounds__(256)
+row_planes3_kernel(const float* __restrict__ master, int KP, int Lp, __nv_bfloat16* __restrict__ out) {
+    const int r = blockIdx.x * 256 + threadIdx.x;
+    if (r >= Lp) return;
+    const long plane = static_cast<long>(Lp) * KP;
+    for (int c0 = 0; c0 < KP; c0 += 8) {
+        __align__(16) __nv_bfloat16 p0[8], p1[8], p2[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) split3(master[static_cast<long>(c0 + q) * Lp + r], p0[q], p1[q], p2[q]);
+        const long ro = static_cast<long>(r) * KP + c0;
+        *reinterpret_cast<uint4*>(out + ro) = *reinterpret_cast<const uint4*>(p0);
+        *reinterpret_cast<uint4*>(out + plane + ro) = *reinterpret_cast<const uint4*>(p1);
+        *reinterpret_cast<uint4*>(out + 2 * plane + ro) = *reinterpret_cast<const uint4*>(p2);
+    }
+}
+
+cudaError_t row_planes3_launch(const float* master, int KP, int Lp, __nv_bfloat16* out, cudaStream_t stream) {
+    row_planes3_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, KP, Lp, out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// words[0..n) = 0 unless *done_flag != 0 (the |max| tables of the KL data step, whose kernel honours the same flag)
+__global__ void __launch_bounds__(256)
+zero_words_guarded_kernel(unsigned int* __restrict__ a, int na, unsigned int* __restrict__ b, int nb,
+                          const int* __restrict__ done_flag) {
+    if (done_flag != nullptr && *done_flag != 0) return;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < na) a[i] = 0u;
+    if (i < nb) b[i] = 0u;
+}
+
+cudaError_t zero_words_guarded_launch(unsigned int* a, int na, unsigned int* b, int nb, const int* done_flag,
+                                      cudaStream_t stream) {
+    const int n = na > nb ? na : nb;
+    zero_words_guarded_kernel<<<(n + 255) / 256, 256, 0, stream>>>(a, na, b, nb, done_flag);
     count_launch();
     return cudaGetLastError();
 }

@@ -15,6 +15,9 @@ cudaError_t fixed_planes_launch(const float* master, int KP, int Lp, __nv_bfloat
                                 cudaStream_t stream);
 cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int Lp, __nv_bfloat16* cpl,
                                   long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream);
+cudaError_t row_planes3_launch(const float* master, int KP, int Lp, __nv_bfloat16* out, cudaStream_t stream);
+cudaError_t zero_words_guarded_launch(unsigned int* a, int na, unsigned int* b, int nb, const int* done_flag,
+                                      cudaStream_t stream);
 cudaError_t import_factor_launch(const void* src, int is_f64, long stride_l, long stride_c, int L, int k,
                                  float* master, int KP, int Lp, cudaStream_t stream);
 cudaError_t export_factor_launch(const float* master, int KP, int Lp, void* dst, int is_f64, long stride_l,

@@ -72,4 +72,24 @@ int residual_n256_smem_bytes(int KP, int NV);
 cudaError_t residual_ts_launch(const ResidualArgs& args, int grid, cudaStream_t stream);
 int residual_ts_smem_bytes(int KP, int NV);
 
+// ------------------------------------------------------------------ KL data step of ADMM / AO-ADMM (kl_data.cu)
+struct alignas(64) KlDataArgs {
+    CUtensorMap br[3];       // B operand: three row-major planes [Np][KP] of the right factor, box {64, 128 / cluster}
+    CUtensorMap v[2];        // V planes (K-blocked), box {64, 128}
+    const __nv_bfloat16* a_rpl[3];   // A operand: three row-major planes [rows][KP] of the left factor (this rank's rows)
+    float* dual_v;           // [rows_p][ld] fp32, updated in place
+    float* d_out;            // [rows_p][ld] fp32: D = v_aux + dual_v
+    long ld;
+    unsigned int* rowmax;    // |max| bits of D per row (index row_origin + local row) and per column
+    unsigned int* colmax;
+    const int* done_flag;    // AO-ADMM: != 0 -> the kernel does nothing
+    int row_origin;
+    int KP, NV;
+    int mtiles, ntiles;
+    int v_rows_p;
+    int cluster;
+};
+cudaError_t kl_data_launch(const KlDataArgs& args, int grid, cudaStream_t stream);
+int kl_data_smem_bytes(int KP, int NV);
+
 }  // namespace nmfb

@@ -1,8 +1,8 @@
 """Device-side state of one factorisation and the calls that advance it.
 
-PyTorch is used for what it is good at here -- device memory, streams, pinned host buffers --
-and nothing else: every arithmetic step is a kernel of libnmf_b200.so reached through the C ABI
-(`_lib.py`).  There is no CPU path; constructing an Engine without a CUDA device raises.
+PyTorch is used for what it is good at here -- device memory, streams, pinned host buffers, the
+process group -- and nothing else: every arithmetic step of every solver is a kernel of libnmf_b200.so
+reached through the C ABI (`_lib.py`); no library GEMM runs on the loop.  There is no CPU path; constructing an Engine without a CUDA device raises.
 """
 from __future__ import annotations
 
@@ -659,46 +659,59 @@ class Engine:
         if ao:                                   # AO-ADMM contracts against W and H themselves (ao_admm.py:83)
             self._fixed_planes(self.w)
             self._fixed_planes(self.h)
-        rows = self.row_range[1] - self.row_range[0]
-        self.kl_dual_v = torch.zeros((rows, self.n), dtype=torch.float32, device=dev)
-        self.kl_prod = torch.empty((rows, self.n), dtype=torch.float32, device=dev)
-        self.kl_d = torch.zeros((rows, self.n), dtype=torch.float32, device=dev)
+        # dual_v and D for this rank's rows of V, padded to whole 128 x 128 tiles (per_m rows, pitch Np) so that the
+        # fused data step (kl_data.cu) needs no edge cases; the padding stays zero
+        self.kl_dual_v = torch.zeros((self.per_m, self.Np), dtype=torch.float32, device=dev)
+        self.kl_d = torch.zeros((self.per_m, self.Np), dtype=torch.float32, device=dev)
+        # 24-bit row planes of the two operands of P = left . right (nmfb_row_planes3)
+        self.kl_pl_a = torch.zeros((3, self.Mp, self.KP), dtype=torch.bfloat16, device=dev)
+        self.kl_pl_b = torch.zeros((3, self.Np, self.KP), dtype=torch.bfloat16, device=dev)
+        self.kl_scr_r = torch.zeros(self.Mp, dtype=torch.int32, device=dev)
+        self.kl_scr_c = torch.zeros(self.Np, dtype=torch.int32, device=dev)
         self.kl_panel = (torch.empty((self.m, self.col_range[1] - self.col_range[0]), dtype=torch.float32, device=dev)
                          if self.world > 1 else None)
-        self.d_rows = torch.zeros((2, self.Np // 64, self.per_m, 64), dtype=torch.bfloat16, device=dev)
-        self.d_cols = torch.zeros((2, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=dev)
+        # three planes (fixed-point slice + two bf16 remainders = 23 bits): D is an arbitrary fp32 matrix, and two
+        # planes (15 bits) cost 1.2e-4 / 5e-4 of the objective at k = 64 / 128 (profiles/r02c)
+        self.d_rows = torch.zeros((3, self.Np // 64, self.per_m, 64), dtype=torch.bfloat16, device=dev)
+        self.d_cols = torch.zeros((3, self.Mp // 64, self.per_n, 64), dtype=torch.bfloat16, device=dev)
         self.d_rowmax = torch.zeros(self.Mp, dtype=torch.int32, device=dev)
         self.d_colmax = torch.zeros(self.Np, dtype=torch.int32, device=dev)
         self.d_stats = torch.zeros(4, dtype=torch.int32, device=dev)
         vr, vc = self._data_structs()
-        self._d_structs = (Data(self.d_rows.data_ptr(), vr.rows, vr.cols, vr.rows_p, vr.ld, 2, 1, 1, vr.origin),
-                           Data(self.d_cols.data_ptr(), vc.rows, vc.cols, vc.rows_p, vc.ld, 2, 1, 1, vc.origin))
+        self._d_structs = (Data(self.d_rows.data_ptr(), vr.rows, vr.cols, vr.rows_p, vr.ld, 3, 1, 1, vr.origin),
+                           Data(self.d_cols.data_ptr(), vc.rows, vc.cols, vc.rows_p, vc.ld, 3, 1, 1, vc.origin))
         self._problem_d = Problem.from_buffer_copy(self.problem())
         self._problem_d.v_rows, self._problem_d.v_cols = self._d_structs
         self._problem_d.phase_events, self._problem_d.n_phase_events = None, 0
 
     def kl_data_step(self, left: "FactorBuffers", right: "FactorBuffers", done_flag: Optional[int] = None):
-        """admm.py:309-313 / ao_admm.py:88-94 on this rank's rows: P = left^T-master[rows] @ right-master, i.e.
-        (rows x k) @ (k x n) -- a plain fp32 library GEMM --, then one element-wise kernel for v_aux / dual_v
-        that writes D = v_aux + dual_v, then D -> fixed-point planes of both layouts (sharded: the column copy
-        through the all-to-all).  done_flag: device address of the AO-ADMM break flag; once it is set D, dual_v
+        """admm.py:309-313 / ao_admm.py:88-94 on this rank's rows: ONE tcgen05 kernel forms P = left^T[rows] . right
+        tile by tile in tensor memory (never in HBM), does the v_aux / dual_v step and writes D = v_aux + dual_v with
+        its row / column |max| (nmfb_kl_data_step); then D -> fixed-point planes of both layouts (sharded: the column
+        copy through the all-to-all).  done_flag: device address of the AO-ADMM break flag; once it is set D, dual_v
         and therefore the planes stay what they are."""
-        k, n = self.k, self.n
+        KP, n = self.KP, self.n
         r0, r1 = self.row_range
-        torch.matmul(left.master[:k, r0:r1].t(), right.master[:k, :n], out=self.kl_prod)
+        ls, rs = left.struct(), right.struct()
+        check(self.lib.nmfb_row_planes3(KP, C.byref(ls), self.kl_pl_a.data_ptr(), self.stream))
+        check(self.lib.nmfb_row_planes3(KP, C.byref(rs), self.kl_pl_b.data_ptr(), self.stream))
         vr, _vc = self._data_structs()
         d = self.kl_d
-        check(self.lib.nmfb_kl_vaux(C.byref(vr), self.kl_prod.data_ptr(), d.data_ptr(), d.stride(0),
-                                    self.kl_dual_v.data_ptr(), done_flag, self.stream))
-        self.d_rowmax.zero_()
-        self.d_colmax.zero_()
+        sharded = self.world > 1
+        rowmax = self.kl_scr_r if sharded else self.d_rowmax      # sharded: the ingest below takes its own maxima
+        colmax = self.kl_scr_c if sharded else self.d_colmax
+        check(self.lib.nmfb_kl_data_step(C.byref(vr), self.kl_pl_a.data_ptr(), self.Mp, r0 if sharded else 0,
+                                         self.kl_pl_b.data_ptr(), self.Np, KP, self.kl_dual_v.data_ptr(), d.data_ptr(),
+                                         d.stride(0), rowmax.data_ptr(), colmax.data_ptr(), done_flag, self.num_sms,
+                                         self.stream))
         dr, dc = self._d_structs
-        if self.world > 1:
-            self._panel_from_shards(d, self.kl_panel)
-            self._ingest_shard_and_panel(d, self.kl_panel, dr, dc, self.d_stats, self.d_rowmax, self.d_colmax, True)
+        if sharded:
+            self.d_rowmax.zero_()
+            self.d_colmax.zero_()
+            live = d[: r1 - r0, :n]
+            self._panel_from_shards(live, self.kl_panel)
+            self._ingest_shard_and_panel(live, self.kl_panel, dr, dc, self.d_stats, self.d_rowmax, self.d_colmax, True)
             return
-        check(self.lib.nmfb_data_absmax(d.data_ptr(), 0, d.stride(0), 0, self.m, n, self.d_rowmax.data_ptr(),
-                                        self.d_colmax.data_ptr(), self.stream))
         check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, d.stride(0), 0, self.m, C.byref(dr), C.byref(dc),
                                               self.d_stats.data_ptr(), self.d_rowmax.data_ptr(),
                                               self.d_colmax.data_ptr(), self.stream))
@@ -805,6 +818,6 @@ class Engine:
         self.partial = self.obj_partial = self.gram32 = self.gram64 = None
         self.peer = self.peer_aux = None
         for name in ('dual_w', 'dual_h', 'ainv', 'c64', 'w_aux', 'h_aux', 'norm_partial', 'chol_scratch', 'binv', 'tik_scratch',
-                     'kl_dual_v', 'kl_prod', 'kl_d', 'kl_panel', 'd_rows', 'd_cols'):
+                     'kl_dual_v', 'kl_d', 'kl_panel', 'd_rows', 'd_cols', 'kl_pl_a', 'kl_pl_b'):
             setattr(self, name, None)
         self._problem = None

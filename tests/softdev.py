@@ -100,16 +100,23 @@ def _planes(d):
     return mem(d.planes, np.uint16, d.nv * nb * d.rows_p * 64).reshape(d.nv, nb, d.rows_p, 64)
 
 
-def _split(x, unit):
-    """(hi, lo, inexact) of one copy: fixed-point slice + bf16 remainder when `unit` is given, else hi / lo."""
+def _split(x, unit, nv=2):
+    """((hi, lo, lo2), inexact) of one copy: fixed-point slice + bf16 remainder(s) when `unit` is given, else hi / lo.
+    nv = 3 (the KL data term of ADMM): a second remainder plane, exactness judged after it."""
+    zero = np.zeros_like(x, dtype=np.float32)
     if unit is None:
         hi = bf16_grid(x)
         lo = bf16_grid(x - hi)
-        return hi, lo, lo != 0
+        return (hi, lo, zero), lo != 0
     hi0 = (np.rint(x * (np.float32(1.0) / unit)) * unit).astype(np.float32)
     rem = (x - hi0).astype(np.float32)
     lo = bf16_grid(rem)
-    return bf16_grid(hi0), lo, lo != rem
+    left = (rem - lo).astype(np.float32)
+    lo2 = zero
+    if nv > 2:
+        lo2 = bf16_grid(left)
+        left = (left - lo2).astype(np.float32)
+    return (bf16_grid(hi0), lo, lo2), left != 0
 
 
 def np_ingest(x, row0, vr, vc, stats, rowmax, colmax):
@@ -117,12 +124,12 @@ def np_ingest(x, row0, vr, vc, stats, rowmax, colmax):
     nrows, ncols = x.shape
     fixed = rowmax is not None
     with np.errstate(all="ignore"):
-        hi, lo, inex = _split(x, fixed_units(rowmax[row0:row0 + nrows])[:, None] if fixed else None)
+        planes, inex = _split(x, fixed_units(rowmax[row0:row0 + nrows])[:, None] if fixed else None, vr.nv)
         pr = _planes(vr)
         lr = np.arange(nrows) + row0 - vr.origin
         ok = (lr >= 0) & (lr < vr.rows)
         pad = np.zeros((nrows, vr.ld), np.uint16)
-        for q, val in enumerate((hi, lo)[:vr.nv]):
+        for q, val in enumerate(planes[:vr.nv]):
             pad[:, :ncols] = bf16_bits(val)
             blk = pad.reshape(nrows, vr.ld // 64, 64).transpose(1, 0, 2)       # [nb][nrows][64]
             nbc = (ncols + 63) // 64
@@ -134,13 +141,13 @@ def np_ingest(x, row0, vr, vc, stats, rowmax, colmax):
         c0, c1 = vc.origin, min(vc.origin + vc.rows, ncols)
         if c1 > c0:
             xt = np.ascontiguousarray(x[:, c0:c1].T)                           # (cols in window, nrows)
-            hi, lo, inex = _split(xt, fixed_units(colmax[c0:c1])[:, None] if fixed else None)
+            planes, inex = _split(xt, fixed_units(colmax[c0:c1])[:, None] if fixed else None, vc.nv)
             if fixed:
                 need_lo = need_lo or bool(inex.any())
             pc = _planes(vc)
             g = np.arange(nrows) + row0                                        # column index in the V^T copy
             lc = np.arange(c1 - c0)[None, :]                                   # local column = row of the V^T copy
-            for q, val in enumerate((hi, lo)[:vc.nv]):
+            for q, val in enumerate(planes[:vc.nv]):
                 pc[q][(g >> 6)[:, None], lc, (g & 63)[:, None]] = bf16_bits(val).T
     vmin = np.float32(x.min()) if x.size else np.float32(np.inf)
     bits = int(np.array([vmin], np.float32).view(np.uint32)[0])
@@ -304,6 +311,36 @@ class SoftLib:
         view = lambda ptr: np.lib.stride_tricks.as_strided(mem(ptr, np.float32, n), shape, st)   # noqa: E731
         np_kl_vaux(view(prod), view(d_out), view(dual_v), self.decode(vr))
         self.launches += 1
+        return 0
+
+    def nmfb_row_planes3(self, KP, f, planes3, stream):
+        """The three 24-bit row planes of a master: the stand-in keeps the fp32 values they represent."""
+        fac = Fac(_obj(f), KP)
+        if not hasattr(self, "planes3"):
+            self.planes3 = {}
+        self.planes3[int(planes3)] = fac.master.copy()
+        self.launches += 1
+        return 0
+
+    def nmfb_kl_data_step(self, vr, a_planes3, a_Lp, a_row0, b_planes3, b_Lp, KP, dual_v, d_out, ld, rowmax, colmax,
+                          done_flag, num_sms, stream):
+        """kl_data.cu at the semantic level: P = A.B in fp32-grade arithmetic, the v_aux / dual_v step, |max| of D."""
+        vr = _obj(vr)
+        assert vr.blocked and 1 <= vr.nv <= 2 and ld >= vr.cols and KP <= 128
+        if done_flag and mem(done_flag, np.int32, 1)[0] != 0:
+            return 0
+        a = self.planes3[int(a_planes3)][:, a_row0:a_row0 + vr.rows].T.astype(np.float64)
+        b = self.planes3[int(b_planes3)][:, :vr.cols].astype(np.float64)
+        prod = (a @ b).astype(np.float32)
+        n = (vr.rows - 1) * ld + vr.cols
+        shape, st = (vr.rows, vr.cols), (ld * 4, 4)
+        view = lambda ptr: np.lib.stride_tricks.as_strided(mem(ptr, np.float32, n), shape, st)   # noqa: E731
+        np_kl_vaux(prod, view(d_out), view(dual_v), self.decode(vr))
+        rm, cm = mem(rowmax, np.uint32, vr.origin + vr.rows), mem(colmax, np.uint32, vr.cols)
+        rm[vr.origin:] = 0
+        cm[:] = 0
+        np_absmax(view(d_out), vr.origin, rm, cm)
+        self.launches += 2
         return 0
 
     # ------------------------------------------------------------------ factors
@@ -538,7 +575,7 @@ class SoftLib:
         fac = self.cpl_owner[int(cplanes)]
         fac = Fac(fac.f, KP)
         self._need_cpl(fac, "fixed", "panel_gemm_exact: factor operand")
-        assert data.fixed and data.nv == 2 and factor_Lp == fac.Lp and data.cols == fac.L
+        assert data.fixed and data.nv in (2, 3) and factor_Lp == fac.Lp and data.cols == fac.L
         k = self._k
         self.numer = fac.master[:k, :fac.L].astype(np.float64) @ self.decode(data).T
         self.launches += 1
