@@ -93,6 +93,7 @@ unsigned long long nmfb_launch_count(void);
 int nmfb_padded_components(int k);                 /* 64 / 128 / 256, or NMFB_ERR_ARG if k > 256 */
 int nmfb_padded_length(int L);                     /* round_up(L, 256) */
 size_t nmfb_partial_bytes(int m, int n, int k, int num_sms);   /* workspace for any GEMM of the problem */
+size_t nmfb_gram_partial_bytes(int k, int L, int num_sms);     /* scratch of a Gram over a factor of length L */
 int nmfb_obj_partial_len(int m, int n, int num_sms);
 
 /* ---- ingest / export ------------------------------------------------------------------------ */
@@ -212,6 +213,17 @@ typedef struct nmfb_admm_state {
     double* binv;                   /* fp64 [2][KP][KP] or NULL: inverse Tikhonov systems of prox l2n,    */
                                     /* ((lambda/rho) T^T T + I)^-1, [0] H-side, [1] W-side (admm.py:141-156) */
     double* tik_scratch;            /* fp64 [KP][KP] + [4] scratch for building them (NULL iff binv NULL) */
+    /* Optional overlap of the k x k work with the m x n x k numerator GEMM (all NULL / 0: everything on `stream`).
+     * The Gram, its Cholesky inverse (a single-CTA latency chain, ~0.2 ms at k = 128) and the Tikhonov system do not
+     * depend on the numerator; with a side stream they run next to it: the half step records ev_fork on `stream`,
+     * the side stream waits for it, does the k x k work with gram_partial as its scratch, records ev_join, and
+     * `stream` waits for ev_join before the solve / prox / dual kernel.  The numerator GEMM then leaves two SMs
+     * free for the single-CTA kernels. */
+    void* side_stream;              /* cudaStream_t or NULL                                               */
+    void* ev_fork;                  /* cudaEvent_t (timing disabled is fine)                              */
+    void* ev_join;                  /* cudaEvent_t                                                        */
+    float* gram_partial;            /* scratch of the Gram contraction on the side stream                 */
+    size_t gram_partial_bytes;      /* >= nmfb_gram_partial_bytes(k, max(m, n), num_sms)                  */
 } nmfb_admm_state;
 
 /* prox l2n with lambda > 0 (k <= 128): (re)build s->binv[side] from lambda and the rho of that side's system

@@ -45,7 +45,9 @@ class AdmmState(C.Structure):       # struct nmfb_admm_state
     _fields_ = [("w_aux", Factor), ("h_aux", Factor), ("dual_w", c_void_p), ("dual_h", c_void_p),
                 ("ainv", c_void_p), ("chol_scratch", c_void_p), ("c64", c_void_p), ("scal", c_void_p),
                 ("flags", c_void_p), ("norm_partial", c_void_p), ("exact", c_int),
-                ("binv", c_void_p), ("tik_scratch", c_void_p)]
+                ("binv", c_void_p), ("tik_scratch", c_void_p),
+                ("side_stream", c_void_p), ("ev_fork", c_void_p), ("ev_join", c_void_p),
+                ("gram_partial", c_void_p), ("gram_partial_bytes", c_size_t)]
 
 
 _SIGNATURES = {
@@ -56,6 +58,7 @@ _SIGNATURES = {
     "nmfb_padded_length": (c_int, [c_int]),
     "nmfb_partial_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "nmfb_obj_partial_len": (c_int, [c_int, c_int, c_int]),
+    "nmfb_gram_partial_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nmfb_ingest_data": (c_int, [c_void_p, c_int, c_long, c_int, c_int, P(Data), P(Data), c_void_p, c_void_p]),
     "nmfb_ingest_data_fixed": (c_int, [c_void_p, c_int, c_long, c_int, c_int, P(Data), P(Data), c_void_p, c_void_p,
                                        c_void_p, c_void_p]),

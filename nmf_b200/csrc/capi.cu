@@ -109,14 +109,15 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
                 const size_t b = static_cast<size_t>(pl.slots) * KP * nmfb_padded_length(Ls[i]) * 4;
                 if (b > best) best = b;
             }
-    for (int side = 0; side < 2; ++side)             // exact-hi ADMM contractions (2 data planes; 3 for the KL data term)
-        for (int na = 2; na <= 3; ++na) {
-            PanelGemmPlan xp;
-            const int R = side == 0 ? m : n, T = side == 0 ? n : m;
-            if (panel_gemm_exact_plan(KP, na, R, T, 1, num_sms, &xp) != 0) continue;
-            const size_t b = static_cast<size_t>(xp.slots) * KP * nmfb_padded_length(R) * 4;
-            if (b > best) best = b;
-        }
+    for (int side = 0; side < 2; ++side)             // exact-hi ADMM contractions (2 data planes; 3 for the KL data term),
+        for (int na = 2; na <= 3; ++na)              // on all SMs or with one CTA pair left to the side stream
+            for (int sms = num_sms - 2; sms <= num_sms; sms += 2) {
+                PanelGemmPlan xp;
+                const int R = side == 0 ? m : n, T = side == 0 ? n : m;
+                if (sms < 2 || panel_gemm_exact_plan(KP, na, R, T, 1, sms, &xp) != 0) continue;
+                const size_t b = static_cast<size_t>(xp.slots) * KP * nmfb_padded_length(R) * 4;
+                if (b > best) best = b;
+            }
     {
         PanelGemmPlan xp;                            // exact Gram: data = the factor's own three planes
         if (panel_gemm_exact_plan(KP, 3, KP, m > n ? m : n, 0, num_sms, &xp) == 0) {
@@ -132,6 +133,24 @@ size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
             const size_t b = static_cast<size_t>(kp.slots) * KP * nmfb_padded_length(R) * 4;
             if (b > best) best = b;
         }
+    return best;
+}
+
+size_t nmfb_gram_partial_bytes(int k, int L, int num_sms) {
+    const int KP = nmfb_padded_components(k);
+    if (KP < 0) return 0;
+    size_t best = 0;
+    for (int nb = 2; nb <= 3; ++nb) {
+        PanelGemmPlan pl;
+        if (panel_gemm_plan(KP, nb, nb, KP, L, 128, 0, num_sms, &pl) != 0) continue;
+        const size_t b = static_cast<size_t>(pl.slots) * KP * 256 * 4;
+        if (b > best) best = b;
+    }
+    PanelGemmPlan xp;
+    if (panel_gemm_exact_plan(KP, 3, KP, L, 0, num_sms, &xp) == 0) {
+        const size_t b = static_cast<size_t>(xp.slots) * KP * 256 * 4;
+        if (b > best) best = b;
+    }
     return best;
 }
 
@@ -652,22 +671,51 @@ int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* par
 }
 
 // Gram and numerator contraction of one ADMM side, in the floating 3-plane or the exact-hi arithmetic.
-int admm_gram(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_factor* f, int side, void* stream) {
+// The k x k work of a half step may run on the caller's side stream next to the numerator GEMM (nmfb_admm_state).
+struct KxK {
+    void* stream;            // where Gram / Cholesky / Tikhonov go
+    float* partial;          // scratch of the Gram contraction
+    size_t partial_bytes;
+    bool forked;
+};
+KxK kxk_begin(const nmfb_problem* p, const nmfb_admm_state* s, void* stream) {
+    KxK k{stream, p->partial, p->partial_bytes, false};
+    if (s->side_stream && s->ev_fork && s->ev_join && s->gram_partial) {
+        if (cudaEventRecord(static_cast<cudaEvent_t>(s->ev_fork), st(stream)) == cudaSuccess &&
+            cudaStreamWaitEvent(st(s->side_stream), static_cast<cudaEvent_t>(s->ev_fork), 0) == cudaSuccess) {
+            k.stream = s->side_stream; k.partial = s->gram_partial; k.partial_bytes = s->gram_partial_bytes;
+            k.forked = true;
+        }
+    }
+    return k;
+}
+int kxk_join(const nmfb_admm_state* s, const KxK& k, void* stream) {
+    if (!k.forked) return 0;
+    CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(s->ev_join), st(k.stream)));
+    CUDA_TRY(cudaStreamWaitEvent(st(stream), static_cast<cudaEvent_t>(s->ev_join), 0));
+    return 0;
+}
+
+int admm_gram(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_factor* f, int side, const KxK& k) {
     const size_t gsz = static_cast<size_t>(p->KP) * p->KP;
     if (s->exact)
-        return nmfb_gram_exact(f, p->KP, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
-                               p->num_sms, stream);
-    return nmfb_gram(f, p->KP, 3, p->partial, p->partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
-                     p->num_sms, stream);
+        return nmfb_gram_exact(f, p->KP, k.partial, k.partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
+                               p->num_sms, k.stream);
+    return nmfb_gram(f, p->KP, 3, k.partial, k.partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
+                     p->num_sms, k.stream);
 }
 int admm_gemm(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_data* data, const nmfb_factor* other,
-              const nmfb_factor* self, void* stream) {
+              const nmfb_factor* self, bool leave_room, void* stream) {
     // sharded runs: this rank's rows of the product land at its window of the full-pitch partial
     float* out = p->partial + window_of(self).w0;
+    // leave_room: the k x k kernels run next to this GEMM on the side stream; the single-CTA Cholesky needs an SM
+    // of its own (it cannot share one with a GEMM CTA: 132 KB + ~200 KB of shared memory), so the persistent grid
+    // leaves one CTA pair out
+    const int sms = leave_room ? p->num_sms - 2 : p->num_sms;
     if (s->exact) {
         if (!data->fixed) return fail(NMFB_ERR_ARG, "admm: exact mode needs fixed-point data planes");
         return nmfb_panel_gemm_exact(data, other->cplanes, other->Lp, p->KP, out, p->partial_bytes, self->Lp,
-                                     p->num_sms, stream);
+                                     sms, stream);
     }
     return nmfb_panel_gemm(data, other->cplanes, other->Lp, p->KP, 3, out, p->partial_bytes, self->Lp,
                            p->num_sms, 0, 0, stream);
@@ -707,13 +755,15 @@ int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int sid
     const nmfb_factor* self_aux = side == 0 ? &s->h_aux : &s->w_aux;
     const nmfb_data* data = side == 0 ? &p->v_cols : &p->v_rows;
     float* dual = side == 0 ? s->dual_h : s->dual_w;
-    if ((rc = admm_gram(p, s, other_aux, side, stream)) < 0) return rc;
+    const KxK kx = kxk_begin(p, s, stream);
+    if ((rc = admm_gram(p, s, other_aux, side, kx)) < 0) return rc;
     if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + side * gsz,
-                                s->scal + side, s->flags, stream)) < 0) return rc;
-    if (prox == NMFB_PROX_L2N && lambda != 0.f && (rc = nmfb_admm_prepare_l2n(p, s, side, lambda, stream)) < 0) return rc;
+                                s->scal + side, s->flags, kx.stream)) < 0) return rc;
+    if (prox == NMFB_PROX_L2N && lambda != 0.f && (rc = nmfb_admm_prepare_l2n(p, s, side, lambda, kx.stream)) < 0) return rc;
     mark(p, 1 + 3 * side, stream);
-    const int slots = admm_gemm(p, s, data, other_aux, self, stream);
+    const int slots = admm_gemm(p, s, data, other_aux, self, kx.forked, stream);
     if (slots < 0) return slots;
+    if ((rc = kxk_join(s, kx, stream)) < 0) return rc;
     mark(p, 2 + 3 * side, stream);
     return admm_apply(p, s, p->partial, slots, false, side, self, dual, self_aux, lambda, prox, false, false, stream);
 }
@@ -818,12 +868,14 @@ int nmfb_aoadmm_side_begin(const nmfb_problem* p, const nmfb_admm_state* s, int 
     const size_t gsz = static_cast<size_t>(KP) * KP;
     int rc;
     CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
-    if ((rc = admm_gram(p, s, other, side, stream)) < 0) return rc;                   // ao_admm.py:53-55
+    const KxK kx = kxk_begin(p, s, stream);
+    if ((rc = admm_gram(p, s, other, side, kx)) < 0) return rc;                       // ao_admm.py:53-55
     if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
-                                s->scal + side, s->flags, stream)) < 0) return rc;
+                                s->scal + side, s->flags, kx.stream)) < 0) return rc;
     mark(p, 1 + 3 * side, stream);
-    const int slots = admm_gemm(p, s, data, other, self, stream);                     // ao_admm.py:56
+    const int slots = admm_gemm(p, s, data, other, self, kx.forked, stream);          // ao_admm.py:56
     if (slots < 0) return slots;
+    if ((rc = kxk_join(s, kx, stream)) < 0) return rc;
     mark(p, 2 + 3 * side, stream);
     return slots;
 }

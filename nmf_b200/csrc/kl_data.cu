@@ -24,6 +24,13 @@ constexpr int kThreadsD = 384;
 constexpr int kBox = 128 * 128;      // bytes of one [128 rows x 64 bf16] box
 constexpr int kPrefetchD = 6;        // L2 prefetch distance of the V stream, in 128 x 128 tiles
 
+// 16-byte global load issued where it is written (the epilogue reads dual_v and writes it back in place).
+__device__ __forceinline__ float4 ld_global_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
 struct KdLayout {
     int b_stage_bytes, v_buf_bytes;
     int nbs, nvs;
@@ -323,33 +330,43 @@ kl_data_kernel(const __grid_constant__ KlDataArgs args) {
                     if (lane == 0) mbar_arrive(a_full);
                 }
             }
-            mbar_wait(&acc_full[acc], accph);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + hb * 64;
-            // Both halves of this warp's 64 columns go to registers first and the accumulator is handed
-            // back at once: the issuer of tile t + 2 waits for the TMEM read-out only (64 B/cycle/SM, i.e.
-            // ~1000 cycles per tile), not for the arithmetic below.
-            uint32_t s[2][32];
-            tmem_ld32(taddr, s[0]);
-            tmem_ld32(taddr + 32, s[1]);
-            tmem_ld_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[acc]);
-            mbar_wait(&v_full[vs], vph);
-            const uint8_t* vrow = v_smem + vs * L.v_buf_bytes + hb * kBox + row * 128;
             // v_aux / dual_v step (admm.py:309-313, ao_admm.py:88-94) on this thread's row, 64 columns:
             //   v_bar = P - dual_v;  v_aux = ((v_bar - 1) + sqrt((v_bar - 1)^2 + 4 v)) / 2  (cancellation-free form
             //   for v_bar < 1, fp64);  dual_v += v_aux - P;  D = v_aux + dual_v  -> fp32, plus |max| of D per row / column
+            // The kernel is bound by the 12 B per element of dual_v / D traffic, not by the MMAs: the 32 dual_v values of
+            // a column half are requested BEFORE the wait for the accumulator / the TMEM read-out, so that 128 B per
+            // thread (32 KB per SM) are in flight -- the first version loaded 32 B per thread between two fp64 square
+            // roots and ran at 2 TB/s (profiles/r02d).
             const int ti_e = min(static_cast<int>(t / args.ntiles) * CS + static_cast<int>(crank), args.mtiles - 1);
             const int tj_e = static_cast<int>(t - (t / args.ntiles) * args.ntiles);
             const long grow = static_cast<long>(ti_e) * 128 + row;                  // row of this rank's shard
             const int col0 = tj_e * 128 + hb * 64;
             float* dvp = args.dual_v + grow * args.ld + col0;
             float* dop = args.d_out + grow * args.ld + col0;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + hb * 64;
             unsigned int rmax = 0, cmine = 0, cmine2 = 0;
+            const uint8_t* vrow = nullptr;
 #pragma unroll
             for (int g = 0; g < 2; ++g) {
+                float4 dq[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    dq[j] = live ? ld_global_f4(dvp + g * 32 + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (g == 0) {
+                    mbar_wait(&acc_full[acc], accph);
+                    tc_fence_after();
+                }
+                uint32_t s[32];
+                tmem_ld32(taddr + g * 32, s);
+                tmem_ld_wait();
+                if (g == 1) {                                  // both halves read: the accumulator goes back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[acc]);
+                } else {
+                    mbar_wait(&v_full[vs], vph);
+                    vrow = v_smem + vs * L.v_buf_bytes + hb * kBox + row * 128;
+                }
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     const int chunk = (g * 4 + c8) ^ (row & 7);          // SWIZZLE_128B
@@ -371,19 +388,12 @@ kl_data_kernel(const __grid_constant__ KlDataArgs args) {
                         }
                     }
                     const int cofs = g * 32 + c8 * 8;
-                    float dv[8], dn[8], dd[8];
-                    if (live) {
-                        const float4 x0 = *reinterpret_cast<const float4*>(dvp + cofs);
-                        const float4 x1 = *reinterpret_cast<const float4*>(dvp + cofs + 4);
-                        dv[0] = x0.x; dv[1] = x0.y; dv[2] = x0.z; dv[3] = x0.w;
-                        dv[4] = x1.x; dv[5] = x1.y; dv[6] = x1.z; dv[7] = x1.w;
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) dv[e] = 0.f;
-                    }
+                    const float dv[8] = {dq[2 * c8].x, dq[2 * c8].y, dq[2 * c8].z, dq[2 * c8].w,
+                                         dq[2 * c8 + 1].x, dq[2 * c8 + 1].y, dq[2 * c8 + 1].z, dq[2 * c8 + 1].w};
+                    float dn[8], dd[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        const double P = static_cast<double>(__uint_as_float(s[g][c8 * 8 + e]));
+                        const double P = static_cast<double>(__uint_as_float(s[c8 * 8 + e]));
                         const double v = static_cast<double>(vv[e]);
                         const double tq = P - static_cast<double>(dv[e]) - 1.0;
                         const double root = sqrt(fma(tq, tq, 4.0 * v));

@@ -298,6 +298,7 @@ int panel_gemm_exact_plan(int KP, int NA, int L, int R, int blocked, int num_sms
         ncl = probe.max_clusters;
     else if (cluster > 1)
         ncl = num_sms / cluster * 3 / 4;
+    if (ncl > num_sms / cluster) ncl = num_sms / cluster;     // a caller may hand over fewer SMs than the device has
     int nsplit = 1;
     double best = 1e30;
     for (int s = 1; s <= 64; ++s) {

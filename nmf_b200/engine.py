@@ -642,10 +642,26 @@ class Engine:
             if exact:                           # AO-ADMM contracts against W and H themselves
                 self._fixed_planes(self.w)
                 self._fixed_planes(self.h)
+        side = self._side_stream_handles(Lmax)
         self._admm = AdmmState(wa, ha, self.dual_w.data_ptr(), self.dual_h.data_ptr(), self.ainv.data_ptr(),
                                self.chol_scratch.data_ptr(), self.c64.data_ptr(), self.admm_scal.data_ptr(),
                                self.admm_flags.data_ptr(), self.norm_partial.data_ptr(), int(exact),
-                               self.binv.data_ptr(), self.tik_scratch.data_ptr())
+                               self.binv.data_ptr(), self.tik_scratch.data_ptr(), *side)
+
+    def _side_stream_handles(self, Lmax: int):
+        """(side stream, fork event, join event, Gram scratch, its bytes) of nmfb_admm_state: the k x k work of a
+        half step (Gram, single-CTA Cholesky inverse, Tikhonov system) runs next to the numerator GEMM.  The host
+        stand-in of the CPU tests has no streams: all NULL, i.e. everything on the one stream."""
+        if torch.device(self.device).type != "cuda":
+            return (None, None, None, None, 0)
+        nbytes = int(self.lib.nmfb_gram_partial_bytes(self.k, Lmax, self.num_sms))
+        self.gram_partial = torch.empty(max(nbytes, 4) // 4, dtype=torch.float32, device=self.device)
+        self.side_stream = torch.cuda.Stream(device=self.device)
+        self._side_events = (torch.cuda.Event(), torch.cuda.Event())
+        for ev in self._side_events:
+            ev.record(torch.cuda.current_stream(self.device))         # materialises the cudaEvent_t
+        return (self.side_stream.cuda_stream, int(self._side_events[0].cuda_event),
+                int(self._side_events[1].cuda_event), self.gram_partial.data_ptr(), self.gram_partial.numel() * 4)
 
     # ------------------------------------------------------------------ ADMM, Kullback-Leibler branch
     def alloc_admm_kl(self, ao: bool = False):
