@@ -520,8 +520,9 @@ def run_b200(args):
                    "v_storage": "bf16 (lossless, V and V^T resident)", "l2": "inputs_exceed_l2",
                    "objective_every_iteration": True, "parallelism": f"rows/cols x{world}",
                    "exchange": ("none" if world == 1 else
-                                "peer-memory stores + device barrier (csrc/peer.cu), k x k Gram terms reduced in the "
-                                "same exchange" if getattr(eng, "peer", None) is not None else "torch.distributed"),
+                                ("NVSwitch multicast stores (multimem.st)" if getattr(eng.peer, "mc_ptr", 0) else
+                                 "peer-memory stores") + " + device barrier (csrc/peer.cu), k x k Gram terms reduced in "
+                                "the same exchange" if getattr(eng, "peer", None) is not None else "torch.distributed"),
                    **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
         "clocks": clk.summary(),
         "gpu_launches": int(launches_per_step * steps),

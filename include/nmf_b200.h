@@ -97,8 +97,8 @@ size_t nmfb_gram_partial_bytes(int k, int L, int num_sms);     /* scratch of a G
 int nmfb_obj_partial_len(int m, int n, int num_sms);
 
 /* ---- ingest / export ------------------------------------------------------------------------ */
-/* Split a chunk of `nrows` rows of the caller's V (fp32 or fp64, row-major, pitch src_ld elements,
- * already on the device) starting at global row `row0` into the row-major planes of `v_rows` and the
+/* Split a chunk of `nrows` rows of the caller's V (fp32 or fp64, row-major, pitch src_ld elements -- or, with
+ * src_ld < 0, K-blocked [cols / 64][-src_ld][64] like the data planes --, already on the device) starting at global row `row0` into the row-major planes of `v_rows` and the
  * transposed planes of `v_cols`.  stats[0] = order-preserving key of min(V) (init 0xFFFFFFFF),
  * stats[1] = 1 if a lo plane is needed, stats[2] = 1 if a non-finite value was seen.
  * Replaces the implicit float64 view of `x` in mur.py:52 / admm.py:233 / ao_admm.py:201. */
@@ -288,9 +288,10 @@ int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int 
 int nmfb_row_planes3(int KP, const nmfb_factor* f, void* planes3, void* stream);
 /* admm.py:309-313 (`w_aux @ h_aux`, v_aux, dual_v) and ao_admm.py:88-94 (`a @ aux`, ...) fused on this rank's rows
  * of V: P = A.B is formed tile by tile in tensor memory from the planes of nmfb_row_planes3 (A: rows a_row0.. of the
- * left factor, B: the right factor) and never written; dual_v is updated in place, d_out = v_aux + dual_v (both fp32
- * [v_rows->rows_p][ld], ld >= round_up(cols, 128)); rowmax [origin + rows] / colmax [cols] receive the |max| bit
- * patterns of D for the fixed-point re-ingest (nmfb_ingest_data_fixed).  *done_flag != 0: nothing is touched.
+ * left factor, B: the right factor) and never written; dual_v is updated in place, d_out = v_aux + dual_v (both fp32,
+ * K-blocked like the data planes: [ld / 64][v_rows->rows_p][64], ld >= round_up(cols, 128)); rowmax [origin + rows] /
+ * colmax [cols] receive the |max| bit patterns of D for the fixed-point re-ingest (nmfb_ingest_data_fixed with
+ * src_ld = -rows_p).  *done_flag != 0: nothing is touched.
  * k <= 128.  Replaces the cuBLAS SGEMM + element-wise kernel + |max| pass of round 1. */
 int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, int a_row0, const void* b_planes3,
                       int b_Lp, int KP, float* dual_v, float* d_out, long ld, uint32_t* rowmax, uint32_t* colmax,
@@ -315,6 +316,11 @@ int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, 
  * Buffers must be double-buffered by the caller (see nmf_b200/csrc/peer.cu for the ordering argument). */
 int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
                    long dst_pitch, int rows, long row_bytes, void* stream);
+/* peer_push through the NVSwitch multicast mapping of the arenas (mc_base: the multicast device address that aliases
+ * every rank's arena, from the caller's symmetric-memory handle): one multimem.st per 16 bytes, replicated by the
+ * switch into all ranks -- 1/world of the unicast version's NVLink egress. */
+int nmfb_peer_push_mc(const void* src, long src_pitch, void* mc_base, long dst_off, long dst_pitch, int rows,
+                      long row_bytes, void* stream);
 int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int seq, void* stream);
 int nmfb_sum_rank_slots(const double* slots, int world, long stride, int n, double* out64, float* out32,
                         void* stream);

@@ -235,6 +235,15 @@ int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int
     return 0;
 }
 
+int nmfb_peer_push_mc(const void* src, long src_pitch, void* mc_base, long dst_off, long dst_pitch, int rows,
+                      long row_bytes, void* stream) {
+    if (!src || !mc_base) return fail(NMFB_ERR_ARG, "peer_push_mc: null argument");
+    if (rows < 1 || (row_bytes & 15) || (dst_off & 15) || (src_pitch & 15) || (dst_pitch & 15))
+        return fail(NMFB_ERR_ARG, "peer_push_mc: 16-byte multiples (rows=%d row_bytes=%ld)", rows, row_bytes);
+    CUDA_TRY(peer_push_mc_launch(src, src_pitch, mc_base, dst_off, dst_pitch, rows, row_bytes, st(stream)));
+    return 0;
+}
+
 int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int seq, void* stream) {
     if (!flags_host || world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
         return fail(NMFB_ERR_ARG, "peer_barrier: bad argument");
@@ -805,7 +814,7 @@ int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, 
     a.mtiles = (v_rows->rows + 127) / 128;
     a.ntiles = (v_rows->cols + 127) / 128;
     if (a.mtiles < 1 || a.ntiles < 1) return fail(NMFB_ERR_ARG, "kl_data_step: empty shard");
-    if (ld < static_cast<long>(a.ntiles) * 128 || (ld & 3) || a.mtiles * 128 > v_rows->rows_p ||
+    if (ld < static_cast<long>(a.ntiles) * 128 || (ld & 63) || a.mtiles * 128 > v_rows->rows_p ||
         a.ntiles * 128 > b_Lp || a_row0 + a.mtiles * 128 > a_Lp)
         return fail(NMFB_ERR_ARG, "kl_data_step: padded extents too small (ld=%ld rows_p=%d)", ld, v_rows->rows_p);
     int cs = 2;
@@ -819,7 +828,7 @@ int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, 
     for (int q = 0; q < v_rows->nv; ++q)
         if ((rc = make_map(&a.v[q], bf(v_rows->planes) + static_cast<long>(q) * v_rows->rows_p * v_rows->ld,
                            static_cast<long>(v_rows->ld / 64) * v_rows->rows_p, 64, 128))) return rc;
-    a.dual_v = dual_v; a.d_out = d_out; a.ld = ld;
+    a.dual_v = dual_v; a.d_out = d_out; a.rows_p = v_rows->rows_p;
     a.rowmax = rowmax; a.colmax = colmax; a.done_flag = done_flag; a.row_origin = v_rows->origin;
     a.KP = KP; a.NV = v_rows->nv; a.v_rows_p = v_rows->rows_p;
     const long ntot = static_cast<long>((a.mtiles + cs - 1) / cs) * a.ntiles;

@@ -35,7 +35,10 @@ ingest_data_kernel(const T* __restrict__ src, long src_ld, int row0, int nrows, 
         const int r = r0 + rr, c = c0 + tx;
         float x = 0.f;
         if (r < nrows && c < ncols) {
-            x = static_cast<float>(src[static_cast<long>(r) * src_ld + c]);
+            // src_ld < 0: K-blocked source [cols / 64][-src_ld][64] (the data term of the KL branch, kl_data.cu)
+            const long si = src_ld >= 0 ? static_cast<long>(r) * src_ld + c
+                                        : (static_cast<long>(c >> 6) * (-src_ld) + r) * 64 + (c & 63);
+            x = static_cast<float>(src[si]);
             vmin = fminf(vmin, x);
             if (!isfinite(x)) bad = 1;
             __nv_bfloat16 hi, lo, lo2 = __float2bfloat16_rn(0.f);

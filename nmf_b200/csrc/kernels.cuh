@@ -77,9 +77,9 @@ struct alignas(64) KlDataArgs {
     CUtensorMap br[3];       // B operand: three row-major planes [Np][KP] of the right factor, box {64, 128 / cluster}
     CUtensorMap v[2];        // V planes (K-blocked), box {64, 128}
     const __nv_bfloat16* a_rpl[3];   // A operand: three row-major planes [rows][KP] of the left factor (this rank's rows)
-    float* dual_v;           // [rows_p][ld] fp32, updated in place
-    float* d_out;            // [rows_p][ld] fp32: D = v_aux + dual_v
-    long ld;
+    float* dual_v;           // K-blocked fp32 [ld / 64][rows_p][64], updated in place
+    float* d_out;            // K-blocked fp32: D = v_aux + dual_v
+    long rows_p;
     unsigned int* rowmax;    // |max| bits of D per row (index row_origin + local row) and per column
     unsigned int* colmax;
     const int* done_flag;    // AO-ADMM: != 0 -> the kernel does nothing

@@ -335,14 +335,17 @@ kl_data_kernel(const __grid_constant__ KlDataArgs args) {
             //   for v_bar < 1, fp64);  dual_v += v_aux - P;  D = v_aux + dual_v  -> fp32, plus |max| of D per row / column
             // The kernel is bound by the 12 B per element of dual_v / D traffic, not by the MMAs: the 32 dual_v values of
             // a column half are requested BEFORE the wait for the accumulator / the TMEM read-out, so that 128 B per
-            // thread (32 KB per SM) are in flight -- the first version loaded 32 B per thread between two fp64 square
-            // roots and ran at 2 TB/s (profiles/r02d).
+            // thread (32 KB per SM) are in flight.
             const int ti_e = min(static_cast<int>(t / args.ntiles) * CS + static_cast<int>(crank), args.mtiles - 1);
             const int tj_e = static_cast<int>(t - (t / args.ntiles) * args.ntiles);
             const long grow = static_cast<long>(ti_e) * 128 + row;                  // row of this rank's shard
             const int col0 = tj_e * 128 + hb * 64;
-            float* dvp = args.dual_v + grow * args.ld + col0;
-            float* dop = args.d_out + grow * args.ld + col0;
+            // dual_v and D are K-blocked like V ([col / 64][rows_p][64] fp32): this thread's 64 columns are 256
+            // contiguous bytes and the warp's 32 rows one 8 KB run -- with a row-major pitch of 64 KB every warp
+            // instruction touched 32 DRAM pages (2 TB/s, profiles/r02d)
+            const long boff = (static_cast<long>(col0 >> 6) * args.rows_p + grow) * 64;
+            float* dvp = args.dual_v + boff;
+            float* dop = args.d_out + boff;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + hb * 64;
             unsigned int rmax = 0, cmine = 0, cmine2 = 0;
             const uint8_t* vrow = nullptr;

@@ -42,12 +42,30 @@ peer_push_kernel(const char* __restrict__ src, long src_pitch, PeerPtrs dst, lon
     }
 }
 
+// The same copy through the NVSwitch multicast address of the arena (multimem.st): ONE store per 16 bytes leaves
+// this GPU and the switch replicates it into every rank's arena (this rank's included), instead of `world` unicast
+// stores -- 1/world of the NVLink egress.
+__global__ void __launch_bounds__(256)
+peer_push_mc_kernel(const char* __restrict__ src, long src_pitch, char* __restrict__ mc, long dst_pitch, int rows,
+                    long row_bytes) {
+    const long vec_per_row = row_bytes >> 4;
+    const long total = vec_per_row * rows;
+    for (long i = static_cast<long>(blockIdx.x) * 256 + threadIdx.x; i < total;
+         i += static_cast<long>(gridDim.x) * 256) {
+        const long r = i / vec_per_row, c = i - r * vec_per_row;
+        const float4 v = *reinterpret_cast<const float4*>(src + r * src_pitch + (c << 4));
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(mc + r * dst_pitch + (c << 4)), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+}
+
 // flags: [world] uint32 on every rank (symmetric).  Thread p publishes seq into peer p's flags[rank] and
 // waits for flags[p] >= seq on this rank.
 __global__ void __launch_bounds__(kMaxPeers)
 peer_barrier_kernel(PeerPtrs flags, int rank, int world, unsigned int seq) {
     const int p = threadIdx.x;
     if (p >= world) return;
+    asm volatile("fence.proxy.alias;" ::: "memory");       // earlier multimem.st went through the multicast alias
     __threadfence_system();
     unsigned int* theirs = static_cast<unsigned int*>(flags.p[p]) + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(seq) : "memory");
@@ -57,6 +75,7 @@ peer_barrier_kernel(PeerPtrs flags, int rank, int world, unsigned int seq) {
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
     } while (static_cast<int>(seen - seq) < 0);
     __threadfence_system();
+    asm volatile("fence.proxy.alias;" ::: "memory");
 }
 
 // out[i] = sum over ranks (fixed order) of slots[p * stride + i]; optional fp32 copy.
@@ -84,6 +103,19 @@ cudaError_t peer_push_launch(const void* src, long src_pitch, void* const* peers
     if (blocks < 1) blocks = 1;
     peer_push_kernel<<<dim3(static_cast<unsigned>(blocks), world), 256, 0, stream>>>(
         static_cast<const char*>(src), src_pitch, d, dst_off, dst_pitch, rows, row_bytes);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t peer_push_mc_launch(const void* src, long src_pitch, void* mc_base, long dst_off, long dst_pitch,
+                                int rows, long row_bytes, cudaStream_t stream) {
+    if (!mc_base || (row_bytes & 15) || rows < 1) return cudaErrorInvalidValue;
+    const long total = (row_bytes >> 4) * rows;
+    long blocks = (total + 255) / 256;
+    if (blocks > 148) blocks = 148;
+    if (blocks < 1) blocks = 1;
+    peer_push_mc_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+        static_cast<const char*>(src), src_pitch, static_cast<char*>(mc_base) + dst_off, dst_pitch, rows, row_bytes);
     count_launch();
     return cudaGetLastError();
 }

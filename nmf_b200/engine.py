@@ -677,8 +677,9 @@ class Engine:
             self._fixed_planes(self.h)
         # dual_v and D for this rank's rows of V, padded to whole 128 x 128 tiles (per_m rows, pitch Np) so that the
         # fused data step (kl_data.cu) needs no edge cases; the padding stays zero
-        self.kl_dual_v = torch.zeros((self.per_m, self.Np), dtype=torch.float32, device=dev)
-        self.kl_d = torch.zeros((self.per_m, self.Np), dtype=torch.float32, device=dev)
+        # (K-blocked like V: [Np / 64][per_m][64], so that a tile is contiguous runs of HBM)
+        self.kl_dual_v = torch.zeros((self.Np // 64, self.per_m, 64), dtype=torch.float32, device=dev)
+        self.kl_d = torch.zeros((self.Np // 64, self.per_m, 64), dtype=torch.float32, device=dev)
         # 24-bit row planes of the two operands of P = left . right (nmfb_row_planes3)
         self.kl_pl_a = torch.zeros((3, self.Mp, self.KP), dtype=torch.bfloat16, device=dev)
         self.kl_pl_b = torch.zeros((3, self.Np, self.KP), dtype=torch.bfloat16, device=dev)
@@ -718,17 +719,17 @@ class Engine:
         colmax = self.kl_scr_c if sharded else self.d_colmax
         check(self.lib.nmfb_kl_data_step(C.byref(vr), self.kl_pl_a.data_ptr(), self.Mp, r0 if sharded else 0,
                                          self.kl_pl_b.data_ptr(), self.Np, KP, self.kl_dual_v.data_ptr(), d.data_ptr(),
-                                         d.stride(0), rowmax.data_ptr(), colmax.data_ptr(), done_flag, self.num_sms,
+                                         self.Np, rowmax.data_ptr(), colmax.data_ptr(), done_flag, self.num_sms,
                                          self.stream))
         dr, dc = self._d_structs
         if sharded:
             self.d_rowmax.zero_()
             self.d_colmax.zero_()
-            live = d[: r1 - r0, :n]
+            live = d.permute(1, 0, 2).reshape(self.per_m, self.Np)[: r1 - r0, :n].contiguous()     # row-major rows of D
             self._panel_from_shards(live, self.kl_panel)
             self._ingest_shard_and_panel(live, self.kl_panel, dr, dc, self.d_stats, self.d_rowmax, self.d_colmax, True)
             return
-        check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, d.stride(0), 0, self.m, C.byref(dr), C.byref(dc),
+        check(self.lib.nmfb_ingest_data_fixed(d.data_ptr(), 0, -self.per_m, 0, self.m, C.byref(dr), C.byref(dc),
                                               self.d_stats.data_ptr(), self.d_rowmax.data_ptr(),
                                               self.d_colmax.data_ptr(), self.stream))
 

@@ -8,6 +8,7 @@ path is nmfb_peer_push / nmfb_peer_barrier / nmfb_sum_rank_slots / nmfb_adopt_ex
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Tuple
 
 import torch
@@ -48,6 +49,15 @@ class PeerArena:
         assert len(self.ptrs) == world and self.ptrs[rank] == self.local.data_ptr()
         self._ptr_arr = (C.c_void_p * world)(*self.ptrs)
         self.seq = 0
+        # NVSwitch multicast mapping of the arenas (one store, replicated by the switch into every rank), when the
+        # symmetric-memory handle has one; NMFB_NO_MULTICAST=1 keeps the unicast stores (A/B measurements)
+        mc = 0
+        try:
+            if bool(getattr(self._handle, "has_multicast_support", False)):
+                mc = int(self._handle.multicast_ptr or 0)
+        except Exception:                        # noqa: BLE001
+            mc = 0
+        self.mc_ptr = 0 if os.environ.get("NMFB_NO_MULTICAST", "0") == "1" else mc
 
     def view(self, name: str, shape, dtype) -> torch.Tensor:
         """Tensor view of the LOCAL copy of a region."""
@@ -61,6 +71,10 @@ class PeerArena:
     def push(self, src_ptr: int, src_pitch: int, region: str, dst_off: int, dst_pitch: int, rows: int,
              row_bytes: int, stream: int):
         """rows x row_bytes from src (device pointer, pitch in bytes) into EVERY rank's `region` at dst_off."""
+        if self.mc_ptr:
+            check(self.lib.nmfb_peer_push_mc(src_ptr, src_pitch, self.mc_ptr, self.offsets[region] + dst_off, dst_pitch,
+                                             rows, row_bytes, stream))
+            return
         check(self.lib.nmfb_peer_push(src_ptr, src_pitch, self._ptr_arr, self.world, self.offsets[region] + dst_off,
                                       dst_pitch, rows, row_bytes, stream))
 

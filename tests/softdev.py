@@ -269,8 +269,13 @@ class SoftLib:
         vr, vc = _obj(vr), _obj(vc)
         assert vr.origin + vr.rows <= vc.cols and vc.origin + vc.rows <= vr.cols and vr.nv == vc.nv
         assert 0 <= row0 and row0 + nrows <= vc.cols
-        chunk = mem(src, np.float64 if is64 else np.float32, (nrows - 1) * ld + vr.cols)
-        x = np.lib.stride_tricks.as_strided(chunk, (nrows, vr.cols), (ld * chunk.itemsize, chunk.itemsize))
+        if ld < 0:                                                # K-blocked source [cols / 64][-ld][64]
+            nbk = (vr.cols + 63) // 64
+            b = mem(src, np.float64 if is64 else np.float32, nbk * (-ld) * 64).reshape(nbk, -ld, 64)
+            x = b.transpose(1, 0, 2).reshape(-ld, nbk * 64)[:nrows, :vr.cols]
+        else:
+            chunk = mem(src, np.float64 if is64 else np.float32, (nrows - 1) * ld + vr.cols)
+            x = np.lib.stride_tricks.as_strided(chunk, (nrows, vr.cols), (ld * chunk.itemsize, chunk.itemsize))
         np_ingest(x.astype(np.float32), row0, vr, vc, mem(stats, np.uint32, 4),
                   mem(rowmax, np.uint32, vc.cols) if rowmax else None,
                   mem(colmax, np.uint32, vr.cols) if colmax else None)
@@ -332,14 +337,23 @@ class SoftLib:
         a = self.planes3[int(a_planes3)][:, a_row0:a_row0 + vr.rows].T.astype(np.float64)
         b = self.planes3[int(b_planes3)][:, :vr.cols].astype(np.float64)
         prod = (a @ b).astype(np.float32)
-        n = (vr.rows - 1) * ld + vr.cols
-        shape, st = (vr.rows, vr.cols), (ld * 4, 4)
-        view = lambda ptr: np.lib.stride_tricks.as_strided(mem(ptr, np.float32, n), shape, st)   # noqa: E731
-        np_kl_vaux(prod, view(d_out), view(dual_v), self.decode(vr))
+        nb = ld // 64                                             # K-blocked fp32 [ld / 64][rows_p][64]
+        blk = lambda ptr: mem(ptr, np.float32, nb * vr.rows_p * 64).reshape(nb, vr.rows_p, 64)   # noqa: E731
+        rowmajor = lambda b: b.transpose(1, 0, 2).reshape(vr.rows_p, ld)[:vr.rows, :vr.cols].copy()   # noqa: E731
+
+        def put(b, x):
+            full = b.transpose(1, 0, 2).reshape(vr.rows_p, ld).copy()
+            full[:vr.rows, :vr.cols] = x
+            b[...] = full.reshape(vr.rows_p, nb, 64).transpose(1, 0, 2)
+
+        dv, dd = rowmajor(blk(dual_v)), np.zeros((vr.rows, vr.cols), np.float32)
+        np_kl_vaux(prod, dd, dv, self.decode(vr))
+        put(blk(dual_v), dv)
+        put(blk(d_out), dd)
         rm, cm = mem(rowmax, np.uint32, vr.origin + vr.rows), mem(colmax, np.uint32, vr.cols)
         rm[vr.origin:] = 0
         cm[:] = 0
-        np_absmax(view(d_out), vr.origin, rm, cm)
+        np_absmax(dd, vr.origin, rm, cm)
         self.launches += 2
         return 0
 
