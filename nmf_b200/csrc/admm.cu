@@ -161,7 +161,7 @@ cudaError_t chol_inverse_launch(const double* gram, int KP, int k, int rho_mode,
 //   aux[c][r] = sum_c' Ainv[c][c'] b[c'][r]                      (fp64 FMA, register tile CPT x 4)
 //   x' = max(aux - u - lambda/rho, 0),  u' = u + x' - aux
 template <int CPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CPT <= 8 ? 2 : 1)
 admm_apply_kernel(const AdmmApplyArgs p) {
     constexpr int KP = CPT * 16;
     constexpr int TR = 64;
@@ -178,19 +178,65 @@ admm_apply_kernel(const AdmmApplyArgs p) {
     const double rho = *p.rho;
     const double thr = (p.prox == 1) ? static_cast<double>(p.lambda) / rho : 0.0;
 
-    for (int i = tid; i < KP * TR; i += 256) {
-        const int c = i / TR, rr = i - c * TR;
-        const long off = static_cast<long>(c) * Lp + r0 + rr;
-        double cv;
-        if (p.part != nullptr) {
-            cv = 0.0;
-            for (int s = 0; s < p.slots; ++s)
-                cv += static_cast<double>(p.part[static_cast<long>(s) * KP * Lp + off]);
-            if (p.c64 != nullptr && !p.base_only) p.c64[off] = cv;
-        } else {
-            cv = p.c64[off];
+    // b tile: four float4 positions per thread and pass, every global load of a pass issued before the first use
+    // (the first version walked 32 scalar positions with `slots` dependent loads each: ~100 serialised round trips
+    // to L2 / HBM per block, 280 us per launch at 65536 rows -- ncu r02h)
+    constexpr int NV4 = KP * TR / 4 / 256;
+#pragma unroll 1
+    for (int h = 0; h < NV4; h += 4) {
+        float4 xr[4], ur[4];
+        double cv[4][4];
+        long offs[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = tid + (h + j) * 256;
+            const int c = i / (TR / 4), q4 = i - c * (TR / 4);
+            offs[j] = static_cast<long>(c) * Lp + r0 + q4 * 4;
+            if (!p.base_only) {
+                xr[j] = *reinterpret_cast<const float4*>(p.x + offs[j]);
+                ur[j] = *reinterpret_cast<const float4*>(p.u + offs[j]);
+            } else {
+                xr[j] = ur[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         }
-        bs[i] = p.base_only ? cv : cv + rho * (static_cast<double>(p.x[off]) + static_cast<double>(p.u[off]));
+        if (p.part != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) cv[j][0] = cv[j][1] = cv[j][2] = cv[j][3] = 0.0;
+            for (int s = 0; s < p.slots; ++s) {
+                float4 pr[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    pr[j] = *reinterpret_cast<const float4*>(p.part + static_cast<long>(s) * KP * Lp + offs[j]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    cv[j][0] += static_cast<double>(pr[j].x); cv[j][1] += static_cast<double>(pr[j].y);
+                    cv[j][2] += static_cast<double>(pr[j].z); cv[j][3] += static_cast<double>(pr[j].w);
+                }
+            }
+            if (p.c64 != nullptr && !p.base_only) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    *reinterpret_cast<double2*>(p.c64 + offs[j]) = make_double2(cv[j][0], cv[j][1]);
+                    *reinterpret_cast<double2*>(p.c64 + offs[j] + 2) = make_double2(cv[j][2], cv[j][3]);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double2 c01 = *reinterpret_cast<const double2*>(p.c64 + offs[j]);
+                const double2 c23 = *reinterpret_cast<const double2*>(p.c64 + offs[j] + 2);
+                cv[j][0] = c01.x; cv[j][1] = c01.y; cv[j][2] = c23.x; cv[j][3] = c23.y;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int i = tid + (h + j) * 256;
+            const float xs4[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w}, us4[4] = {ur[j].x, ur[j].y, ur[j].z, ur[j].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                bs[i * 4 + e] = p.base_only ? cv[j][e]
+                                            : cv[j][e] + rho * (static_cast<double>(xs4[e]) + static_cast<double>(us4[e]));
+        }
     }
     double acc[CPT][4];
 #pragma unroll
@@ -200,9 +246,15 @@ admm_apply_kernel(const AdmmApplyArgs p) {
 
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
-        for (int i = tid; i < CK * KP / 2; i += 256)
-            reinterpret_cast<double2*>(gs)[i] =
-                *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + i * 2);
+        {
+            constexpr int NG = CK * KP / 2 / 256;          // all loads of the chunk in flight at once
+            double2 gr[NG];
+#pragma unroll
+            for (int j = 0; j < NG; ++j)
+                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + (tid + j * 256) * 2);
+#pragma unroll
+            for (int j = 0; j < NG; ++j) reinterpret_cast<double2*>(gs)[tid + j * 256] = gr[j];
+        }
         __syncthreads();
 #pragma unroll 2
         for (int cc = 0; cc < CK; ++cc) {
@@ -317,7 +369,7 @@ admm_apply_kernel(const AdmmApplyArgs p) {
 // reference's own functions: fp64 apply 1.8e-7, split 1.1e-6; bar 1e-4).  The inner iterations then cost a
 // quarter of the fp64 pipe time and their bytes.
 template <int CPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CPT <= 8 ? 2 : 1)
 admm_apply32_kernel(const AdmmApplyArgs p) {
     constexpr int KP = CPT * 16;
     constexpr int TR = 64;
@@ -334,12 +386,21 @@ admm_apply32_kernel(const AdmmApplyArgs p) {
     const double rho = *p.rho;
     const double thr = (p.prox == 1) ? static_cast<double>(p.lambda) / rho : 0.0;
 
-    for (int i = tid; i < KP * TR / 4; i += 256) {
-        const int c = i / (TR / 4), q4 = i - c * (TR / 4);
-        const long off = static_cast<long>(c) * Lp + r0 + q4 * 4;
-        const float4 xv = *reinterpret_cast<const float4*>(p.x + off);
-        const float4 uv = *reinterpret_cast<const float4*>(p.u + off);
-        reinterpret_cast<float4*>(bs)[i] = make_float4(xv.x + uv.x, xv.y + uv.y, xv.z + uv.z, xv.w + uv.w);
+    {
+        constexpr int NV4 = KP * TR / 4 / 256;             // all loads of the tile in flight at once
+        float4 xr[NV4], ur[NV4];
+#pragma unroll
+        for (int j = 0; j < NV4; ++j) {
+            const int i = tid + j * 256;
+            const int c = i / (TR / 4), q4 = i - c * (TR / 4);
+            const long off = static_cast<long>(c) * Lp + r0 + q4 * 4;
+            xr[j] = *reinterpret_cast<const float4*>(p.x + off);
+            ur[j] = *reinterpret_cast<const float4*>(p.u + off);
+        }
+#pragma unroll
+        for (int j = 0; j < NV4; ++j)
+            reinterpret_cast<float4*>(bs)[tid + j * 256] =
+                make_float4(xr[j].x + ur[j].x, xr[j].y + ur[j].y, xr[j].z + ur[j].z, xr[j].w + ur[j].w);
     }
     float acc[CPT][4];
 #pragma unroll
@@ -349,9 +410,16 @@ admm_apply32_kernel(const AdmmApplyArgs p) {
 
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
-        for (int i = tid; i < CK * KP / 2; i += 256) {
-            const double2 g2 = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + i * 2);
-            reinterpret_cast<float2*>(gs)[i] = make_float2(static_cast<float>(g2.x), static_cast<float>(g2.y));
+        {
+            constexpr int NG = CK * KP / 2 / 256;
+            double2 gr[NG];
+#pragma unroll
+            for (int j = 0; j < NG; ++j)
+                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + (tid + j * 256) * 2);
+#pragma unroll
+            for (int j = 0; j < NG; ++j)
+                reinterpret_cast<float2*>(gs)[tid + j * 256] =
+                    make_float2(static_cast<float>(gr[j].x), static_cast<float>(gr[j].y));
         }
         __syncthreads();
 #pragma unroll 4

@@ -31,24 +31,22 @@ __device__ __forceinline__ float4 ld_global_f4(const float* p) {
     return v;
 }
 
-// sqrt and reciprocal in fp64 from an fp32 MUFU seed and Newton steps (relative error ~1e-14 / ~1e-15): the
-// correctly-rounded library routines cost ~25 instructions each and made the epilogue -- 58 instructions per element
-// at 0.24 IPC, ncu r02f -- the pace-setter of a kernel that should be bound by its 14 B per element of HBM traffic.
+// sqrt and quotient in fp64 from an fp32 MUFU seed and Newton steps (relative error ~1e-14): the correctly-rounded
+// library routines cost ~25 instructions each and made the epilogue -- 58 instructions per element at 0.24 IPC, ncu
+// r02f -- the pace-setter of a kernel that should be bound by its 14 B per element of HBM traffic.  Branch-free on
+// purpose: the eight elements of a group are independent chains that the scheduler interleaves; a first version
+// with early-out branches lost that and ran 30 % slower than the library calls.  Arguments are data-scale
+// (|x| within fp32 range); x <= 0 gives 0.
 __device__ __forceinline__ double sqrt_newton(double x) {
-    if (!(x > 0.0)) return 0.0;                          // the radicand t^2 + 4v is >= 0 for non-negative data
-    const float xf = static_cast<float>(x);
-    if (!(xf > 1e-30f && xf < 1e30f)) return sqrt(x);    // out of the seed's range: the library routine
-    const double y = static_cast<double>(rsqrtf(xf));    // ~2^-22
+    const double y = static_cast<double>(rsqrtf(fmaxf(static_cast<float>(x), 1e-37f)));     // ~2^-22
     double r = x * y;
-    r = fma(0.5 * y, fma(-r, r, x), r);                  // ~1e-14
-    return r;
+    r = fma(0.5 * y, fma(-r, r, x), r);                                                      // ~1e-14
+    return x > 0.0 ? r : 0.0;
 }
-__device__ __forceinline__ double div_newton(double a, double b) {      // a / b, b > 0
-    const float bf = static_cast<float>(b);
-    if (!(bf > 1e-30f && bf < 1e30f)) return a / b;
-    double y = static_cast<double>(__frcp_rn(bf));
-    y = fma(y, fma(-b, y, 1.0), y);                      // ~1e-14
+__device__ __forceinline__ double div_newton(double a, double b) {      // a / b for b > 0 (callers select otherwise)
+    double y = static_cast<double>(__frcp_rn(fmaxf(static_cast<float>(b), 1e-37f)));
     y = fma(y, fma(-b, y, 1.0), y);
+    y = fma(y, fma(-b, y, 1.0), y);                                                          // ~1e-15
     return a * y;
 }
 
@@ -421,9 +419,9 @@ kl_data_kernel(const __grid_constant__ KlDataArgs args) {
                         const double v = static_cast<double>(vv[e]);
                         const double tq = P - static_cast<double>(dv[e]) - 1.0;
                         const double root = sqrt_newton(fma(tq, tq, 4.0 * v));
-                        double va;
-                        if (tq >= 0.0) va = 0.5 * (tq + root);
-                        else           va = (root - tq > 0.0) ? div_newton(2.0 * v, root - tq) : 0.0;
+                        const double den = root - tq;
+                        const double va_neg = den > 0.0 ? div_newton(2.0 * v, den) : 0.0;
+                        const double va = tq >= 0.0 ? 0.5 * (tq + root) : va_neg;
                         dn[e] = static_cast<float>(static_cast<double>(dv[e]) + va - P);
                         dd[e] = static_cast<float>(va + static_cast<double>(dn[e]));
                         const unsigned int bits = live ? __float_as_uint(fabsf(dd[e])) : 0u;
