@@ -693,8 +693,9 @@ def _e2e_timed_out(line, rank):
 
 def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank, obj0=None):
     """N > 1: the same call on every rank, NMF(V_host, k).factorize(..., comm=True) -- each rank is handed the
-    whole host V (the public API of a sharded run) and reads ONLY its rows and its
-    columns of it (Engine._shard_and_panel: 2/P of V per PCIe link, nothing between the GPUs).  Timed from a
+    whole host V (the public API of a sharded run) and reads ONLY its rows of it
+    (Engine._shard_and_panel: 1/P of V per PCIe link; the column copy is assembled over NVLink by peer-memory
+    stores).  Timed from a
     barrier to the slowest rank's return (engine set-up incl. the peer arena, upload, `steps` iterations with the
     objective read back every iteration, download of W and H on every rank); `breakdown` = the slowest rank's
     wall seconds per leg.  The host V is ONE shared-memory file that rank 0 fills and every rank maps, so the node
@@ -779,13 +780,13 @@ def run_e2e_sharded(eng, method, dtype_, m, n, k, extra, steps, world, rank, obj
 
     res, dt, breakdown, _ = timed(min_iter=10**9, max_iter=steps, w0=w0, h0=h0)
     assert res.i == steps - 1 and len(res.obj_history) == steps + 1
-    # each rank uploads its rows and its columns of V (2/P of V) and both initial factors
-    h2d = 2 * v_np.nbytes + world * (w0.nbytes + h0.nbytes)
+    # each rank uploads its rows of V (the columns travel between the GPUs) and both initial factors
+    h2d = v_np.nbytes + world * (w0.nbytes + h0.nbytes)
     d2h = world * (res.w.nbytes // 2 + res.h.nbytes // 2 + 8 * (steps + 1))
     out = {"value": steps / dt, "unit": "it/s", "seconds_total": dt, "breakdown": breakdown,
            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps, "host_v_pinned": pinned,
            "what": f"on each of {world} ranks NMF(V_host fp32 in shared memory, k).factorize(max_iter=steps, comm=True): "
-                   "engine + peer arena, upload of the rank's rows and columns of V, iterations, factor download; "
+                   "engine + peer arena, upload of the rank's rows of V (columns over NVLink), iterations, factor download; "
                    "slowest rank"}
     if obj0 is not None:
         try:

@@ -316,6 +316,12 @@ int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, 
  * Buffers must be double-buffered by the caller (see nmf_b200/csrc/peer.cu for the ordering argument). */
 int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
                    long dst_pitch, int rows, long row_bytes, void* stream);
+/* All-to-all of row blocks over peer memory (the sharded upload): rank q's arena receives, at dst_off / dst_pitch,
+ * `rows` rows of row_bytes_host[q] bytes taken from src + q * src_peer_stride (pitch src_pitch) -- the columns of
+ * this rank's rows of V that belong to rank q.  After nmfb_peer_barrier every rank holds ALL rows of its columns,
+ * although each row shard crossed PCIe exactly once. */
+int nmfb_peer_scatter(const void* src, long src_pitch, long src_peer_stride, void* const* peers_host, int world,
+                      long dst_off, long dst_pitch, int rows, const long* row_bytes_host, void* stream);
 /* peer_push through the NVSwitch multicast mapping of the arenas (mc_base: the multicast device address that aliases
  * every rank's arena, from the caller's symmetric-memory handle): one multimem.st per 16 bytes, replicated by the
  * switch into all ranks -- 1/world of the unicast version's NVLink egress. */

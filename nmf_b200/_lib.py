@@ -97,6 +97,7 @@ _SIGNATURES = {
 
 _SIGNATURES.update({
     "nmfb_peer_push": (c_int, [c_void_p, c_long, c_void_p, c_int, c_long, c_long, c_int, c_long, c_void_p]),
+    "nmfb_peer_scatter": (c_int, [c_void_p, c_long, c_long, c_void_p, c_int, c_long, c_long, c_int, c_void_p, c_void_p]),
     "nmfb_peer_push_mc": (c_int, [c_void_p, c_long, c_void_p, c_long, c_long, c_int, c_long, c_void_p]),
     "nmfb_peer_barrier": (c_int, [c_void_p, c_int, c_int, C.c_uint, c_void_p]),
     "nmfb_sum_rank_slots": (c_int, [c_void_p, c_int, c_long, c_int, c_void_p, c_void_p, c_void_p]),

@@ -408,18 +408,22 @@ admm_apply32_kernel(const AdmmApplyArgs p) {
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
 
+    // rows of Ainv: chunk ck + 1 travels from L2 to registers while chunk ck is multiplied (the k x k matrix does not
+    // fit shared memory next to the tile in fp64; the waits for these loads were 1/4 of the kernel, ncu r02h)
+    constexpr int NG = CK * KP / 2 / 256;
+    double2 gr[NG];
+#pragma unroll
+    for (int j = 0; j < NG; ++j) gr[j] = *reinterpret_cast<const double2*>(p.ainv + (tid + j * 256) * 2);
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
-        {
-            constexpr int NG = CK * KP / 2 / 256;
-            double2 gr[NG];
+#pragma unroll
+        for (int j = 0; j < NG; ++j)
+            reinterpret_cast<float2*>(gs)[tid + j * 256] =
+                make_float2(static_cast<float>(gr[j].x), static_cast<float>(gr[j].y));
+        if (ck + CK < KP) {
 #pragma unroll
             for (int j = 0; j < NG; ++j)
-                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + (tid + j * 256) * 2);
-#pragma unroll
-            for (int j = 0; j < NG; ++j)
-                reinterpret_cast<float2*>(gs)[tid + j * 256] =
-                    make_float2(static_cast<float>(gr[j].x), static_cast<float>(gr[j].y));
+                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck + CK) * KP + (tid + j * 256) * 2);
         }
         __syncthreads();
 #pragma unroll 4
@@ -443,15 +447,23 @@ admm_apply32_kernel(const AdmmApplyArgs p) {
 
     double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
     __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
+    float4 xo_n = *reinterpret_cast<const float4*>(p.x + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
+    float4 uo_n = *reinterpret_cast<const float4*>(p.u + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
+    double2 b01_n = *reinterpret_cast<const double2*>(p.c64 + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
+    double2 b23_n = *reinterpret_cast<const double2*>(p.c64 + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4 + 2);
 #pragma unroll
     for (int a = 0; a < CPT; ++a) {
         const int c = tc * CPT + a;
         const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
-        const float4 xo4 = *reinterpret_cast<const float4*>(p.x + off);
-        const float4 uo4 = *reinterpret_cast<const float4*>(p.u + off);
+        const float4 xo4 = xo_n, uo4 = uo_n;
+        const double2 b01 = b01_n, b23 = b23_n;          // base = Ainv . C (fp64)
+        if (a + 1 < CPT) {                               // next component's operands: in flight during this one's math
+            xo_n = *reinterpret_cast<const float4*>(p.x + off + Lp);
+            uo_n = *reinterpret_cast<const float4*>(p.u + off + Lp);
+            b01_n = *reinterpret_cast<const double2*>(p.c64 + off + Lp);
+            b23_n = *reinterpret_cast<const double2*>(p.c64 + off + Lp + 2);
+        }
         const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
-        const double2 b01 = *reinterpret_cast<const double2*>(p.c64 + off);          // base = Ainv . C (fp64)
-        const double2 b23 = *reinterpret_cast<const double2*>(p.c64 + off + 2);
         const double base[4] = {b01.x, b01.y, b23.x, b23.y};
         float xn[4], un[4], ax[4];
 #pragma unroll

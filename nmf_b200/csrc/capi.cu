@@ -235,6 +235,18 @@ int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int
     return 0;
 }
 
+int nmfb_peer_scatter(const void* src, long src_pitch, long src_peer_stride, void* const* peers_host, int world,
+                      long dst_off, long dst_pitch, int rows, const long* row_bytes_host, void* stream) {
+    if (!src || !peers_host || !row_bytes_host) return fail(NMFB_ERR_ARG, "peer_scatter: null argument");
+    if (world < 1 || world > kMaxPeers || rows < 1) return fail(NMFB_ERR_ARG, "peer_scatter: bad world / rows");
+    for (int q = 0; q < world; ++q)
+        if (row_bytes_host[q] < 0 || (row_bytes_host[q] & 3))
+            return fail(NMFB_ERR_ARG, "peer_scatter: row widths must be multiples of 4 bytes");
+    CUDA_TRY(peer_scatter_launch(src, src_pitch, src_peer_stride, peers_host, world, dst_off, dst_pitch, rows,
+                                 row_bytes_host, st(stream)));
+    return 0;
+}
+
 int nmfb_peer_push_mc(const void* src, long src_pitch, void* mc_base, long dst_off, long dst_pitch, int rows,
                       long row_bytes, void* stream) {
     if (!src || !mc_base) return fail(NMFB_ERR_ARG, "peer_push_mc: null argument");

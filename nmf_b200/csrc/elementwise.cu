@@ -293,7 +293,7 @@ cudaError_t gram_reduce_launch(const float* part, int slots, int KP, int Lp, flo
 // and all KP components: a register-tiled (CPT x 4) fp32 product against G staged through smem,
 // then the multiplicative update and all plane stores straight from registers.
 template <int CPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CPT <= 8 ? 2 : 1)
 mur_eu_update_kernel(const float* __restrict__ part, int slots, const float* __restrict__ gram,
                      float* __restrict__ master, __nv_bfloat16* __restrict__ cpl, long cpl_plane,
                      __nv_bfloat16* __restrict__ rpl, long rpl_plane, int k, int L, int Lp, float lambda) {
@@ -307,10 +307,17 @@ mur_eu_update_kernel(const float* __restrict__ part, int slots, const float* __r
     const int tr = tid & 15, tc = tid >> 4;
     const int r0 = blockIdx.x * TR;
 
-    for (int i = tid; i < KP * TR / 4; i += 256) {
-        const int c = i / (TR / 4), q = i - c * (TR / 4);
-        reinterpret_cast<float4*>(xs)[i] =
-            *reinterpret_cast<const float4*>(master + static_cast<long>(c) * Lp + r0 + q * 4);
+    {
+        constexpr int NV4 = KP * TR / 4 / 256;             // all loads of the tile in flight at once
+        float4 xr[NV4];
+#pragma unroll
+        for (int j = 0; j < NV4; ++j) {
+            const int i = tid + j * 256;
+            const int c = i / (TR / 4), q = i - c * (TR / 4);
+            xr[j] = *reinterpret_cast<const float4*>(master + static_cast<long>(c) * Lp + r0 + q * 4);
+        }
+#pragma unroll
+        for (int j = 0; j < NV4; ++j) reinterpret_cast<float4*>(xs)[tid + j * 256] = xr[j];
     }
     float acc[CPT][4];
 #pragma unroll
@@ -318,11 +325,20 @@ mur_eu_update_kernel(const float* __restrict__ part, int slots, const float* __r
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
 
+    // rows of G: chunk ck + 1 travels from L2 to registers while chunk ck is multiplied
+    constexpr int NG = CK * KP / 4 / 256;
+    float4 gr[NG];
+#pragma unroll
+    for (int j = 0; j < NG; ++j) gr[j] = *reinterpret_cast<const float4*>(gram + (tid + j * 256) * 4);
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
-        for (int i = tid; i < CK * KP / 4; i += 256)
-            reinterpret_cast<float4*>(gs)[i] =
-                *reinterpret_cast<const float4*>(gram + static_cast<long>(ck) * KP + i * 4);
+#pragma unroll
+        for (int j = 0; j < NG; ++j) reinterpret_cast<float4*>(gs)[tid + j * 256] = gr[j];
+        if (ck + CK < KP) {
+#pragma unroll
+            for (int j = 0; j < NG; ++j)
+                gr[j] = *reinterpret_cast<const float4*>(gram + static_cast<long>(ck + CK) * KP + (tid + j * 256) * 4);
+        }
         __syncthreads();
 #pragma unroll 4
         for (int cc = 0; cc < CK; ++cc) {
@@ -341,13 +357,33 @@ mur_eu_update_kernel(const float* __restrict__ part, int slots, const float* __r
 
     // epilogue: numerator from the partial slots, multiplicative update, stores
     __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
+    // numerator = sum of the GEMM's partial slots: the slots of component a + 1 are requested before the stores of
+    // component a (up to kPre slots ahead; the waits for these loads were the largest stall of the kernel)
+    constexpr int kPre = 4;
+    const long slot_stride = static_cast<long>(KP) * Lp;
+    float4 pre[kPre];
+    {
+        const long off0 = static_cast<long>(tc * CPT) * Lp + r0 + tr * 4;
+#pragma unroll
+        for (int s = 0; s < kPre; ++s)
+            pre[s] = s < slots ? *reinterpret_cast<const float4*>(part + s * slot_stride + off0)
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
     for (int a = 0; a < CPT; ++a) {
         const int c = tc * CPT + a;
         const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
         float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int s = 0; s < slots; ++s) {
-            const float4 p = *reinterpret_cast<const float4*>(part + static_cast<long>(s) * KP * Lp + off);
+#pragma unroll
+        for (int s = 0; s < kPre; ++s) { num.x += pre[s].x; num.y += pre[s].y; num.z += pre[s].z; num.w += pre[s].w; }
+        if (a + 1 < CPT) {
+#pragma unroll
+            for (int s = 0; s < kPre; ++s)
+                pre[s] = s < slots ? *reinterpret_cast<const float4*>(part + s * slot_stride + off + Lp)
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int s = kPre; s < slots; ++s) {
+            const float4 p = *reinterpret_cast<const float4*>(part + s * slot_stride + off);
             num.x += p.x; num.y += p.y; num.z += p.z; num.w += p.w;
         }
         const float4 x = *reinterpret_cast<const float4*>(xs + c * TR + tr * 4);

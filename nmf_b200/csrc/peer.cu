@@ -42,6 +42,32 @@ peer_push_kernel(const char* __restrict__ src, long src_pitch, PeerPtrs dst, lon
     }
 }
 
+// All-to-all of row blocks: destination q receives rows x row_bytes[q] bytes taken from src + q * src_peer_stride
+// (the columns of this rank's rows that belong to rank q), at dst_off of its buffer.  VEC = bytes per access.
+struct ScatterWidths {
+    long row_bytes[kMaxPeers];
+};
+template <int VEC>
+__global__ void __launch_bounds__(256)
+peer_scatter_kernel(const char* __restrict__ src, long src_pitch, long src_peer_stride, PeerPtrs dst, long dst_off,
+                    long dst_pitch, int rows, ScatterWidths w) {
+    const int q = blockIdx.y;
+    const char* in = src + q * src_peer_stride;
+    char* out = static_cast<char*>(dst.p[q]) + dst_off;
+    const long per_row = w.row_bytes[q] / VEC;
+    const long total = per_row * rows;
+    for (long i = static_cast<long>(blockIdx.x) * 256 + threadIdx.x; i < total;
+         i += static_cast<long>(gridDim.x) * 256) {
+        const long r = i / per_row, c = i - r * per_row;
+        if (VEC == 16)
+            *reinterpret_cast<uint4*>(out + r * dst_pitch + c * 16) =
+                *reinterpret_cast<const uint4*>(in + r * src_pitch + c * 16);
+        else
+            *reinterpret_cast<unsigned int*>(out + r * dst_pitch + c * 4) =
+                *reinterpret_cast<const unsigned int*>(in + r * src_pitch + c * 4);
+    }
+}
+
 // The same copy through the NVSwitch multicast address of the arena (multimem.st): ONE store per 16 bytes leaves
 // this GPU and the switch replicates it into every rank's arena (this rank's included), instead of `world` unicast
 // stores -- 1/world of the NVLink egress.
@@ -103,6 +129,31 @@ cudaError_t peer_push_launch(const void* src, long src_pitch, void* const* peers
     if (blocks < 1) blocks = 1;
     peer_push_kernel<<<dim3(static_cast<unsigned>(blocks), world), 256, 0, stream>>>(
         static_cast<const char*>(src), src_pitch, d, dst_off, dst_pitch, rows, row_bytes);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t peer_scatter_launch(const void* src, long src_pitch, long src_peer_stride, void* const* peers_host,
+                                int world, long dst_off, long dst_pitch, int rows, const long* row_bytes_host,
+                                cudaStream_t stream) {
+    if (world < 1 || world > kMaxPeers || rows < 1) return cudaErrorInvalidValue;
+    PeerPtrs d;
+    ScatterWidths w;
+    bool vec16 = ((src_pitch | src_peer_stride | dst_off | dst_pitch) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    for (int p = 0; p < kMaxPeers; ++p) {
+        d.p[p] = p < world ? peers_host[p] : nullptr;
+        w.row_bytes[p] = p < world ? row_bytes_host[p] : 0;
+        if (w.row_bytes[p] & 3) return cudaErrorInvalidValue;
+        if (w.row_bytes[p] & 15) vec16 = false;
+    }
+    const dim3 grid(148, world);
+    if (vec16)
+        peer_scatter_kernel<16><<<grid, 256, 0, stream>>>(static_cast<const char*>(src), src_pitch, src_peer_stride, d,
+                                                         dst_off, dst_pitch, rows, w);
+    else
+        peer_scatter_kernel<4><<<grid, 256, 0, stream>>>(static_cast<const char*>(src), src_pitch, src_peer_stride, d,
+                                                        dst_off, dst_pitch, rows, w);
     count_launch();
     return cudaGetLastError();
 }

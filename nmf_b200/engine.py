@@ -405,27 +405,42 @@ class Engine:
     # ranks' row shards by an all-to-all over NVLink (1/P of V over each PCIe link instead of all of it)
     def _shard_and_panel(self, v: np.ndarray):
         """(shard, panel): this rank's rows V[I_p, :] and columns V[:, J_p] on the device, in the host dtype.
-        Both come straight from host memory -- the rows as one contiguous run, the columns as a strided 2-D copy
-        (cudaMemcpy2DAsync, 1/P of every row) -- so each PCIe link carries 2/P of V and no inter-GPU step, no
-        staging copy and no lazily-built point-to-point channels are involved (round 1 assembled the columns by
-        an all-to-all of the row shards: 7.4 s at 8 GPUs, mostly NCCL channel setup)."""
+        The rows come from host memory as one contiguous run: 1/P of V per PCIe link.  On GPUs the columns are then
+        assembled over NVLink: every rank stores, for each peer q, the columns J_q of ITS rows straight into q's
+        panel (nmfb_peer_scatter into a peer-memory arena, one device barrier) -- V crosses PCIe exactly once in
+        total.  Round 1 did that exchange with point-to-point NCCL operations whose channels are built lazily on
+        first use (7.4 s at 8 GPUs).  Without peer memory (host stand-in of the CPU tests) the columns are read
+        from host memory as a strided 2-D copy."""
         cache = getattr(self, "_chunk_cache", None)
         if cache is not None and cache[0] is v:
-            return cache[1]
+            return cache[1][:2]
         (r0, r1), (c0, c1) = self.row_range, self.col_range
         tdt = torch.float64 if v.dtype == np.float64 else torch.float32
         es, n = v.itemsize, self.n
         shard = torch.empty((r1 - r0, n), dtype=tdt, device=self.device)
-        panel = torch.empty((self.m, c1 - c0), dtype=tdt, device=self.device)
         host = v.ctypes.data
         check(self.lib.nmfb_upload_2d(shard.data_ptr(), n * es, host + r0 * n * es, n * es, n * es, r1 - r0,
                                       self.stream))
-        check(self.lib.nmfb_upload_2d(panel.data_ptr(), (c1 - c0) * es, host + c0 * es, n * es, (c1 - c0) * es,
-                                      self.m, self.stream))
-        out = (shard, panel)
+        arena = None
+        if self.peer is not None:
+            from .peer import PeerArena
+            per = self.per_n
+            arena = PeerArena(self.lib, [("panel", self.Mp * per * es)], self.device, self.rank, self.world, self.group)
+            nb = shard_bounds(self.n, self.world)[2]
+            widths = [live_rows(self.n, lo, hi) * es for lo, hi in nb]
+            arena.scatter(shard.data_ptr(), n * es, per * es, "panel", r0 * per * es, per * es, r1 - r0, widths,
+                          self.stream)
+            arena.barrier(self.stream)
+            panel = arena.view("panel", (self.Mp, per), tdt)[: self.m, : c1 - c0]
+        else:
+            panel = torch.empty((self.m, c1 - c0), dtype=tdt, device=self.device)
+            check(self.lib.nmfb_upload_2d(panel.data_ptr(), (c1 - c0) * es, host + c0 * es, n * es, (c1 - c0) * es,
+                                          self.m, self.stream))
+        out = (shard, panel, arena)                      # the arena owns the panel's memory
+        self._last_upload = out                          # alive until the ingest kernels have run (upload_data syncs)
         if getattr(self, "_keep_chunks", False):
             self._chunk_cache = (v, out)
-        return out
+        return shard, panel
 
     def _panel_from_shards(self, shard: torch.Tensor, panel: torch.Tensor):
         """panel (m x my columns) <- every rank's rows of those columns: all-to-all of the row shards."""
@@ -498,8 +513,12 @@ class Engine:
         try:
             return self._upload_data(v, planes, fixed)
         finally:
-            self._sync_stream()
-            self.timings["upload_s"] = self.timings.get("upload_s", 0.0) + time.perf_counter() - t_up
+            if torch.device(self.device).type == "cuda":
+                self._sync_stream()
+            self._last_upload = None
+            t = getattr(self, "timings", None)
+            if t is not None:
+                t["upload_s"] = t.get("upload_s", 0.0) + time.perf_counter() - t_up
 
     def _upload_data(self, v: np.ndarray, planes: Optional[int] = None, fixed: bool = False) -> float:
         if v.ndim != 2 or v.shape != (self.m, self.n):

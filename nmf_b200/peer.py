@@ -78,6 +78,13 @@ class PeerArena:
         check(self.lib.nmfb_peer_push(src_ptr, src_pitch, self._ptr_arr, self.world, self.offsets[region] + dst_off,
                                       dst_pitch, rows, row_bytes, stream))
 
+    def scatter(self, src_ptr: int, src_pitch: int, src_peer_stride: int, region: str, dst_off: int, dst_pitch: int,
+                rows: int, row_bytes, stream: int):
+        """All-to-all: rank q's `region` receives rows x row_bytes[q] from src + q * src_peer_stride at dst_off."""
+        arr = (C.c_long * self.world)(*[int(b) for b in row_bytes])
+        check(self.lib.nmfb_peer_scatter(src_ptr, src_pitch, src_peer_stride, self._ptr_arr, self.world,
+                                         self.offsets[region] + dst_off, dst_pitch, rows, arr, stream))
+
     def barrier(self, stream: int):
         """All ranks call this the same number of times, in the same order."""
         self.seq += 1
