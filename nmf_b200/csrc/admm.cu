@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256, CPT <= 8 ? 2 : 1)
 admm_apply_kernel(const AdmmApplyArgs p) {
     constexpr int KP = CPT * 16;
     constexpr int TR = 64;
-    constexpr int CK = 32;
+    constexpr int CK = 16;                // rows of Ainv per shared-memory chunk (the next one waits in registers)
     extern __shared__ double sm_d[];
     double* bs = sm_d;                    // [KP][TR]
     double* gs = sm_d + KP * TR;          // [CK][KP]
@@ -192,12 +192,8 @@ admm_apply_kernel(const AdmmApplyArgs p) {
             const int i = tid + (h + j) * 256;
             const int c = i / (TR / 4), q4 = i - c * (TR / 4);
             offs[j] = static_cast<long>(c) * Lp + r0 + q4 * 4;
-            if (!p.base_only) {
-                xr[j] = *reinterpret_cast<const float4*>(p.x + offs[j]);
-                ur[j] = *reinterpret_cast<const float4*>(p.u + offs[j]);
-            } else {
-                xr[j] = ur[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+            xr[j] = *reinterpret_cast<const float4*>(p.x + offs[j]);
+            ur[j] = *reinterpret_cast<const float4*>(p.u + offs[j]);
         }
         if (p.part != nullptr) {
 #pragma unroll
@@ -213,7 +209,7 @@ admm_apply_kernel(const AdmmApplyArgs p) {
                     cv[j][2] += static_cast<double>(pr[j].z); cv[j][3] += static_cast<double>(pr[j].w);
                 }
             }
-            if (p.c64 != nullptr && !p.base_only) {
+            if (p.c64 != nullptr) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     *reinterpret_cast<double2*>(p.c64 + offs[j]) = make_double2(cv[j][0], cv[j][1]);
@@ -234,8 +230,7 @@ admm_apply_kernel(const AdmmApplyArgs p) {
             const float xs4[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w}, us4[4] = {ur[j].x, ur[j].y, ur[j].z, ur[j].w};
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                bs[i * 4 + e] = p.base_only ? cv[j][e]
-                                            : cv[j][e] + rho * (static_cast<double>(xs4[e]) + static_cast<double>(us4[e]));
+                bs[i * 4 + e] = cv[j][e] + rho * (static_cast<double>(xs4[e]) + static_cast<double>(us4[e]));
         }
     }
     double acc[CPT][4];
@@ -244,16 +239,19 @@ admm_apply_kernel(const AdmmApplyArgs p) {
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
 
+    // rows of Ainv: chunk ck + 1 travels from L2 to registers while chunk ck is multiplied
+    constexpr int NG = CK * KP / 2 / 256;
+    double2 gr[NG];
+#pragma unroll
+    for (int j = 0; j < NG; ++j) gr[j] = *reinterpret_cast<const double2*>(p.ainv + (tid + j * 256) * 2);
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
-        {
-            constexpr int NG = CK * KP / 2 / 256;          // all loads of the chunk in flight at once
-            double2 gr[NG];
+#pragma unroll
+        for (int j = 0; j < NG; ++j) reinterpret_cast<double2*>(gs)[tid + j * 256] = gr[j];
+        if (ck + CK < KP) {
 #pragma unroll
             for (int j = 0; j < NG; ++j)
-                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck) * KP + (tid + j * 256) * 2);
-#pragma unroll
-            for (int j = 0; j < NG; ++j) reinterpret_cast<double2*>(gs)[tid + j * 256] = gr[j];
+                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck + CK) * KP + (tid + j * 256) * 2);
         }
         __syncthreads();
 #pragma unroll 2
@@ -272,204 +270,25 @@ admm_apply_kernel(const AdmmApplyArgs p) {
         }
     }
 
-    if (p.base_only) {                    // AO-ADMM: base = Ainv . C, the part of aux that is fixed during the inner loop
-        __syncthreads();                  // every thread is done reading the C tile that the prologue may have
-#pragma unroll                            // taken from c64 itself
-        for (int a = 0; a < CPT; ++a) {
-            const long off = static_cast<long>(tc * CPT + a) * Lp + r0 + tr * 4;
-            *reinterpret_cast<double2*>(p.c64 + off) = make_double2(acc[a][0], acc[a][1]);
-            *reinterpret_cast<double2*>(p.c64 + off + 2) = make_double2(acc[a][2], acc[a][3]);
-        }
-        return;
-    }
     double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
     __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
+    float4 xo_n = *reinterpret_cast<const float4*>(p.x + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
+    float4 uo_n = *reinterpret_cast<const float4*>(p.u + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
 #pragma unroll
     for (int a = 0; a < CPT; ++a) {
         const int c = tc * CPT + a;
         const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
-        const float4 xo4 = *reinterpret_cast<const float4*>(p.x + off);
-        const float4 uo4 = *reinterpret_cast<const float4*>(p.u + off);
+        const float4 xo4 = xo_n, uo4 = uo_n;
+        if (a + 1 < CPT) {                               // next component's operands: in flight during this one's math
+            xo_n = *reinterpret_cast<const float4*>(p.x + off + Lp);
+            uo_n = *reinterpret_cast<const float4*>(p.u + off + Lp);
+        }
         const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
         float xn[4], un[4], ax[4];
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
             const double aux = live ? acc[a][b] : 0.0;
-            double xv = aux - static_cast<double>(uo[b]) - thr;
-            xv = (live && xv > 0.0) ? xv : 0.0;
-            const double uv = live ? static_cast<double>(uo[b]) + xv - aux : 0.0;
-            xn[b] = static_cast<float>(xv);
-            un[b] = static_cast<float>(uv);
-            ax[b] = static_cast<float>(aux);
-            const double d0 = xv - aux, d2 = xv - static_cast<double>(xo[b]);
-            n_ra = fma(d0, d0, n_ra); n_x = fma(xv, xv, n_x); n_dx = fma(d2, d2, n_dx); n_u = fma(uv, uv, n_u);
-        }
-        *reinterpret_cast<float4*>(p.x + off) = make_float4(xn[0], xn[1], xn[2], xn[3]);
-        *reinterpret_cast<float4*>(p.u + off) = make_float4(un[0], un[1], un[2], un[3]);
-        if (p.aux_master != nullptr)
-            *reinterpret_cast<float4*>(p.aux_master + off) = make_float4(ax[0], ax[1], ax[2], ax[3]);
-        if (p.aux_cpl != nullptr) {
-            __align__(8) __nv_bfloat16 p0[4], p1[4], p2[4];
-#pragma unroll
-            for (int b = 0; b < 4; ++b) split3(ax[b], p0[b], p1[b], p2[b]);
-            *reinterpret_cast<uint2*>(p.aux_cpl + off) = *reinterpret_cast<const uint2*>(p0);
-            *reinterpret_cast<uint2*>(p.aux_cpl + p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p1);
-            *reinterpret_cast<uint2*>(p.aux_cpl + 2 * p.aux_cpl_plane + off) = *reinterpret_cast<const uint2*>(p2);
-        }
-        __align__(8) __nv_bfloat16 q0[4], q1[4], q2[4];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            split3(xn[b], q0[b], q1[b], q2[b]);
-            rh[b][a] = q0[b];
-            rl[b][a] = q1[b];
-        }
-        if (p.x_cpl != nullptr) {
-            *reinterpret_cast<uint2*>(p.x_cpl + off) = *reinterpret_cast<const uint2*>(q0);
-            *reinterpret_cast<uint2*>(p.x_cpl + p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q1);
-            *reinterpret_cast<uint2*>(p.x_cpl + 2 * p.x_cpl_plane + off) = *reinterpret_cast<const uint2*>(q2);
-        }
-    }
-    if (p.x_rpl != nullptr) {
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const long ro = static_cast<long>(r0 + tr * 4 + b) * KP + tc * CPT;
-#pragma unroll
-            for (int a = 0; a < CPT; a += 4) {
-                *reinterpret_cast<uint2*>(p.x_rpl + ro + a) = *reinterpret_cast<const uint2*>(&rh[b][a]);
-                *reinterpret_cast<uint2*>(p.x_rpl + p.x_rpl_plane + ro + a) = *reinterpret_cast<const uint2*>(&rl[b][a]);
-            }
-        }
-    }
-    if (p.norm_partial != nullptr) {
-        for (int o = 16; o; o >>= 1) {
-            n_ra += __shfl_xor_sync(0xffffffffu, n_ra, o);
-            n_x += __shfl_xor_sync(0xffffffffu, n_x, o);
-            n_dx += __shfl_xor_sync(0xffffffffu, n_dx, o);
-            n_u += __shfl_xor_sync(0xffffffffu, n_u, o);
-        }
-        if ((tid & 31) == 0) {
-            red[tid >> 5][0] = n_ra; red[tid >> 5][1] = n_x; red[tid >> 5][2] = n_dx; red[tid >> 5][3] = n_u;
-        }
-        __syncthreads();
-        if (tid < 4) {
-            double t = 0.0;
-            for (int w = 0; w < 8; ++w) t += red[w][tid];
-            p.norm_partial[static_cast<long>(blockIdx.x) * 4 + tid] = t;
-        }
-    }
-}
-
-// ------------------------------------------------------------------ AO-ADMM inner iteration, split precision
-// aux = Ainv . (C + rho (x + u)) = base + rho * Ainv . (x + u).  base = Ainv . C does not change during the inner
-// loop of a factor update (ao_admm.py:56-62: `w.T @ y` is formed once) and needs fp64 -- C is large and the solve
-// amplifies its rounding -- so the fp64 kernel above computes it ONCE per factor update
-// (base_only).  The per-iteration term multiplies fp32 state; formed in fp32 (Ainv rounded to fp32, FFMA) the
-// trajectory stays within 1.2e-6 of the fp64 oracle over 60 outer iterations at k = 32 and 128 (emulation with the
-// reference's own functions: fp64 apply 1.8e-7, split 1.1e-6; bar 1e-4).  The inner iterations then cost a
-// quarter of the fp64 pipe time and their bytes.
-template <int CPT>
-__global__ void __launch_bounds__(256, CPT <= 8 ? 2 : 1)
-admm_apply32_kernel(const AdmmApplyArgs p) {
-    constexpr int KP = CPT * 16;
-    constexpr int TR = 64;
-    constexpr int CK = 32;
-    extern __shared__ float smem_f[];
-    float* bs = smem_f;                   // [KP][TR]  s = x + u
-    float* gs = smem_f + KP * TR;         // [CK][KP]  rows of Ainv, rounded to fp32
-    __shared__ double red[8][4];
-    if (p.done_flag != nullptr && *p.done_flag != 0) return;
-    const int tid = threadIdx.x;
-    const int tr = tid & 15, tc = tid >> 4;
-    const int r0 = blockIdx.x * TR;
-    const int Lp = p.Lp;
-    const double rho = *p.rho;
-    const double thr = (p.prox == 1) ? static_cast<double>(p.lambda) / rho : 0.0;
-
-    {
-        constexpr int NV4 = KP * TR / 4 / 256;             // all loads of the tile in flight at once
-        float4 xr[NV4], ur[NV4];
-#pragma unroll
-        for (int j = 0; j < NV4; ++j) {
-            const int i = tid + j * 256;
-            const int c = i / (TR / 4), q4 = i - c * (TR / 4);
-            const long off = static_cast<long>(c) * Lp + r0 + q4 * 4;
-            xr[j] = *reinterpret_cast<const float4*>(p.x + off);
-            ur[j] = *reinterpret_cast<const float4*>(p.u + off);
-        }
-#pragma unroll
-        for (int j = 0; j < NV4; ++j)
-            reinterpret_cast<float4*>(bs)[tid + j * 256] =
-                make_float4(xr[j].x + ur[j].x, xr[j].y + ur[j].y, xr[j].z + ur[j].z, xr[j].w + ur[j].w);
-    }
-    float acc[CPT][4];
-#pragma unroll
-    for (int a = 0; a < CPT; ++a)
-#pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-
-    // rows of Ainv: chunk ck + 1 travels from L2 to registers while chunk ck is multiplied (the k x k matrix does not
-    // fit shared memory next to the tile in fp64; the waits for these loads were 1/4 of the kernel, ncu r02h)
-    constexpr int NG = CK * KP / 2 / 256;
-    double2 gr[NG];
-#pragma unroll
-    for (int j = 0; j < NG; ++j) gr[j] = *reinterpret_cast<const double2*>(p.ainv + (tid + j * 256) * 2);
-    for (int ck = 0; ck < KP; ck += CK) {
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < NG; ++j)
-            reinterpret_cast<float2*>(gs)[tid + j * 256] =
-                make_float2(static_cast<float>(gr[j].x), static_cast<float>(gr[j].y));
-        if (ck + CK < KP) {
-#pragma unroll
-            for (int j = 0; j < NG; ++j)
-                gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck + CK) * KP + (tid + j * 256) * 2);
-        }
-        __syncthreads();
-#pragma unroll 4
-        for (int cc = 0; cc < CK; ++cc) {
-            const float4 xv = *reinterpret_cast<const float4*>(bs + (ck + cc) * TR + tr * 4);
-            const float* grow = gs + cc * KP + tc * CPT;          // Ainv symmetric: row (ck+cc)
-#pragma unroll
-            for (int a = 0; a < CPT; a += 4) {
-                const float4 g = *reinterpret_cast<const float4*>(grow + a);
-                acc[a + 0][0] = fmaf(g.x, xv.x, acc[a + 0][0]); acc[a + 0][1] = fmaf(g.x, xv.y, acc[a + 0][1]);
-                acc[a + 0][2] = fmaf(g.x, xv.z, acc[a + 0][2]); acc[a + 0][3] = fmaf(g.x, xv.w, acc[a + 0][3]);
-                acc[a + 1][0] = fmaf(g.y, xv.x, acc[a + 1][0]); acc[a + 1][1] = fmaf(g.y, xv.y, acc[a + 1][1]);
-                acc[a + 1][2] = fmaf(g.y, xv.z, acc[a + 1][2]); acc[a + 1][3] = fmaf(g.y, xv.w, acc[a + 1][3]);
-                acc[a + 2][0] = fmaf(g.z, xv.x, acc[a + 2][0]); acc[a + 2][1] = fmaf(g.z, xv.y, acc[a + 2][1]);
-                acc[a + 2][2] = fmaf(g.z, xv.z, acc[a + 2][2]); acc[a + 2][3] = fmaf(g.z, xv.w, acc[a + 2][3]);
-                acc[a + 3][0] = fmaf(g.w, xv.x, acc[a + 3][0]); acc[a + 3][1] = fmaf(g.w, xv.y, acc[a + 3][1]);
-                acc[a + 3][2] = fmaf(g.w, xv.z, acc[a + 3][2]); acc[a + 3][3] = fmaf(g.w, xv.w, acc[a + 3][3]);
-            }
-        }
-    }
-
-    double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
-    __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
-    float4 xo_n = *reinterpret_cast<const float4*>(p.x + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
-    float4 uo_n = *reinterpret_cast<const float4*>(p.u + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
-    double2 b01_n = *reinterpret_cast<const double2*>(p.c64 + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4);
-    double2 b23_n = *reinterpret_cast<const double2*>(p.c64 + static_cast<long>(tc * CPT) * Lp + r0 + tr * 4 + 2);
-#pragma unroll
-    for (int a = 0; a < CPT; ++a) {
-        const int c = tc * CPT + a;
-        const long off = static_cast<long>(c) * Lp + r0 + tr * 4;
-        const float4 xo4 = xo_n, uo4 = uo_n;
-        const double2 b01 = b01_n, b23 = b23_n;          // base = Ainv . C (fp64)
-        if (a + 1 < CPT) {                               // next component's operands: in flight during this one's math
-            xo_n = *reinterpret_cast<const float4*>(p.x + off + Lp);
-            uo_n = *reinterpret_cast<const float4*>(p.u + off + Lp);
-            b01_n = *reinterpret_cast<const double2*>(p.c64 + off + Lp);
-            b23_n = *reinterpret_cast<const double2*>(p.c64 + off + Lp + 2);
-        }
-        const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
-        const double base[4] = {b01.x, b01.y, b23.x, b23.y};
-        float xn[4], un[4], ax[4];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
-            const double aux = live ? fma(rho, static_cast<double>(acc[a][b]), base[b]) : 0.0;
             double xv = aux - static_cast<double>(uo[b]) - thr;
             xv = (live && xv > 0.0) ? xv : 0.0;
             const double uv = live ? static_cast<double>(uo[b]) + xv - aux : 0.0;
@@ -725,26 +544,6 @@ cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
         admm_apply_kernel<16><<<grid, 256, smem, stream>>>(a);
     }
     if (e != cudaSuccess) return e;
-    count_launch();
-    return cudaGetLastError();
-}
-
-cudaError_t admm_apply32_launch(const AdmmApplyArgs& a, cudaStream_t stream) {
-    const int grid = (a.nrows_p > 0 ? a.nrows_p : a.Lp) / 64;
-    const size_t smem = (static_cast<size_t>(a.KP) * 64 + 32 * static_cast<size_t>(a.KP)) * sizeof(float);
-    if (a.binv != nullptr || a.c64 == nullptr) return cudaErrorInvalidValue;
-    cudaError_t e = cudaSuccess;
-    if (a.KP == 64) {
-        admm_apply32_kernel<4><<<grid, 256, smem, stream>>>(a);
-    } else if (a.KP == 128) {
-        e = cudaFuncSetAttribute(admm_apply32_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        if (e != cudaSuccess) return e;
-        admm_apply32_kernel<8><<<grid, 256, smem, stream>>>(a);
-    } else {
-        e = cudaFuncSetAttribute(admm_apply32_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
-        if (e != cudaSuccess) return e;
-        admm_apply32_kernel<16><<<grid, 256, smem, stream>>>(a);
-    }
     count_launch();
     return cudaGetLastError();
 }

@@ -31,11 +31,7 @@ struct AdmmApplyArgs {
     int nrows_p;              // padded rows of the window (grid = nrows_p / 64); 0 = Lp
     const double* binv;       // fp64 [KP][KP] inverse Tikhonov system (prox l2n) or nullptr; LAST on purpose:
                               // a field in the middle moved the hot kernel from 128 to 132 registers (one CTA/SM)
-    int base_only;            // 1: c64 <- Ainv . (sum of the slots) in fp64 and nothing else (AO-ADMM, see admm.cu)
 };
-// AO-ADMM inner iteration in split precision: aux = base + rho * (Ainv . (x + u)) with base = Ainv . C from the
-// fp64 kernel above (c64) and the per-iteration product in fp32 (FFMA), then prox / dual / norms / planes.
-cudaError_t admm_apply32_launch(const AdmmApplyArgs& a, cudaStream_t stream);
 cudaError_t admm_apply_launch(const AdmmApplyArgs& a, cudaStream_t stream);
 // out[KP][KP] = (lambda / *rho) * T^T T, T = tridiag(-1, 2, -1) of order k (admm.py:142-146)
 cudaError_t tikhonov_gram_launch(int k, int KP, double lambda, const double* rho, double* out, cudaStream_t stream);

@@ -662,11 +662,9 @@ int nmfb_chol_inverse(const double* gram64, int k, int KP, int rho_mode, double 
 namespace {
 
 // aux / prox / dual of one factor (x = `f`, dual `u`) from the numerator in p->partial (or s->c64).
-// mode 0: the fused fp64 kernel (aux = Ainv (C + rho (x + u)), prox, dual); 1: base only (c64 <- Ainv . C, fp64);
-// 2: split-precision inner iteration (aux = c64 + rho * fp32(Ainv . (x + u)), prox, dual) -- see admm.cu
 int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* part, int slots, bool use_c64,
                int side /*0 = H, 1 = W*/, const nmfb_factor* f, float* u, const nmfb_factor* aux, float lambda,
-               int prox, bool want_cpl, bool norms, void* stream, int mode = 0) {
+               int prox, bool want_cpl, bool norms, void* stream) {
     AdmmApplyArgs a;
     memset(&a, 0, sizeof(a));
     const Window w = window_of(f);                        // sharded runs: this rank's rows of the factor only
@@ -689,9 +687,7 @@ int admm_apply(const nmfb_problem* p, const nmfb_admm_state* s, const float* par
     a.x_rpl = bf(f->rplanes) + static_cast<long>(w.w0) * p->KP; a.x_rpl_plane = static_cast<long>(f->Lp) * p->KP;
     if (norms) { a.norm_partial = s->norm_partial + static_cast<long>(w.w0 / 64) * 4; a.done_flag = s->flags + 1; }
     a.KP = p->KP; a.k = p->k; a.L = w.live; a.Lp = f->Lp; a.nrows_p = w.wp;
-    a.base_only = mode == 1 ? 1 : 0;
-    if (mode == 2) { CUDA_TRY(admm_apply32_launch(a, st(stream))); }
-    else           { CUDA_TRY(admm_apply_launch(a, st(stream))); }
+    CUDA_TRY(admm_apply_launch(a, st(stream)));
     return 0;
 }
 
@@ -914,14 +910,12 @@ int nmfb_aoadmm_inner(const nmfb_problem* p, const nmfb_admm_state* s, int side,
     ao_roles(p, s, side, &other, &self, &data, &dual);
     // the auxiliary itself is kept only when the state carries buffers for it (KL branch: a.aux, ao_admm.py:88)
     const nmfb_factor* aux = side == 0 ? &s->h_aux : &s->w_aux;
-    if (prox == NMFB_PROX_L2N && lambda != 0.f)          // two k x k applies in fp64 (admm_apply_l2n_kernel)
-        return admm_apply(p, s, first ? p->partial : nullptr, slots, true, side, self, dual,
-                          aux->master ? aux : nullptr, lambda, prox, true, true, stream);
-    // split precision: base = Ainv . C in fp64 once per right-hand side, the iteration's own term in fp32
-    if (first && (rc = admm_apply(p, s, p->partial, slots, true, side, self, dual, nullptr, lambda, prox, false, false,
-                                  stream, 1)) < 0) return rc;
-    return admm_apply(p, s, nullptr, slots, true, side, self, dual, aux->master ? aux : nullptr, lambda, prox, true,
-                      true, stream, 2);                                                 // ao_admm.py:59-62
+    // The k x k apply stays in fp64 for every inner iteration.  Splitting it (base = Ainv . C in fp64 once per factor
+    // update, the iteration's own term rho * Ainv . (x + u) in fp32) was tried in round 2: 1.6x faster inner loops, but
+    // the transient of the k = 64 trajectory check moved from 9.3e-5 to 1.5e-4 of the objective -- Ainv has
+    // cancelling entries (cond ~ k + 1) and fp32 accumulation of the product is amplified by that factor.
+    return admm_apply(p, s, first ? p->partial : nullptr, slots, true, side, self, dual,
+                      aux->master ? aux : nullptr, lambda, prox, true, true, stream);  // ao_admm.py:59-62
 }
 
 int nmfb_aoadmm_inner_flag(const nmfb_problem* p, const nmfb_admm_state* s, int side, void* stream) {
