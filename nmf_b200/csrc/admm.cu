@@ -19,6 +19,120 @@
 
 namespace nmfb {
 
+// ------------------------------------------------------------------ Gram matrix in fp64
+// G = F F^T of a factor (the sum of its three bf16 cplanes; products and sums in fp64) for the k x k systems of ADMM /
+// AO-ADMM.  The tensor-core Gram (exact-hi contraction of the 23-bit planes) is accurate to ~4e-9 -- the rounding of
+// the operands to their planes -- and the inverse of G + rho I amplifies that to ~7e-8 (measured on a B200 against
+// fp64 NumPy, tools/diag_admm_step.py); being a smooth function of the slowly changing factor it perturbs every
+// iteration in the same direction: the objective drifted by ~3e-6 per iteration on the Kullback-Leibler branch and
+// the 100-iteration Euclidean check sat at 7.5e-5 of its 1e-4 bar.  2 k^2 L fp64 FLOP are a few tens of microseconds
+// on the FP64 pipe and run on the side stream next to the m x n x k numerator GEMM.
+// Block (ti <= tj, split): the 64 x 64 tile (ti, tj) of G over rows [split * rows_per, +rows_per) of the factor.
+// The operand is read from the factor's three bf16 cplanes, not from its fp32 master: the numerator GEMM contracts
+// exactly these planes (23 of the master's 24 bits, fewer for entries far below the row maximum), and a Gram of the
+// master next to a numerator of the planes leaves a 2e-9 mismatch that the solve amplifies a hundredfold (h_aux off by
+// 2.2e-7 although Gram and inverse were exact: tools/diag_admm_step.py, round 2).  With both sides built from the
+// same operand the half step is the exact ridge solution for that operand.
+__global__ void __launch_bounds__(256)
+gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int KP, int rows_per,
+                 double* __restrict__ slots) {
+    __shared__ double As[32][66];
+    __shared__ double Bs[32][66];
+    const int nt = KP / 64;
+    int ti = 0, rem = blockIdx.x;                      // blockIdx.x enumerates the upper triangle row by row
+    while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
+    const int tj = ti + rem;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int r_begin = blockIdx.y * rows_per;
+    const int r_end = min(Lp, r_begin + rows_per);
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+    const __nv_bfloat16* ap = cpl + static_cast<long>(ti) * 64 * Lp;
+    const __nv_bfloat16* bp = cpl + static_cast<long>(tj) * 64 * Lp;
+    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
+        double av[8], bv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {                  // lanes along r: coalesced rows of the planes
+            const int idx = tid + j * 256, rr = idx & 31, c = idx >> 5;
+            const bool ok = r0 + rr < r_end;
+            const long o = static_cast<long>(c) * Lp + r0 + rr;
+            av[j] = bv[j] = 0.0;
+            if (ok) {
+                av[j] = static_cast<double>(__bfloat162float(ap[o])) + static_cast<double>(__bfloat162float(ap[plane + o])) +
+                        static_cast<double>(__bfloat162float(ap[2 * plane + o]));
+                bv[j] = static_cast<double>(__bfloat162float(bp[o])) + static_cast<double>(__bfloat162float(bp[plane + o])) +
+                        static_cast<double>(__bfloat162float(bp[2 * plane + o]));
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int idx = tid + j * 256, rr = idx & 31, c = idx >> 5;
+            As[rr][c] = av[j];
+            Bs[rr][c] = bv[j];
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = As[rr][ty * 4 + i]; b[i] = Bs[rr][tx * 4 + i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+        }
+    }
+    double* out = slots + static_cast<long>(blockIdx.y) * KP * KP;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            out[static_cast<long>(ti * 64 + ty * 4 + i) * KP + tj * 64 + tx * 4 + j] = acc[i][j];
+}
+
+// G[i][j] = sum over the splits (fixed order) of the tile that holds (min, max) of (i / 64, j / 64); mirrored below.
+__global__ void __launch_bounds__(256)
+gram_fp64_reduce_kernel(const double* __restrict__ slots, int nsplit, int KP, float* __restrict__ g32,
+                        double* __restrict__ g64) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= KP * KP) return;
+    const int i = idx / KP, j = idx - i * KP;
+    const bool upper = (i >> 6) <= (j >> 6);
+    const long src = upper ? static_cast<long>(i) * KP + j : static_cast<long>(j) * KP + i;
+    double acc = 0.0;
+    for (int s = 0; s < nsplit; ++s) acc += slots[static_cast<long>(s) * KP * KP + src];
+    g64[idx] = acc;
+    g32[idx] = static_cast<float>(acc);
+}
+
+int gram_fp64_splits(int KP, int Lp) {
+    int s = (Lp + 1023) / 1024;
+    const int cap = KP == 256 ? 48 : 96;
+    if (s > cap) s = cap;
+    return s < 1 ? 1 : s;
+}
+
+size_t gram_fp64_scratch_bytes(int KP, int Lp) {
+    return static_cast<size_t>(gram_fp64_splits(KP, Lp)) * KP * KP * sizeof(double);
+}
+
+cudaError_t gram_fp64_launch(const __nv_bfloat16* cpl, long plane, int KP, int Lp, double* scratch, float* g32,
+                             double* g64, cudaStream_t stream) {
+    const int nsplit = gram_fp64_splits(KP, Lp);
+    int rows_per = (Lp + nsplit - 1) / nsplit;
+    rows_per = (rows_per + 31) / 32 * 32;
+    const int nt = KP / 64;
+    gram_fp64_kernel<<<dim3(nt * (nt + 1) / 2, nsplit), 256, 0, stream>>>(cpl, plane, Lp, KP, rows_per, scratch);
+    count_launch();
+    gram_fp64_reduce_kernel<<<(KP * KP + 255) / 256, 256, 0, stream>>>(scratch, nsplit, KP, g32, g64);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ Cholesky + inverse
 // One CTA of 1024 threads.  `a` is the working matrix (pitch lda doubles): shared memory when
 // KP <= 128, a global scratch otherwise.  Threads are grouped 8 per column for the substitutions;

@@ -4,6 +4,11 @@
 
 namespace nmfb {
 
+// G = F F^T in fp64 of the factor held by three bf16 cplanes [3][256][Lp]; scratch >= gram_fp64_scratch_bytes(KP, Lp)
+cudaError_t gram_fp64_launch(const __nv_bfloat16* cpl, long plane, int KP, int Lp, double* scratch, float* g32,
+                             double* g64, cudaStream_t stream);
+size_t gram_fp64_scratch_bytes(int KP, int Lp);
+
 cudaError_t chol_inverse_launch(const double* gram, int KP, int k, int rho_mode, double rho_in,
                                 double* gscratch, double* ainv, double* rho_out, int* flags,
                                 cudaStream_t stream);

@@ -99,7 +99,7 @@ int nmfb_padded_length(int L) { return round_up(L, 256); }
 size_t nmfb_partial_bytes(int m, int n, int k, int num_sms) {
     const int KP = nmfb_padded_components(k);
     if (KP < 0) return 0;
-    size_t best = 0;
+    size_t best = gram_fp64_scratch_bytes(KP, nmfb_padded_length(m > n ? m : n) + 256 * 16);   // fp64 Gram (ADMM)
     const int Ls[3] = {m, n, 256}, Rs[3] = {n, m, (m > n ? m : n)};
     for (int i = 0; i < 3; ++i)
         for (int nb = 2; nb <= 3; ++nb)
@@ -151,6 +151,8 @@ size_t nmfb_gram_partial_bytes(int k, int L, int num_sms) {
         const size_t b = static_cast<size_t>(xp.slots) * KP * 256 * 4;
         if (b > best) best = b;
     }
+    const size_t f64 = gram_fp64_scratch_bytes(KP, nmfb_padded_length(L) + 256 * 16);    // + sharding pad
+    if (f64 > best) best = f64;
     return best;
 }
 
@@ -718,12 +720,17 @@ int kxk_join(const nmfb_admm_state* s, const KxK& k, void* stream) {
 }
 
 int admm_gram(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_factor* f, int side, const KxK& k) {
+    // fp64 Gram on the FP64 pipe of the SAME three planes the numerator GEMM contracts (admm.cu: the tensor-core Gram
+    // is good to 4e-9, which the inverse of G + rho I turns into a systematic 7e-8; a Gram of the master would not
+    // match the numerator's operand)
+    (void)s;
     const size_t gsz = static_cast<size_t>(p->KP) * p->KP;
-    if (s->exact)
-        return nmfb_gram_exact(f, p->KP, k.partial, k.partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
-                               p->num_sms, k.stream);
-    return nmfb_gram(f, p->KP, 3, k.partial, k.partial_bytes, p->gram32 + side * gsz, p->gram64 + side * gsz,
-                     p->num_sms, k.stream);
+    if (gram_fp64_scratch_bytes(p->KP, f->Lp) > k.partial_bytes)
+        return fail(NMFB_ERR_WORKSPACE, "admm: Gram scratch %zu < %zu bytes", k.partial_bytes,
+                    gram_fp64_scratch_bytes(p->KP, f->Lp));
+    CUDA_TRY(gram_fp64_launch(bf(f->cplanes), 256L * f->Lp, p->KP, f->Lp, reinterpret_cast<double*>(k.partial),
+                              p->gram32 + side * gsz, p->gram64 + side * gsz, st(k.stream)));
+    return 0;
 }
 int admm_gemm(const nmfb_problem* p, const nmfb_admm_state* s, const nmfb_data* data, const nmfb_factor* other,
               const nmfb_factor* self, bool leave_room, void* stream) {

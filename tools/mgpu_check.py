@@ -82,19 +82,47 @@ for (m, n, k, iters) in SHAPES:
         same = [tuple(x) for x in inner] == [tuple(x) for x in tr.inner_breaks]
         ok &= same
         print(f"   inner-iteration pattern {'OK' if same else 'BAD'}", flush=True)
-    if os.environ.get("MGPU_CHECK_QUICK", "0") != "1":
-        # SURVEY 8(f) rows sharded: l2n prox, Kullback-Leibler branch of admm / ao_admm
-        kw = dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"), min_iter=10**9, max_iter=iters)
-        if k <= 128:
-            res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
-            report("admm-l2n", res, orc.admm_run(v, k, w0, h0, **kw), shape)
-        kw = dict(rho=100, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), min_iter=10**9, max_iter=iters)
-        res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
-        report("admm-kl", res, orc.admm_run(v, k, w0, h0, **kw), shape)
-        kw = dict(distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), admm_iter=4, min_iter=10**9,
-                  max_iter=iters)
-        res = ao_admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
-        report("ao-admm-kl", res, orc.ao_admm_run(v, k, w0, h0, **kw), shape)
+
+# ---- SURVEY 8(f) rows sharded: l2n prox and the Kullback-Leibler branch of admm / ao_admm.  Against the oracle at the
+# shape of the single-GPU tests (the KL branch amplifies the 2e-9 error of the right-hand-side contraction: 1.2e-4 /
+# 5e-4 of the objective at 2048 x 1536 / 1500 x 2500 on ONE GPU already), and at a larger shape
+# against the unsharded run of the same code on rank 0's GPU (transitive parity: sharding must not change results).
+def consistent(tag, res, ref, shape, tol=2e-5):
+    global ok
+    if rank != 0:
+        return
+    ew, eh = rel(res.w, ref.w), rel(res.h, ref.h)
+    eo = max(abs(a - b) / abs(b) for a, b in zip(res.obj_history, ref.obj_history))
+    good = max(ew, eh, eo) < tol and res.i == ref.i
+    ok &= good
+    print(f"sharded x{world} == 1 GPU {tag} {'OK ' if good else 'BAD'} {shape} relW={ew:.2e} relH={eh:.2e} relObj={eo:.2e}",
+          flush=True)
+
+
+if os.environ.get("MGPU_CHECK_QUICK", "0") != "1":
+    extras = [("admm-l2n", admm, orc.admm_run, dict(rho=50, reg_w=(0.3, "l2n"), reg_h=(0.5, "l2n"))),
+              ("admm-kl", admm, orc.admm_run, dict(rho=100, distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"))),
+              ("ao-admm-kl", ao_admm, orc.ao_admm_run,
+               dict(distance_type="kl", reg_w=(0, "nn"), reg_h=(0.05, "l1n"), admm_iter=4))]
+    small = (768, 640, 64, 30) if world <= 2 else None           # every rank needs live rows / columns
+    big = (2048, 1536, 64, 20) if world <= 2 else (4096, 6144, 64, 12)
+    for tag, fn, ofn, kw in extras:
+        if small is not None:
+            m, n, k, iters = small
+            v = orc.planted(m, n, k, 0).astype(np.float64)
+            w0, h0 = orc.seeded_init(m, n, k, 1)
+            res = fn(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), min_iter=10**9,
+                     max_iter=iters, **kw)
+            report(tag, res, ofn(v, k, w0, h0, min_iter=10**9, max_iter=iters, **kw), f"m={m} n={n} k={k}")
+        m, n, k, iters = big
+        v = orc.planted(m, n, k, 0).astype(np.float64)
+        w0, h0 = orc.seeded_init(m, n, k, 1)
+        res = fn(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), min_iter=10**9,
+                 max_iter=iters, **kw)
+        if rank == 0:
+            one = fn(v, k, w0=w0, h0=h0, verbose=False, nndsvd_init=(False, "zero"), min_iter=10**9, max_iter=iters, **kw)
+            consistent(tag, res, one, f"m={m} n={n} k={k}")
+        dist.barrier()
 
 
 # ---- the sharded upload (each rank reads its rows and its columns of the host V) must build the very planes the
