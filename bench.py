@@ -50,6 +50,7 @@ WORKLOADS = {
     "ao_admm_kl_65536x16384_k128": ("ao_admm", "kl", 65536, 16384, 128,
                                     dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)),
     "mur_eu_4096x4096_k64": ("mur", "eu", 4096, 4096, 64, {}),          # quick functional check
+    "mur_eu_65536x32768_k256": ("mur", "eu", 65536, 32768, 256, {}),    # 1/16 of config 5: the KP = 256 kernels
 }
 DEFAULT_WORKLOAD = "mur_eu_65536x65536_k128"
 

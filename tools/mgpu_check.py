@@ -11,18 +11,45 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-torch.cuda.set_device(lr)
-dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+FREEZE = "--freeze" in sys.argv          # build container, no GPU: compute and freeze the oracle runs of a world size
+if FREEZE:
+    rank, world, lr = 0, int(sys.argv[sys.argv.index("--freeze") + 1]), 0
+else:
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 try:                                   # torchrun sets OMP_NUM_THREADS=1: the fp64 oracle on rank 0 wants the cores
     from threadpoolctl import threadpool_limits
-    threadpool_limits(max(1, (os.cpu_count() or 1) // world))
+    threadpool_limits(max(1, (os.cpu_count() or 1) // (1 if FREEZE else world)))
 except Exception:                      # noqa: BLE001
     pass
 from oracle import nmf_oracle as orc
-from nmf_b200.admm import admm
-from nmf_b200.ao_admm import ao_admm
-from nmf_b200.mur import mur
+if not FREEZE:
+    from nmf_b200.admm import admm
+    from nmf_b200.ao_admm import ao_admm
+    from nmf_b200.mur import mur
+
+GOLD = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "mgpu")
+
+
+def oracle_run(tag, fn, v, k, w0, h0, **kw):
+    """The fp64 oracle's run -- from tests/golden/mgpu/<tag>.npz when it has been frozen (tools/mgpu_check.py --freeze in
+    the build container: on an 8-GPU box every second of rank 0's NumPy costs eight GPU-seconds), else computed here."""
+    from types import SimpleNamespace
+    path = os.path.join(GOLD, tag.replace(" ", "") + ".npz")
+    if os.path.exists(path):
+        z = np.load(path, allow_pickle=True)
+        return SimpleNamespace(w=z["w"], h=z["h"], i=int(z["i"]), obj_history=list(z["obj_history"]),
+                               inner_breaks=[tuple(x) for x in z["inner_breaks"]], stride=int(z["stride"]))
+    tr = fn(v, k, w0, h0, **kw)
+    if FREEZE:
+        os.makedirs(GOLD, exist_ok=True)
+        st = 4                                     # every 4th row of W / column of H: fixtures of a few hundred KB
+        np.savez_compressed(path, w=tr.w[::st].astype(np.float32), h=tr.h[:, ::st].astype(np.float32), i=np.int64(tr.i),
+                            stride=np.int64(st),
+                            obj_history=np.asarray(tr.obj_history), inner_breaks=np.asarray(getattr(tr, "inner_breaks", [])))
+    return tr
+
 
 TOL = 1e-4
 STOP_MAX = 500 if world <= 2 else 60      # the fp64 oracle on rank 0 is the slow part at the larger shapes
@@ -34,7 +61,8 @@ def report(tag, res, tr, shape):
     global ok
     if rank != 0:
         return
-    ew, eh = rel(res.w, tr.w), rel(res.h, tr.h)
+    st = getattr(tr, "stride", 1)                  # frozen oracle runs keep every st-th row of W / column of H
+    ew, eh = rel(res.w[::st], tr.w), rel(res.h[:, ::st], tr.h)
     eo = max(abs(a - b) / b for a, b in zip(res.obj_history, tr.obj_history))
     good = max(ew, eh, eo) < TOL and res.i == tr.i and len(res.obj_history) == len(tr.obj_history)
     ok &= good
@@ -51,37 +79,45 @@ def same_on_all_ranks(value):
 
 SHAPES = [(1000, 700, 10, 30), (2048, 1536, 64, 40), (1500, 2500, 128, 30)] if world <= 2 else \
     [(3700, 3900, 10, 30), (4096, 6144, 64, 40), (7500, 3800, 128, 30)]      # every rank keeps live rows / columns
+ADMM_KW = dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"))
+AO_KW = dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5)
 for (m, n, k, iters) in SHAPES:
     v = orc.planted(m, n, k, 0).astype(np.float64)
     w0, h0 = orc.seeded_init(m, n, k, 1)
     shape = f"m={m} n={n} k={k}"
-    res = mur(v, k, distance_type="eu", min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False, comm=True)
-    report("mur-eu ", res, orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=10**9, max_iter=iters), shape)
-    # stop test must fire at the same iteration on every rank
-    res2 = mur(v, k, distance_type="eu", min_iter=5, max_iter=STOP_MAX, tol1=1.0, tol2=1e-1, w0=w0, h0=h0, verbose=False, comm=True)
-    its = same_on_all_ranks(res2.i)
-    if rank == 0:
-        tr2 = orc.mur_run(v, k, w0, h0, distance_type="eu", min_iter=5, max_iter=STOP_MAX, tol1=1.0, tol2=1e-1)
-        same = all(g == tr2.i for g in its)
-        ok &= same
-        print(f"   stop iteration ranks={its} oracle={tr2.i} {'OK' if same else 'BAD'}", flush=True)
-
-    res = mur(v, k, distance_type="kl", min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False, comm=True)
-    report("mur-kl ", res, orc.mur_run(v, k, w0, h0, distance_type="kl", min_iter=10**9, max_iter=iters), shape)
-
-    kw = dict(rho=100, reg_w=(0, "nn"), reg_h=(0.1, "l1n"), min_iter=10**9, max_iter=iters)
-    res = admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
-    report("admm   ", res, orc.admm_run(v, k, w0, h0, **kw), shape)
-
-    kw = dict(reg_w=(0, "nn"), reg_h=(0.1, "l1n"), admm_iter=5, min_iter=10**9, max_iter=iters)
-    res = ao_admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), **kw)
-    tr = orc.ao_admm_run(v, k, w0, h0, **kw)
-    report("ao-admm", res, tr, shape)
-    inner = ao_admm.last_inner_iterations
-    if rank == 0 and True:
-        same = [tuple(x) for x in inner] == [tuple(x) for x in tr.inner_breaks]
-        ok &= same
-        print(f"   inner-iteration pattern {'OK' if same else 'BAD'}", flush=True)
+    sid = f"{m}x{n}k{k}"
+    runs = [
+        ("mur-eu ", (lambda: mur(v, k, distance_type="eu", min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False, comm=True)),
+         orc.mur_run, dict(distance_type="eu", min_iter=10**9, max_iter=iters)),
+        ("mur-eu-stop", (lambda: mur(v, k, distance_type="eu", min_iter=5, max_iter=STOP_MAX, tol1=1.0, tol2=1e-1, w0=w0, h0=h0, verbose=False, comm=True)),
+         orc.mur_run, dict(distance_type="eu", min_iter=5, max_iter=STOP_MAX, tol1=1.0, tol2=1e-1)),
+        ("mur-kl ", (lambda: mur(v, k, distance_type="kl", min_iter=10**9, max_iter=iters, w0=w0, h0=h0, verbose=False, comm=True)),
+         orc.mur_run, dict(distance_type="kl", min_iter=10**9, max_iter=iters)),
+        ("admm   ", (lambda: admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), min_iter=10**9, max_iter=iters, **ADMM_KW)),
+         orc.admm_run, dict(min_iter=10**9, max_iter=iters, **ADMM_KW)),
+        ("ao-admm", (lambda: ao_admm(v, k, w0=w0, h0=h0, verbose=False, comm=True, nndsvd_init=(False, "zero"), min_iter=10**9, max_iter=iters, **AO_KW)),
+         orc.ao_admm_run, dict(min_iter=10**9, max_iter=iters, **AO_KW)),
+    ]
+    for tag, gpu_run, ofn, okw in runs:
+        tr = oracle_run(f"w{world}_{sid}_{tag}", ofn, v, k, w0, h0, **okw)
+        if FREEZE:
+            print("frozen", world, sid, tag, tr.i, flush=True)
+            continue
+        res = gpu_run()
+        if tag == "mur-eu-stop":                  # the stop test must fire at the same iteration on every rank
+            its = same_on_all_ranks(res.i)
+            if rank == 0:
+                same = all(g == tr.i for g in its)
+                ok &= same
+                print(f"   stop iteration ranks={its} oracle={tr.i} {'OK' if same else 'BAD'}", flush=True)
+            continue
+        report(tag, res, tr, shape)
+        if tag == "ao-admm" and rank == 0:
+            same = [tuple(x) for x in ao_admm.last_inner_iterations] == [tuple(x) for x in tr.inner_breaks]
+            ok &= same
+            print(f"   inner-iteration pattern {'OK' if same else 'BAD'}", flush=True)
+if FREEZE:
+    sys.exit(0)
 
 # ---- SURVEY 8(f) rows sharded: l2n prox and the Kullback-Leibler branch of admm / ao_admm.  Against the oracle at the
 # shape of the single-GPU tests (the KL branch amplifies the 2e-9 error of the right-hand-side contraction: 1.2e-4 /
