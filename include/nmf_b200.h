@@ -153,6 +153,19 @@ int nmfb_gram_exact(const nmfb_factor* f, int KP, float* partial, size_t partial
 int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
               double* gram64, int num_sms, void* stream);
 
+/* nmfb_gram without a caller workspace, for callers that cannot allocate device memory (CUDA graph capture, serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and results as nmfb_gram; the K-split slots live in a device array built into the library
+ * (nmfb_gram_static_max_bytes() = 8 MiB, held by every GPU that loads the library until the process exits).  Calls no
+ * cudaMalloc / cudaFree / allocating routine.  A shape whose slots exceed the array (k > 128 with L above ~32 K) is
+ * rejected with NMFB_ERR_ARG and a message naming both sizes -- use nmfb_gram there.  All calls on one GPU share the
+ * array: calls that overlap on the GPU (different streams, or graphs replayed concurrently) race; calls on one stream
+ * are ordered.  The array keeps the last call's contents; nothing needs clearing, every slot word read is written by
+ * the same call. */
+size_t nmfb_gram_static_max_bytes(void);
+int nmfb_gram_static(const nmfb_factor* f, int KP, int nplanes, float* gram32, double* gram64, int num_sms,
+                     void* stream);
+
 /* Fused multiplicative update  x <- x * num / (G x + lambda x + 1e-9)  (mur.py:29 / mur.py:45):
  * num = sum of `slots` partial slots, G = Gram of the other factor.  Writes master + all planes. */
 int nmfb_mur_eu_update(const float* partial, int slots, const float* gram_other, const nmfb_factor* f,

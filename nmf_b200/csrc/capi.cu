@@ -2,6 +2,7 @@
 // TMA tensor-map construction and kernel sequencing.  No torch types, no allocation, no syncs.
 #include <cstdarg>
 #include <cstring>
+#include <mutex>
 
 #include "../../include/nmf_b200.h"
 #include "admm.cuh"
@@ -405,6 +406,60 @@ int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t 
     if (slots < 0) return slots;
     CUDA_TRY(gram_reduce_launch(partial, slots, KP, 256, gram32, gram64, st(stream)));
     return 0;
+}
+
+// ---- Gram matrix without caller scratch ------------------------------------------------------------------------
+// Same kernels as nmfb_gram (panel_gemm_kernel into K-split partial slots, gram_reduce_kernel over them), but the
+// slots live in a file-scope device array instead of a caller buffer: for callers that cannot allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the array until
+// the process exits.  No counterpart in the reference.
+#define NMFB_GRAM_STATIC_BYTES (8u << 20)
+static __device__ __align__(256) float g_gram_static_scratch[NMFB_GRAM_STATIC_BYTES / 4];
+
+namespace {
+// `g_gram_static_scratch` is a host-side stand-in in host code, not a device address: resolve the address once per
+// device, with that device current, and hand THAT to the kernels.
+constexpr int kMaxDevices = 64;
+float* g_gram_static_ptr[kMaxDevices] = {};
+std::mutex g_gram_static_mu;
+
+int gram_static_scratch(float** out) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(NMFB_ERR_ARG, "gram_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_gram_static_mu);
+    if (!g_gram_static_ptr[dev]) {
+        float* ptr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_gram_static_scratch));
+        if (!ptr) return fail(NMFB_ERR_CUDA, "gram_static: cudaGetSymbolAddress returned a null address");
+        g_gram_static_ptr[dev] = ptr;
+    }
+    *out = g_gram_static_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+size_t nmfb_gram_static_max_bytes(void) { return NMFB_GRAM_STATIC_BYTES; }
+
+int nmfb_gram_static(const nmfb_factor* f, int KP, int nplanes, float* gram32, double* gram64, int num_sms,
+                     void* stream) {
+    if (!f || !gram32 || !gram64) return fail(NMFB_ERR_ARG, "gram_static: null argument");
+    if (nplanes != 2 && nplanes != 3) return fail(NMFB_ERR_ARG, "gram_static: nplanes must be 2 or 3");
+    if (KP == 256) nplanes = 2;                       // as nmfb_gram
+    PanelGemmPlan pl;
+    if (panel_gemm_plan(KP, nplanes, nplanes, KP, f->L, 128, 0, num_sms, &pl) != 0)
+        return fail(NMFB_ERR_ARG, "gram_static: unsupported configuration KP=%d nplanes=%d", KP, nplanes);
+    const size_t need = static_cast<size_t>(pl.slots) * KP * 256 * 4;
+    if (need > NMFB_GRAM_STATIC_BYTES)
+        return fail(NMFB_ERR_ARG,
+                    "gram_static: KP=%d L=%d needs %zu bytes of K-split slots, the built-in scratch holds %u; "
+                    "use nmfb_gram with a caller buffer of nmfb_gram_partial_bytes()",
+                    KP, f->L, need, static_cast<unsigned>(NMFB_GRAM_STATIC_BYTES));
+    float* scratch = nullptr;
+    const int rc = gram_static_scratch(&scratch);
+    if (rc < 0) return rc;
+    // nothing to clear: every word gram_reduce_kernel reads below is written by the contraction of this same call
+    return nmfb_gram(f, KP, nplanes, scratch, NMFB_GRAM_STATIC_BYTES, gram32, gram64, num_sms, stream);
 }
 
 namespace {
