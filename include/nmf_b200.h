@@ -325,7 +325,8 @@ int nmfb_kl_data_step(const nmfb_data* v_rows, const void* a_planes3, int a_Lp, 
  *                   Gram all-reduce (`w.T @ w` ao_admm.py:53, the re-associated Grams of mur.py:29,45) and the
  *                   objective sum (utils.py:29 over the ranks' rows)
  *   adopt_exchange  the factor's master <- the exchange buffer ([KP][Lp] like the master, all windows current);
- *                   refresh != 0 also re-derives cplanes / rplanes in the same pass
+ *                   refresh != 0 also re-derives cplanes / rplanes in the same pass; refresh == 2 leaves the rows
+ *                   of the rank's own window alone (its update kernel wrote master and planes itself: MUR-eu)
  * Buffers must be double-buffered by the caller (see nmf_b200/csrc/peer.cu for the ordering argument). */
 int nmfb_peer_push(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
                    long dst_pitch, int rows, long row_bytes, void* stream);

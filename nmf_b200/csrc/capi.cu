@@ -210,16 +210,20 @@ int nmfb_fixed_planes(int KP, const nmfb_factor* f, void* stream) {
 }
 
 int nmfb_refresh_planes(int KP, const nmfb_factor* f, void* stream) {
+    if (!f) return fail(NMFB_ERR_ARG, "refresh_planes: null factor");
     CUDA_TRY(refresh_planes_launch(f->master, nullptr, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
-                                   static_cast<long>(f->Lp) * KP, st(stream)));
+                                   static_cast<long>(f->Lp) * KP, 0, 0, st(stream)));
     return 0;
 }
 
 int nmfb_adopt_exchange(int KP, const nmfb_factor* f, const float* xchg, int refresh, void* stream) {
     if (!f || !xchg) return fail(NMFB_ERR_ARG, "adopt_exchange: null argument");
     if (refresh) {
+        // refresh == 2: the rank's own window already holds master and planes of its update kernel (MUR-eu)
+        const int lo = refresh == 2 && f->win_p > 0 ? f->win0 : 0;
+        const int hi = refresh == 2 && f->win_p > 0 ? f->win0 + f->win_p : 0;
         CUDA_TRY(refresh_planes_launch(xchg, f->master, KP, f->Lp, bf(f->cplanes), 256L * f->Lp, bf(f->rplanes),
-                                       static_cast<long>(f->Lp) * KP, st(stream)));
+                                       static_cast<long>(f->Lp) * KP, lo, hi, st(stream)));
     } else {
         CUDA_TRY(cudaMemcpyAsync(f->master, xchg, static_cast<size_t>(KP) * f->Lp * 4, cudaMemcpyDeviceToDevice,
                                  st(stream)));

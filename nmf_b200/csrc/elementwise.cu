@@ -136,37 +136,45 @@ cudaError_t ingest_data_launch(const void* src, int is_f64, long src_ld, int row
 // by solvers whose update kernel does not write planes itself).
 // adopt != nullptr: the values come from `master` (an exchange buffer of the same [KP][Lp] layout that the ranks'
 // windows were stored into, peer.cu) and are also written to `adopt`, the factor's own master.
+// Rows [skip_lo, skip_hi) are left alone (a rank's own window, whose update kernel wrote master and planes itself).
+// grid = (Lp / 256, KP / 16): a thread owns one r and 16 components -- 32-byte runs of the row-major planes, and
+// enough CTAs in flight to cover the latency of the strided master reads (one thread per r over all components was
+// the pace-setter of the sharded exchange: 443 threads per SM, each a serial chain of 128 loads).
 __global__ void __launch_bounds__(256)
 refresh_planes_kernel(const float* __restrict__ master, float* __restrict__ adopt, int KP, int Lp,
                       __nv_bfloat16* __restrict__ cpl, long cpl_plane, __nv_bfloat16* __restrict__ rpl,
-                      long rpl_plane) {
+                      long rpl_plane, int skip_lo, int skip_hi) {
     const int r = blockIdx.x * 256 + threadIdx.x;
-    if (r >= Lp) return;
-    for (int c0 = 0; c0 < KP; c0 += 8) {
-        __align__(16) __nv_bfloat16 h8[8], l8[8];
+    if (r >= Lp || (r >= skip_lo && r < skip_hi)) return;
+    const int c0 = blockIdx.y * 16;
+    float x[16];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const float x = master[static_cast<long>(c0 + q) * Lp + r];
-            if (adopt) adopt[static_cast<long>(c0 + q) * Lp + r] = x;
-            __nv_bfloat16 p0, p1, p2;
-            split3(x, p0, p1, p2);
-            const long o = static_cast<long>(c0 + q) * Lp + r;
-            cpl[o] = p0;
-            cpl[cpl_plane + o] = p1;
-            cpl[2 * cpl_plane + o] = p2;
-            h8[q] = p0;
-            l8[q] = p1;
-        }
-        const long ro = static_cast<long>(r) * KP + c0;
-        *reinterpret_cast<uint4*>(rpl + ro) = *reinterpret_cast<const uint4*>(h8);
-        *reinterpret_cast<uint4*>(rpl + rpl_plane + ro) = *reinterpret_cast<const uint4*>(l8);
+    for (int q = 0; q < 16; ++q) x[q] = master[static_cast<long>(c0 + q) * Lp + r];
+    __align__(16) __nv_bfloat16 h16[16], l16[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        const long o = static_cast<long>(c0 + q) * Lp + r;
+        if (adopt) adopt[o] = x[q];
+        __nv_bfloat16 p0, p1, p2;
+        split3(x[q], p0, p1, p2);
+        cpl[o] = p0;
+        cpl[cpl_plane + o] = p1;
+        cpl[2 * cpl_plane + o] = p2;
+        h16[q] = p0;
+        l16[q] = p1;
     }
+    const long ro = static_cast<long>(r) * KP + c0;
+    *reinterpret_cast<uint4*>(rpl + ro) = *reinterpret_cast<const uint4*>(h16);
+    *reinterpret_cast<uint4*>(rpl + ro + 8) = *reinterpret_cast<const uint4*>(h16 + 8);
+    *reinterpret_cast<uint4*>(rpl + rpl_plane + ro) = *reinterpret_cast<const uint4*>(l16);
+    *reinterpret_cast<uint4*>(rpl + rpl_plane + ro + 8) = *reinterpret_cast<const uint4*>(l16 + 8);
 }
 
 cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int Lp, __nv_bfloat16* cpl,
-                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream) {
-    refresh_planes_kernel<<<(Lp + 255) / 256, 256, 0, stream>>>(master, adopt, KP, Lp, cpl, cpl_plane, rpl,
-                                                               rpl_plane);
+                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, int skip_lo, int skip_hi,
+                                  cudaStream_t stream) {
+    refresh_planes_kernel<<<dim3((Lp + 255) / 256, KP / 16), 256, 0, stream>>>(master, adopt, KP, Lp, cpl, cpl_plane,
+                                                                             rpl, rpl_plane, skip_lo, skip_hi);
     count_launch();
     return cudaGetLastError();
 }

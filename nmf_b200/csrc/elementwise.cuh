@@ -14,7 +14,8 @@ cudaError_t data_absmax_launch(const void* src, int is_f64, long src_ld, int row
 cudaError_t fixed_planes_launch(const float* master, int KP, int Lp, __nv_bfloat16* cpl, long cpl_plane,
                                 cudaStream_t stream);
 cudaError_t refresh_planes_launch(const float* master, float* adopt, int KP, int Lp, __nv_bfloat16* cpl,
-                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, cudaStream_t stream);
+                                  long cpl_plane, __nv_bfloat16* rpl, long rpl_plane, int skip_lo, int skip_hi,
+                                  cudaStream_t stream);
 cudaError_t row_planes3_launch(const float* master, int KP, int Lp, __nv_bfloat16* out, cudaStream_t stream);
 cudaError_t zero_words_guarded_launch(unsigned int* a, int na, unsigned int* b, int nb, const int* done_flag,
                                       cudaStream_t stream);

@@ -40,6 +40,8 @@ class MurEuStepper:
             e.gather_factor(e.h, gram_index=1)
         e.objective_eu(slot=ring_slot * 8)
         e.reduce_scalar(ring_slot * 8)
+        if e.peer is not None:
+            e._mark(7)
 
     def phase_names(self):
         return self.phases
@@ -48,7 +50,12 @@ class MurEuStepper:
         """(name, first event, last event) triples that are recorded in this mode."""
         if self.eng.world == 1:
             return [(nm, j, j + 1) for j, nm in enumerate(self.phases)]
-        return [("gemm_w", 1, 2), ("update_w", 2, 3), ("gemm_h", 4, 5), ("update_h", 5, 6)]
+        # update_*: the wait for the Gram terms of the side streams (cross-GPU barrier + sum) and the fused update;
+        # exchange_w: window push, barrier, adoption of all windows; the last interval also holds the objective
+        if self.eng.peer is None:
+            return [("gemm_w", 1, 2), ("update_w", 2, 3), ("gemm_h", 4, 5), ("update_h", 5, 6)]
+        return [("gemm_w", 1, 2), ("update_w", 2, 3), ("exchange_w", 3, 4), ("gemm_h", 4, 5), ("update_h", 5, 6),
+                ("exchange_h_objective", 6, 7)]
 
     def roofline(self, phase_ms, peaks):
         """Dominant kernel = the split-bf16 panel GEMM (two launches per iteration: V.H^T and

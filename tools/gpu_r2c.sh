@@ -10,7 +10,7 @@ import json, sys
 for ln in open(sys.argv[1]):
     if ln.startswith('{'):
         d = json.loads(ln)
-        print('  value', round(d['value'], 1), 'it/s', round(d['ms_per_step'], 3), 'ms', d['phase_ms'], d['config'].get('exchange', '')[:40], 'e2e', d.get('e2e'), 'ttt', d.get('time_to_tol'))
+        print('  value', round(d['value'], 1), 'it/s', round(d['ms_per_step'], 3), 'ms', d['phase_ms'], d['config'].get('exchange', '')[:40], 'xchg', d.get('exchange_ms'), 'e2e', d.get('e2e'), 'ttt', d.get('time_to_tol'))
 PY
 }
 for w in ${WORKLOADS:-mur_eu_65536x65536_k128 mur_kl_20000x50000_k128 admm_65536x16384_k128 ao_admm_65536x16384_k128}; do
@@ -27,4 +27,8 @@ for w in ${SINGLE:-}; do
   timeout 600 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu --no-e2e > gpurun_out/r2c_bench_g1_$w.json 2> gpurun_out/r2c_bench_g1_$w.err
   echo "bench $w x1 exit $?" >> $S; line gpurun_out/r2c_bench_g1_$w.json $S
 done
+if [ "${PYTEST_MULTI:-0}" = 1 ]; then
+  timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -x -q > gpurun_out/r2c_pytest_multi_$N.log 2>&1; echo "pytest test_gpu_multi exit $?" >> $S
+  tail -3 gpurun_out/r2c_pytest_multi_$N.log >> $S
+fi
 cat $S

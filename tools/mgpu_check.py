@@ -173,9 +173,11 @@ def planes_of(v, fixed, full_walk):
     return out
 
 
-for tag, v, fixed in (("exact fp32", orc.planted(1800, 2300, 16, 3), False),
-                      ("inexact fp64", np.random.default_rng(4).random((1800, 2300)), False),
-                      ("fixed-point", orc.planted(2300, 1800, 16, 5).astype(np.float64), True)):
+# ragged shapes that leave every rank rows and columns (shards are multiples of 256)
+um, un = 1024 * world - 248, 768 * world - 100
+for tag, v, fixed in (("exact fp32", orc.planted(um, un, 16, 3), False),
+                      ("inexact fp64", np.random.default_rng(4).random((um, un)), False),
+                      ("fixed-point", orc.planted(un, um, 16, 5).astype(np.float64), True)):
     a, b = planes_of(v, fixed, False), planes_of(v, fixed, True)
     same = a[0] == b[0] and a[1] == b[1] and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
     flags = same_on_all_ranks(int(same))
