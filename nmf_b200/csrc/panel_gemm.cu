@@ -375,8 +375,6 @@ int panel_gemm_plan(int KP, int NB, int NA, int L, int R, int force_bn, int forc
     const int kblocks = (R + kBK - 1) / kBK;
     // cluster size: the factor tiles are multicast across the cluster; needs enough panels.
     int cluster = (KP == 64) ? 4 : 2;
-    if (const char* e = getenv("NMFB_CLUSTER")) cluster = atoi(e);
-    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) cluster = 1;
     while (cluster > 1 && npanels < cluster) cluster >>= 1;
     const int ngroups = (npanels + cluster - 1) / cluster;
     const int ncl = max_resident_clusters(cluster, num_sms);
@@ -399,8 +397,7 @@ int panel_gemm_plan(int KP, int NB, int NA, int L, int R, int force_bn, int forc
     if (nsplit > kblocks) nsplit = kblocks;
     int kb_per = (kblocks + nsplit - 1) / nsplit;
     nsplit = (kblocks + kb_per - 1) / kb_per;            // no empty splits
-    int chunk_kb = 8;
-    if (const char* e = getenv("NMFB_CHUNK_KB")) chunk_kb = atoi(e) > 0 ? atoi(e) : 8;
+    const int chunk_kb = 8;
     plan->BN = BN;
     plan->nstages = nstages;
     plan->npanels = npanels;
@@ -412,13 +409,8 @@ int panel_gemm_plan(int KP, int NB, int NA, int L, int R, int force_bn, int forc
     plan->cluster = cluster;
     plan->ngroups = ngroups;
     plan->chunk_kb = chunk_kb;
-    int dbr = BN, pf = 0;
-    if (const char* e = getenv("NMFB_DAT_BOX")) dbr = atoi(e);
-    if (dbr != 64 && dbr != 128 && dbr != 256) dbr = BN;
-    if (dbr > BN) dbr = BN;
-    if (const char* e = getenv("NMFB_PREFETCH")) pf = atoi(e);
-    plan->dat_box_rows = dbr;
-    plan->prefetch_kb = pf < 0 ? 0 : pf;
+    plan->dat_box_rows = BN;
+    plan->prefetch_kb = 0;
     plan->max_clusters = ncl;
     return 0;
 }

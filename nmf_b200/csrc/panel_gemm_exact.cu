@@ -288,8 +288,6 @@ int panel_gemm_exact_plan(int KP, int NA, int L, int R, int blocked, int num_sms
     const int npanels = (L + BN - 1) / BN;
     const int kblocks = (R + kBKx - 1) / kBKx;
     int cluster = 2;
-    if (const char* e = getenv("NMFB_CLUSTER_X")) cluster = atoi(e);
-    if (cluster != 1 && cluster != 2 && cluster != 4) cluster = 1;
     while (cluster > 1 && npanels < cluster) cluster >>= 1;
     const int ngroups = (npanels + cluster - 1) / cluster;
     PanelGemmPlan probe;                      // resident-cluster count of the sibling kernel (same footprint)

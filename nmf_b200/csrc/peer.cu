@@ -125,7 +125,7 @@ cudaError_t peer_push_launch(const void* src, long src_pitch, void* const* peers
     for (int p = 0; p < kMaxPeers; ++p) d.p[p] = p < world ? peers_host[p] : nullptr;
     const long total = (row_bytes >> 4) * rows;
     long blocks = (total + 255) / 256;
-    if (blocks > 64) blocks = 64;                 // 64 CTAs per destination are plenty for NVLink stores
+    if (blocks > 592 / world) blocks = 592 / world;   // ~4 CTAs per SM over all destinations
     if (blocks < 1) blocks = 1;
     peer_push_kernel<<<dim3(static_cast<unsigned>(blocks), world), 256, 0, stream>>>(
         static_cast<const char*>(src), src_pitch, d, dst_off, dst_pitch, rows, row_bytes);
@@ -163,7 +163,7 @@ cudaError_t peer_push_mc_launch(const void* src, long src_pitch, void* mc_base, 
     if (!mc_base || (row_bytes & 15) || rows < 1) return cudaErrorInvalidValue;
     const long total = (row_bytes >> 4) * rows;
     long blocks = (total + 255) / 256;
-    if (blocks > 148) blocks = 148;
+    if (blocks > 592) blocks = 592;               // 4 CTAs per SM: the copy is a load-latency chain per thread
     if (blocks < 1) blocks = 1;
     peer_push_mc_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
         static_cast<const char*>(src), src_pitch, static_cast<char*>(mc_base) + dst_off, dst_pitch, rows, row_bytes);

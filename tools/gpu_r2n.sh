@@ -3,8 +3,6 @@
 N=${1:-8}
 mkdir -p gpurun_out; S=gpurun_out/r2n_summary_$N.log; : > $S
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512"
-MGPU_CHECK_QUICK=1 timeout 900 $TR tools/mgpu_check.py > gpurun_out/r2n_mgpu_check_$N.log 2>&1; echo "mgpu_check x$N exit $?" >> $S
-grep -E "sharded|stop iteration|inner-iteration|MGPU|Error|error" gpurun_out/r2n_mgpu_check_$N.log | head -60 >> $S
 line() { python - "$1" <<'PY' >> "$2" 2>&1
 import json, sys
 for ln in open(sys.argv[1]):
@@ -12,7 +10,7 @@ for ln in open(sys.argv[1]):
         d = json.loads(ln)
         r = d.get('roofline') or {}
         print('  value', round(d['value'], 2), 'it/s', round(d['ms_per_step'], 3), 'ms', d['phase_ms'], 'roof', r.get('bound'), round(r.get('frac') or 0, 3),
-              d['config'].get('exchange', '')[:24], 'e2e', d.get('e2e'), 'ttt', d.get('time_to_tol'))
+              d['config'].get('exchange', '')[:24], 'xchg', d.get('exchange_ms'), 'e2e', d.get('e2e'), 'ttt', d.get('time_to_tol'))
 PY
 }
 for w in ${WORKLOADS:-mur_eu_65536x65536_k128 mur_eu_262144x131072_k256 admm_65536x16384_k128 ao_admm_65536x16384_k128 mur_kl_20000x50000_k128}; do
@@ -21,4 +19,6 @@ for w in ${WORKLOADS:-mur_eu_65536x65536_k128 mur_eu_262144x131072_k256 admm_655
   echo "bench $w x$N exit $?" >> $S
   line gpurun_out/r2n_bench_g${N}_$w.json $S || grep -v "^W0\|^\*\*\*\|OMP_NUM" gpurun_out/r2n_bench_g${N}_$w.err | tail -12 >> $S
 done
+MGPU_CHECK_QUICK=1 timeout 900 $TR tools/mgpu_check.py > gpurun_out/r2n_mgpu_check_$N.log 2>&1; echo "mgpu_check x$N exit $?" >> $S
+grep -E "sharded|stop iteration|inner-iteration|MGPU|Error|error" gpurun_out/r2n_mgpu_check_$N.log | head -60 >> $S
 cat $S
