@@ -54,13 +54,17 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "mur_eu_65536x65536_k128"
 
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the
-# `ncu --set full` captures of these workloads (profiles/r01b_all_paths.md); per launch, like `achieved`.
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from an `ncu --set full` capture
+# of the same kernel at the same shape (per launch, like `achieved`), with the capture it comes from.
 NCU_TRAFFIC = {
-    ("panel_gemm_kernel", "mur_eu_65536x65536_k128"): 8.624068e9 + 85.743104e6,
-    ("kl_panel_kernel", "mur_kl_20000x50000_k128"): 2.061042e9 + 64.324352e6,
-    ("panel_gemm_kernel", "admm_65536x16384_k128"): 4.393657e9 + 188.351488e6,        # exact-hi variant
-    ("panel_gemm_kernel", "ao_admm_65536x16384_k128"): 4.393657e9 + 188.351488e6,
+    ("panel_gemm_kernel", "mur_eu_65536x65536_k128"):
+        (8.624068e9 + 85.743104e6, "profiles/r01b_all_paths.md (kernel unchanged since)"),
+    ("kl_panel_ts2_kernel", "mur_kl_20000x50000_k128"):
+        (2.099853e9 + 65.275136e6, "profiles/r02a_ncu_full_variants.md"),
+    ("panel_gemm_exact_kernel", "admm_65536x16384_k128"):
+        (4.393657e9 + 188.351488e6, "profiles/r01b_all_paths.md (kernel unchanged since)"),
+    ("panel_gemm_exact_kernel", "ao_admm_65536x16384_k128"):
+        (4.393657e9 + 188.351488e6, "profiles/r01b_all_paths.md (kernel unchanged since)"),
 }
 
 
@@ -509,8 +513,8 @@ def run_b200(args):
     if roof is not None and world == 1:
         t = NCU_TRAFFIC.get((roof.get("kernel"), args.workload))
         if t is not None:
-            roof["traffic"] = t
-            roof["traffic_source"] = "ncu --set full, one launch, profiles/r01b_all_paths.md"
+            roof["traffic"] = t[0]
+            roof["traffic_source"] = "ncu --set full, one launch: " + t[1]
 
     line = {
         "metric": "nmf_outer_iterations_per_second", "value": value, "unit": "it/s", "n_gpus": world,

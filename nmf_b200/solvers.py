@@ -75,7 +75,7 @@ class MurEuStepper:
         # 2-byte V read once these shapes sit on the ridge or on the HBM side); the executed-MMA fraction
         # (mpp MMAs per algorithmic product) is reported next to it
         bound = "tensor" if tensor_frac >= hbm_frac else "hbm"
-        out = {"kernel": "panel_gemm_kernel", "bound": bound, "ms_per_launch": ms,
+        out = {"kernel": "panel_gemm_exact_kernel" if mpp == 5 else "panel_gemm_kernel", "bound": bound, "ms_per_launch": ms,
                "executed_mma_per_product": mpp, "traffic": None,
                "tensor": {"achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tensor_frac,
                           "executed_frac": mpp * tensor_frac},
@@ -133,7 +133,7 @@ class MurKlStepper:
         tf = 4.0 * e.m * e.n * e.k / e.world / (ms * 1e-3) / 1e12      # per rank (its shard of V)
         gbs = 2.0 * e.m * e.n * e.nv / e.world / (ms * 1e-3) / 1e9
         peak = peaks["bf16_tflops_sustained"]
-        return {"kernel": "kl_panel_kernel", "bound": "tensor", "ms_per_launch": ms, "executed_mma_per_product": 3,
+        return {"kernel": "kl_panel_ts2_kernel" if e.KP == 128 else "kl_panel_ts_kernel", "bound": "tensor", "ms_per_launch": ms, "executed_mma_per_product": 3,
                 "traffic": None, "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                 "executed_frac": 3 * tf / peak,
                 "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"]},

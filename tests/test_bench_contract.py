@@ -78,7 +78,7 @@ def test_roofline_reports_are_per_rank_and_pick_the_binding_roof():
     peaks = dict(hbm_gbs=6500.0, bf16_tflops=1600.0, bf16_tflops_sustained=1400.0, source="measured")
     m, n, k = 65536, 65536, 128
     for world in (1, 8):
-        eng = SimpleNamespace(m=m, n=n, k=k, world=world, nv=1, fixed=False)
+        eng = SimpleNamespace(m=m, n=n, k=k, KP=128, world=world, nv=1, fixed=False)
         ms = 1.6 / world
         r = solvers.MurEuStepper(eng).roofline({"gemm_w": ms, "gemm_h": ms}, peaks)
         assert r["kernel"] == "panel_gemm_kernel" and r["bound"] == "hbm"          # 2-byte V read once: HBM side
@@ -86,7 +86,7 @@ def test_roofline_reports_are_per_rank_and_pick_the_binding_roof():
         assert r["frac"] == r["achieved"] / r["peak"] and r["unit"] == "GB/s" and r["peak"] == 6500.0
         assert 0 < r["frac"] < 1 and 0 < r["tensor"]["frac"] < 1
         q = solvers.MurKlStepper(eng).roofline({"kl_w": ms, "kl_h": ms}, peaks)
-        assert q["kernel"] == "kl_panel_kernel" and q["unit"] == "TFLOP/s"
+        assert q["kernel"] == "kl_panel_ts2_kernel" and q["unit"] == "TFLOP/s"
         assert abs(q["achieved"] - 4.0 * m * n * k / 1.6e-3 / 1e12) < 1e-6 * q["achieved"]
         assert 0 < q["frac"] < 1 and 0 < q["hbm"]["frac"] < 1
     # exact-hi ADMM contraction: 5 executed MMAs per algorithmic product
