@@ -174,18 +174,10 @@ class Engine:
         self.peer = PeerArena(self.lib, layout, self.device, self.rank, self.world, self.group)
         self._attach_exchange(self.w, self.peer, "xw")
         self._attach_exchange(self.h, self.peer, "xh")
-        self.gram_term = torch.zeros((KP, KP), dtype=torch.float64, device=self.device)
-        self.gram_term32 = torch.zeros((KP, KP), dtype=torch.float32, device=self.device)
         self._scal_count = self._norm_count = self._gram_count = 0
-        # MUR-eu: a rank's term of the Gram matrix of the factor it just updated is contracted and pushed on a side
-        # stream, next to the window exchange and the GEMM of the next half step (which do not need it); the update
-        # kernel behind that GEMM is the first consumer (_finish_pending_gram)
-        Lwin = max(self.per_m, self.per_n)
-        nbytes = int(self.lib.nmfb_gram_partial_bytes(self.k, Lwin, self.num_sms))
-        self.mur_gram_scratch = torch.empty(max(nbytes, 4) // 4, dtype=torch.float32, device=self.device)
-        self.mur_side = torch.cuda.Stream(device=self.device)
-        self._gram_fork, self._gram_join = torch.cuda.Event(), torch.cuda.Event()
-        self._pending_gram = None
+        # MUR-eu: scratch of a rank's term of the Gram matrix of the factor it just updated (nmfb_gram_term_push)
+        nbytes = int(self.lib.nmfb_gram_term_scratch_bytes(self.k))
+        self.gram_term_scratch = torch.empty(max(nbytes, 8) // 8, dtype=torch.float64, device=self.device)
         self.exchange_probe = None            # bench: list that collects (label, event) pairs of the exchange steps
 
     @staticmethod
@@ -221,22 +213,17 @@ class Engine:
             return
         KP, w = self.KP, self.world
         g = KP * KP * 8
-        main = torch.cuda.current_stream(self.device)
         self._probe("x0")
         if gram_index is not None:
-            # side stream: my term of the Gram matrix (contraction over my window) into slot `rank` of every rank
+            # my term of the Gram matrix (contraction over my window, FP64 pipe) into slot `rank` of every rank
             gpar = self._gram_count & 1
             self._gram_count += 1
             goff = (gpar * 2 + gram_index) * w * g
-            self._gram_fork.record(main)
-            self.mur_side.wait_event(self._gram_fork)
-            side = self.mur_side.cuda_stream
-            check(self.lib.nmfb_gram_window(C.byref(fs), KP, 2, self.mur_gram_scratch.data_ptr(),
-                                            self.mur_gram_scratch.numel() * 4, self.gram_term32.data_ptr(),
-                                            self.gram_term.data_ptr(), self.num_sms, side))
-            self.peer.push(self.gram_term.data_ptr(), g, "gram", goff + self.rank * g, g, 1, g, side)
-            self._gram_join.record(self.mur_side)
-            self._pending_gram = (gram_index, goff)
+            check(self.lib.nmfb_gram_term_push(C.byref(fs), KP, 2, self.gram_term_scratch.data_ptr(),
+                                               self.gram_term_scratch.numel() * 8, self.peer._ptr_arr, w,
+                                               self.peer.mc_ptr or None,
+                                               self.peer.offsets["gram"] + goff + self.rank * g, self.stream))
+            self._probe("gram_term")
         xptr = self._push_window(fac)
         self._probe("push")
         fac.arena.barrier(self.stream)
@@ -246,21 +233,12 @@ class Engine:
         if fixed:
             check(self.lib.nmfb_fixed_planes(KP, C.byref(fs), self.stream))
         self._probe("adopt")
-
-    def _finish_pending_gram(self):
-        """Second half of the k x k Gram all-reduce: every rank's term has been pushed on the side streams; wait for
-        mine, pass a cross-GPU barrier, sum the terms in rank order (bit-identical on all ranks)."""
-        if self._pending_gram is None:
-            return
-        gram_index, goff = self._pending_gram
-        self._pending_gram = None
-        KP, g = self.KP, self.KP * self.KP * 8
-        torch.cuda.current_stream(self.device).wait_event(self._gram_join)
-        self.peer.barrier(self.stream)
-        slots = self.peer.local.data_ptr() + self.peer.offsets["gram"] + goff
-        check(self.lib.nmfb_sum_rank_slots(slots, self.world, KP * KP, KP * KP,
-                                           self.gram64.data_ptr() + gram_index * g,
-                                           self.gram32.data_ptr() + gram_index * (g // 2), self.stream))
+        if gram_index is not None:
+            # second half of the k x k all-reduce: the ranks' terms summed in rank order (bit-identical everywhere)
+            slots = self.peer.local.data_ptr() + self.peer.offsets["gram"] + goff
+            check(self.lib.nmfb_sum_rank_slots(slots, w, KP * KP, KP * KP, self.gram64.data_ptr() + gram_index * g,
+                                               self.gram32.data_ptr() + gram_index * (g // 2), self.stream))
+            self._probe("gram_sum")
 
     def _probe(self, label: str):
         if self.exchange_probe is not None:
@@ -286,24 +264,8 @@ class Engine:
         del p
 
     def mur_eu_window_step(self, side: int, lam: float):
-        """One factor update of a sharded MUR-eu iteration on this rank's window: the panel GEMM on my rows /
-        columns of V, then -- only now -- the Gram matrix of the other factor (its ranks' terms were pushed on the
-        side streams during the last exchange), then the fused update.  Same kernels and arguments as
-        nmfb_mur_eu_window_step, which runs them back to back."""
         p = self.problem()
-        KP, g = self.KP, self.KP * self.KP
-        me, other = (self.w, self.h) if side == 0 else (self.h, self.w)
-        data = p.v_rows if side == 0 else p.v_cols
-        self._mark(1 + 3 * side)
-        slots = check(self.lib.nmfb_panel_gemm(C.byref(data), other.cplanes.data_ptr(), other.Lp, KP, 2,
-                                               self.partial.data_ptr() + 4 * me.win0, self.partial.numel() * 4,
-                                               me.Lp, self.num_sms, 0, 0, self.stream))
-        self._mark(2 + 3 * side)
-        self._finish_pending_gram()
-        fs = me.struct()
-        check(self.lib.nmfb_mur_eu_update(self.partial.data_ptr(), slots, self.gram32.data_ptr() + 4 * g * (1 - side),
-                                          C.byref(fs), self.k, KP, float(lam), self.stream))
-        self._mark(3 + 3 * side)
+        check(self.lib.nmfb_mur_eu_window_step(C.byref(p), int(side), float(lam), self.stream))
 
     def gather_norm_partials(self, fac: "FactorBuffers"):
         """AO-ADMM residual test (ao_admm.py:33-43): every rank needs all blocks of the four norm partials."""

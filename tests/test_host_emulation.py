@@ -493,3 +493,52 @@ def test_fixed_planes_kernel_on_signed_factors(emu):
     err = np.abs(p.sum(0) - x)
     assert np.all(err[live] <= np.ldexp(mx[live], -21)[:, None])
     assert not p[:, ~live].any()
+
+
+# ----------------------------------------------------------------------------------------------
+# Sharded exchange (round 2): a rank's window term of the Gram matrix on the FP64 pipe, and the plane refresh that
+# adopts the exchanged windows.
+# ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("KP,k,nplanes", [(64, 10, 2), (128, 100, 2), (128, 128, 3), (256, 200, 2)])
+def test_gram_window_term_kernels(emu, KP, k, nplanes):
+    """nmfb_gram_term_push without the peer stores: the term equals the float64 Gram of the window rows of the
+    operand the planes hold (exact products of 16 / 24-bit operands), symmetric, zero in the padded components."""
+    Lp, r_lo, rows = 1024, 256, 512                     # window [256, 768) of a factor of 1024 rows
+    rng = np.random.default_rng(KP + nplanes)
+    x = _factor(KP, k, Lp, Lp, rng)
+    p0 = orc.round_to_bf16_grid(x)
+    p1 = orc.round_to_bf16_grid(x - p0)
+    p2 = orc.round_to_bf16_grid(x - p0 - p1)
+    cpl = np.zeros((3, 256, Lp), np.uint16)
+    cpl[0, :KP], cpl[1, :KP] = f32_to_bf16(p0), f32_to_bf16(p1)
+    cpl[2, :KP] = f32_to_bf16(p2) if nplanes == 3 else 0x7FC0          # a stale third plane must not be read
+    operand = (p0.astype(np.float64) + p1 + (p2 if nplanes == 3 else 0.0))[:, r_lo:r_lo + rows]
+    want = operand @ operand.T
+    for rows_per in (64, 96, 512):
+        nsplit = (rows + rows_per - 1) // rows_per
+        scratch = np.full((nsplit, KP, KP), np.nan)
+        out = np.full((KP, KP), np.nan)
+        emu.emu_gram_term(ptr(cpl), KP, Lp, r_lo, rows, rows_per, nsplit, nplanes, ptr(scratch), ptr(out))
+        np.testing.assert_allclose(out, want, rtol=1e-13, atol=1e-13 * np.abs(want).max())
+        assert np.array_equal(out, out.T) and not out[k:].any()
+
+
+@pytest.mark.parametrize("KP", [64, 256])
+def test_refresh_planes_kernel_adopts_windows_and_skips_the_own_one(emu, KP):
+    Lp, lo, hi = 768, 256, 512
+    rng = np.random.default_rng(KP)
+    xchg = _factor(KP, KP - 3, Lp, Lp, rng)
+    master = np.full((KP, Lp), -1.0, np.float32)
+    cpl, rpl = np.full((3, 256, Lp), 7, np.uint16), np.full((2, Lp, KP), 7, np.uint16)
+    emu.emu_refresh_planes(ptr(xchg), ptr(master), KP, Lp, ptr(cpl), ptr(rpl), lo, hi)
+    keep = np.r_[0:lo, hi:Lp]
+    assert np.array_equal(master[:, keep], xchg[:, keep]) and (master[:, lo:hi] == -1.0).all()
+    h = orc.round_to_bf16_grid(xchg)
+    l1 = orc.round_to_bf16_grid(xchg - h)
+    l2 = orc.round_to_bf16_grid(xchg - h - l1)
+    for pl, want in enumerate((h, l1, l2)):
+        assert np.array_equal(bf16_to_f32(cpl[pl, :KP][:, keep]), want[:, keep]) and (cpl[pl, :KP, lo:hi] == 7).all()
+    assert np.array_equal(bf16_to_f32(rpl[0][keep]), h.T[keep]) and np.array_equal(bf16_to_f32(rpl[1][keep]), l1.T[keep])
+    assert (rpl[:, lo:hi] == 7).all()
+    emu.emu_refresh_planes(ptr(xchg), None, KP, Lp, ptr(cpl), ptr(rpl), 0, 0)          # nmfb_refresh_planes
+    assert np.array_equal(bf16_to_f32(cpl[0, :KP]), h) and np.array_equal(bf16_to_f32(rpl[1]), l1.T)

@@ -126,4 +126,25 @@ void emu_objective_simt(const std::uint16_t* vpl, long v_plane, int v_rows_p, in
     });
 }
 
+// gram_fp64_terms_launch + gram_term_push_launch without the stores to the peers: a rank's window term of F F^T
+// from 2 or 3 bf16 planes, split over `nsplit` row ranges, then reduced / mirrored pair by pair into out [KP][KP]
+void emu_gram_term(const std::uint16_t* cpl, int KP, int Lp, int r_lo, int rows, int rows_per, int nsplit, int nplanes,
+                   double* scratch, double* out) {
+    const int nt = KP / 64;
+    emu::launch({static_cast<unsigned>(nt * (nt + 1) / 2), static_cast<unsigned>(nsplit), 1}, {256, 1, 1}, 0, [&] {
+        gram_fp64_kernel(reinterpret_cast<const bf16*>(cpl), 256L * Lp, Lp, KP, rows_per, r_lo, r_lo + rows, nplanes,
+                         scratch);
+    });
+    for (int idx = 0; idx < KP * KP; idx += 2) gram_term_pair(scratch, nsplit, KP, idx, out[idx], out[idx + 1]);
+}
+
+// refresh_planes_launch: grid = (Lp / 256, KP / 16)
+void emu_refresh_planes(const float* src, float* adopt, int KP, int Lp, std::uint16_t* cpl, std::uint16_t* rpl,
+                        int skip_lo, int skip_hi) {
+    emu::launch({static_cast<unsigned>((Lp + 255) / 256), static_cast<unsigned>(KP / 16), 1}, {256, 1, 1}, 0, [&] {
+        refresh_planes_kernel(src, adopt, KP, Lp, reinterpret_cast<bf16*>(cpl), 256L * Lp, reinterpret_cast<bf16*>(rpl),
+                              static_cast<long>(Lp) * KP, skip_lo, skip_hi);
+    });
+}
+
 }  // extern "C"
