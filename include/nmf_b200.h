@@ -345,15 +345,6 @@ int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int
 int nmfb_sum_rank_slots(const double* slots, int world, long stride, int n, double* out64, float* out32,
                         void* stream);
 int nmfb_adopt_exchange(int KP, const nmfb_factor* f, const float* xchg, int refresh, void* stream);
-/* First half of the k x k Gram all-reduce of a sharded run (`w.T @ w` ao_admm.py:53 and the re-associated Grams of
- * mur.py:29,45, whose contraction over L splits over the ranks): this rank's term -- the contraction over the rows
- * of its window, on the FP64 pipe from nplanes (2: hi/lo, MUR; 3: ADMM family) bf16 cplanes -- is reduced over its
- * K-splits and stored at byte offset dst_off of EVERY rank's arena (through mc_base when non-NULL, else to
- * peers_host[0..world)).  After nmfb_peer_barrier, nmfb_sum_rank_slots adds the terms in rank order.
- * scratch >= nmfb_gram_term_scratch_bytes(k). */
-size_t nmfb_gram_term_scratch_bytes(int k);
-int nmfb_gram_term_push(const nmfb_factor* f, int KP, int nplanes, double* scratch, size_t scratch_bytes,
-                        void* const* peers_host, int world, void* mc_base, long dst_off, void* stream);
 /* This rank's term of the Gram matrix: nmfb_gram over the rows of the factor's window only. */
 int nmfb_gram_window(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes,
                      float* gram32, double* gram64, int num_sms, void* stream);

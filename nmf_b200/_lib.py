@@ -105,9 +105,6 @@ _SIGNATURES.update({
     "nmfb_sum_rank_slots": (c_int, [c_void_p, c_int, c_long, c_int, c_void_p, c_void_p, c_void_p]),
     "nmfb_adopt_exchange": (c_int, [c_int, P(Factor), c_void_p, c_int, c_void_p]),
     "nmfb_gram_window": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
-    "nmfb_gram_term_scratch_bytes": (c_size_t, [c_int]),
-    "nmfb_gram_term_push": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_int, c_void_p, c_long,
-                                    c_void_p]),
     "nmfb_mur_eu_window_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
     "nmfb_row_planes3": (c_int, [c_int, P(Factor), c_void_p, c_void_p]),
     "nmfb_kl_data_step": (c_int, [P(Data), c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_long,

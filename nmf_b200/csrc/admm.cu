@@ -33,11 +33,9 @@ namespace nmfb {
 // master next to a numerator of the planes leaves a 2e-9 mismatch that the solve amplifies a hundredfold (h_aux off by
 // 2.2e-7 although Gram and inverse were exact: tools/diag_admm_step.py, round 2).  With both sides built from the
 // same operand the half step is the exact ridge solution for that operand.
-// Rows [r_lo, r_hi) of the planes (row pitch Lp) are contracted; nplanes = 3 for the ADMM family, 2 for factors whose
-// update kernel maintains hi / lo only (MUR-eu: the ranks' window terms of the sharded Gram all-reduce).
 __global__ void __launch_bounds__(256)
-gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int KP, int rows_per, int r_lo, int r_hi,
-                 int nplanes, double* __restrict__ slots) {
+gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int KP, int rows_per,
+                 double* __restrict__ slots) {
     __shared__ double As[32][66];
     __shared__ double Bs[32][66];
     const int nt = KP / 64;
@@ -45,8 +43,8 @@ gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int 
     while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
     const int tj = ti + rem;
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int r_begin = r_lo + blockIdx.y * rows_per;
-    const int r_end = min(r_hi, r_begin + rows_per);
+    const int r_begin = blockIdx.y * rows_per;
+    const int r_end = min(Lp, r_begin + rows_per);
     const long plane2 = 2 * plane;
     double acc[4][4];
 #pragma unroll
@@ -57,8 +55,7 @@ gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int 
     const __nv_bfloat16* bp = cpl + static_cast<long>(tj) * 64 * Lp;
     const bool diag = ti == tj;                        // diagonal tile: one operand
     // 32 rows x 64 components of both operands per chunk, lanes along r (coalesced rows of the planes); the loads of
-    // chunk t + 1 are in flight while chunk t is multiplied (the first version loaded, waited, multiplied: 199 us for
-    // a 32768-row window term that is 30 us of FP64 work)
+    // chunk t + 1 are in flight while chunk t is multiplied (the first version loaded, waited, multiplied)
     auto load = [&](int r0, double (&av)[8], double (&bv)[8]) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -67,13 +64,13 @@ gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int 
             const long o = static_cast<long>(c) * Lp + r0 + rr;
             av[j] = bv[j] = 0.0;
             if (ok) {
-                av[j] = static_cast<double>(__bfloat162float(ap[o])) + static_cast<double>(__bfloat162float(ap[plane + o]));
-                if (nplanes > 2) av[j] += static_cast<double>(__bfloat162float(ap[plane2 + o]));
+                av[j] = static_cast<double>(__bfloat162float(ap[o])) + static_cast<double>(__bfloat162float(ap[plane + o])) +
+                        static_cast<double>(__bfloat162float(ap[plane2 + o]));
                 if (diag) {
                     bv[j] = av[j];
                 } else {
-                    bv[j] = static_cast<double>(__bfloat162float(bp[o])) + static_cast<double>(__bfloat162float(bp[plane + o]));
-                    if (nplanes > 2) bv[j] += static_cast<double>(__bfloat162float(bp[plane2 + o]));
+                    bv[j] = static_cast<double>(__bfloat162float(bp[o])) + static_cast<double>(__bfloat162float(bp[plane + o])) +
+                            static_cast<double>(__bfloat162float(bp[plane2 + o]));
                 }
             }
         }
@@ -141,39 +138,10 @@ cudaError_t gram_fp64_launch(const __nv_bfloat16* cpl, long plane, int KP, int L
     int rows_per = (Lp + nsplit - 1) / nsplit;
     rows_per = (rows_per + 31) / 32 * 32;
     const int nt = KP / 64;
-    gram_fp64_kernel<<<dim3(nt * (nt + 1) / 2, nsplit), 256, 0, stream>>>(cpl, plane, Lp, KP, rows_per, 0, Lp, 3,
-                                                                        scratch);
+    gram_fp64_kernel<<<dim3(nt * (nt + 1) / 2, nsplit), 256, 0, stream>>>(cpl, plane, Lp, KP, rows_per, scratch);
     count_launch();
     gram_fp64_reduce_kernel<<<(KP * KP + 255) / 256, 256, 0, stream>>>(scratch, nsplit, KP, g32, g64);
     count_launch();
-    return cudaGetLastError();
-}
-
-// A rank's term of a sharded Gram matrix: rows [r_lo, r_lo + rows) only, split finely enough to fill the GPU although
-// the window is short (a window of 8192 rows is 0.27 GFLOP: launch-bound on the tensor-core path, microseconds here).
-// Leaves *nsplit_out slots [KP][KP] (upper-triangle tiles) in scratch for gram_term_push_launch (peer.cu).
-static int gram_term_splits_cap(int KP) {
-    const int nt = KP / 64, tiles = nt * (nt + 1) / 2;
-    int s = 296 / tiles;
-    return s > 128 ? 128 : (s < 1 ? 1 : s);
-}
-
-size_t gram_term_scratch_bytes(int KP) {
-    return static_cast<size_t>(gram_term_splits_cap(KP)) * KP * KP * sizeof(double);
-}
-
-cudaError_t gram_fp64_terms_launch(const __nv_bfloat16* cpl, long plane, int KP, int Lp, int r_lo, int rows,
-                                   int nplanes, double* scratch, int* nsplit_out, cudaStream_t stream) {
-    int nsplit = gram_term_splits_cap(KP);
-    int rows_per = (rows + nsplit - 1) / nsplit;
-    rows_per = (rows_per + 31) / 32 * 32;
-    if (rows_per < 64) rows_per = 64;
-    nsplit = (rows + rows_per - 1) / rows_per;
-    const int nt = KP / 64;
-    gram_fp64_kernel<<<dim3(nt * (nt + 1) / 2, nsplit), 256, 0, stream>>>(cpl, plane, Lp, KP, rows_per, r_lo,
-                                                                        r_lo + rows, nplanes, scratch);
-    count_launch();
-    *nsplit_out = nsplit;
     return cudaGetLastError();
 }
 

@@ -8,11 +8,6 @@ namespace nmfb {
 cudaError_t gram_fp64_launch(const __nv_bfloat16* cpl, long plane, int KP, int Lp, double* scratch, float* g32,
                              double* g64, cudaStream_t stream);
 size_t gram_fp64_scratch_bytes(int KP, int Lp);
-// Window term of a sharded Gram matrix (rows [r_lo, r_lo + rows) of 2 or 3 planes) as *nsplit_out slots in scratch
-// (>= gram_term_scratch_bytes(KP)); reduced and stored into the peers' tables by gram_term_push_launch (peer.cuh).
-cudaError_t gram_fp64_terms_launch(const __nv_bfloat16* cpl, long plane, int KP, int Lp, int r_lo, int rows,
-                                   int nplanes, double* scratch, int* nsplit_out, cudaStream_t stream);
-size_t gram_term_scratch_bytes(int KP);
 
 cudaError_t chol_inverse_launch(const double* gram, int KP, int k, int rho_mode, double rho_in,
                                 double* gscratch, double* ainv, double* rho_out, int* flags,

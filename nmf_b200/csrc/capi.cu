@@ -586,31 +586,6 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
     return objective_common(p, 0, 1, obj_out, stream);
 }
 
-size_t nmfb_gram_term_scratch_bytes(int k) {
-    const int KP = nmfb_padded_components(k);
-    return KP < 0 ? 0 : gram_term_scratch_bytes(KP);
-}
-
-int nmfb_gram_term_push(const nmfb_factor* f, int KP, int nplanes, double* scratch, size_t scratch_bytes,
-                        void* const* peers_host, int world, void* mc_base, long dst_off, void* stream) {
-    // This rank's term of F F^T (contraction over its window) on the FP64 pipe from the bf16 planes, reduced over its
-    // K-splits and stored into every rank's table at dst_off: the first half of the k x k Gram all-reduce.
-    if (!f || !scratch) return fail(NMFB_ERR_ARG, "gram_term_push: null argument");
-    if (nplanes != 2 && nplanes != 3) return fail(NMFB_ERR_ARG, "gram_term_push: nplanes must be 2 or 3");
-    if (KP != 64 && KP != 128 && KP != 256) return fail(NMFB_ERR_ARG, "gram_term_push: KP must be 64 / 128 / 256");
-    if (scratch_bytes < gram_term_scratch_bytes(KP))
-        return fail(NMFB_ERR_WORKSPACE, "gram_term_push: scratch %zu < %zu bytes", scratch_bytes,
-                    gram_term_scratch_bytes(KP));
-    const Window w = window_of(f);
-    if (w.wp <= 0) return fail(NMFB_ERR_ARG, "gram_term_push: empty window");
-    int nsplit = 0;
-    // padded rows of the window hold zeros in every plane: whole 32-row chunks may be read
-    CUDA_TRY(gram_fp64_terms_launch(bf(f->cplanes), 256L * f->Lp, KP, f->Lp, w.w0, w.wp, nplanes, scratch, &nsplit,
-                                    st(stream)));
-    CUDA_TRY(gram_term_push_launch(scratch, nsplit, KP, peers_host, world, mc_base, dst_off, st(stream)));
-    return 0;
-}
-
 namespace {
 int mur_eu_half(const nmfb_problem* p, int side, float lambda, bool with_gram, void* stream) {
     if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_eu_half_step: bad argument");

@@ -116,57 +116,7 @@ sum_rank_slots_kernel(const double* __restrict__ slots, int world, long stride, 
     if (out32) out32[i] = static_cast<float>(acc);
 }
 
-// A rank's term of a sharded Gram matrix into slot `rank` of every rank's table: the K-split slots of
-// gram_fp64_terms_launch (upper-triangle 64 x 64 tiles) are summed in a fixed order, mirrored, and stored -- two
-// doubles per thread -- through the multicast mapping (one multimem.st, the bits of the doubles as four b32 words)
-// or to every peer's pointer.
-__device__ __forceinline__ void gram_term_pair(const double* __restrict__ slots, int nsplit, int KP, int idx,
-                                               double& a0, double& a1) {
-    const int i = idx / KP, j = idx - i * KP;                          // (i, j) and (i, j + 1): same 64 x 64 tile
-    const bool upper = (i >> 6) <= (j >> 6);
-    const long s0 = upper ? static_cast<long>(i) * KP + j : static_cast<long>(j) * KP + i;
-    const long s1 = upper ? s0 + 1 : s0 + KP;
-    a0 = 0.0;
-    a1 = 0.0;
-    for (int s = 0; s < nsplit; ++s) {
-        a0 += slots[static_cast<long>(s) * KP * KP + s0];
-        a1 += slots[static_cast<long>(s) * KP * KP + s1];
-    }
-}
-
-__global__ void __launch_bounds__(256)
-gram_term_push_kernel(const double* __restrict__ slots, int nsplit, int KP, PeerPtrs dst, int world,
-                      char* __restrict__ mc, long dst_off) {
-    const int pair = blockIdx.x * 256 + threadIdx.x;
-    if (pair * 2 >= KP * KP) return;
-    const int idx = pair * 2;
-    double a0, a1;
-    gram_term_pair(slots, nsplit, KP, idx, a0, a1);
-    const long off = dst_off + static_cast<long>(idx) * 8;
-    if (mc != nullptr) {
-        float4 v;                                                     // low word first (little endian)
-        v.x = __int_as_float(__double2loint(a0)); v.y = __int_as_float(__double2hiint(a0));
-        v.z = __int_as_float(__double2loint(a1)); v.w = __int_as_float(__double2hiint(a1));
-        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
-                     ::"l"(mc + off), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-    } else {
-        for (int p = 0; p < world; ++p)
-            *reinterpret_cast<double2*>(static_cast<char*>(dst.p[p]) + off) = make_double2(a0, a1);
-    }
-}
-
 }  // namespace
-
-cudaError_t gram_term_push_launch(const double* slots, int nsplit, int KP, void* const* peers_host, int world,
-                                  void* mc_base, long dst_off, cudaStream_t stream) {
-    if (world < 1 || world > kMaxPeers || (dst_off & 15) || (!mc_base && !peers_host)) return cudaErrorInvalidValue;
-    PeerPtrs d;
-    for (int p = 0; p < kMaxPeers; ++p) d.p[p] = (peers_host && p < world) ? peers_host[p] : nullptr;
-    gram_term_push_kernel<<<(KP * KP / 2 + 255) / 256, 256, 0, stream>>>(slots, nsplit, KP, d, world,
-                                                                        static_cast<char*>(mc_base), dst_off);
-    count_launch();
-    return cudaGetLastError();
-}
 
 cudaError_t peer_push_launch(const void* src, long src_pitch, void* const* peers_host, int world, long dst_off,
                              long dst_pitch, int rows, long row_bytes, cudaStream_t stream) {

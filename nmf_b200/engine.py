@@ -175,9 +175,14 @@ class Engine:
         self._attach_exchange(self.w, self.peer, "xw")
         self._attach_exchange(self.h, self.peer, "xh")
         self._scal_count = self._norm_count = self._gram_count = 0
-        # MUR-eu: scratch of a rank's term of the Gram matrix of the factor it just updated (nmfb_gram_term_push)
-        nbytes = int(self.lib.nmfb_gram_term_scratch_bytes(self.k))
-        self.gram_term_scratch = torch.empty(max(nbytes, 8) // 8, dtype=torch.float64, device=self.device)
+        # MUR-eu: a rank's term of the Gram matrix of the factor it just updated is contracted (tensor cores, a few
+        # CTAs) and stored into the peers' tables on a side stream, under the NVLink-bound push of its window
+        self.gram_term = torch.zeros((KP, KP), dtype=torch.float64, device=self.device)
+        self.gram_term32 = torch.zeros((KP, KP), dtype=torch.float32, device=self.device)
+        nbytes = int(self.lib.nmfb_gram_partial_bytes(self.k, max(self.per_m, self.per_n), self.num_sms))
+        self.gram_scratch = torch.empty(max(nbytes, 4) // 4, dtype=torch.float32, device=self.device)
+        self.gram_stream = torch.cuda.Stream(device=self.device)
+        self._gram_fork, self._gram_join = torch.cuda.Event(), torch.cuda.Event()
         self.exchange_probe = None            # bench: list that collects (label, event) pairs of the exchange steps
 
     @staticmethod
@@ -215,16 +220,22 @@ class Engine:
         g = KP * KP * 8
         self._probe("x0")
         if gram_index is not None:
-            # my term of the Gram matrix (contraction over my window, FP64 pipe) into slot `rank` of every rank
+            # my term of the Gram matrix (contraction over my window) into slot `rank` of every rank's table
             gpar = self._gram_count & 1
             self._gram_count += 1
             goff = (gpar * 2 + gram_index) * w * g
-            check(self.lib.nmfb_gram_term_push(C.byref(fs), KP, 2, self.gram_term_scratch.data_ptr(),
-                                               self.gram_term_scratch.numel() * 8, self.peer._ptr_arr, w,
-                                               self.peer.mc_ptr or None,
-                                               self.peer.offsets["gram"] + goff + self.rank * g, self.stream))
-            self._probe("gram_term")
+            main = torch.cuda.current_stream(self.device)
+            self._gram_fork.record(main)
         xptr = self._push_window(fac)
+        if gram_index is not None:
+            self.gram_stream.wait_event(self._gram_fork)
+            side = self.gram_stream.cuda_stream
+            check(self.lib.nmfb_gram_window(C.byref(fs), KP, 2, self.gram_scratch.data_ptr(),
+                                            self.gram_scratch.numel() * 4, self.gram_term32.data_ptr(),
+                                            self.gram_term.data_ptr(), self.num_sms, side))
+            self.peer.push(self.gram_term.data_ptr(), g, "gram", goff + self.rank * g, g, 1, g, side)
+            self._gram_join.record(self.gram_stream)
+            main.wait_event(self._gram_join)          # the one barrier below covers the window and the Gram term
         self._probe("push")
         fac.arena.barrier(self.stream)
         self._probe("barrier")

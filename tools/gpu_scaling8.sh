@@ -15,7 +15,7 @@ PY
 }
 for w in ${WORKLOADS:-mur_eu_65536x65536_k128 mur_eu_262144x131072_k256 admm_65536x16384_k128 ao_admm_65536x16384_k128 mur_kl_20000x50000_k128}; do
   E2E="--no-e2e"; [ $w = mur_eu_65536x65536_k128 ] && [ "${NO_E2E:-0}" != 1 ] && E2E=""
-  timeout 600 $TR bench.py --gpus $N --workload $w --steps 20 --warmup 5 $E2E > gpurun_out/s8_bench_g${N}_$w.json 2> gpurun_out/s8_bench_g${N}_$w.err
+  timeout ${BENCH_TIMEOUT:-600} $TR bench.py --gpus $N --workload $w --steps 20 --warmup 5 $E2E > gpurun_out/s8_bench_g${N}_$w.json 2> gpurun_out/s8_bench_g${N}_$w.err
   echo "bench $w x$N exit $?" >> $S
   line gpurun_out/s8_bench_g${N}_$w.json $S || grep -v "^W0\|^\*\*\*\|OMP_NUM" gpurun_out/s8_bench_g${N}_$w.err | tail -12 >> $S
 done

@@ -126,16 +126,15 @@ void emu_objective_simt(const std::uint16_t* vpl, long v_plane, int v_rows_p, in
     });
 }
 
-// gram_fp64_terms_launch + gram_term_push_launch without the stores to the peers: a rank's window term of F F^T
-// from 2 or 3 bf16 planes, split over `nsplit` row ranges, then reduced / mirrored pair by pair into out [KP][KP]
-void emu_gram_term(const std::uint16_t* cpl, int KP, int Lp, int r_lo, int rows, int rows_per, int nsplit, int nplanes,
-                   double* scratch, double* out) {
+// gram_fp64_launch: upper-triangle 64 x 64 tiles x row splits on the FP64 pipe, then the fixed-order reduction
+void emu_gram_fp64(const std::uint16_t* cpl, int KP, int Lp, int rows_per, int nsplit, double* scratch, float* g32,
+                   double* g64) {
     const int nt = KP / 64;
     emu::launch({static_cast<unsigned>(nt * (nt + 1) / 2), static_cast<unsigned>(nsplit), 1}, {256, 1, 1}, 0, [&] {
-        gram_fp64_kernel(reinterpret_cast<const bf16*>(cpl), 256L * Lp, Lp, KP, rows_per, r_lo, r_lo + rows, nplanes,
-                         scratch);
+        gram_fp64_kernel(reinterpret_cast<const bf16*>(cpl), 256L * Lp, Lp, KP, rows_per, scratch);
     });
-    for (int idx = 0; idx < KP * KP; idx += 2) gram_term_pair(scratch, nsplit, KP, idx, out[idx], out[idx + 1]);
+    emu::launch({static_cast<unsigned>((KP * KP + 255) / 256), 1, 1}, {256, 1, 1}, 0,
+                [&] { gram_fp64_reduce_kernel(scratch, nsplit, KP, g32, g64); });
 }
 
 // refresh_planes_launch: grid = (Lp / 256, KP / 16)
