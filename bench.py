@@ -539,19 +539,16 @@ def run_b200(args):
     }
 
     # where an exchange spends its time (sharded runs over peer memory): a few extra, untimed steps with an event
-    # after every leg of Engine.gather_factor -- window push | cross-GPU barrier | adoption of all windows
+    # after every leg of nmfb_exchange_factor -- window store (+ Gram term) | cross-GPU barrier | adoption | Gram sum
     if world > 1 and getattr(eng, "peer", None) is not None:
         eng.exchange_probe = []
         for i in range(5):
             do_step(i)
         torch.cuda.synchronize(dev)
         probe, eng.exchange_probe = eng.exchange_probe, None
-        legs = {}
-        for (_, e0), (lab, e1) in zip(probe[:-1], probe[1:]):
-            if lab != "x0":
-                legs.setdefault(lab, []).append(e0.elapsed_time(e1))
+        legs = {lab: [evs[j].elapsed_time(evs[j + 1]) for evs, _ in probe] for j, lab in enumerate(eng.PROBE_LABELS)}
         line["exchange_ms"] = {lab: round(float(np.mean(v)), 4) for lab, v in legs.items()}
-        line["exchange_ms"]["exchanges_per_step"] = round(sum(1 for lab, _ in probe if lab == "x0") / 5, 2)
+        line["exchange_ms"]["exchanges_per_step"] = round(len(probe) / 5, 2)
 
     # ---- end to end through the public API with HOST buffers ----
     line["e2e"] = None

@@ -345,6 +345,39 @@ int nmfb_peer_barrier(void* const* flags_host, int rank, int world, unsigned int
 int nmfb_sum_rank_slots(const double* slots, int world, long stride, int n, double* out64, float* out32,
                         void* stream);
 int nmfb_adopt_exchange(int KP, const nmfb_factor* f, const float* xchg, int refresh, void* stream);
+
+/* The whole exchange of a factor window in ONE call (what the building blocks above do, sequenced here so that the
+ * host issues one call instead of eight: at 8 GPUs an iteration is ~1 ms and the per-launch cost of the caller's
+ * language decides whether the GPUs wait for their host):
+ *   1. store this rank's window of the master into every rank's exchange buffer at byte offset xchg_off of the arenas
+ *      (multicast when ctx->mc_base != NULL, unicast otherwise);
+ *   2. gram_nplanes != 0: on ctx->side_stream (forked / joined with ctx->ev_fork / ev_join), next to 1., contract this
+ *      rank's term of F F^T over its window (nmfb_gram_window) and store it at gram_off + rank * KP*KP*8 of every arena;
+ *   3. cross-GPU barrier `seq` (the caller's per-arena counter);
+ *   4. adopt all windows (refresh as in nmfb_adopt_exchange), fixed != 0: nmfb_fixed_planes on top;
+ *   5. gram_nplanes != 0: sum the ranks' terms in rank order into gram64 / gram32 (k x k all-reduce).
+ * probe_events: NULL or five cudaEvent_t recorded on `stream` before 1. and after 1.+2., 3., 4., 5. */
+typedef struct {
+    void* const* peers;             /* [world] base pointers of the ranks' arenas (host array)                 */
+    void* mc_base;                  /* multicast alias of the arenas, or NULL                                   */
+    int rank, world;
+    void* side_stream;              /* stream / events of step 2 (all NULL: step 2 runs on `stream`)            */
+    void* ev_fork;
+    void* ev_join;
+    float* gram_scratch;            /* >= nmfb_gram_partial_bytes(k, window length, num_sms)                    */
+    size_t gram_scratch_bytes;
+    double* gram_term64;            /* [KP][KP] this rank's term (source of the store)                          */
+    float* gram_term32;             /* [KP][KP]                                                                 */
+    int num_sms;
+} nmfb_peer_ctx;
+int nmfb_exchange_factor(const nmfb_peer_ctx* ctx, int KP, const nmfb_factor* f, long xchg_off, int refresh, int fixed,
+                         int gram_nplanes, long gram_off, double* gram64, float* gram32, unsigned int seq,
+                         void* const* probe_events, void* stream);
+/* Sum of the double at src (16-byte aligned; the granule src[0..1] travels) over the ranks: stored into slot `rank`
+ * of the table at table_off (64-byte slots) of every arena, barrier `seq`, summed in rank order into out[0] (the
+ * objective: utils.py:29 over the ranks' rows). */
+int nmfb_exchange_scalar(const nmfb_peer_ctx* ctx, const double* src, long table_off, unsigned int seq, double* out,
+                         void* stream);
 /* This rank's term of the Gram matrix: nmfb_gram over the rows of the factor's window only. */
 int nmfb_gram_window(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes,
                      float* gram32, double* gram64, int num_sms, void* stream);

@@ -27,6 +27,13 @@ class Data(C.Structure):            # struct nmfb_data
                 ("ld", c_int), ("nv", c_int), ("blocked", c_int), ("fixed", c_int), ("origin", c_int)]
 
 
+class PeerCtx(C.Structure):         # struct nmfb_peer_ctx
+    _fields_ = [("peers", c_void_p), ("mc_base", c_void_p), ("rank", c_int), ("world", c_int),
+                ("side_stream", c_void_p), ("ev_fork", c_void_p), ("ev_join", c_void_p),
+                ("gram_scratch", c_void_p), ("gram_scratch_bytes", c_size_t),
+                ("gram_term64", c_void_p), ("gram_term32", c_void_p), ("num_sms", c_int)]
+
+
 class Factor(C.Structure):          # struct nmfb_factor
     _fields_ = [("master", c_void_p), ("cplanes", c_void_p), ("rplanes", c_void_p),
                 ("L", c_int), ("Lp", c_int), ("win0", c_int), ("win_p", c_int)]
@@ -105,6 +112,9 @@ _SIGNATURES.update({
     "nmfb_sum_rank_slots": (c_int, [c_void_p, c_int, c_long, c_int, c_void_p, c_void_p, c_void_p]),
     "nmfb_adopt_exchange": (c_int, [c_int, P(Factor), c_void_p, c_int, c_void_p]),
     "nmfb_gram_window": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
+    "nmfb_exchange_factor": (c_int, [P(PeerCtx), c_int, P(Factor), c_long, c_int, c_int, c_int, c_long, c_void_p,
+                                     c_void_p, C.c_uint, c_void_p, c_void_p]),
+    "nmfb_exchange_scalar": (c_int, [P(PeerCtx), c_void_p, c_long, C.c_uint, c_void_p, c_void_p]),
     "nmfb_mur_eu_window_step": (c_int, [P(Problem), c_int, c_float, c_void_p]),
     "nmfb_row_planes3": (c_int, [c_int, P(Factor), c_void_p, c_void_p]),
     "nmfb_kl_data_step": (c_int, [P(Data), c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_long,

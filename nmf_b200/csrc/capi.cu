@@ -587,6 +587,78 @@ int nmfb_objective_kl(const nmfb_problem* p, double* obj_out, void* stream) {
 }
 
 namespace {
+int push_to_all(const nmfb_peer_ctx* x, const void* src, long src_pitch, long dst_off, long dst_pitch, int rows,
+                long row_bytes, void* stream) {
+    if (x->mc_base) return nmfb_peer_push_mc(src, src_pitch, x->mc_base, dst_off, dst_pitch, rows, row_bytes, stream);
+    return nmfb_peer_push(src, src_pitch, x->peers, x->world, dst_off, dst_pitch, rows, row_bytes, stream);
+}
+inline void probe(void* const* ev, int i, void* stream) {
+    if (ev && ev[i]) cudaEventRecord(static_cast<cudaEvent_t>(ev[i]), st(stream));
+}
+}  // namespace
+
+int nmfb_exchange_factor(const nmfb_peer_ctx* x, int KP, const nmfb_factor* f, long xchg_off, int refresh, int fixed,
+                         int gram_nplanes, long gram_off, double* gram64, float* gram32, unsigned int seq,
+                         void* const* probe_events, void* stream) {
+    if (!x || !f || !x->peers) return fail(NMFB_ERR_ARG, "exchange_factor: null argument");
+    if (x->world < 2 || x->world > kMaxPeers || x->rank < 0 || x->rank >= x->world)
+        return fail(NMFB_ERR_ARG, "exchange_factor: rank %d of %d", x->rank, x->world);
+    if (f->win_p <= 0) return fail(NMFB_ERR_ARG, "exchange_factor: the factor has no window");
+    const bool gram = gram_nplanes != 0;
+    if (gram && (!x->gram_scratch || !x->gram_term64 || !x->gram_term32 || (!gram64 && !gram32)))
+        return fail(NMFB_ERR_ARG, "exchange_factor: Gram workspaces missing");
+    const bool forked = gram && x->side_stream && x->ev_fork && x->ev_join;
+    const long g = static_cast<long>(KP) * KP * 8;
+    int rc;
+    probe(probe_events, 0, stream);
+    if (forked) CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(x->ev_fork), st(stream)));
+    // 1. my rows of the master into every rank's exchange buffer
+    if ((rc = push_to_all(x, f->master + f->win0, 4L * f->Lp, xchg_off + 4L * f->win0, 4L * f->Lp, KP, 4L * f->win_p,
+                          stream)) < 0)
+        return rc;
+    // 2. my term of the Gram matrix, under the NVLink-bound store above
+    if (gram) {
+        void* gs = forked ? x->side_stream : stream;
+        if (forked) CUDA_TRY(cudaStreamWaitEvent(st(gs), static_cast<cudaEvent_t>(x->ev_fork), 0));
+        if ((rc = nmfb_gram_window(f, KP, gram_nplanes, x->gram_scratch, x->gram_scratch_bytes, x->gram_term32,
+                                   x->gram_term64, x->num_sms, gs)) < 0)
+            return rc;
+        if ((rc = push_to_all(x, x->gram_term64, g, gram_off + x->rank * g, g, 1, g, gs)) < 0) return rc;
+        if (forked) {
+            CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(x->ev_join), st(gs)));
+            CUDA_TRY(cudaStreamWaitEvent(st(stream), static_cast<cudaEvent_t>(x->ev_join), 0));
+        }
+    }
+    probe(probe_events, 1, stream);
+    // 3. one barrier covers the window and the Gram term
+    if ((rc = nmfb_peer_barrier(x->peers, x->rank, x->world, seq, stream)) < 0) return rc;
+    probe(probe_events, 2, stream);
+    // 4. all windows into master + planes
+    const char* local = static_cast<const char*>(x->peers[x->rank]);
+    if ((rc = nmfb_adopt_exchange(KP, f, reinterpret_cast<const float*>(local + xchg_off), refresh, stream)) < 0)
+        return rc;
+    if (fixed && (rc = nmfb_fixed_planes(KP, f, stream)) < 0) return rc;
+    probe(probe_events, 3, stream);
+    // 5. k x k all-reduce, second half
+    if (gram && (rc = nmfb_sum_rank_slots(reinterpret_cast<const double*>(local + gram_off), x->world,
+                                          static_cast<long>(KP) * KP, KP * KP, gram64, gram32, stream)) < 0)
+        return rc;
+    probe(probe_events, 4, stream);
+    return 0;
+}
+
+int nmfb_exchange_scalar(const nmfb_peer_ctx* x, const double* src, long table_off, unsigned int seq, double* out,
+                         void* stream) {
+    if (!x || !src || !out || !x->peers) return fail(NMFB_ERR_ARG, "exchange_scalar: null argument");
+    int rc;
+    if ((rc = push_to_all(x, src, 16, table_off + 64L * x->rank, 64, 1, 16, stream)) < 0) return rc;
+    if ((rc = nmfb_peer_barrier(x->peers, x->rank, x->world, seq, stream)) < 0) return rc;
+    const char* local = static_cast<const char*>(x->peers[x->rank]);
+    return nmfb_sum_rank_slots(reinterpret_cast<const double*>(local + table_off), x->world, 8, 1, out, nullptr,
+                               stream);
+}
+
+namespace {
 int mur_eu_half(const nmfb_problem* p, int side, float lambda, bool with_gram, void* stream) {
     if (!p || (side != 0 && side != 1)) return fail(NMFB_ERR_ARG, "mur_eu_half_step: bad argument");
     const int KP = p->KP;

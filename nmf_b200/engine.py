@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import AdmmState, Data, Factor, Problem, check
+from ._lib import AdmmState, Data, Factor, PeerCtx, Problem, check
 from .sharding import (allgather_flat, allgather_windows, allreduce_max_, allreduce_min_key_, allreduce_sum_,
                        exchange_blocks, live_rows, shard_bounds)
 
@@ -182,22 +182,15 @@ class Engine:
         nbytes = int(self.lib.nmfb_gram_partial_bytes(self.k, max(self.per_m, self.per_n), self.num_sms))
         self.gram_scratch = torch.empty(max(nbytes, 4) // 4, dtype=torch.float32, device=self.device)
         self.gram_stream = torch.cuda.Stream(device=self.device)
-        self._gram_fork, self._gram_join = torch.cuda.Event(), torch.cuda.Event()
-        self.exchange_probe = None            # bench: list that collects (label, event) pairs of the exchange steps
+        self._gram_events = (torch.cuda.Event(), torch.cuda.Event())
+        for ev in self._gram_events:
+            ev.record(torch.cuda.current_stream(self.device))            # materialises the cudaEvent_t
+        self._peer_ctx = {}
+        self.exchange_probe = None            # bench: list that collects the timing events of every exchange
 
     @staticmethod
     def _attach_exchange(fac: "FactorBuffers", arena, name: str):
         fac.arena, fac.xname, fac.xcount = arena, name, 0
-
-    def _push_window(self, fac: "FactorBuffers") -> int:
-        """Store this rank's rows of the master into every rank's exchange buffer; returns the device address of
-        the LOCAL buffer that holds all windows once the barrier has been passed."""
-        KP, par = self.KP, fac.xcount & 1
-        fac.xcount += 1
-        base = par * KP * fac.Lp * 4
-        fac.arena.push(fac.master.data_ptr() + 4 * fac.win0, 4 * fac.Lp, fac.xname, base + 4 * fac.win0, 4 * fac.Lp,
-                       KP, 4 * fac.win_p, self.stream)
-        return fac.arena.local.data_ptr() + fac.arena.offsets[fac.xname] + base
 
     def gather_factor(self, fac: "FactorBuffers", refresh: bool = True, fixed: bool = False, gram_index=None):
         """Exchange the windows of a factor (or ADMM auxiliary) every rank just updated, then re-derive its bf16
@@ -216,46 +209,51 @@ class Engine:
             if fixed:
                 check(self.lib.nmfb_fixed_planes(self.KP, C.byref(fs), self.stream))
             return
+        # ONE call of the C ABI per exchange (nmfb_exchange_factor): at 8 GPUs an iteration is ~1 ms, and eight
+        # ctypes calls per exchange left the GPUs waiting for their hosts
         KP, w = self.KP, self.world
         g = KP * KP * 8
-        self._probe("x0")
+        arena = fac.arena
+        par = fac.xcount & 1
+        fac.xcount += 1
+        xoff = arena.offsets[fac.xname] + par * KP * fac.Lp * 4
+        goff, g64, g32 = 0, None, None
         if gram_index is not None:
-            # my term of the Gram matrix (contraction over my window) into slot `rank` of every rank's table
             gpar = self._gram_count & 1
             self._gram_count += 1
-            goff = (gpar * 2 + gram_index) * w * g
-            main = torch.cuda.current_stream(self.device)
-            self._gram_fork.record(main)
-        xptr = self._push_window(fac)
-        if gram_index is not None:
-            self.gram_stream.wait_event(self._gram_fork)
-            side = self.gram_stream.cuda_stream
-            check(self.lib.nmfb_gram_window(C.byref(fs), KP, 2, self.gram_scratch.data_ptr(),
-                                            self.gram_scratch.numel() * 4, self.gram_term32.data_ptr(),
-                                            self.gram_term.data_ptr(), self.num_sms, side))
-            self.peer.push(self.gram_term.data_ptr(), g, "gram", goff + self.rank * g, g, 1, g, side)
-            self._gram_join.record(self.gram_stream)
-            main.wait_event(self._gram_join)          # the one barrier below covers the window and the Gram term
-        self._probe("push")
-        fac.arena.barrier(self.stream)
-        self._probe("barrier")
+            goff = arena.offsets["gram"] + (gpar * 2 + gram_index) * w * g
+            g64 = self.gram64.data_ptr() + gram_index * g
+            g32 = self.gram32.data_ptr() + gram_index * (g // 2)
         mode = 0 if not refresh else (2 if gram_index is not None else 1)     # 2: my window is current already
-        check(self.lib.nmfb_adopt_exchange(KP, C.byref(fs), xptr, mode, self.stream))
-        if fixed:
-            check(self.lib.nmfb_fixed_planes(KP, C.byref(fs), self.stream))
-        self._probe("adopt")
-        if gram_index is not None:
-            # second half of the k x k all-reduce: the ranks' terms summed in rank order (bit-identical everywhere)
-            slots = self.peer.local.data_ptr() + self.peer.offsets["gram"] + goff
-            check(self.lib.nmfb_sum_rank_slots(slots, w, KP * KP, KP * KP, self.gram64.data_ptr() + gram_index * g,
-                                               self.gram32.data_ptr() + gram_index * (g // 2), self.stream))
-            self._probe("gram_sum")
+        arena.seq += 1
+        check(self.lib.nmfb_exchange_factor(C.byref(self._ctx_of(arena)), KP, C.byref(fs), xoff, mode, int(fixed),
+                                            2 if gram_index is not None else 0, goff, g64, g32,
+                                            arena.seq & 0xFFFFFFFF, self._probe_events(), self.stream))
 
-    def _probe(self, label: str):
-        if self.exchange_probe is not None:
-            ev = torch.cuda.Event(enable_timing=True)
-            ev.record(torch.cuda.current_stream(self.device))
-            self.exchange_probe.append((label, ev))
+    def _ctx_of(self, arena) -> PeerCtx:
+        """nmfb_peer_ctx of an arena (built once; the Gram workspaces belong to the main arena's exchanges)."""
+        ctx = self._peer_ctx.get(id(arena))
+        if ctx is None:
+            ctx = PeerCtx(C.cast(arena._ptr_arr, C.c_void_p), arena.mc_ptr or None, self.rank, self.world,
+                          self.gram_stream.cuda_stream, int(self._gram_events[0].cuda_event),
+                          int(self._gram_events[1].cuda_event), self.gram_scratch.data_ptr(),
+                          self.gram_scratch.numel() * 4, self.gram_term.data_ptr(), self.gram_term32.data_ptr(),
+                          self.num_sms)
+            self._peer_ctx[id(arena)] = ctx
+        return ctx
+
+    PROBE_LABELS = ("push", "barrier", "adopt", "gram_sum")
+
+    def _probe_events(self):
+        """bench: five timing events per exchange (start | window store + Gram term | barrier | adoption | Gram sum)."""
+        if self.exchange_probe is None:
+            return None
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        for ev in evs:
+            ev.record(torch.cuda.current_stream(self.device))            # materialises the cudaEvent_t
+        arr = (C.c_void_p * 5)(*[int(ev.cuda_event) for ev in evs])
+        self.exchange_probe.append((evs, arr))
+        return arr
 
     def _mark(self, idx: int):
         ev = getattr(self, "_phase_torch", None)
@@ -339,13 +337,12 @@ class Engine:
         # barrier, so that all ranks hold the bit-identical objective (and take the same stop decision)
         par = self._scal_count & 1
         self._scal_count += 1
-        base = par * self.world * 64
         assert index % 2 == 0                                       # 16-byte granules
-        self.peer.push(self.scalars.data_ptr() + 8 * index, 16, "scal", base + 64 * self.rank, 64, 1, 16, self.stream)
-        self.peer.barrier(self.stream)
-        slots = self.peer.local.data_ptr() + self.peer.offsets["scal"] + base
-        check(self.lib.nmfb_sum_rank_slots(slots, self.world, 8, 1, self.scalars.data_ptr() + 8 * index, None,
-                                           self.stream))
+        self.peer.seq += 1
+        ptr = self.scalars.data_ptr() + 8 * index
+        check(self.lib.nmfb_exchange_scalar(C.byref(self._ctx_of(self.peer)), ptr,
+                                            self.peer.offsets["scal"] + par * self.world * 64,
+                                            self.peer.seq & 0xFFFFFFFF, ptr, self.stream))
 
     def _data_structs(self) -> Tuple[Data, Data]:
         vr = Data(self.v_rows.data_ptr(), self.row_range[1] - self.row_range[0], self.n, self.per_m, self.Np,

@@ -48,7 +48,7 @@ def test_struct_layouts_match_header():
     import subprocess, tempfile
     from nmf_b200 import _lib
     pairs = [("nmfb_data", _lib.Data), ("nmfb_factor", _lib.Factor), ("nmfb_problem", _lib.Problem),
-             ("nmfb_admm_state", _lib.AdmmState)]
+             ("nmfb_admm_state", _lib.AdmmState), ("nmfb_peer_ctx", _lib.PeerCtx)]
     lines, want = [], []
     for cname, cls in pairs:
         lines.append(f'printf("%zu\\n", sizeof({cname}));')
@@ -75,7 +75,7 @@ def test_ctypes_signatures_match_header_prototypes():
     protos = re.findall(r"([A-Za-z_][\w \*]*?)\b(nmfb_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", text)
     assert len(protos) == len(_lib.exported_symbols())
     structs = {"nmfb_data": _lib.Data, "nmfb_factor": _lib.Factor, "nmfb_problem": _lib.Problem,
-               "nmfb_admm_state": _lib.AdmmState}
+               "nmfb_admm_state": _lib.AdmmState, "nmfb_peer_ctx": _lib.PeerCtx}
     scalars = {"int": C.c_int, "long": C.c_long, "float": C.c_float, "double": C.c_double, "size_t": C.c_size_t,
                "unsigned long long": C.c_ulonglong, "unsigned int": C.c_uint}
 
