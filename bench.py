@@ -493,9 +493,11 @@ def run_b200(args):
     torch.cuda.synchronize(dev)
     with ClockSampler(local_rank) as clk:
         t0.record()
+        h0 = time.perf_counter()
         for i in range(steps):
             eng.set_phase_events(evs[i])
             do_step(i)
+        host_ms_step = (time.perf_counter() - h0) * 1e3 / steps      # time the HOST needs to enqueue one step
         t1.record()
         torch.cuda.synchronize(dev)
     eng.set_phase_events(None)
@@ -531,6 +533,8 @@ def run_b200(args):
                    **{kk: (list(vv) if isinstance(vv, tuple) else vv) for kk, vv in extra.items()}},
         "clocks": clk.summary(),
         "gpu_launches": int(launches_per_step * steps),
+        # enqueue time of one step on this rank's host thread: when it approaches ms_per_step the GPU waits for its host
+        "host_enqueue_ms_per_step": round(host_ms_step, 4),
         "phase_ms": {kk: round(vv, 4) for kk, vv in phase_ms.items()},
         "roofline": roof,
         "alg_tflops": alg_flops_per_iter(method, dtype_, m, n, k, extra) / (ms_step * 1e-3) / 1e12 / world,
