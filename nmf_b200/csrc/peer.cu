@@ -13,6 +13,9 @@
 // (parity of an exchange counter): a peer's push(t+1) into buffer (t+1)&1 can then never overtake this rank's
 // consume(t) of buffer t&1, and its push(t+2) is ordered behind barrier(t+1), which this rank enters only after
 // consume(t) in stream order.
+//
+// nmfb_exchange_factor (capi.cu) sequences one exchange: window store on the caller's stream, the rank's Gram term on
+// a side stream under it (joined by events before the barrier), barrier, adoption, sum of the Gram terms.
 #include "elementwise.cuh"
 #include "kernels.cuh"
 #include "peer.cuh"
