@@ -843,6 +843,14 @@ KxK kxk_begin(const nmfb_problem* p, const nmfb_admm_state* s, void* stream) {
     }
     return k;
 }
+// The fp64 Gram fills the GPU (tiles x row splits) and runs on the caller's stream BEFORE the fork: next to the
+// persistent numerator GEMM it only got the two SMs that GEMM leaves free (measured: the "hidden" Gram stretched the
+// GEMM phase from 1.10 to 1.43 - 1.65 ms).  What the side stream hides is the single-CTA work: Cholesky inverse,
+// Tikhonov system.
+KxK kxk_main(const nmfb_problem* p, const nmfb_admm_state* s, void* stream) {
+    if (s->gram_partial) return KxK{stream, s->gram_partial, s->gram_partial_bytes, false};
+    return KxK{stream, p->partial, p->partial_bytes, false};
+}
 int kxk_join(const nmfb_admm_state* s, const KxK& k, void* stream) {
     if (!k.forked) return 0;
     CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(s->ev_join), st(k.stream)));
@@ -914,8 +922,8 @@ int nmfb_admm_half_step(const nmfb_problem* p, const nmfb_admm_state* s, int sid
     const nmfb_factor* self_aux = side == 0 ? &s->h_aux : &s->w_aux;
     const nmfb_data* data = side == 0 ? &p->v_cols : &p->v_rows;
     float* dual = side == 0 ? s->dual_h : s->dual_w;
+    if ((rc = admm_gram(p, s, other_aux, side, kxk_main(p, s, stream))) < 0) return rc;
     const KxK kx = kxk_begin(p, s, stream);
-    if ((rc = admm_gram(p, s, other_aux, side, kx)) < 0) return rc;
     if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 0, rho, s->chol_scratch, s->ainv + side * gsz,
                                 s->scal + side, s->flags, kx.stream)) < 0) return rc;
     if (prox == NMFB_PROX_L2N && lambda != 0.f && (rc = nmfb_admm_prepare_l2n(p, s, side, lambda, kx.stream)) < 0) return rc;
@@ -1027,8 +1035,8 @@ int nmfb_aoadmm_side_begin(const nmfb_problem* p, const nmfb_admm_state* s, int 
     const size_t gsz = static_cast<size_t>(KP) * KP;
     int rc;
     CUDA_TRY(admm_flags_reset_launch(s->flags, (1 << 1) | (1 << (2 + side)), st(stream)));
+    if ((rc = admm_gram(p, s, other, side, kxk_main(p, s, stream))) < 0) return rc;   // ao_admm.py:53-55
     const KxK kx = kxk_begin(p, s, stream);
-    if ((rc = admm_gram(p, s, other, side, kx)) < 0) return rc;                       // ao_admm.py:53-55
     if ((rc = nmfb_chol_inverse(p->gram64 + side * gsz, p->k, KP, 1, 0.0, s->chol_scratch, s->ainv + side * gsz,
                                 s->scal + side, s->flags, kx.stream)) < 0) return rc;
     mark(p, 1 + 3 * side, stream);
