@@ -153,6 +153,13 @@ int nmfb_gram_exact(const nmfb_factor* f, int KP, float* partial, size_t partial
 int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t partial_bytes, float* gram32,
               double* gram64, int num_sms, void* stream);
 
+/* The Gram matrix of the ADMM / AO-ADMM systems (`other_aux.T @ other_aux` admm.py:220, `w.T @ w` ao_admm.py:53):
+ * products and sums in fp64 on the FP64 tensor cores, operand = the sum of the factor's three bf16 cplanes (the very
+ * operand the numerator contraction reads, so that the k x k solve sees a consistent system).
+ * scratch >= nmfb_gram_partial_bytes(k, L, num_sms). */
+int nmfb_gram_fp64(const nmfb_factor* f, int KP, double* scratch, size_t scratch_bytes, float* gram32, double* gram64,
+                   void* stream);
+
 /* nmfb_gram without a caller workspace, for callers that cannot allocate device memory (CUDA graph capture, serving
  * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same kernels and results as nmfb_gram; the K-split slots live in a device array built into the library

@@ -79,6 +79,7 @@ _SIGNATURES = {
     "nmfb_panel_gemm": (c_int, [P(Data), c_void_p, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_int,
                                 c_int, c_int, c_void_p]),
     "nmfb_gram": (c_int, [P(Factor), c_int, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_int, c_void_p]),
+    "nmfb_gram_fp64": (c_int, [P(Factor), c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p]),
     "nmfb_gram_static_max_bytes": (c_size_t, []),
     "nmfb_gram_static": (c_int, [P(Factor), c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "nmfb_mur_eu_update": (c_int, [c_void_p, c_int, c_void_p, P(Factor), c_int, c_int, c_float, c_void_p]),

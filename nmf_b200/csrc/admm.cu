@@ -33,29 +33,39 @@ namespace nmfb {
 // master next to a numerator of the planes leaves a 2e-9 mismatch that the solve amplifies a hundredfold (h_aux off by
 // 2.2e-7 although Gram and inverse were exact: tools/diag_admm_step.py, round 2).  With both sides built from the
 // same operand the half step is the exact ridge solution for that operand.
+// The multiply runs on the FP64 tensor cores (mma.sync m8n8k4, "DMMA"): the register-tiled FMA version was bound by its
+// shared-memory operand reads at ~15 % of the FP64 rate (0.37 ms for 65536 rows at k = 128).  Warp w owns rows
+// [8w, 8w + 8) of the tile and all eight 8-column blocks: per step of four contraction rows one A fragment, eight B
+// fragments (one double per lane each), eight DMMAs.  Row pitch 68 doubles: the (k = lane & 3, m = lane >> 2) fragment
+// addresses of a half-warp fall into 16 distinct 8-byte banks.
+__device__ __forceinline__ void dmma_884(double (&d)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
+}
+
 __global__ void __launch_bounds__(256)
 gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int KP, int rows_per,
                  double* __restrict__ slots) {
-    __shared__ double As[32][66];
-    __shared__ double Bs[32][66];
+    constexpr int PITCH = 68;
+    __shared__ double As[32][PITCH];
+    __shared__ double Bs[32][PITCH];
     const int nt = KP / 64;
     int ti = 0, rem = blockIdx.x;                      // blockIdx.x enumerates the upper triangle row by row
     while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
     const int tj = ti + rem;
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int fk = lane & 3, fm = lane >> 2;           // fragment coordinates of this lane
     const int r_begin = blockIdx.y * rows_per;
     const int r_end = min(Lp, r_begin + rows_per);
     const long plane2 = 2 * plane;
-    double acc[4][4];
+    double acc[8][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+    for (int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = 0.0;
     const __nv_bfloat16* ap = cpl + static_cast<long>(ti) * 64 * Lp;
     const __nv_bfloat16* bp = cpl + static_cast<long>(tj) * 64 * Lp;
     const bool diag = ti == tj;                        // diagonal tile: one operand
     // 32 rows x 64 components of both operands per chunk, lanes along r (coalesced rows of the planes); the loads of
-    // chunk t + 1 are in flight while chunk t is multiplied (the first version loaded, waited, multiplied)
+    // chunk t + 1 are in flight while chunk t is multiplied
     auto load = [&](int r0, double (&av)[8], double (&bv)[8]) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -87,23 +97,21 @@ gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int 
         }
         __syncthreads();
         if (r0 + 32 < r_end) load(r0 + 32, av, bv);
-#pragma unroll 4
-        for (int rr = 0; rr < 32; ++rr) {
-            double a[4], b[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { a[i] = As[rr][ty * 4 + i]; b[i] = Bs[rr][tx * 4 + i]; }
+        for (int kk = 0; kk < 8; ++kk) {
+            const double a = As[kk * 4 + fk][warp * 8 + fm];         // A[m][k]: m = component of tile row block
+            double b[8];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int nb = 0; nb < 8; ++nb) b[nb] = Bs[kk * 4 + fk][nb * 8 + fm];   // B[k][n]
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+            for (int nb = 0; nb < 8; ++nb) dmma_884(acc[nb], a, b[nb]);
         }
     }
-    double* out = slots + static_cast<long>(blockIdx.y) * KP * KP;
+    // C fragment: row = lane >> 2, columns 2 * (lane & 3) + {0, 1}
+    double* out = slots + static_cast<long>(blockIdx.y) * KP * KP +
+                  static_cast<long>(ti * 64 + warp * 8 + fm) * KP + tj * 64 + 2 * fk;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            out[static_cast<long>(ti * 64 + ty * 4 + i) * KP + tj * 64 + tx * 4 + j] = acc[i][j];
+    for (int nb = 0; nb < 8; ++nb) *reinterpret_cast<double2*>(out + nb * 8) = make_double2(acc[nb][0], acc[nb][1]);
 }
 
 // G[i][j] = sum over the splits (fixed order) of the tile that holds (min, max) of (i / 64, j / 64); mirrored below.

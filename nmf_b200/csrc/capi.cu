@@ -412,6 +412,17 @@ int nmfb_gram(const nmfb_factor* f, int KP, int nplanes, float* partial, size_t 
     return 0;
 }
 
+int nmfb_gram_fp64(const nmfb_factor* f, int KP, double* scratch, size_t scratch_bytes, float* gram32, double* gram64,
+                   void* stream) {
+    if (!f || !scratch || !gram32 || !gram64) return fail(NMFB_ERR_ARG, "gram_fp64: null argument");
+    if (KP != 64 && KP != 128 && KP != 256) return fail(NMFB_ERR_ARG, "gram_fp64: KP must be 64 / 128 / 256");
+    if (gram_fp64_scratch_bytes(KP, f->Lp) > scratch_bytes)
+        return fail(NMFB_ERR_WORKSPACE, "gram_fp64: scratch %zu < %zu bytes", scratch_bytes,
+                    gram_fp64_scratch_bytes(KP, f->Lp));
+    CUDA_TRY(gram_fp64_launch(bf(f->cplanes), 256L * f->Lp, KP, f->Lp, scratch, gram32, gram64, st(stream)));
+    return 0;
+}
+
 // ---- Gram matrix without caller scratch ------------------------------------------------------------------------
 // Same kernels as nmfb_gram (panel_gemm_kernel into K-split partial slots, gram_reduce_kernel over them), but the
 // slots live in a file-scope device array instead of a caller buffer: for callers that cannot allocate (CUDA graph

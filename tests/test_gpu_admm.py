@@ -127,3 +127,39 @@ def test_unknown_prox_and_distance():
         admm(v, 4, reg_h=(0.1, "bogus"), nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
     with pytest.raises(TypeError):
         admm(v, 4, distance_type="xx", nndsvd_init=(False, "zero"), max_iter=2, verbose=False)
+
+
+@pytest.mark.parametrize("k,KP,L", [(10, 64, 700), (128, 128, 20000), (200, 256, 5000)])
+def test_fp64_gram_of_the_planes_is_exact(k, KP, L):
+    """nmfb_gram_fp64 (FP64 tensor cores, admm.cu): G == float64 Gram of the operand the three bf16 planes hold --
+    the operand of the numerator contraction --, symmetric, zero in the padded components."""
+    import ctypes as C
+    import torch
+    from nmf_b200._lib import Factor, check, load
+    lib = load()
+    dev = torch.device("cuda:0")
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    Lp = (L + 255) // 256 * 256
+    rng = np.random.default_rng(k)
+    host = (rng.random((L, k)) * np.exp(rng.normal(0, 3, (1, k)))).astype(np.float32)       # columns of mixed scale
+    with torch.cuda.device(dev):
+        master = torch.zeros((KP, Lp), dtype=torch.float32, device=dev)
+        cpl = torch.zeros((3, 256, Lp), dtype=torch.bfloat16, device=dev)
+        rpl = torch.zeros((2, Lp, KP), dtype=torch.bfloat16, device=dev)
+        fs = Factor(master.data_ptr(), cpl.data_ptr(), rpl.data_ptr(), L, Lp, 0, 0)
+        src = torch.from_numpy(host).to(dev)
+        check(lib.nmfb_import_factor(src.data_ptr(), 0, k, 1, k, KP, C.byref(fs), None))
+        nbytes = int(lib.nmfb_gram_partial_bytes(k, L, sms))
+        scratch = torch.empty(nbytes // 8 + 1, dtype=torch.float64, device=dev)
+        g32 = torch.zeros((KP, KP), dtype=torch.float32, device=dev)
+        g64 = torch.zeros((KP, KP), dtype=torch.float64, device=dev)
+        check(lib.nmfb_gram_fp64(C.byref(fs), KP, scratch.data_ptr(), nbytes, g32.data_ptr(), g64.data_ptr(), None))
+        torch.cuda.synchronize(dev)
+        operand = cpl[:, :KP].to(torch.float64).sum(0).cpu().numpy()                          # [KP][Lp]
+    got, want = g64.cpu().numpy(), operand @ operand.T
+    err = np.abs(got - want).max() / np.abs(want).max()
+    print(f"k={k} L={L}: max |G - G64| / max |G64| = {err:.1e}")
+    assert err < 1e-13 and np.array_equal(got, got.T) and not got[k:].any()
+    assert np.array_equal(g32.cpu().numpy(), got.astype(np.float32))
+    ref = host.astype(np.float64).T @ host.astype(np.float64)
+    assert np.linalg.norm(got[:k, :k] - ref) / np.linalg.norm(ref) < 1e-6                     # planes = 24-bit operand
