@@ -60,7 +60,7 @@ NCU_TRAFFIC = {
     ("panel_gemm_kernel", "mur_eu_65536x65536_k128"):
         (8.624068e9 + 85.743104e6, "profiles/r01b_all_paths.md (kernel unchanged since)"),
     ("kl_panel_ts2_kernel", "mur_kl_20000x50000_k128"):
-        (2.099853e9 + 65.275136e6, "profiles/r02a_ncu_full_variants.md"),
+        (2.098872e9 + 65.014016e6, "profiles/r02z_ncu_full_summary.md"),
     ("panel_gemm_exact_kernel", "admm_65536x16384_k128"):
         (4.393657e9 + 188.351488e6, "profiles/r01b_all_paths.md (kernel unchanged since)"),
     ("panel_gemm_exact_kernel", "ao_admm_65536x16384_k128"):

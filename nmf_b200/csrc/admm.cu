@@ -38,11 +38,6 @@ namespace nmfb {
 // [8w, 8w + 8) of the tile and all eight 8-column blocks: per step of four contraction rows one A fragment, eight B
 // fragments (one double per lane each), eight DMMAs.  Row pitch 68 doubles: the (k = lane & 3, m = lane >> 2) fragment
 // addresses of a half-warp fall into 16 distinct 8-byte banks.
-__device__ __forceinline__ void dmma_884(double (&d)[2], double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
-                 : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
-}
-
 __global__ void __launch_bounds__(256)
 gram_fp64_kernel(const __nv_bfloat16* __restrict__ cpl, long plane, int Lp, int KP, int rows_per,
                  double* __restrict__ slots) {
@@ -304,9 +299,12 @@ admm_apply_kernel(const AdmmApplyArgs p) {
     constexpr int KP = CPT * 16;
     constexpr int TR = 64;
     constexpr int CK = 16;                // rows of Ainv per shared-memory chunk (the next one waits in registers)
+    constexpr int BP = TR + 4;            // row pitches = 4 (mod 16) doubles: the DMMA fragment reads of a half-warp
+    constexpr int GP = KP + 4;            // (k = lane & 3, m = lane >> 2) fall into 16 distinct 8-byte banks
+    constexpr int MB = CPT / 4;           // 8-row blocks of the output per warp (KP / 8 blocks over 8 warps)
     extern __shared__ double sm_d[];
-    double* bs = sm_d;                    // [KP][TR]
-    double* gs = sm_d + KP * TR;          // [CK][KP]
+    double* bs = sm_d;                    // [KP][BP]  right-hand side b, later the product A^-1 b
+    double* gs = sm_d + KP * BP;          // [CK][GP]
     __shared__ double red[8][4];
     if (p.done_flag != nullptr && *p.done_flag != 0) return;
     const int tid = threadIdx.x;
@@ -365,17 +363,23 @@ admm_apply_kernel(const AdmmApplyArgs p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int i = tid + (h + j) * 256;
+            const int c = i / (TR / 4), q4 = i - c * (TR / 4);
             const float xs4[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w}, us4[4] = {ur[j].x, ur[j].y, ur[j].z, ur[j].w};
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                bs[i * 4 + e] = cv[j][e] + rho * (static_cast<double>(xs4[e]) + static_cast<double>(us4[e]));
+                bs[c * BP + q4 * 4 + e] = cv[j][e] + rho * (static_cast<double>(xs4[e]) + static_cast<double>(us4[e]));
         }
     }
-    double acc[CPT][4];
+    // aux[c][r] = sum_c' Ainv[c][c'] b[c'][r] on the FP64 tensor cores (mma.sync m8n8k4): warp w owns the 8-row blocks
+    // [w * MB, (w + 1) * MB) of the components and all eight 8-column blocks of the 64 r.  The register-tiled FMA
+    // version read one Ainv element from shared memory per four FMAs and sat at L1/tex 83 %, FP64 pipe 45 % (ncu
+    // r02z); a fragment load here feeds eight FMAs per lane.
+    const int lane = tid & 31, warp = tid >> 5, fk = lane & 3, fm = lane >> 2;
+    double dacc[MB][8][2];
 #pragma unroll
-    for (int a = 0; a < CPT; ++a)
+    for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        for (int nb = 0; nb < 8; ++nb) dacc[mb][nb][0] = dacc[mb][nb][1] = 0.0;
 
     // rows of Ainv: chunk ck + 1 travels from L2 to registers while chunk ck is multiplied
     constexpr int NG = CK * KP / 2 / 256;
@@ -385,28 +389,39 @@ admm_apply_kernel(const AdmmApplyArgs p) {
     for (int ck = 0; ck < KP; ck += CK) {
         __syncthreads();
 #pragma unroll
-        for (int j = 0; j < NG; ++j) reinterpret_cast<double2*>(gs)[tid + j * 256] = gr[j];
+        for (int j = 0; j < NG; ++j) {
+            const int e = (tid + j * 256) * 2, cc = e / KP, c = e - cc * KP;
+            *reinterpret_cast<double2*>(gs + cc * GP + c) = gr[j];
+        }
         if (ck + CK < KP) {
 #pragma unroll
             for (int j = 0; j < NG; ++j)
                 gr[j] = *reinterpret_cast<const double2*>(p.ainv + static_cast<long>(ck + CK) * KP + (tid + j * 256) * 2);
         }
         __syncthreads();
-#pragma unroll 2
-        for (int cc = 0; cc < CK; ++cc) {
-            const double2 x01 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4);
-            const double2 x23 = *reinterpret_cast<const double2*>(bs + (ck + cc) * TR + tr * 4 + 2);
-            const double* grow = gs + cc * KP + tc * CPT;         // Ainv symmetric: row (ck+cc)
 #pragma unroll
-            for (int a = 0; a < CPT; a += 2) {
-                const double2 g = *reinterpret_cast<const double2*>(grow + a);
-                acc[a][0] = fma(g.x, x01.x, acc[a][0]);     acc[a][1] = fma(g.x, x01.y, acc[a][1]);
-                acc[a][2] = fma(g.x, x23.x, acc[a][2]);     acc[a][3] = fma(g.x, x23.y, acc[a][3]);
-                acc[a + 1][0] = fma(g.y, x01.x, acc[a + 1][0]); acc[a + 1][1] = fma(g.y, x01.y, acc[a + 1][1]);
-                acc[a + 1][2] = fma(g.y, x23.x, acc[a + 1][2]); acc[a + 1][3] = fma(g.y, x23.y, acc[a + 1][3]);
+        for (int kk = 0; kk < CK / 4; ++kk) {
+            double bf[8];                                              // B[k = c'][n = r]
+#pragma unroll
+            for (int nb = 0; nb < 8; ++nb) bf[nb] = bs[(ck + kk * 4 + fk) * BP + nb * 8 + fm];
+#pragma unroll
+            for (int mb = 0; mb < MB; ++mb) {
+                const double af = gs[(kk * 4 + fk) * GP + (warp * MB + mb) * 8 + fm];   // A[m = c][k = c'] (symmetric)
+#pragma unroll
+                for (int nb = 0; nb < 8; ++nb) dmma_884(dacc[mb][nb], af, bf[nb]);
             }
         }
     }
+    // the product replaces b in shared memory (D fragment: row lane >> 2, columns 2 * (lane & 3) + {0, 1}); the
+    // epilogue below reads it back in its own thread layout (4 consecutive r x CPT consecutive components)
+    __syncthreads();
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb)
+            *reinterpret_cast<double2*>(bs + ((warp * MB + mb) * 8 + fm) * BP + nb * 8 + 2 * fk) =
+                make_double2(dacc[mb][nb][0], dacc[mb][nb][1]);
+    __syncthreads();
 
     double n_ra = 0.0, n_x = 0.0, n_dx = 0.0, n_u = 0.0;
     __align__(16) __nv_bfloat16 rh[4][CPT], rl[4][CPT];
@@ -423,10 +438,13 @@ admm_apply_kernel(const AdmmApplyArgs p) {
         }
         const float xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, uo[4] = {uo4.x, uo4.y, uo4.z, uo4.w};
         float xn[4], un[4], ax[4];
+        const double2 p01 = *reinterpret_cast<const double2*>(bs + c * BP + tr * 4);
+        const double2 p23 = *reinterpret_cast<const double2*>(bs + c * BP + tr * 4 + 2);
+        const double prod[4] = {p01.x, p01.y, p23.x, p23.y};
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const bool live = (c < p.k) && (r0 + tr * 4 + b < p.L);
-            const double aux = live ? acc[a][b] : 0.0;
+            const double aux = live ? prod[b] : 0.0;
             double xv = aux - static_cast<double>(uo[b]) - thr;
             xv = (live && xv > 0.0) ? xv : 0.0;
             const double uv = live ? static_cast<double>(uo[b]) + xv - aux : 0.0;

@@ -333,4 +333,11 @@ __device__ __forceinline__ float kl_term_r(float v, float s, float r) {
 }
 __device__ __forceinline__ float kl_term(float v, float s) { return kl_term_r(v, s, rcp_approx(s + 1e-9f)); }
 
+// FP64 tensor-core MMA (DMMA): D (8 x 8) += A (8 x 4) . B (4 x 8).  Lane l holds A[l >> 2][l & 3], B[l & 3][l >> 2]
+// and D[l >> 2][2 * (l & 3) + {0, 1}].
+__device__ __forceinline__ void dmma_884(double (&d)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
+}
+
 }  // namespace nmfb

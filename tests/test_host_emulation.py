@@ -116,7 +116,7 @@ def check_apply(r, KP, Lp):
     np.testing.assert_allclose(r["norms"], want, rtol=1e-5, atol=1e-9)
 
 
-@pytest.mark.parametrize("KP,k", [(64, 40), (128, 128)])
+@pytest.mark.parametrize("KP,k", [(64, 40), (128, 128), (256, 200)])
 @pytest.mark.parametrize("prox,lam", [(0, 0.0), (1, 0.7)])
 def test_control_nn_l1n_kernel_matches_numpy(emu, KP, k, prox, lam):
     """The kernel the GPU tests validated, through the emulator: if this fails the emulator is wrong."""
@@ -498,6 +498,29 @@ def test_fixed_planes_kernel_on_signed_factors(emu):
 # ----------------------------------------------------------------------------------------------
 # Round 2: the plane refresh that adopts the exchanged windows of a sharded run.
 # ----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("KP,k", [(64, 10), (128, 128)])
+def test_fp64_gram_kernels(emu, KP, k):
+    """gram_fp64_launch (admm.cu; the DMMA emulated lane by lane): G equals the float64 Gram of the operand the three
+    bf16 planes hold -- the operand the numerator GEMM contracts --, symmetric, zero in the padded components."""
+    Lp = 256
+    rng = np.random.default_rng(KP)
+    x = _factor(KP, k, Lp - 60, Lp, rng)
+    p0 = orc.round_to_bf16_grid(x)
+    p1 = orc.round_to_bf16_grid(x - p0)
+    p2 = orc.round_to_bf16_grid(x - p0 - p1)
+    cpl = np.zeros((3, 256, Lp), np.uint16)
+    cpl[0, :KP], cpl[1, :KP], cpl[2, :KP] = f32_to_bf16(p0), f32_to_bf16(p1), f32_to_bf16(p2)
+    operand = p0.astype(np.float64) + p1 + p2
+    want = operand @ operand.T
+    for rows_per in (96, 256):
+        nsplit = (Lp + rows_per - 1) // rows_per
+        scratch = np.full((nsplit, KP, KP), np.nan)
+        g32, g64 = np.full((KP, KP), np.nan, np.float32), np.full((KP, KP), np.nan)
+        emu.emu_gram_fp64(ptr(cpl), KP, Lp, rows_per, nsplit, ptr(scratch), ptr(g32), ptr(g64))
+        np.testing.assert_allclose(g64, want, rtol=1e-13, atol=1e-13 * np.abs(want).max())
+        assert np.array_equal(g64, g64.T) and not g64[k:].any() and np.array_equal(g32, g64.astype(np.float32))
+
+
 @pytest.mark.parametrize("KP", [64, 256])
 def test_refresh_planes_kernel_adopts_windows_and_skips_the_own_one(emu, KP):
     Lp, lo, hi = 768, 256, 512

@@ -93,6 +93,32 @@ inline T __shfl_sync(unsigned, T v, int src_lane) {
     return out;
 }
 
+// mma.sync.m8n8k4.f64 (ptx.cuh: dmma_884) on the host: every lane publishes its A and B element, then computes its
+// two D elements from the fragments' documented lane layout.
+namespace nmfb {
+inline void dmma_884(double (&d)[2], double a, double b) {
+    emu::Block& blk = *emu::tl_block;
+    const int tid = emu::tl_tid, w = tid >> 5, lane = tid & 31, base = tid & ~31;
+    double av[32], bv[32];
+    std::uint64_t bits;
+    std::memcpy(&bits, &a, 8);
+    blk.xchg[tid] = bits;
+    blk.warp[w]->arrive_and_wait();
+    for (int l = 0; l < 32; ++l) std::memcpy(&av[l], &blk.xchg[base + l], 8);
+    blk.warp[w]->arrive_and_wait();
+    std::memcpy(&bits, &b, 8);
+    blk.xchg[tid] = bits;
+    blk.warp[w]->arrive_and_wait();
+    for (int l = 0; l < 32; ++l) std::memcpy(&bv[l], &blk.xchg[base + l], 8);
+    blk.warp[w]->arrive_and_wait();
+    const int m = lane >> 2;
+    for (int j = 0; j < 2; ++j) {
+        const int n = 2 * (lane & 3) + j;
+        for (int k = 0; k < 4; ++k) d[j] = std::fma(av[m * 4 + k], bv[n * 4 + k], d[j]);   // A[m][k], B[k][n]
+    }
+}
+}  // namespace nmfb
+
 inline unsigned atomicMax(unsigned* a, unsigned v) {
     unsigned old = __atomic_load_n(a, __ATOMIC_RELAXED);
     while (old < v && !__atomic_compare_exchange_n(a, &old, v, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}

@@ -126,6 +126,17 @@ void emu_objective_simt(const std::uint16_t* vpl, long v_plane, int v_rows_p, in
     });
 }
 
+// gram_fp64_launch: upper-triangle 64 x 64 tiles x row splits on the FP64 tensor cores, then the fixed-order reduction
+void emu_gram_fp64(const std::uint16_t* cpl, int KP, int Lp, int rows_per, int nsplit, double* scratch, float* g32,
+                   double* g64) {
+    const int nt = KP / 64;
+    emu::launch({static_cast<unsigned>(nt * (nt + 1) / 2), static_cast<unsigned>(nsplit), 1}, {256, 1, 1}, 0, [&] {
+        gram_fp64_kernel(reinterpret_cast<const bf16*>(cpl), 256L * Lp, Lp, KP, rows_per, scratch);
+    });
+    emu::launch({static_cast<unsigned>((KP * KP + 255) / 256), 1, 1}, {256, 1, 1}, 0,
+                [&] { gram_fp64_reduce_kernel(scratch, nsplit, KP, g32, g64); });
+}
+
 // refresh_planes_launch: grid = (Lp / 256, KP / 16)
 void emu_refresh_planes(const float* src, float* adopt, int KP, int Lp, std::uint16_t* cpl, std::uint16_t* rpl,
                         int skip_lo, int skip_hi) {
