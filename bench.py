@@ -492,6 +492,11 @@ def run_b200(args):
         dist.barrier()
     torch.cuda.synchronize(dev)
     with ClockSampler(local_rank) as clk:
+        if world > 1 and getattr(eng, "peer", None) is not None:
+            # the ranks' hosts leave the collective above milliseconds apart; without this every rank's first exchange
+            # barrier waits for the last host to start, and at 8 GPUs (1 ms per step) that start-up skew was 15 % of a
+            # 20-step measurement.  The GPUs leave this device-side barrier together; t0 is taken behind it.
+            eng.peer.barrier(eng.stream)
         t0.record()
         h0 = time.perf_counter()
         for i in range(steps):
