@@ -293,3 +293,32 @@ def test_reference_package_name_resolves_to_the_b200_build():
     from nmf import NMF
     from nmf.mur import mur
     assert NMF is nmf_b200.NMF and mur is nmf_b200.mur.mur and nmf.admm.admm is nmf_b200.admm.admm
+
+
+def test_round2_entry_points_reject_bad_arguments_before_touching_the_gpu():
+    """Argument stage of the entry points added in round 2 (exchange, fp64 Gram, no-allocation Gram): clear status
+    codes and messages, no CUDA call needed."""
+    from nmf_b200 import _lib
+    lib = _lib.load()
+    err = lambda: lib.nmfb_last_error().decode()
+    fac = _lib.Factor(0x1000, 0x1000, 0x1000, 1000, 1024, 0, 0)                       # no window
+    ctx = _lib.PeerCtx()                                                              # all NULL / zero
+    assert lib.nmfb_exchange_factor(None, 128, C.byref(fac), 0, 1, 0, 0, 0, None, None, 1, None, None) == -1
+    assert lib.nmfb_exchange_factor(C.byref(ctx), 128, C.byref(fac), 0, 1, 0, 0, 0, None, None, 1, None, None) == -1
+    peers = (C.c_void_p * 2)(0x1000, 0x2000)
+    ctx = _lib.PeerCtx(C.cast(peers, C.c_void_p), None, 5, 2, None, None, None, None, 0, None, None, 148)
+    assert lib.nmfb_exchange_factor(C.byref(ctx), 128, C.byref(fac), 0, 1, 0, 0, 0, None, None, 1, None, None) == -1
+    assert "rank 5 of 2" in err()
+    ctx.rank = 1
+    assert lib.nmfb_exchange_factor(C.byref(ctx), 128, C.byref(fac), 0, 1, 0, 0, 0, None, None, 1, None, None) == -1
+    assert "no window" in err()
+    fac.win0, fac.win_p = 512, 512
+    assert lib.nmfb_exchange_factor(C.byref(ctx), 128, C.byref(fac), 0, 1, 0, 2, 0, 0x1000, 0x1000, 1, None, None) == -1
+    assert "Gram workspaces" in err()
+    assert lib.nmfb_exchange_scalar(None, 0x1000, 0, 1, 0x1000, None) == -1
+    assert lib.nmfb_gram_fp64(C.byref(fac), 100, 0x1000, 1 << 30, 0x1000, 0x1000, None) == -1 and "64 / 128 / 256" in err()
+    assert lib.nmfb_gram_fp64(C.byref(fac), 128, 0x1000, 16, 0x1000, 0x1000, None) == -3 and "scratch" in err()
+    big = _lib.Factor(0x1000, 0x1000, 0x1000, 262144, 262144, 0, 0)
+    assert lib.nmfb_gram_static(C.byref(big), 256, 2, 0x1000, 0x1000, 148, None) == -1 and "built-in scratch" in err()
+    assert lib.nmfb_gram_static(C.byref(big), 128, 5, 0x1000, 0x1000, 148, None) == -1 and "nplanes" in err()
+    assert int(lib.nmfb_gram_static_max_bytes()) == 8 << 20
